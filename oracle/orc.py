@@ -1,0 +1,271 @@
+"""ctypes binding for the CPU oracle (TEST INFRASTRUCTURE -- see oracle/ydorb_oracle.h).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import this.
+"""
+import ctypes as C
+import os
+import pathlib
+import subprocess
+
+import numpy as np
+
+_HERE = pathlib.Path(__file__).resolve().parent
+_SO = _HERE / "_build" / "libydorb_oracle.so"
+
+MAX_LEVELS = 16
+PAD = 19
+BORDER = 16
+
+KP_DTYPE = np.dtype(
+    [("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")]
+)
+CAND_DTYPE = np.dtype([("x", "<i4"), ("y", "<i4"), ("response", "<f4")])
+TOP2_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i4"), ("second_dist", "<i4"), ("second_idx", "<i4")])
+MPPROJ_DTYPE = np.dtype(
+    [("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_right_x", "<f4"), ("view_cos", "<f4"), ("level", "<i4"), ("active", "<i4")]
+)
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("n_features", C.c_int32),
+        ("scale_factor", C.c_float),
+        ("n_levels", C.c_int32),
+        ("ini_th", C.c_int32),
+        ("min_th", C.c_int32),
+        ("sf", C.c_float * MAX_LEVELS),
+        ("inv_sf", C.c_float * MAX_LEVELS),
+        ("sf2", C.c_float * MAX_LEVELS),
+        ("inv_sf2", C.c_float * MAX_LEVELS),
+        ("quota", C.c_int32 * MAX_LEVELS),
+        ("umax", C.c_int32 * 16),
+    ]
+
+
+class FrameGeom(C.Structure):
+    _fields_ = [
+        ("min_x", C.c_float),
+        ("min_y", C.c_float),
+        ("max_x", C.c_float),
+        ("max_y", C.c_float),
+        ("n_levels", C.c_int32),
+        ("sf", C.c_float * MAX_LEVELS),
+    ]
+
+
+def build(force=False):
+    if force or not _SO.exists() or _SO.stat().st_mtime < (_HERE / "ydorb_oracle.cpp").stat().st_mtime:
+        subprocess.check_call(["make", "-C", str(_HERE)], stdout=subprocess.DEVNULL)
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(str(_SO))
+        _lib.orc_fast_atan2.restype = C.c_float
+        _lib.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+        _lib.orc_ic_angle.restype = C.c_float
+        _lib.orc_pyramid_bytes.restype = C.c_int64
+        _lib.orc_cvround.argtypes = [C.c_float]
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def make_params(n_features=1000, scale=1.2, n_levels=8, ini_th=20, min_th=None):
+    """min_th=None reproduces the reference ctor (min := ini, orbExtractor.cpp:318)."""
+    p = Params()
+    if min_th is None:
+        min_th = ini_th
+    rc = lib().orc_params_init(C.byref(p), n_features, C.c_float(scale), n_levels, ini_th, min_th)
+    assert rc == 0
+    return p
+
+
+def level_size(p, w, h, level):
+    lw, lh = C.c_int(), C.c_int()
+    lib().orc_level_size(C.byref(p), w, h, level, C.byref(lw), C.byref(lh))
+    return lw.value, lh.value
+
+
+def pyramid(p, img):
+    """Returns list of padded level arrays (views into one buffer)."""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w = img.shape
+    off = (C.c_int64 * MAX_LEVELS)()
+    tot = lib().orc_pyramid_bytes(C.byref(p), w, h, off)
+    buf = np.zeros(tot, dtype=np.uint8)
+    lib().orc_pyramid(C.byref(p), _p(img), w, h, w, _p(buf))
+    out = []
+    for l in range(p.n_levels):
+        lw, lh = level_size(p, w, h, l)
+        out.append(buf[off[l] : off[l] + (lw + 2 * PAD) * (lh + 2 * PAD)].reshape(lh + 2 * PAD, lw + 2 * PAD))
+    return out, buf
+
+
+def resize_linear(src, dw, dh):
+    src = np.ascontiguousarray(src, dtype=np.uint8)
+    dst = np.zeros((dh, dw), dtype=np.uint8)
+    lib().orc_resize_linear(_p(src), src.shape[1], src.shape[0], src.shape[1], _p(dst), dw, dh, dw)
+    return dst
+
+
+def gauss7(src):
+    src = np.ascontiguousarray(src, dtype=np.uint8)
+    dst = np.zeros_like(src)
+    lib().orc_gauss7(_p(src), src.shape[1], src.shape[0], src.shape[1], _p(dst), src.shape[1])
+    return dst
+
+
+def fast(img, th):
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    cap = img.size
+    xs = np.zeros(cap, np.int32)
+    ys = np.zeros(cap, np.int32)
+    rs = np.zeros(cap, np.int32)
+    n = lib().orc_fast(_p(img), img.shape[1], img.shape[0], img.shape[1], th, _p(xs), _p(ys), _p(rs), cap)
+    return xs[:n], ys[:n], rs[:n]
+
+
+def fast_atan2(y, x):
+    return float(lib().orc_fast_atan2(C.c_float(y), C.c_float(x)))
+
+
+def level_candidates(padded_level, ini_th, min_th):
+    """padded_level: (lh+38, lw+38) array.  Returns CAND_DTYPE array in reference order."""
+    lh, lw = padded_level.shape[0] - 2 * PAD, padded_level.shape[1] - 2 * PAD
+    st = padded_level.strides[0]
+    base = padded_level.ctypes.data + PAD * st + PAD
+    n = lib().orc_level_candidates(C.c_void_p(base), lw, lh, st, ini_th, min_th, None, 0)
+    out = np.zeros(max(n, 1), CAND_DTYPE)
+    lib().orc_level_candidates(C.c_void_p(base), lw, lh, st, ini_th, min_th, _p(out), n)
+    return out[:n]
+
+
+def quadtree(cand, rootw, rooth, want, form="list"):
+    cand = np.ascontiguousarray(cand, dtype=CAND_DTYPE)
+    sel = np.zeros(max(want, 1), np.int32)
+    fn = lib().orc_quadtree_list if form == "list" else lib().orc_quadtree_sortkey
+    m = fn(_p(cand), len(cand), rootw, rooth, want, _p(sel))
+    return sel[:m]
+
+
+def ic_angle(p, padded_level, x, y):
+    st = padded_level.strides[0]
+    base = padded_level.ctypes.data + PAD * st + PAD
+    return float(lib().orc_ic_angle(C.byref(p), C.c_void_p(base), st, int(x), int(y)))
+
+
+def descriptor(blurred, x, y, angle):
+    blurred = np.ascontiguousarray(blurred, dtype=np.uint8)
+    d = np.zeros(32, np.uint8)
+    lib().orc_descriptor(_p(blurred), blurred.shape[1], int(x), int(y), C.c_float(angle), _p(d))
+    return d
+
+
+def extract(p, img, cap=None):
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w = img.shape
+    cap = cap or (p.n_features + 64)
+    kps = np.zeros(cap, KP_DTYPE)
+    desc = np.zeros((cap, 32), np.uint8)
+    per = np.zeros(MAX_LEVELS, np.int32)
+    n = lib().orc_extract(C.byref(p), _p(img), w, h, w, _p(kps), _p(desc), cap, _p(per))
+    assert n <= cap
+    return kps[:n], desc[:n], per[: p.n_levels]
+
+
+def extract_batch(p, imgs, threads, cap=None):
+    imgs = np.ascontiguousarray(imgs, dtype=np.uint8)
+    b, h, w = imgs.shape
+    cap = cap or (p.n_features + 64)
+    kps = np.zeros((b, cap), KP_DTYPE)
+    desc = np.zeros((b, cap, 32), np.uint8)
+    n = np.zeros(b, np.int32)
+    lib().orc_extract_batch(C.byref(p), _p(imgs), w, h, w, C.c_int64(h * w), b, _p(kps), _p(desc), cap, _p(n), threads)
+    return kps, desc, n
+
+
+def hamming(a, b):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    b = np.ascontiguousarray(b, dtype=np.uint8)
+    return int(lib().orc_hamming(_p(a), _p(b)))
+
+
+def top2(q, db, idx_base=0, threads=None):
+    q = np.ascontiguousarray(q, dtype=np.uint8)
+    db = np.ascontiguousarray(db, dtype=np.uint8)
+    out = np.zeros(len(q), TOP2_DTYPE)
+    lib().orc_top2(_p(q), len(q), _p(db), len(db), idx_base, _p(out), threads or os.cpu_count())
+    return out
+
+
+def top2_merge(parts):
+    """parts: (nshards, nq) TOP2 array."""
+    parts = np.ascontiguousarray(parts, dtype=TOP2_DTYPE)
+    ns, nq = parts.shape
+    out = np.zeros(nq, TOP2_DTYPE)
+    lib().orc_top2_merge(_p(parts), ns, nq, _p(out))
+    return out
+
+
+def ratio_accept(t, ratio, th):
+    t = np.ascontiguousarray(t, dtype=TOP2_DTYPE)
+    acc = np.zeros(len(t), np.uint8)
+    lib().orc_ratio_accept(_p(t), len(t), C.c_float(ratio), th, _p(acc))
+    return acc
+
+
+def make_geom(p, w, h):
+    g = FrameGeom()
+    g.min_x, g.min_y, g.max_x, g.max_y = 0.0, 0.0, float(w), float(h)
+    g.n_levels = p.n_levels
+    for i in range(p.n_levels):
+        g.sf[i] = p.sf[i]
+    return g
+
+
+def keypoints_in_area(g, kps, x, y, r, min_level=-1, max_level=-1):
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+    out = np.zeros(max(len(kps), 1), np.int32)
+    n = lib().orc_keypoints_in_area(
+        C.byref(g), _p(kps), len(kps), C.c_float(x), C.c_float(y), C.c_float(r), min_level, max_level, _p(out), len(out)
+    )
+    return out[:n]
+
+
+def search_by_projection(g, kps, desc, right_x, kp_occupied, mps, mp_desc, mp_obs_positive, th, ratio):
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+    desc = np.ascontiguousarray(desc, dtype=np.uint8)
+    right_x = np.ascontiguousarray(right_x, dtype=np.float32)
+    kp_occupied = np.ascontiguousarray(kp_occupied, dtype=np.uint8)
+    mps = np.ascontiguousarray(mps, dtype=MPPROJ_DTYPE)
+    mp_desc = np.ascontiguousarray(mp_desc, dtype=np.uint8)
+    mp_obs_positive = np.ascontiguousarray(mp_obs_positive, dtype=np.uint8)
+    out = np.zeros(len(kps), np.int32)
+    n = lib().orc_search_by_projection(
+        C.byref(g), _p(kps), _p(desc), _p(right_x), len(kps), _p(kp_occupied), _p(mps), _p(mp_desc), _p(mp_obs_positive),
+        len(mps), C.c_float(th), C.c_float(ratio), _p(out),
+    )
+    return n, out
+
+
+def stereo_match(p, w, h, pyr_l, pyr_r, kpl, dl, kpr, dr, bf, max_d, mode=0):
+    kpl = np.ascontiguousarray(kpl, dtype=KP_DTYPE)
+    kpr = np.ascontiguousarray(kpr, dtype=KP_DTYPE)
+    dl = np.ascontiguousarray(dl, dtype=np.uint8)
+    dr = np.ascontiguousarray(dr, dtype=np.uint8)
+    rx = np.zeros(len(kpl), np.float32)
+    dp = np.zeros(len(kpl), np.float32)
+    lib().orc_stereo_match(
+        C.byref(p), w, h, _p(pyr_l), _p(pyr_r), _p(kpl), _p(dl), len(kpl), _p(kpr), _p(dr), len(kpr),
+        C.c_float(bf), C.c_float(max_d), mode, _p(rx), _p(dp),
+    )
+    return rx, dp

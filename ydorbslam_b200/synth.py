@@ -1,0 +1,146 @@
+"""Seeded synthetic inputs for parity tests and bench.py (numpy only, reproducible on any box).
+
+Shapes follow BASELINE.json `configs`; generators follow SURVEY.md 8(d).  All randomness is a counter-based
+hash (splitmix64 finaliser of seed/stream/index), so any frame can be produced independently and identically
+from Python on any machine.
+"""
+import numpy as np
+
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def _mix64(z):
+    """splitmix64 finaliser, vectorised over uint64 arrays."""
+    with np.errstate(over="ignore"):
+        z = (z + np.uint64(0x9E3779B97F4A7C15)) & _M64
+        z = ((z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)) & _M64
+        z = ((z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)) & _M64
+        return z ^ (z >> np.uint64(31))
+
+
+def rand_u64(seed, stream, n):
+    """n pseudo-random uint64 for (seed, stream)."""
+    with np.errstate(over="ignore"):
+        base = _mix64(np.uint64(seed) * np.uint64(0xD1B54A32D192ED03) + np.uint64(stream) * np.uint64(0x8CB92BA72F3D8DD7))
+        idx = np.arange(n, dtype=np.uint64)
+        return _mix64(idx * np.uint64(0x2545F4914F6CDD1D) + base)
+
+
+def rand_bytes(seed, stream, n):
+    nq = (n + 7) // 8
+    return rand_u64(seed, stream, nq).view(np.uint8)[:n].copy()
+
+
+def _binomial5(a):
+    """separable [1 4 6 4 1] in exact integers, reflect-101 borders; returns uint16 sums (x256)."""
+    a = a.astype(np.int32)
+    p = np.pad(a, ((0, 0), (2, 2)), mode="reflect")
+    hsum = p[:, 0:-4] + 4 * p[:, 1:-3] + 6 * p[:, 2:-2] + 4 * p[:, 3:-1] + p[:, 4:]
+    p = np.pad(hsum, ((2, 2), (0, 0)), mode="reflect")
+    return p[0:-4, :] + 4 * p[1:-3, :] + 6 * p[2:-2, :] + 4 * p[3:-1, :] + p[4:, :]
+
+
+def synth_frame(w, h, seed, n_rect=64, contrast=3):
+    """Textured synthetic gray frame: smoothed hash noise (contrast-stretched) + filled rectangles.
+
+    Dense enough that every pyramid level yields more FAST candidates than its quota (truncation,
+    tie and >16-point node paths all run)."""
+    noise = rand_bytes(seed, 1, w * h).reshape(h, w)
+    s = (_binomial5(noise) + 128) >> 8  # 0..255
+    s = np.clip((s - 128) * contrast + 128, 0, 255).astype(np.uint8)
+    r = rand_u64(seed, 2, n_rect * 5)
+    for i in range(n_rect):
+        x0 = int(r[5 * i] % np.uint64(w))
+        y0 = int(r[5 * i + 1] % np.uint64(h))
+        rw = 8 + int(r[5 * i + 2] % np.uint64(max(w // 6, 9)))
+        rh = 8 + int(r[5 * i + 3] % np.uint64(max(h // 6, 9)))
+        g = int(r[5 * i + 4] % np.uint64(256))
+        s[y0 : min(y0 + rh, h), x0 : min(x0 + rw, w)] = g
+    return s
+
+
+def synth_sparse_frame(w, h, seed, n_rect=24):
+    """Flat background with a few rectangles: few corners, many empty FAST cells (no-growth quadtree exit)."""
+    s = np.full((h, w), 96, np.uint8)
+    r = rand_u64(seed, 3, n_rect * 5)
+    for i in range(n_rect):
+        x0 = int(r[5 * i] % np.uint64(w))
+        y0 = int(r[5 * i + 1] % np.uint64(h))
+        rw = 6 + int(r[5 * i + 2] % np.uint64(max(w // 5, 7)))
+        rh = 6 + int(r[5 * i + 3] % np.uint64(max(h // 5, 7)))
+        g = int(r[5 * i + 4] % np.uint64(256))
+        s[y0 : min(y0 + rh, h), x0 : min(x0 + rw, w)] = g
+    return s
+
+
+def synth_batch(w, h, batch, seed0=0, **kw):
+    return np.stack([synth_frame(w, h, seed0 + i, **kw) for i in range(batch)])
+
+
+def synth_stereo_pair(w, h, seed):
+    """Right image = left shifted by a per-row-band disparity in 4..60 px, plus +-2 noise."""
+    left = synth_frame(w, h, seed)
+    bands = 8
+    disp = 4 + (rand_u64(seed, 4, bands) % np.uint64(57)).astype(np.int64)
+    right = np.empty_like(left)
+    wide = synth_frame(w + 64, h, seed + 7919)  # fills the strip uncovered by the shift
+    for b in range(bands):
+        y0, y1 = b * h // bands, (b + 1) * h // bands
+        d = int(disp[b])
+        right[y0:y1, : w - d] = left[y0:y1, d:]
+        right[y0:y1, w - d :] = wide[y0:y1, :d]
+    n = (rand_bytes(seed, 5, w * h).reshape(h, w) % 5).astype(np.int16) - 2
+    right = np.clip(right.astype(np.int16) + n, 0, 255).astype(np.uint8)
+    return left, right
+
+
+def synth_descriptors(n, seed):
+    return rand_bytes(seed, 6, n * 32).reshape(n, 32)
+
+
+def flip_bits(desc, p, seed):
+    """Flip each bit with probability p (p quantised to 1/256)."""
+    n = desc.shape[0]
+    thr = int(round(p * 256))
+    r = rand_bytes(seed, 7, n * 256).reshape(n, 256)
+    flips = np.packbits((r < thr).astype(np.uint8), axis=1, bitorder="little")
+    return desc ^ flips
+
+
+def synth_query_descriptors(db, nq, seed, p=0.08):
+    """Half: perturbed database rows (true matches); half: uniform random."""
+    n_true = nq // 2
+    rows = (rand_u64(seed, 8, n_true) % np.uint64(len(db))).astype(np.int64)
+    a = flip_bits(db[rows], p, seed)
+    b = synth_descriptors(nq - n_true, seed + 104729)
+    return np.concatenate([a, b], axis=0), rows
+
+
+def synth_map_points(kps, desc, n_mp, w, h, n_levels, seed):
+    """Projected local-map points for searchByProjection.
+
+    Returns dict of arrays: proj_x, proj_y, proj_right_x, view_cos, level, active, desc, obs_positive."""
+    r = rand_u64(seed, 9, n_mp * 6)
+    u = (r[0::6] >> np.uint64(11)).astype(np.float64) / float(1 << 53)
+    v = (r[1::6] >> np.uint64(11)).astype(np.float64) / float(1 << 53)
+    nk = max(len(kps), 1)
+    src = (r[2::6] % np.uint64(nk)).astype(np.int64)
+    near = (r[3::6] & np.uint64(1)).astype(bool)  # half project near an existing keypoint, half anywhere
+    px = np.where(near & (len(kps) > 0), (kps["x"][src] if len(kps) else 0) + (u - 0.5) * 6.0, u * w).astype(np.float32)
+    py = np.where(near & (len(kps) > 0), (kps["y"][src] if len(kps) else 0) + (v - 0.5) * 6.0, v * h).astype(np.float32)
+    lvl_rand = (r[4::6] % np.uint64(n_levels)).astype(np.int32)
+    level = np.where(near & (len(kps) > 0), kps["octave"][src] if len(kps) else 0, lvl_rand).astype(np.int32)
+    vc = (0.9 + 0.1 * ((r[5::6] >> np.uint64(11)).astype(np.float64) / float(1 << 53))).astype(np.float32)
+    if len(kps):
+        d_near = flip_bits(desc[src], 0.08, seed + 1)
+    else:
+        d_near = synth_descriptors(n_mp, seed + 2)
+    d_rand = synth_descriptors(n_mp, seed + 3)
+    d = np.where(near[:, None], d_near, d_rand)
+    r2 = rand_u64(seed, 10, n_mp * 2)
+    active = ((r2[0::2] % np.uint64(16)) != 0).astype(np.int32)  # 1/16 not in view
+    obs_pos = ((r2[1::2] % np.uint64(8)) != 0).astype(np.uint8)  # 1/8 have no observations yet
+    return dict(
+        proj_x=px, proj_y=py, proj_right_x=(px - 10.0).astype(np.float32), view_cos=vc, level=level, active=active,
+        desc=np.ascontiguousarray(d), obs_positive=obs_pos,
+    )
