@@ -1,0 +1,171 @@
+/*
+ * ydorb.h -- C ABI of libydorb.so: the B200 (sm_100a) implementation of YDORBSLAM's ORB front-end hot path.
+ *
+ * The reference has no FFI layer; its boundary is the C++ class surface of
+ *   YDORBSLAM::OrbExtractor   (src/orbExtractor.hpp:31-73)
+ *   YDORBSLAM::OrbMatcher     (src/orbMatcher.hpp:24-66)
+ *   YDORBSLAM::Frame hooks    (src/frame.hpp:83,96,166: computeStereoMatches, getKeyPointsInArea,
+ *                              assignKeyPointsToGrid)
+ * Each entry point below names the reference member it replaces.  INTEGRATION.md shows the C++ shim a
+ * maintainer adds on the reference side (ydorbslam_b200/cpp/ydorb.hpp is that shim without OpenCV types).
+ *
+ * Conventions: plain pointers and sizes, no exceptions, int status return (0 = ok, <0 = YDORB_E_*),
+ * caller-owned output buffers.  "host" entry points take host memory and synchronise before returning;
+ * "_device" entry points take device memory, enqueue on the handle's stream and do NOT synchronise.
+ * There is no CPU fallback: every entry point fails with YDORB_E_CUDA if no sm_100 device is usable.
+ * Handles may be used from different host threads, one thread at a time per handle (the reference runs the
+ * left and right extractor concurrently on two instances, src/frame.cpp:84-87).
+ */
+#ifndef YDORB_H
+#define YDORB_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define YDORB_OK 0
+#define YDORB_E_INVALID (-1)  /* bad argument */
+#define YDORB_E_CUDA (-2)     /* CUDA runtime error / no device */
+#define YDORB_E_CAPACITY (-3) /* an internal or caller buffer is too small */
+#define YDORB_E_STATE (-4)    /* call order (e.g. pyramid requested before any extract) */
+
+#define YDORB_MAX_LEVELS 16
+
+/* cv::KeyPoint (28 bytes): pt.x, pt.y, size, angle [deg], response, octave, class_id */
+typedef struct {
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+} YdKeyPoint;
+
+/* OrbExtractor ctor arguments, src/orbExtractor.hpp:33-34.  NOTE the reference ctor ignores minThFAST and uses
+ * iniThFAST for the fallback (src/orbExtractor.cpp:318); set reference_min_th_quirk=1 to reproduce that. */
+typedef struct {
+  int32_t n_features;
+  float scale_factor;
+  int32_t n_levels;
+  int32_t ini_th_fast;
+  int32_t min_th_fast;
+  int32_t reference_min_th_quirk;
+} YdExtractorParams;
+
+typedef struct YdExtractor YdExtractor;
+
+const char* ydorb_last_error(void); /* thread-local message of the last failing call */
+int ydorb_device_count(void);
+
+/* ---- OrbExtractor -------------------------------------------------------------------------------------- */
+/* OrbExtractor::OrbExtractor (src/orbExtractor.cpp:315-354).  max_* size the device buffers. */
+int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int max_height, int max_batch, int device,
+                           YdExtractor** out);
+void ydorb_extractor_destroy(YdExtractor* ex);
+/* getLevelsNum / getScaleFactor(s) / getInvScaleFactors / getScaleFactorSquares / getInvScaleFactorSquares
+ * (src/orbExtractor.hpp:42-48); each output array has n_levels entries, any may be NULL. */
+int ydorb_extractor_levels(const YdExtractor* ex);
+int ydorb_extractor_scale_tables(const YdExtractor* ex, float* sf, float* inv_sf, float* sf2, float* inv_sf2);
+int ydorb_extractor_quotas(const YdExtractor* ex, int32_t* per_level);
+/* CUDA stream (cudaStream_t) the handle enqueues on; lets callers time with events on that stream. */
+void* ydorb_extractor_stream(const YdExtractor* ex);
+
+/* OrbExtractor::extractAndCompute (src/orbExtractor.cpp:355-399): one CV_8UC1 image in; keypoints (level-major)
+ * and an N x 32 descriptor matrix out.  Fresh-extractor semantics (pyramid staleness not
+ * reproduced).  *n_out = keypoints written (<= capacity; YDORB_E_CAPACITY if more were produced). */
+int ydorb_extract(YdExtractor* ex, const uint8_t* image, int width, int height, int stride, YdKeyPoint* keypoints,
+                  uint8_t* descriptors, int capacity, int32_t* n_out);
+/* batch of same-sized frames: frame b at images + b*frame_stride; outputs at keypoints + b*capacity,
+ * descriptors + b*capacity*32; n_out[b]. */
+int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int height, int stride, size_t frame_stride,
+                        int batch, YdKeyPoint* keypoints, uint8_t* descriptors, int capacity, int32_t* n_out);
+/* same, all pointers in device memory, asynchronous on the handle's stream */
+int ydorb_extract_batch_device(YdExtractor* ex, const uint8_t* d_images, int width, int height, int stride,
+                               size_t frame_stride, int batch, YdKeyPoint* d_keypoints, uint8_t* d_descriptors,
+                               int capacity, int32_t* d_n_out);
+int ydorb_extractor_sync(YdExtractor* ex);
+
+/* m_v_imagePyramid (src/orbExtractor.hpp:50): padded level of the last extract call, device memory.
+ * *d_level points at the level's (0,0) pixel; 19 px of REFLECT_101 border are readable around it. */
+int ydorb_pyramid_level(const YdExtractor* ex, int frame, int level, const uint8_t** d_level, int* width, int* height,
+                        int* stride);
+/* copy a level to host; padded!=0 copies (w+38)x(h+38) including the border */
+int ydorb_pyramid_download(YdExtractor* ex, int frame, int level, int padded, uint8_t* dst, int dst_stride);
+
+/* Stage outputs of the last extract call, for parity tests (computeKeyPointsPyramid, src/orbExtractor.cpp:545-604):
+ * FAST candidates of one level in reference order (cells row-major, row-major inside a cell), coordinates relative
+ * to the 16 px border as distributeQuadTree sees them.  xy[2*i], xy[2*i+1]; resp[i]. */
+int ydorb_debug_candidates(YdExtractor* ex, int frame, int level, int32_t* xy, float* resp, int capacity, int32_t* n_out);
+
+/* ---- OrbMatcher ---------------------------------------------------------------------------------------- */
+typedef struct YdMatcher YdMatcher;
+
+/* per-query result of a top-2 scan (rule of src/orbMatcher.cpp:319-334: strict <, else-if strict <) */
+typedef struct {
+  int32_t best_idx;    /* -1 if no candidate */
+  int32_t best_dist;   /* 256 if none */
+  int32_t second_dist; /* 256 if none */
+  int32_t second_idx;  /* -1 if none */
+} YdTop2;
+
+int ydorb_matcher_create(int device, YdMatcher** out);
+void ydorb_matcher_destroy(YdMatcher* m);
+void* ydorb_matcher_stream(const YdMatcher* m);
+int ydorb_matcher_sync(YdMatcher* m);
+
+/* OrbMatcher::computeDescriptorsDistance (src/orbMatcher.cpp:11-23), n pairs: dist[i] = |a_i xor b_i| */
+int ydorb_hamming_pairs(YdMatcher* m, const uint8_t* a, const uint8_t* b, int n, int32_t* dist);
+/* dense top-2 of every query against a descriptor database shard (inner loops of searchByBow*,
+ * src/orbMatcher.cpp:319-334, without the greedy exclusion); idx_base is added to the indices (shard offset) */
+int ydorb_hamming_top2(YdMatcher* m, const uint8_t* queries, int nq, const uint8_t* db, int ndb, int idx_base,
+                       YdTop2* out);
+int ydorb_hamming_top2_device(YdMatcher* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, int ndb, int idx_base,
+                              YdTop2* d_out);
+/* merge per-shard results (shards[s*nq + i]) into the result of one scan over the whole database */
+int ydorb_top2_merge_device(YdMatcher* m, const YdTop2* d_shards, int nshards, int nq, YdTop2* d_out);
+/* accept[i] = best<=th && (float)best < ratio*(float)second   (src/orbMatcher.cpp:336) */
+int ydorb_ratio_accept_device(YdMatcher* m, const YdTop2* d_top2, int nq, float ratio, int th, uint8_t* d_accept);
+
+/* ---- Frame hooks + projection search -------------------------------------------------------------------- */
+typedef struct YdFrame YdFrame;
+
+typedef struct {
+  float min_x, min_y, max_x, max_y; /* image bounds, src/frame.cpp:223-248 */
+  int32_t n_levels;
+  float scale_factors[YDORB_MAX_LEVELS];
+} YdFrameGeom;
+
+/* one local map point as Frame::isInCameraFrustum left it (src/frame.cpp:295-326) */
+typedef struct {
+  float proj_x, proj_y, proj_right_x, view_cos;
+  int32_t level;  /* m_int_trackScaleLevel */
+  int32_t active; /* m_b_isTrackInView && !isBad() */
+} YdMapPointProj;
+
+/* Frame feature state on the device + Frame::assignKeyPointsToGrid (src/frame.cpp:249-264).
+ * right_x may be NULL (all -1). Host pointers. */
+int ydorb_frame_create(YdMatcher* m, const YdFrameGeom* geom, const YdKeyPoint* keypoints, const uint8_t* descriptors,
+                       const float* right_x, int n, YdFrame** out);
+void ydorb_frame_destroy(YdFrame* f);
+/* Frame::getKeyPointsInArea (src/frame.cpp:337-361), reference predicate and order; *n_out may exceed capacity */
+int ydorb_frame_keypoints_in_area(YdFrame* f, float x, float y, float r, int min_level, int max_level, int32_t* out,
+                                  int capacity, int32_t* n_out);
+/* OrbMatcher::searchByProjectionInFrameAndMapPoint (src/orbMatcher.cpp:24-64).  kp_occupied[i]!=0: slot i holds a
+ * map point with observations>0 before the call; mp_obs_positive[j]: map point j has observations>0.
+ * match_out[i] = map point index assigned to keypoint i by this call or -1; *n_matches = return value of the
+ * reference function. Host pointers. */
+int ydorb_search_by_projection(YdFrame* f, const YdMapPointProj* map_points, const uint8_t* mp_descriptors,
+                               const uint8_t* mp_obs_positive, int n_map_points, const uint8_t* kp_occupied, float th,
+                               float ratio, int32_t* match_out, int32_t* n_matches);
+
+/* Frame::computeStereoMatches (src/frame.cpp:362-472) on the pyramids held by two extractor handles
+ * (frame index = position in their last batch).  mode 0 = reference (leftIdx lag etc.),
+ * 1 = corrected (descriptor row and output slot follow the keypoint).  max_d = bf/baseline (+inf on the
+ * reference's first frame).  Host pointers; right_x/depth have n_left entries. */
+int ydorb_stereo_match(YdMatcher* m, const YdExtractor* left, int left_frame, const YdExtractor* right, int right_frame,
+                       const YdKeyPoint* kp_left, const uint8_t* desc_left, int n_left, const YdKeyPoint* kp_right,
+                       const uint8_t* desc_right, int n_right, float bf, float max_d, int mode, float* right_x,
+                       float* depth);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* YDORB_H */

@@ -1,0 +1,105 @@
+"""GPU parity: CUDA extractor (through the C ABI) vs cv2-generated golden fixtures and vs the CPU oracle."""
+import numpy as np
+import pytest
+
+from oracle import orc
+from tests.util import golden_input, sha
+from ydorbslam_b200 import OrbExtractor, synth
+
+pytestmark = pytest.mark.gpu
+
+CASES = ["image0", "synth640", "sparse640", "synth1241", "tiny97"]
+
+
+def _check_against(ex, img, kps, desc, gk, gd):
+    assert len(kps) == len(gk)
+    for f in ("x", "y", "size", "response", "octave", "class_id"):
+        assert np.array_equal(kps[f], gk[f]), f
+    # angles: bit-exact expected; north_star tolerance is 1e-4 rad
+    dang = np.abs(kps["angle"] - gk["angle"])
+    dang = np.minimum(dang, 360.0 - dang)
+    assert float(dang.max(initial=0.0)) * np.pi / 180.0 <= 1e-4
+    bits = np.unpackbits(desc ^ gd).sum()
+    assert bits <= 0.001 * desc.size * 8, f"{bits} descriptor bits differ"
+    return int((kps["angle"].view(np.uint32) != gk["angle"].view(np.uint32)).sum()), int(bits)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_extract_matches_golden(golden_dir, name):
+    g = np.load(golden_dir / f"extract_{name}.npz")
+    img = golden_input(name, g)
+    nf = int(g["n_features"])
+    h, w = img.shape
+    ex = OrbExtractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=1)
+    kps, desc = ex.extractAndCompute(img)
+    # stages
+    for l in range(8):
+        assert sha(ex.pyramid_level(0, l, padded=True)) == str(g[f"pyr_sha_{l}"]), f"pyramid level {l}"
+        xy, resp = ex.debug_candidates(0, l)
+        gc = g[f"cand_{l}"]
+        assert len(xy) == len(gc), f"candidate count level {l}: {len(xy)} vs {len(gc)}"
+        if len(gc):
+            assert np.array_equal(np.concatenate([xy, resp[:, None]], 1).astype(np.float32), gc), f"candidates level {l}"
+    nang, nbits = _check_against(ex, img, kps, desc, g["kps"], g["desc"])
+    assert nang == 0 and nbits == 0, (nang, nbits)  # bit-exact on the fixtures
+    ex.close()
+
+
+@pytest.mark.parametrize("shape,nf,seed", [((480, 640), 1000, 21), ((376, 1241), 2000, 22), ((1080, 1920), 4000, 23),
+                                           ((333, 517), 700, 24)])
+def test_extract_matches_oracle(shape, nf, seed):
+    h, w = shape
+    img = synth.synth_frame(w, h, seed)
+    p = orc.make_params(nf, 1.2, 8, 20)
+    ok, od, _ = orc.extract(p, img, cap=nf + 64)
+    ex = OrbExtractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=1)
+    kps, desc = ex.extractAndCompute(img)
+    _check_against(ex, img, kps, desc, ok, od)
+    ex.close()
+
+
+def test_batch_and_reuse():
+    """Batch of different frames == frame-by-frame; a reused handle gives fresh-extractor results."""
+    imgs = synth.synth_batch(640, 480, 5, seed0=100)
+    imgs[3] = synth.synth_sparse_frame(640, 480, 9)
+    imgs[4] = 50  # flat: no keypoints
+    ex = OrbExtractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480, max_batch=5)
+    kps, desc, n = ex.extract_batch(imgs)
+    p = orc.make_params(1000, 1.2, 8, 20)
+    for b in range(5):
+        ok, od, _ = orc.extract(p, imgs[b])
+        assert n[b] == len(ok), (b, n[b], len(ok))
+        for f in ("x", "y", "size", "response", "octave", "angle"):
+            assert np.array_equal(kps[b, : n[b]][f], ok[f]), (b, f)
+        assert np.array_equal(desc[b, : n[b]], od)
+    assert n[4] == 0
+    # second call on the same handle with another size
+    img2 = synth.synth_frame(320, 240, 5)
+    k2, d2 = ex.extractAndCompute(img2)
+    ok, od, _ = orc.extract(p, img2)
+    assert np.array_equal(k2["x"], ok["x"]) and np.array_equal(d2, od)
+    ex.close()
+
+
+def test_min_threshold_fallback():
+    """True two-threshold fallback (library) vs reference quirk min:=ini."""
+    img = (synth.synth_frame(640, 480, 31, contrast=1) // 2 + 64).astype(np.uint8)  # low contrast: many empty cells at th=20
+    for quirk in (True, False):
+        p = orc.make_params(1000, 1.2, 8, 20, 20 if quirk else 7)
+        ok, od, _ = orc.extract(p, img)
+        ex = OrbExtractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480, reference_min_th_quirk=quirk)
+        k, d = ex.extractAndCompute(img)
+        assert len(k) == len(ok)
+        assert np.array_equal(k["x"], ok["x"]) and np.array_equal(k["y"], ok["y"]) and np.array_equal(d, od)
+        ex.close()
+
+
+def test_empty_image_and_errors():
+    ex = OrbExtractor(500, 1.2, 8, 20, 7, max_width=320, max_height=240)
+    k, d = ex.extractAndCompute(np.zeros((0, 0), np.uint8))
+    assert len(k) == 0 and d.shape == (0, 32)
+    from ydorbslam_b200 import YdorbError
+
+    with pytest.raises(YdorbError):
+        ex.extractAndCompute(np.zeros((480, 640), np.uint8))  # larger than max
+    ex.close()

@@ -1,0 +1,78 @@
+"""ctypes loader for libydorb.so.  There is no fallback: if the CUDA library is missing, importing fails."""
+import ctypes as C
+import pathlib
+
+import numpy as np
+
+HERE = pathlib.Path(__file__).resolve().parent
+LIB_PATH = HERE / "libydorb.so"
+MAX_LEVELS = 16
+
+KP_DTYPE = np.dtype(
+    [("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")]
+)
+TOP2_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i4"), ("second_dist", "<i4"), ("second_idx", "<i4")])
+MPPROJ_DTYPE = np.dtype(
+    [("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_right_x", "<f4"), ("view_cos", "<f4"), ("level", "<i4"), ("active", "<i4")]
+)
+
+
+class ExtractorParams(C.Structure):
+    _fields_ = [
+        ("n_features", C.c_int32),
+        ("scale_factor", C.c_float),
+        ("n_levels", C.c_int32),
+        ("ini_th_fast", C.c_int32),
+        ("min_th_fast", C.c_int32),
+        ("reference_min_th_quirk", C.c_int32),
+    ]
+
+
+class FrameGeom(C.Structure):
+    _fields_ = [
+        ("min_x", C.c_float),
+        ("min_y", C.c_float),
+        ("max_x", C.c_float),
+        ("max_y", C.c_float),
+        ("n_levels", C.c_int32),
+        ("scale_factors", C.c_float * MAX_LEVELS),
+    ]
+
+
+class YdorbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libydorb error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -m ydorbslam_b200.build` (nvcc, sm_100a). "
+                "There is no CPU fallback."
+            )
+        _lib = C.CDLL(str(LIB_PATH))
+        _lib.ydorb_last_error.restype = C.c_char_p
+        _lib.ydorb_extractor_stream.restype = C.c_void_p
+        _lib.ydorb_matcher_stream.restype = C.c_void_p
+        for name in ("ydorb_extractor_destroy", "ydorb_matcher_destroy", "ydorb_frame_destroy"):
+            getattr(_lib, name).restype = None
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise YdorbError(rc, lib().ydorb_last_error().decode())
+
+
+def ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(C.c_void_p)
+    return C.c_void_p(int(a))  # raw device pointer

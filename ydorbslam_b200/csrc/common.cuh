@@ -1,0 +1,106 @@
+// Internal definitions shared by the libydorb.so translation units (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/ydorb.h"
+
+namespace ydorb {
+
+constexpr int kPad = 19;       // m_int_maxPadSize    src/orbExtractor.hpp:72
+constexpr int kBorder = 16;    // kPad - 3            src/orbExtractor.cpp:550
+constexpr int kHalfPatch = 15; // m_int_halfPatchSize src/orbExtractor.hpp:71
+constexpr int kPatch = 31;     // m_int_patchSize     src/orbExtractor.hpp:70
+constexpr int kMaxLevels = YDORB_MAX_LEVELS;
+constexpr int kQtDigits = 16;  // quadtree path digits per code (2 bits each)
+
+void set_error(const std::string& msg);
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define YD_CUDA(expr)                                                         \
+  do {                                                                        \
+    cudaError_t _e = (expr);                                                  \
+    if (_e != cudaSuccess) return ::ydorb::cuda_fail(_e, #expr, __FILE__, __LINE__); \
+  } while (0)
+
+#define YD_REQUIRE(cond, msg)             \
+  do {                                    \
+    if (!(cond)) {                        \
+      ::ydorb::set_error(msg);            \
+      return YDORB_E_INVALID;             \
+    }                                     \
+  } while (0)
+
+// Geometry of one pyramid level for the current image size (device copy lives in constant-like global memory).
+struct LevelGeom {
+  int w, h;            // level size (E2, src/orbExtractor.cpp:608-609)
+  int stride;          // row stride of the padded buffer (multiple of 16)
+  int64_t offset;      // byte offset of the padded buffer inside a frame's pyramid block
+  int cell_cols, cell_rows, cell_w, cell_h;  // FAST grid (E3, src/orbExtractor.cpp:556-561)
+  int cell_base;       // index of this level's first cell in the frame's cell table
+  int quota;           // m_v_keyPointsNumsPerLevel[level]
+  int quota_base;      // prefix sum of quotas
+  int root_w, root_h;  // quadtree root extents (maxBorder - minBorder)
+  int tab_base;        // offset of this level's resize tables (x then y) in the table arrays; level 0 unused
+  float sf;            // m_v_scaleFactors[level]
+  float size;          // (float)(int)(31*sf)
+};
+
+struct FrameGeomDev {
+  int n_levels;
+  int n_cells;          // total cells over all levels
+  int n_quota;          // sum of quotas
+  int64_t pyr_bytes;    // bytes of one frame's pyramid block
+  int raw_cap;          // candidate capacity per frame
+  LevelGeom lv[kMaxLevels];
+};
+
+// device pointer to the padded level origin (pixel (0,0) of the level, pad readable around it)
+__host__ __device__ inline int64_t level_origin(const LevelGeom& g) {
+  return g.offset + (int64_t)kPad * g.stride + kPad;
+}
+
+}  // namespace ydorb
+
+// The extractor handle (opaque to C callers).
+struct YdExtractor {
+  YdExtractorParams params;
+  int device;
+  int max_w, max_h, max_batch;
+  cudaStream_t stream;
+  float sf[ydorb::kMaxLevels], inv_sf[ydorb::kMaxLevels], sf2[ydorb::kMaxLevels], inv_sf2[ydorb::kMaxLevels];
+  int quota[ydorb::kMaxLevels];
+  int umax[16];
+  // geometry for the current (w,h)
+  int cur_w, cur_h, cur_batch;
+  ydorb::FrameGeomDev geom;       // host copy
+  ydorb::FrameGeomDev* d_geom;    // device copy
+  // capacities computed for (max_w,max_h)
+  int64_t cap_pyr_bytes;
+  int cap_cells, cap_raw, cap_tab;
+  // device buffers
+  uint8_t* d_pyr;        // [max_batch][cap_pyr_bytes]
+  int* d_tab_ofs;        // resize source offsets
+  short* d_tab_a;        // resize weights (a0,a1 interleaved)
+  int4* d_cells;         // per-cell ROI {x0,y0,x1,y1} (level coords), [cap_cells]
+  int* d_cell_count;     // [max_batch][cap_cells]
+  int* d_cell_start;     // [max_batch][cap_cells]
+  int* d_cell_rank;      // [max_batch][cap_cells+1] exclusive scan of counts (candidate order)
+  uint32_t* d_raw;       // [max_batch][cap_raw] packed candidates (y:12 | x:12 | response:8, border-relative)
+  int* d_raw_counter;    // [max_batch]
+  uint32_t* d_qt_keys[3];  // [max_batch][cap_raw] quadtree sort scratch
+  uint32_t* d_qt_vals[3];
+  int* d_level_ncand;    // [max_batch][kMaxLevels]
+  int4* d_sel;           // [max_batch][n_quota] selected keypoints {x,y (level coords), response bits, level}
+  int* d_sel_n;          // [max_batch][kMaxLevels]
+  int* d_status;         // device-side error flags
+  // staging for the host entry points
+  uint8_t* d_images;     // [max_batch][max_w*max_h]
+  YdKeyPoint* d_kps;
+  uint8_t* d_desc;
+  int32_t* d_nout;
+  int out_cap;           // per-frame capacity of d_kps/d_desc
+};

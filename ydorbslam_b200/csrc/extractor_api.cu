@@ -1,0 +1,443 @@
+// C ABI of the extractor (include/ydorb.h): handle life cycle, per-size geometry and OpenCV-compatible resize
+// tables built on the host, stage orchestration on the handle's stream.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "kernels.cuh"
+
+namespace ydorb {
+
+static thread_local std::string g_last_error;
+
+void set_error(const std::string& msg) { g_last_error = msg; }
+
+int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  char buf[512];
+  snprintf(buf, sizeof buf, "CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+  g_last_error = buf;
+  return YDORB_E_CUDA;
+}
+
+static inline int cv_round(float v) { return (int)lrintf(v); }  // cvRound(float): half to even
+static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// OrbExtractor ctor tables, src/orbExtractor.cpp:325-353
+static void ctor_tables(YdExtractor* ex) {
+  const YdExtractorParams& p = ex->params;
+  const float sf = p.scale_factor;
+  int per_level = (int)round(p.n_features * (1 - 1.0 / sf) / (1.0 - pow(1.0 / sf, p.n_levels)));
+  int sum = 0;
+  for (int i = 0; i < p.n_levels; i++) {
+    ex->sf[i] = (float)pow((double)sf, (double)i);
+    ex->sf2[i] = (float)pow((double)sf, (double)(2 * i));
+    ex->inv_sf[i] = (float)pow((double)sf, (double)(-i));
+    ex->inv_sf2[i] = (float)pow((double)sf, (double)(-2 * i));
+    if (i < p.n_levels - 1) {
+      ex->quota[i] = per_level;
+      sum += per_level;
+      per_level = (int)round((double)((float)per_level / sf));
+    } else {
+      ex->quota[i] = std::max(p.n_features - sum, 0);
+    }
+  }
+  // m_v_maxXcords as the reference computes it (resize + push_back, "+v^2"): {0 x11, 26,25,22,19,15}; the kernel
+  // hard-codes this footprint, recompute here only to assert the constant stays what describe.cu assumes.
+  static const int expect[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 26, 25, 22, 19, 15};
+  memcpy(ex->umax, expect, sizeof expect);
+}
+
+// one axis of cv::resize INTER_LINEAR 8U: source offset and 11-bit weights
+static void linear_axis(int sn, int dn, int* ofs, short* a) {
+  const double scale = 1.0 / ((double)dn / (double)sn);
+  for (int d = 0; d < dn; d++) {
+    float f = (float)((d + 0.5) * scale - 0.5);
+    int s = (int)floorf(f);
+    f -= (float)s;
+    if (s < 0) { s = 0; f = 0.f; }
+    if (s >= sn - 1) { s = sn - 1; f = 0.f; }
+    ofs[d] = s;
+    a[2 * d] = (short)cv_round((1.f - f) * 2048.f);
+    a[2 * d + 1] = (short)cv_round(f * 2048.f);
+  }
+}
+
+struct HostGeom {
+  FrameGeomDev g;
+  std::vector<int> tab_ofs;
+  std::vector<short> tab_a;
+  std::vector<int4> cells;
+  int64_t tested_px;
+};
+
+// Geometry for an image size: level sizes (:608-609), padded layout, FAST cell grid (:550-579), quadtree roots.
+static int build_geom(const YdExtractor* ex, int w, int h, HostGeom* out) {
+  FrameGeomDev& g = out->g;
+  memset(&g, 0, sizeof g);
+  const int L = ex->params.n_levels;
+  g.n_levels = L;
+  int64_t off = 0;
+  int cell_base = 0, quota_base = 0, tab_base = 0;
+  out->tested_px = 0;
+  for (int l = 0; l < L; l++) {
+    LevelGeom& lv = g.lv[l];
+    lv.w = cv_round((float)w * ex->inv_sf[l]);
+    lv.h = cv_round((float)h * ex->inv_sf[l]);
+    if (lv.w <= kPad || lv.h <= kPad) {
+      set_error("image too small: every pyramid level must be larger than the 19 px border");
+      return YDORB_E_INVALID;
+    }
+    if (lv.w - 2 * kBorder > 4095 || lv.h - 2 * kBorder > 4095) {
+      set_error("image too large: level extents above 4127 px are not supported by the candidate packing");
+      return YDORB_E_INVALID;
+    }
+    lv.stride = round_up(lv.w + 2 * kPad, 16);
+    lv.offset = off;
+    off += (int64_t)round_up(lv.stride * (lv.h + 2 * kPad), 256);
+    const int minB = kBorder, maxBX = lv.w - kBorder, maxBY = lv.h - kBorder;
+    const float width = (float)(maxBX - minB), height = (float)(maxBY - minB);
+    const int cols = width > 0 ? (int)(width / 30.0f) : 0, rows = height > 0 ? (int)(height / 30.0f) : 0;
+    lv.cell_base = cell_base;
+    lv.root_w = maxBX - minB;
+    lv.root_h = maxBY - minB;
+    if (cols > 0 && rows > 0) {
+      lv.cell_cols = cols;
+      lv.cell_rows = rows;
+      lv.cell_w = (int)ceilf(width / cols);
+      lv.cell_h = (int)ceilf(height / rows);
+      for (int i = 0; i < rows; i++) {
+        const float iniY = (float)(minB + i * lv.cell_h);
+        float maxY = iniY + lv.cell_h + 6;
+        const bool skip_row = iniY >= maxBY - 3;
+        if (maxY > maxBY) maxY = (float)maxBY;
+        for (int j = 0; j < cols; j++) {
+          const float iniX = (float)(minB + j * lv.cell_w);
+          float maxX = iniX + lv.cell_w + 6;
+          const bool skip = skip_row || iniX >= maxBX - 6;
+          if (maxX > maxBX) maxX = (float)maxBX;
+          int4 c = make_int4((int)iniX, (int)iniY, (int)maxX, (int)maxY);
+          if (skip || c.z - c.x < 7 || c.w - c.y < 7) c = make_int4(0, 0, 0, 0);
+          else out->tested_px += (int64_t)(c.z - c.x - 6) * (c.w - c.y - 6);
+          if (c.z - c.x > 66 || c.w - c.y > 66) {
+            set_error("internal: FAST cell larger than the shared-memory tile");
+            return YDORB_E_INVALID;
+          }
+          out->cells.push_back(c);
+        }
+      }
+      cell_base += cols * rows;
+    }
+    lv.quota = ex->quota[l];
+    lv.quota_base = quota_base;
+    quota_base += lv.quota;
+    lv.sf = ex->sf[l];
+    lv.size = (float)(int)(kPatch * ex->sf[l]);
+    lv.tab_base = tab_base;
+    if (l > 0) {
+      out->tab_ofs.resize(tab_base + lv.w + lv.h);
+      out->tab_a.resize(2 * (size_t)(tab_base + lv.w + lv.h));
+      linear_axis(g.lv[l - 1].w, lv.w, out->tab_ofs.data() + tab_base, out->tab_a.data() + 2 * (size_t)tab_base);
+      linear_axis(g.lv[l - 1].h, lv.h, out->tab_ofs.data() + tab_base + lv.w,
+                  out->tab_a.data() + 2 * (size_t)(tab_base + lv.w));
+      tab_base += lv.w + lv.h;
+    }
+  }
+  g.n_cells = cell_base;
+  g.n_quota = quota_base;
+  g.pyr_bytes = off;
+  // candidate capacity: NMS keeps at most one pixel per 2x2 block; default provision is one per 8 tested pixels
+  g.raw_cap = (int)std::max<int64_t>(out->tested_px / 8 + 1024, 4096);
+  return YDORB_OK;
+}
+
+static int set_size(YdExtractor* ex, int w, int h) {
+  if (ex->cur_w == w && ex->cur_h == h) return YDORB_OK;
+  HostGeom hg;
+  int rc = build_geom(ex, w, h, &hg);
+  if (rc != YDORB_OK) return rc;
+  if (hg.g.pyr_bytes > ex->cap_pyr_bytes || hg.g.n_cells > ex->cap_cells || hg.g.raw_cap > ex->cap_raw ||
+      (int)hg.tab_ofs.size() > ex->cap_tab) {
+    set_error("image larger than the max_width/max_height the extractor was created with");
+    return YDORB_E_CAPACITY;
+  }
+  ex->geom = hg.g;
+  YD_CUDA(cudaMemcpyAsync(ex->d_geom, &ex->geom, sizeof(FrameGeomDev), cudaMemcpyHostToDevice, ex->stream));
+  if (!hg.tab_ofs.empty()) {
+    YD_CUDA(cudaMemcpyAsync(ex->d_tab_ofs, hg.tab_ofs.data(), hg.tab_ofs.size() * sizeof(int), cudaMemcpyHostToDevice, ex->stream));
+    YD_CUDA(cudaMemcpyAsync(ex->d_tab_a, hg.tab_a.data(), hg.tab_a.size() * sizeof(short), cudaMemcpyHostToDevice, ex->stream));
+  }
+  if (!hg.cells.empty())
+    YD_CUDA(cudaMemcpyAsync(ex->d_cells, hg.cells.data(), hg.cells.size() * sizeof(int4), cudaMemcpyHostToDevice, ex->stream));
+  YD_CUDA(cudaStreamSynchronize(ex->stream));  // host vectors go out of scope
+  ex->cur_w = w;
+  ex->cur_h = h;
+  return YDORB_OK;
+}
+
+static int check_status(YdExtractor* ex) {
+  int st = 0;
+  YD_CUDA(cudaMemcpyAsync(&st, ex->d_status, sizeof(int), cudaMemcpyDeviceToHost, ex->stream));
+  YD_CUDA(cudaStreamSynchronize(ex->stream));
+  if (st == 0) return YDORB_OK;
+  YD_CUDA(cudaMemsetAsync(ex->d_status, 0, sizeof(int), ex->stream));
+  if (st & kStatusRawOverflow) { set_error("FAST candidate buffer overflow (more than 1 corner per 8 px)"); return YDORB_E_CAPACITY; }
+  if (st & kStatusSortDepth) { set_error("std::sort emulation stack overflow"); return YDORB_E_CAPACITY; }
+  if (st & kStatusOutOverflow) { set_error("keypoint capacity too small"); return YDORB_E_CAPACITY; }
+  return YDORB_OK;
+}
+
+static int run_pipeline(YdExtractor* ex, const uint8_t* d_images, int w, int h, int stride, size_t frame_stride,
+                        int batch, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity, int32_t* d_nout) {
+  int rc = set_size(ex, w, h);
+  if (rc != YDORB_OK) return rc;
+  ex->cur_batch = batch;
+  cudaStream_t s = ex->stream;
+  if ((rc = launch_pyramid(ex, d_images, stride, frame_stride, batch, s)) != YDORB_OK) return rc;
+  if (ex->geom.n_cells == 0 || ex->geom.n_quota == 0) {
+    YD_CUDA(cudaMemsetAsync(d_nout, 0, sizeof(int32_t) * batch, s));
+    YD_CUDA(cudaMemsetAsync(ex->d_sel_n, 0, sizeof(int) * kMaxLevels * batch, s));
+    YD_CUDA(cudaMemsetAsync(ex->d_level_ncand, 0, sizeof(int) * kMaxLevels * batch, s));
+    return YDORB_OK;
+  }
+  if ((rc = launch_fast(ex, batch, s)) != YDORB_OK) return rc;
+  if ((rc = launch_quadtree(ex, batch, s)) != YDORB_OK) return rc;
+  if ((rc = launch_describe(ex, batch, d_kps, d_desc, capacity, d_nout, s)) != YDORB_OK) return rc;
+  return YDORB_OK;
+}
+
+}  // namespace ydorb
+
+using namespace ydorb;
+
+extern "C" {
+
+const char* ydorb_last_error(void) { return g_last_error.c_str(); }
+
+int ydorb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int max_height, int max_batch, int device,
+                           YdExtractor** out) {
+  YD_REQUIRE(params && out, "null argument");
+  YD_REQUIRE(params->n_levels >= 1 && params->n_levels <= kMaxLevels, "n_levels out of range");
+  YD_REQUIRE(params->scale_factor > 1.0f, "scale_factor must be > 1");
+  YD_REQUIRE(params->n_features >= 0, "n_features must be >= 0");
+  YD_REQUIRE(max_width > 0 && max_height > 0 && max_batch > 0, "bad capacity");
+  int ndev = 0;
+  YD_CUDA(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) { set_error("no such CUDA device"); return YDORB_E_CUDA; }
+  YD_CUDA(cudaSetDevice(device));
+  YdExtractor* ex = new YdExtractor();
+  memset(ex, 0, sizeof *ex);
+  ex->params = *params;
+  ex->device = device;
+  ex->max_w = max_width;
+  ex->max_h = max_height;
+  ex->max_batch = max_batch;
+  ctor_tables(ex);
+  HostGeom hg;
+  int rc = build_geom(ex, max_width, max_height, &hg);
+  if (rc != YDORB_OK) { delete ex; return rc; }
+  // capacities: geometry of the largest size, with slack so smaller sizes with different rounding still fit
+  ex->cap_pyr_bytes = hg.g.pyr_bytes + 64 * 1024;
+  ex->cap_cells = hg.g.n_cells + 64;
+  ex->cap_raw = hg.g.raw_cap;
+  ex->cap_tab = (int)hg.tab_ofs.size() + 64;
+  const int nq = std::max(hg.g.n_quota, 1);
+  ex->out_cap = nq;
+  const size_t B = (size_t)max_batch;
+  cudaError_t e = cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking);
+  auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, std::max<size_t>(bytes, 16)); };
+  alloc((void**)&ex->d_geom, sizeof(FrameGeomDev));
+  alloc((void**)&ex->d_pyr, B * ex->cap_pyr_bytes);
+  alloc((void**)&ex->d_tab_ofs, sizeof(int) * ex->cap_tab);
+  alloc((void**)&ex->d_tab_a, sizeof(short) * 2 * ex->cap_tab);
+  alloc((void**)&ex->d_cells, sizeof(int4) * ex->cap_cells);
+  alloc((void**)&ex->d_cell_count, sizeof(int) * B * ex->cap_cells);
+  alloc((void**)&ex->d_cell_start, sizeof(int) * B * ex->cap_cells);
+  alloc((void**)&ex->d_cell_rank, sizeof(int) * B * (ex->cap_cells + 1));
+  alloc((void**)&ex->d_raw, sizeof(uint32_t) * B * ex->cap_raw);
+  alloc((void**)&ex->d_raw_counter, sizeof(int) * B);
+  for (int i = 0; i < 3; i++) {
+    alloc((void**)&ex->d_qt_keys[i], sizeof(uint32_t) * B * ex->cap_raw);
+    alloc((void**)&ex->d_qt_vals[i], sizeof(uint32_t) * B * ex->cap_raw);
+  }
+  alloc((void**)&ex->d_level_ncand, sizeof(int) * B * kMaxLevels);
+  alloc((void**)&ex->d_sel, sizeof(int4) * B * nq);
+  alloc((void**)&ex->d_sel_n, sizeof(int) * B * kMaxLevels);
+  alloc((void**)&ex->d_status, sizeof(int));
+  alloc((void**)&ex->d_images, B * (size_t)max_width * max_height);
+  alloc((void**)&ex->d_kps, sizeof(YdKeyPoint) * B * nq);
+  alloc((void**)&ex->d_desc, 32 * B * nq);
+  alloc((void**)&ex->d_nout, sizeof(int32_t) * B);
+  if (e == cudaSuccess) e = cudaMemset(ex->d_status, 0, sizeof(int));
+  if (e != cudaSuccess) {
+    int r = cuda_fail(e, "extractor allocation", __FILE__, __LINE__);
+    ydorb_extractor_destroy(ex);
+    return r;
+  }
+  ex->cur_w = ex->cur_h = -1;
+  *out = ex;
+  return YDORB_OK;
+}
+
+void ydorb_extractor_destroy(YdExtractor* ex) {
+  if (!ex) return;
+  cudaSetDevice(ex->device);
+  void* ptrs[] = {ex->d_geom, ex->d_pyr, ex->d_tab_ofs, ex->d_tab_a, ex->d_cells, ex->d_cell_count, ex->d_cell_start,
+                  ex->d_cell_rank, ex->d_raw, ex->d_raw_counter, ex->d_qt_keys[0], ex->d_qt_keys[1], ex->d_qt_keys[2],
+                  ex->d_qt_vals[0], ex->d_qt_vals[1], ex->d_qt_vals[2], ex->d_level_ncand, ex->d_sel, ex->d_sel_n,
+                  ex->d_status, ex->d_images, ex->d_kps, ex->d_desc, ex->d_nout};
+  for (void* p : ptrs)
+    if (p) cudaFree(p);
+  if (ex->stream) cudaStreamDestroy(ex->stream);
+  delete ex;
+}
+
+int ydorb_extractor_levels(const YdExtractor* ex) { return ex ? ex->params.n_levels : 0; }
+
+int ydorb_extractor_scale_tables(const YdExtractor* ex, float* sf, float* inv_sf, float* sf2, float* inv_sf2) {
+  YD_REQUIRE(ex, "null extractor");
+  const size_t n = sizeof(float) * ex->params.n_levels;
+  if (sf) memcpy(sf, ex->sf, n);
+  if (inv_sf) memcpy(inv_sf, ex->inv_sf, n);
+  if (sf2) memcpy(sf2, ex->sf2, n);
+  if (inv_sf2) memcpy(inv_sf2, ex->inv_sf2, n);
+  return YDORB_OK;
+}
+
+int ydorb_extractor_quotas(const YdExtractor* ex, int32_t* per_level) {
+  YD_REQUIRE(ex && per_level, "null argument");
+  for (int i = 0; i < ex->params.n_levels; i++) per_level[i] = ex->quota[i];
+  return YDORB_OK;
+}
+
+void* ydorb_extractor_stream(const YdExtractor* ex) { return ex ? (void*)ex->stream : nullptr; }
+
+int ydorb_extractor_sync(YdExtractor* ex) {
+  YD_REQUIRE(ex, "null extractor");
+  YD_CUDA(cudaSetDevice(ex->device));
+  YD_CUDA(cudaStreamSynchronize(ex->stream));
+  return check_status(ex);
+}
+
+int ydorb_extract_batch_device(YdExtractor* ex, const uint8_t* d_images, int width, int height, int stride,
+                               size_t frame_stride, int batch, YdKeyPoint* d_keypoints, uint8_t* d_descriptors,
+                               int capacity, int32_t* d_n_out) {
+  YD_REQUIRE(ex && d_images && d_keypoints && d_descriptors && d_n_out, "null argument");
+  YD_REQUIRE(batch >= 1 && batch <= ex->max_batch, "batch exceeds max_batch");
+  YD_REQUIRE(width > 0 && height > 0 && stride >= width && capacity > 0, "bad image geometry");
+  YD_CUDA(cudaSetDevice(ex->device));
+  return run_pipeline(ex, d_images, width, height, stride, frame_stride, batch, d_keypoints, d_descriptors, capacity,
+                      d_n_out);
+}
+
+int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int height, int stride, size_t frame_stride,
+                        int batch, YdKeyPoint* keypoints, uint8_t* descriptors, int capacity, int32_t* n_out) {
+  YD_REQUIRE(ex && n_out, "null argument");
+  YD_REQUIRE(batch >= 1 && batch <= ex->max_batch, "batch exceeds max_batch");
+  if (!images || width <= 0 || height <= 0) {  // empty image: silent return (src/orbExtractor.cpp:356-358)
+    for (int b = 0; b < batch; b++) n_out[b] = 0;
+    return YDORB_OK;
+  }
+  YD_REQUIRE(keypoints && descriptors && capacity > 0, "null output");
+  YD_REQUIRE(stride >= width, "stride smaller than width");
+  YD_REQUIRE(width <= ex->max_w && height <= ex->max_h, "image larger than max_width/max_height");
+  YD_CUDA(cudaSetDevice(ex->device));
+  cudaStream_t s = ex->stream;
+  const size_t dpitch = (size_t)width;
+  for (int b = 0; b < batch; b++)
+    YD_CUDA(cudaMemcpy2DAsync(ex->d_images + (size_t)b * width * height, dpitch, images + (size_t)b * frame_stride,
+                              (size_t)stride, (size_t)width, (size_t)height, cudaMemcpyHostToDevice, s));
+  const int dcap = ex->out_cap;
+  int rc = run_pipeline(ex, ex->d_images, width, height, width, (size_t)width * height, batch, ex->d_kps, ex->d_desc,
+                        dcap, ex->d_nout);
+  if (rc != YDORB_OK) return rc;
+  YD_CUDA(cudaMemcpyAsync(n_out, ex->d_nout, sizeof(int32_t) * batch, cudaMemcpyDeviceToHost, s));
+  YD_CUDA(cudaStreamSynchronize(s));
+  rc = check_status(ex);
+  if (rc != YDORB_OK) return rc;
+  int ret = YDORB_OK;
+  for (int b = 0; b < batch; b++) {
+    int n = n_out[b];
+    if (n > capacity) { n = capacity; ret = YDORB_E_CAPACITY; set_error("keypoint capacity too small"); }
+    n_out[b] = n;
+    if (n == 0) continue;
+    YD_CUDA(cudaMemcpyAsync(keypoints + (size_t)b * capacity, ex->d_kps + (size_t)b * dcap, sizeof(YdKeyPoint) * n,
+                            cudaMemcpyDeviceToHost, s));
+    YD_CUDA(cudaMemcpyAsync(descriptors + (size_t)b * capacity * 32, ex->d_desc + (size_t)b * dcap * 32, (size_t)32 * n,
+                            cudaMemcpyDeviceToHost, s));
+  }
+  YD_CUDA(cudaStreamSynchronize(s));
+  return ret;
+}
+
+int ydorb_extract(YdExtractor* ex, const uint8_t* image, int width, int height, int stride, YdKeyPoint* keypoints,
+                  uint8_t* descriptors, int capacity, int32_t* n_out) {
+  return ydorb_extract_batch(ex, image, width, height, stride, 0, 1, keypoints, descriptors, capacity, n_out);
+}
+
+int ydorb_pyramid_level(const YdExtractor* ex, int frame, int level, const uint8_t** d_level, int* width, int* height,
+                        int* stride) {
+  YD_REQUIRE(ex && d_level, "null argument");
+  if (ex->cur_w <= 0) { set_error("no extract call yet"); return YDORB_E_STATE; }
+  YD_REQUIRE(frame >= 0 && frame < ex->cur_batch && level >= 0 && level < ex->geom.n_levels, "frame/level out of range");
+  const LevelGeom& lv = ex->geom.lv[level];
+  *d_level = ex->d_pyr + (size_t)frame * ex->geom.pyr_bytes + level_origin(lv);
+  if (width) *width = lv.w;
+  if (height) *height = lv.h;
+  if (stride) *stride = lv.stride;
+  return YDORB_OK;
+}
+
+int ydorb_pyramid_download(YdExtractor* ex, int frame, int level, int padded, uint8_t* dst, int dst_stride) {
+  const uint8_t* p;
+  int w, h, st;
+  int rc = ydorb_pyramid_level(ex, frame, level, &p, &w, &h, &st);
+  if (rc != YDORB_OK) return rc;
+  YD_REQUIRE(dst, "null dst");
+  YD_CUDA(cudaSetDevice(ex->device));
+  if (padded) { p -= (size_t)kPad * st + kPad; w += 2 * kPad; h += 2 * kPad; }
+  YD_REQUIRE(dst_stride >= w, "dst_stride too small");
+  YD_CUDA(cudaStreamSynchronize(ex->stream));
+  YD_CUDA(cudaMemcpy2D(dst, (size_t)dst_stride, p, (size_t)st, (size_t)w, (size_t)h, cudaMemcpyDeviceToHost));
+  return YDORB_OK;
+}
+
+int ydorb_debug_candidates(YdExtractor* ex, int frame, int level, int32_t* xy, float* resp, int capacity, int32_t* n_out) {
+  YD_REQUIRE(ex && n_out, "null argument");
+  if (ex->cur_w <= 0) { set_error("no extract call yet"); return YDORB_E_STATE; }
+  YD_REQUIRE(frame >= 0 && frame < ex->cur_batch && level >= 0 && level < ex->geom.n_levels, "frame/level out of range");
+  YD_CUDA(cudaSetDevice(ex->device));
+  YD_CUDA(cudaStreamSynchronize(ex->stream));
+  const FrameGeomDev& g = ex->geom;
+  const LevelGeom& lv = g.lv[level];
+  const int nc = lv.cell_cols * lv.cell_rows;
+  std::vector<int> cnt(std::max(nc, 1)), st(std::max(nc, 1));
+  if (nc > 0) {
+    YD_CUDA(cudaMemcpy(cnt.data(), ex->d_cell_count + (size_t)frame * g.n_cells + lv.cell_base, sizeof(int) * nc, cudaMemcpyDeviceToHost));
+    YD_CUDA(cudaMemcpy(st.data(), ex->d_cell_start + (size_t)frame * g.n_cells + lv.cell_base, sizeof(int) * nc, cudaMemcpyDeviceToHost));
+  }
+  int n = 0;
+  std::vector<uint32_t> buf;
+  for (int c = 0; c < nc; c++) {
+    if (cnt[c] == 0) continue;
+    buf.resize(cnt[c]);
+    YD_CUDA(cudaMemcpy(buf.data(), ex->d_raw + (size_t)frame * g.raw_cap + st[c], sizeof(uint32_t) * cnt[c], cudaMemcpyDeviceToHost));
+    for (int e = 0; e < cnt[c]; e++) {
+      if (n < capacity) {
+        if (xy) { xy[2 * n] = (int)((buf[e] >> 8) & 4095u); xy[2 * n + 1] = (int)(buf[e] >> 20); }
+        if (resp) resp[n] = (float)(buf[e] & 255u);
+      }
+      n++;
+    }
+  }
+  *n_out = n;
+  return YDORB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,23 @@
+// Launch wrappers of the extraction stages (one translation unit each).
+#pragma once
+#include "common.cuh"
+
+namespace ydorb {
+
+// E2 computePyramid (src/orbExtractor.cpp:605-621)
+int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, size_t frame_stride, int batch,
+                   cudaStream_t s);
+// E3 per-cell FAST with threshold fallback (src/orbExtractor.cpp:562-593)
+int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s);
+// E4 distributeQuadTree (src/orbExtractor.cpp:455-544)
+int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s);
+// E5+E6+E7 orientation, blur, descriptors, output assembly (src/orbExtractor.cpp:379-454)
+int launch_describe(const YdExtractor* ex, int batch, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity,
+                    int32_t* d_nout, cudaStream_t s);
+
+// status bits written by kernels into YdExtractor::d_status
+constexpr int kStatusRawOverflow = 1;   // candidate buffer too small
+constexpr int kStatusSortDepth = 2;     // std::sort emulation hit an internal limit
+constexpr int kStatusOutOverflow = 4;   // caller capacity too small
+
+}  // namespace ydorb

@@ -1,0 +1,18 @@
+// Matcher-side handles (opaque to C callers).
+#pragma once
+#include "common.cuh"
+
+struct YdMatcher {
+  int device;
+  int sm_count;
+  cudaStream_t stream;
+  void* d_scratch;       // kernel scratch (per-chunk partial results, candidate lists)
+  size_t scratch_bytes;
+  void* d_io;            // staging for host entry points
+  size_t io_bytes;
+};
+
+namespace ydorb {
+int matcher_reserve(YdMatcher* m, size_t bytes);
+int matcher_reserve_io(YdMatcher* m, size_t bytes);
+}  // namespace ydorb

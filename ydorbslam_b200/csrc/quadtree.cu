@@ -1,0 +1,501 @@
+// E4  OrbExtractor::distributeQuadTree + QuadTreeNode::divideNode  (src/orbExtractor.cpp:4-54, 455-544)
+//
+// The reference grows a std::list of nodes by splitting EVERY divisible node each pass (the "biggest first"
+// branch is dead code), until the list holds >= want nodes or stops growing, keeps the best-response
+// point of every node (std::sort + front()) and truncates the list to `want` in list order.
+//
+// Restated without the list (verified against a literal std::list transcription in oracle/):
+//   * the child a point falls into depends only on its coordinates, so every point has a fixed path
+//     q1 q2 ... (2 bits per split, child-4 geometry bug F6 included) -> a 28-bit path code;
+//   * #nodes after d passes = number of distinct d-digit prefixes  => depth D from a prefix histogram;
+//   * final nodes = groups of equal D-digit prefix; a node that became a singleton at depth s<D was frozen there;
+//   * list order = (s descending, then digits with alternating complement ascending);
+//   * per node the winner is what libstdc++ std::sort(a.response > b.response) leaves in front: the first maximum
+//     in candidate order for <= 16 points, the emulated introsort result otherwise.
+//
+// One CTA per (level, frame) segment.  Phases: (1) path codes in candidate order, (2) stable LSD radix sort by
+// code -> prefix histogram -> D, (3) stable radix sort of candidate-ordered points by the D-digit prefix so node
+// members stay in candidate order, (4) node records, (5) radix sort of node order keys, (6) emit.
+#include "kernels.cuh"
+
+namespace ydorb {
+
+constexpr int kQtThreads = 512;
+constexpr int kQtWarps = kQtThreads / 32;
+constexpr int kQtItems = 8;                  // elements per thread and chunk in the scatter step
+constexpr int kQtDig = 14;                   // digits per path code (28 bits): roots up to 16384 px
+constexpr int kQtBits = 2 * kQtDig;
+
+struct QtSmem {
+  int hist[256];
+  int warp_cnt[kQtWarps][256];
+  int scan_tmp[kQtWarps];
+  int lcp_hist[kQtDig + 2];
+  int misc[8];
+};
+
+// path code of a point (coordinates relative to the 16 px border), divideNode geometry :7-33
+__device__ __forceinline__ uint32_t qt_code(int x, int y, int rootw, int rooth) {
+  int tlx = 0, trx = rootw, tly = 0, bly = rooth;
+  uint32_t code = 0;
+#pragma unroll
+  for (int d = 0; d < kQtDig; d++) {
+    const int cx = (trx + tlx + 1) >> 1;  // ceil(float(a+b)/2.0), a+b >= 0
+    const int cy = (bly + tly + 1) >> 1;
+    const bool right = x >= cx, low = y >= cy;
+    uint32_t q;
+    if (!right && !low) { q = 0; trx = cx; bly = cy; }
+    else if (right && !low) { q = 1; tlx = cx; bly = cy; }
+    else if (!right && low) { q = 2; trx = cx; tly = cy; }
+    else { q = 3; const int t = tly; tlx = cx; tly = cy; bly = t; }  // F6: child-4 bl.y := parent tl.y
+    code = (code << 2) | q;
+  }
+  return code;
+}
+
+// number of common leading digits of two ndig-digit values
+__device__ __forceinline__ int lcp_digits(uint32_t a, uint32_t b, int ndig) {
+  const uint32_t x = a ^ b;
+  if (x == 0) return ndig;
+  const int hb = 31 - __clz(x);
+  return ndig - 1 - (hb >> 1);
+}
+
+// ---- CTA-wide stable LSD radix pass on bits [shift, shift+8).  Returns false (nothing moved) if every key
+// has the same digit.  All threads must call it.
+__device__ bool qt_radix_pass(QtSmem& sm, const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin,
+                              uint32_t* __restrict__ kout, uint32_t* __restrict__ vout, int n, int shift) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int b = tid; b < 256; b += kQtThreads) sm.hist[b] = 0;
+  if (tid == 0) sm.misc[0] = 0;
+  __syncthreads();
+  for (int i = tid; i < n; i += kQtThreads) atomicAdd(&sm.hist[(kin[i] >> shift) & 255], 1);
+  __syncthreads();
+  if (tid < 256 && sm.hist[tid] == n) sm.misc[0] = 1;
+  __syncthreads();
+  const int uniform = sm.misc[0];
+  __syncthreads();  // everyone has read the flag before a following pass may reset it
+  if (uniform) return false;
+  // exclusive scan of the 256 bins by warp 0
+  if (warp == 0) {
+    int v[8], s = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { v[k] = sm.hist[lane * 8 + k]; s += v[k]; }
+    int incl = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    int run = incl - s;
+#pragma unroll
+    for (int k = 0; k < 8; k++) { sm.hist[lane * 8 + k] = run; run += v[k]; }
+  }
+  __syncthreads();
+  constexpr int kChunk = kQtThreads * kQtItems;
+  for (int base = 0; base < n; base += kChunk) {
+    const int wbase = base + warp * 32 * kQtItems;
+    for (int b = lane; b < 256; b += 32) sm.warp_cnt[warp][b] = 0;
+    __syncwarp();
+#pragma unroll
+    for (int it = 0; it < kQtItems; it++) {
+      const int i = wbase + it * 32 + lane;
+      if (i < n) atomicAdd(&sm.warp_cnt[warp][(kin[i] >> shift) & 255], 1);
+    }
+    __syncthreads();
+    if (tid < 256) {
+      int run = sm.hist[tid];
+#pragma unroll
+      for (int w = 0; w < kQtWarps; w++) {
+        const int c = sm.warp_cnt[w][tid];
+        sm.warp_cnt[w][tid] = run;
+        run += c;
+      }
+      sm.hist[tid] = run;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < kQtItems; it++) {
+      const int i = wbase + it * 32 + lane;
+      const bool valid = i < n;
+      uint32_t key = 0, val = 0;
+      uint32_t dgt = 256u + lane;  // invalid lanes: unique pseudo-digits so they form singleton groups
+      if (valid) { key = kin[i]; val = vin[i]; dgt = (key >> shift) & 255; }
+      const uint32_t peers = __match_any_sync(0xffffffffu, dgt);
+      int off = 0;
+      if (valid) off = sm.warp_cnt[warp][dgt];
+      __syncwarp();
+      if (valid) {
+        const int rank = __popc(peers & ((1u << lane) - 1u));
+        if (rank == 0) sm.warp_cnt[warp][dgt] = off + __popc(peers);
+        kout[off + rank] = key;
+        vout[off + rank] = val;
+      }
+      __syncwarp();
+    }
+    // next chunk: each warp zeroes only its own counters, and the cross-warp read happens after a barrier
+  }
+  __syncthreads();
+  return true;
+}
+
+// CTA-wide stable sort of (keys, vals) on bits [0, nbits).  Buffers ping-pong; returns index (0/1) of the buffer
+// holding the result.
+__device__ int qt_sort(QtSmem& sm, uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int n, int nbits) {
+  int cur = 0;
+  for (int shift = 0; shift < nbits; shift += 8) {
+    const bool moved = cur == 0 ? qt_radix_pass(sm, k0, v0, k1, v1, n, shift) : qt_radix_pass(sm, k1, v1, k0, v0, n, shift);
+    if (moved) cur ^= 1;
+  }
+  return cur;
+}
+
+// CTA-wide exclusive scan of one int per thread; returns the exclusive prefix, *total = block sum.
+__device__ __forceinline__ int qt_block_scan(QtSmem& sm, int v, int* total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += t;
+  }
+  __syncthreads();  // protect scan_tmp reuse
+  if (lane == 31) sm.scan_tmp[warp] = incl;
+  __syncthreads();
+  int wsum = (lane < kQtWarps) ? sm.scan_tmp[lane] : 0;
+  int wincl = wsum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, wincl, o);
+    if (lane >= o) wincl += t;
+  }
+  const int wexcl = __shfl_sync(0xffffffffu, wincl - wsum, warp);
+  *total = __shfl_sync(0xffffffffu, wincl, kQtWarps - 1);
+  return wexcl + incl - v;
+}
+
+// ---- libstdc++ std::sort emulation (bits/stl_algo.h) on packed entries: response in bits 31..24, payload below.
+// comp(a,b) = a.response > b.response, exactly the reference's lambda at src/orbExtractor.cpp:537-538.
+struct StdSortEmu {
+  uint32_t* a;
+  __device__ __forceinline__ static bool comp(uint32_t x, uint32_t y) { return (x >> 24) > (y >> 24); }
+  __device__ __forceinline__ void swp(int i, int j) { const uint32_t t = a[i]; a[i] = a[j]; a[j] = t; }
+
+  __device__ void move_median_to_first(int res, int x, int y, int z) {
+    if (comp(a[x], a[y])) {
+      if (comp(a[y], a[z])) swp(res, y);
+      else if (comp(a[x], a[z])) swp(res, z);
+      else swp(res, x);
+    } else if (comp(a[x], a[z])) swp(res, x);
+    else if (comp(a[y], a[z])) swp(res, z);
+    else swp(res, y);
+  }
+  __device__ int unguarded_partition(int first, int last, int pivot) {
+    while (true) {
+      while (comp(a[first], a[pivot])) ++first;
+      --last;
+      while (comp(a[pivot], a[last])) --last;
+      if (!(first < last)) return first;
+      swp(first, last);
+      ++first;
+    }
+  }
+  __device__ void adjust_heap(int first, int hole, int len, uint32_t value) {
+    const int top = hole;
+    int child = hole;
+    while (child < (len - 1) / 2) {
+      child = 2 * (child + 1);
+      if (comp(a[first + child], a[first + child - 1])) child--;
+      a[first + hole] = a[first + child];
+      hole = child;
+    }
+    if ((len & 1) == 0 && child == (len - 2) / 2) {
+      child = 2 * (child + 1);
+      a[first + hole] = a[first + child - 1];
+      hole = child - 1;
+    }
+    int parent = (hole - 1) / 2;
+    while (hole > top && comp(a[first + parent], value)) {
+      a[first + hole] = a[first + parent];
+      hole = parent;
+      parent = (hole - 1) / 2;
+    }
+    a[first + hole] = value;
+  }
+  __device__ void heap_sort(int first, int last) {  // __partial_sort(first,last,last)
+    const int len = last - first;
+    if (len >= 2) {
+      int parent = (len - 2) / 2;
+      while (true) {
+        adjust_heap(first, parent, len, a[first + parent]);
+        if (parent == 0) break;
+        parent--;
+      }
+    }
+    int l = last;
+    while (l - first > 1) {
+      --l;
+      const uint32_t v = a[l];
+      a[l] = a[first];
+      adjust_heap(first, 0, l - first, v);
+    }
+  }
+  __device__ void unguarded_linear_insert(int last) {
+    const uint32_t val = a[last];
+    int next = last - 1;
+    while (comp(val, a[next])) { a[last] = a[next]; last = next; --next; }
+    a[last] = val;
+  }
+  __device__ void insertion_sort(int first, int last) {
+    if (first == last) return;
+    for (int i = first + 1; i != last; ++i) {
+      if (comp(a[i], a[first])) {
+        const uint32_t val = a[i];
+        for (int j = i; j > first; --j) a[j] = a[j - 1];
+        a[first] = val;
+      } else {
+        unguarded_linear_insert(i);
+      }
+    }
+  }
+  // returns false if the explicit stack overflowed (never for n < 2^31)
+  __device__ bool sort(int n) {
+    if (n <= 0) return true;
+    int st_first[64], st_last[64], st_depth[64];
+    int sp = 0;
+    st_first[0] = 0; st_last[0] = n; st_depth[0] = 2 * (31 - __clz(n)); sp = 1;
+    while (sp > 0) {
+      --sp;
+      int first = st_first[sp], last = st_last[sp], depth = st_depth[sp];
+      while (last - first > 16) {
+        if (depth == 0) { heap_sort(first, last); break; }
+        --depth;
+        const int mid = first + (last - first) / 2;
+        move_median_to_first(first, first + 1, mid, last - 1);
+        const int cut = unguarded_partition(first + 1, last, first);
+        if (sp >= 64) return false;
+        st_first[sp] = cut; st_last[sp] = last; st_depth[sp] = depth; ++sp;  // right part: disjoint, order-free
+        last = cut;
+      }
+    }
+    if (n > 16) {
+      insertion_sort(0, 16);
+      for (int i = 16; i < n; ++i) unguarded_linear_insert(i);
+    } else {
+      insertion_sort(0, n);
+    }
+    return true;
+  }
+};
+
+// ---- per-frame exclusive scan of the per-cell candidate counts (candidate order = cell-major)
+__global__ void __launch_bounds__(256) k_cell_scan(const FrameGeomDev* __restrict__ g, const int* __restrict__ cell_count,
+                                                   int* __restrict__ cell_rank) {
+  __shared__ int s_warp[8];
+  __shared__ int s_carry;
+  const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nc = g->n_cells;
+  const int* cnt = cell_count + (size_t)frame * nc;
+  int* rank = cell_rank + (size_t)frame * (nc + 1);
+  if (tid == 0) s_carry = 0;
+  __syncthreads();
+  for (int base = 0; base < nc; base += 256) {
+    const int i = base + tid;
+    const int v = i < nc ? cnt[i] : 0;
+    int incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    int woff = 0;
+    for (int w = 0; w < warp; w++) woff += s_warp[w];
+    const int carry = s_carry;
+    if (i < nc) rank[i] = carry + woff + incl - v;
+    __syncthreads();
+    if (tid == 255) s_carry = carry + woff + incl;
+    __syncthreads();
+  }
+  if (tid == 0) rank[nc] = s_carry;
+}
+
+struct QtArgs {
+  const FrameGeomDev* g;
+  const int4* cells;
+  const int* cell_count;
+  const int* cell_start;
+  const int* cell_rank;
+  const uint32_t* raw;
+  uint32_t* keys[3];
+  uint32_t* vals[3];
+  int4* sel;
+  int* sel_n;
+  int* level_ncand;
+  int* status;
+};
+
+// writes (key, packed candidate) of every candidate of the level at its candidate-order position
+__device__ void qt_fill(const QtArgs& A, const LevelGeom& lv, int frame, int level_base, int code_shift, uint32_t* keys,
+                        uint32_t* vals) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int ncell = lv.cell_cols * lv.cell_rows;
+  const size_t cbase = (size_t)frame * A.g->n_cells + lv.cell_base;
+  const int* rank = A.cell_rank + (size_t)frame * (A.g->n_cells + 1) + lv.cell_base;
+  const uint32_t* raw = A.raw + (size_t)frame * A.g->raw_cap;
+  for (int c = warp; c < ncell; c += kQtWarps) {
+    const int cnt = A.cell_count[cbase + c];
+    if (cnt == 0) continue;
+    const int start = A.cell_start[cbase + c];
+    const int pos0 = rank[c] - level_base;
+    for (int e = lane; e < cnt; e += 32) {
+      const uint32_t r = raw[start + e];  // y:12 | x:12 | response:8, border-relative coordinates
+      keys[pos0 + e] = qt_code((int)((r >> 8) & 4095u), (int)(r >> 20), lv.root_w, lv.root_h) >> code_shift;
+      vals[pos0 + e] = r;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kQtThreads) k_quadtree(QtArgs A) {
+  __shared__ QtSmem sm;
+  const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
+  const FrameGeomDev* g = A.g;
+  const LevelGeom lv = g->lv[level];
+  const int* rank = A.cell_rank + (size_t)frame * (g->n_cells + 1);
+  const int level_base = rank[lv.cell_base];
+  const int level_end = rank[lv.cell_base + lv.cell_cols * lv.cell_rows];
+  const int n = level_end - level_base;
+  const int want = lv.quota;
+  int* sel_n = A.sel_n + (size_t)frame * kMaxLevels + level;
+  if (tid == 0) A.level_ncand[(size_t)frame * kMaxLevels + level] = n;
+  if (n == 0 || want <= 0) {
+    if (tid == 0) *sel_n = 0;
+    return;
+  }
+  const size_t seg = (size_t)frame * g->raw_cap + level_base;
+  uint32_t* K[3] = {A.keys[0] + seg, A.keys[1] + seg, A.keys[2] + seg};
+  uint32_t* V[3] = {A.vals[0] + seg, A.vals[1] + seg, A.vals[2] + seg};
+
+  // (1)+(2) full path codes in candidate order, sorted; distinct-prefix counts; depth D (loop condition :479)
+  qt_fill(A, lv, frame, level_base, 0, K[0], V[0]);
+  __syncthreads();
+  int cur = qt_sort(sm, K[0], V[0], K[1], V[1], n, kQtBits);
+  for (int d = tid; d < kQtDig + 2; d += kQtThreads) sm.lcp_hist[d] = 0;
+  __syncthreads();
+  {
+    const uint32_t* ks = K[cur];
+    for (int i = tid + 1; i < n; i += kQtThreads) atomicAdd(&sm.lcp_hist[lcp_digits(ks[i - 1], ks[i], kQtDig)], 1);
+  }
+  __syncthreads();
+  if (tid == 0) {
+    // cnt(d) = 1 + #adjacent pairs with lcp < d
+    int D = 0, last = 0, size = 1, below = 0;
+    while (size > last && size < want && D < kQtDig) {
+      last = size;
+      below += sm.lcp_hist[D];
+      D++;
+      size = 1 + below;
+    }
+    sm.misc[1] = D;
+  }
+  __syncthreads();
+  const int D = sm.misc[1];
+
+  // (3) stable sort of candidate-ordered points by D-digit prefix
+  qt_fill(A, lv, frame, level_base, kQtBits - 2 * D, K[0], V[0]);
+  __syncthreads();
+  cur = (D == 0) ? 0 : qt_sort(sm, K[0], V[0], K[1], V[1], n, 2 * D);
+  const uint32_t* PK = K[cur];
+  const uint32_t* PV = V[cur];
+  uint32_t* node_start = K[cur ^ 1];   // free ping-pong buffer
+  uint32_t* scratch = V[cur ^ 1];      // std::sort emulation workspace, indexed like the points
+
+  // (4a) node boundaries
+  if (tid == 0) sm.misc[2] = 0;
+  __syncthreads();
+  for (int base = 0; base < n; base += kQtThreads) {
+    const int i = base + tid;
+    const int head = (i < n) && (i == 0 || PK[i] != PK[i - 1]);
+    int total;
+    const int ex = qt_block_scan(sm, head, &total);
+    const int off = sm.misc[2];
+    if (head) node_start[off + ex] = (uint32_t)i;
+    __syncthreads();
+    if (tid == 0) sm.misc[2] = off + total;
+    __syncthreads();
+  }
+  const int M = sm.misc[2];
+
+  // (4b) node records: order key + winner
+  uint32_t* NK = K[2];
+  uint32_t* NV = V[2];
+  for (int m = tid; m < M; m += kQtThreads) {
+    const int beg = (int)node_start[m];
+    const int end = (m + 1 < M) ? (int)node_start[m + 1] : n;
+    const uint32_t pre = PK[beg];
+    int s = D;
+    if (end - beg == 1) {
+      int l = 0;
+      if (m > 0) l = max(l, lcp_digits(pre, PK[node_start[m - 1]], D));
+      if (m + 1 < M) l = max(l, lcp_digits(pre, PK[end], D));
+      s = (n == 1) ? 0 : min(D, l + 1);
+    }
+    // best response, first maximum in candidate order, number of maxima
+    uint32_t best_resp = 0, best_val = PV[beg];
+    int ties = 0;
+    for (int i = beg; i < end; i++) {
+      const uint32_t v = PV[i];
+      const uint32_t r = v & 255u;
+      if (i == beg || r > best_resp) { best_resp = r; best_val = v; ties = 1; }
+      else if (r == best_resp) ties++;
+    }
+    if (end - beg > 16 && ties > 1) {  // introsort decides among tied maxima
+      for (int i = beg; i < end; i++) scratch[i] = ((PV[i] & 255u) << 24) | (uint32_t)(i - beg);
+      StdSortEmu emu{scratch + beg};
+      if (!emu.sort(end - beg)) atomicOr(A.status, kStatusSortDepth);
+      best_val = PV[beg + (int)(scratch[beg] & 0xFFFFFFu)];
+    }
+    const uint32_t ps = (s == 0) ? 0u : (pre >> (2 * (D - s)));
+    uint32_t mask = 0;
+    for (int k = s; k >= 1; k -= 2) mask |= 3u << (2 * (s - k));
+    NK[m] = ((uint32_t)(D - s) << kQtBits) | (ps ^ mask);
+    NV[m] = best_val;
+  }
+  __syncthreads();
+
+  // (5) list order
+  const int ncur = qt_sort(sm, NK, NV, K[cur ^ 1], V[cur ^ 1], M, 32);
+  const uint32_t* OV = (ncur == 0) ? NV : V[cur ^ 1];
+
+  // (6) emit the first min(M, want) winners (:541-543), coordinates back in level space (:597-598)
+  const int m_out = min(M, want);
+  int4* sel = A.sel + (size_t)frame * g->n_quota + lv.quota_base;
+  for (int i = tid; i < m_out; i += kQtThreads) {
+    const uint32_t r = OV[i];
+    sel[i] = make_int4((int)((r >> 8) & 4095u) + kBorder, (int)(r >> 20) + kBorder, (int)(r & 255u), level);
+  }
+  if (tid == 0) *sel_n = m_out;
+}
+
+int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
+  k_cell_scan<<<batch, 256, 0, s>>>(ex->d_geom, ex->d_cell_count, ex->d_cell_rank);
+  QtArgs A;
+  A.g = ex->d_geom;
+  A.cells = ex->d_cells;
+  A.cell_count = ex->d_cell_count;
+  A.cell_start = ex->d_cell_start;
+  A.cell_rank = ex->d_cell_rank;
+  A.raw = ex->d_raw;
+  for (int i = 0; i < 3; i++) { A.keys[i] = ex->d_qt_keys[i]; A.vals[i] = ex->d_qt_vals[i]; }
+  A.sel = ex->d_sel;
+  A.sel_n = ex->d_sel_n;
+  A.level_ncand = ex->d_level_ncand;
+  A.status = ex->d_status;
+  dim3 grid(ex->geom.n_levels, batch);
+  k_quadtree<<<grid, kQtThreads, 0, s>>>(A);
+  YD_CUDA(cudaGetLastError());
+  return YDORB_OK;
+}
+
+}  // namespace ydorb
