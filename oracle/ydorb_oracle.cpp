@@ -182,26 +182,37 @@ static inline int fast_m(const uint8_t* p, int stride) {
 int orc_fast(const uint8_t* img, int w, int h, int stride, int th, int* xs, int* ys, int* resp, int cap) {
   th = std::min(std::max(th, 0), 255);
   if (w < 7 || h < 7) return 0;
+  // score map: 0 = not a corner, else m (corner iff m > th; cornerScore returns m-1)
   std::vector<int> score((size_t)w * h, 0);
-  for (int y = 3; y < h - 3; y++)
+  const int o0 = 3 * stride, o4 = 3, o8 = -3 * stride, o12 = -3;
+  for (int y = 3; y < h - 3; y++) {
+    const uint8_t* row = img + (size_t)y * stride;
     for (int x = 3; x < w - 3; x++) {
-      int m = fast_m(img + (size_t)y * stride + x, stride);
-      if (m > th) score[(size_t)y * w + x] = m - 1;  // cornerScore returns m-1; th>=0 so m-1>=th>=0
+      // any 9 contiguous circle pixels contain at least two of the four compass pixels (same pruning idea as
+      // OpenCV's pre-test; does not change the result)
+      const uint8_t* p = row + x;
+      const int c = p[0], lo = c - th, hi = c + th;
+      const int a = p[o0], b = p[o4], e = p[o8], f = p[o12];
+      const int dark = (a < lo) + (b < lo) + (e < lo) + (f < lo);
+      const int bright = (a > hi) + (b > hi) + (e > hi) + (f > hi);
+      if (dark < 2 && bright < 2) continue;
+      const int m = fast_m(p, stride);
+      if (m > th) score[(size_t)y * w + x] = m;
     }
+  }
   int n = 0;
   for (int y = 3; y < h - 3; y++)
     for (int x = 3; x < w - 3; x++) {
-      // a corner has m>th so (m-1)>=th; OpenCV marks corners in a position list, score may be 0 when th==0
-      int m = fast_m(img + (size_t)y * stride + x, stride);
-      if (!(m > th)) continue;
-      int s = m - 1;
       const int* sc = &score[(size_t)y * w + x];
+      const int s = sc[0];
+      if (s == 0) continue;
+      // strictly greater than all 8 neighbours, non-corners count as 0 (comparing m is the same as comparing m-1)
       if (s > sc[-1] && s > sc[1] && s > sc[-w - 1] && s > sc[-w] && s > sc[-w + 1] && s > sc[w - 1] && s > sc[w] &&
           s > sc[w + 1]) {
         if (n < cap) {
           xs[n] = x;
           ys[n] = y;
-          resp[n] = s;
+          resp[n] = s - 1;
         }
         n++;
       }
