@@ -1,0 +1,392 @@
+#!/usr/bin/env python3
+"""bench.py -- ORB extract+match frames/s (640x480, 1000 kp) and Hamming Gmatch/s on B200.
+
+    python bench.py --gpus N --steps K --warmup W                 # this repo's CUDA path (libydorb.so)
+    python bench.py --impl reference --gpus N --steps K --warmup W  # reference CPU path (oracle port) on host cores
+    torchrun --nproc-per-node N ... bench.py --gpus N ...          # one rank per GPU, frames sharded, no collective
+
+One step = one pass of the hot path over one batch of synthetic frames per GPU:
+  OrbExtractor::extractAndCompute(1000, 1.2, 8, 20, 7) on B frames of 640x480, then the Hamming top-2 + ratio test
+  (rule of src/orbMatcher.cpp:319-336) of every frame's descriptors against the previous frame's.
+Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for the byte counts behind `roofline`.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H, NFEAT = 640, 480, 1000
+EXTRACTOR_ARGS = (NFEAT, 1.2, 8, 20, 7)
+RATIO, TH_LOW = 0.6, 50
+HAMMING_NQ, HAMMING_NDB = 2000, 1_000_000
+
+
+def level_sizes(w, h, n_levels=8, scale=1.2):
+    out = []
+    for l in range(n_levels):
+        inv = np.float32(pow(float(np.float32(scale)), -l))
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+    return out
+
+
+def algorithmic_bytes(w, h):
+    """per-stage algorithmic bytes of one frame (1 B/px)."""
+    px = [a * b for a, b in level_sizes(w, h)]
+    pyr = sum(px[:-1]) + sum(px[1:])   # resize reads + writes
+    fast = sum(px)                     # FAST reads every level once
+    blur = 2 * sum(px)                 # blur read + write (the reference blurs whole levels)
+    return {"pyramid": pyr, "fast": fast, "quadtree": 0, "describe": blur, "total": pyr + fast + blur}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.splitlines():
+            f = [t.strip() for t in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def make_frames(batch, rank):
+    from ydorbslam_b200 import synth
+
+    # One textured canvas per rank; frame i is a window sliding 2 px per frame (and wobbling vertically), so
+    # consecutive frames are distinct images that overlap -> the frame-to-frame matcher finds real matches.
+    # Dense texture: ~10k FAST candidates at level 0, every level overshoots its quota (truncation + tie paths run).
+    canvas = synth.synth_frame(W + 2 * batch, H + 8, 100000 * rank + 17, n_rect=64 + batch // 2, contrast=2)
+    return np.stack([canvas[(i * 3) % 8 : (i * 3) % 8 + H, 2 * i : 2 * i + W] for i in range(batch)])
+
+
+# ------------------------------------------------------------------------------------------------ reference arm
+def cpu_extract_match(frames, threads):
+    """The oracle port of the reference CPU path on `frames` with `threads` host threads.  Returns seconds."""
+    from oracle import orc
+
+    p = orc.make_params(*EXTRACTOR_ARGS[:4])
+    t0 = time.perf_counter()
+    kps, desc, n = orc.extract_batch(p, frames, threads, cap=NFEAT + 64)
+    for b in range(len(frames)):
+        a = (b - 1) % len(frames)
+        t = orc.top2(desc[b, : n[b]], desc[a, : n[a]], 0, threads)
+        orc.ratio_accept(t, RATIO, TH_LOW)
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return 0
+    threads = os.cpu_count() or 1
+    sample = max(2 * threads, 8)
+    frames = make_frames(sample, 0)
+    cpu_extract_match(frames[: min(threads, sample)], threads)  # page in / warm up
+    for _ in range(max(args.warmup - 1, 0)):
+        cpu_extract_match(frames, threads)
+    times = [cpu_extract_match(frames, threads) for _ in range(args.steps)]
+    total = sum(times)
+    value = sample * args.steps / total
+    line = {
+        "impl": "reference", "metric": "ORB extract+match frames/s (640x480, 1000 kp)", "value": value, "unit": "frames/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": f"{sample} synthetic 640x480 frames/step (bounded sample of the GPU arm's workload): "
+                               "extractAndCompute(1000,1.2,8,20,7) + Hamming top-2 ratio match vs previous frame, CPU",
+                   "parallelism": f"{threads} host threads"},
+        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": "port",
+                         "sample": f"{sample} frames x {args.steps} steps, oracle/ydorb_oracle.cpp (reference cannot be built: needs OpenCV C++)"},
+        "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+
+    from ydorbslam_b200 import OrbExtractor, OrbMatcher, synth
+    from ydorbslam_b200._lib import lib
+
+    rank, world, local = dist_env()
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+    B, K, Wm = args.batch, args.steps, args.warmup
+
+    frames = make_frames(B, rank)
+    ex = OrbExtractor(*EXTRACTOR_ARGS, max_width=W, max_height=H, max_batch=B, device=local)
+    m = OrbMatcher(RATIO, device=local)
+    cap = ex.capacity
+    stream = torch.cuda.Stream(device=dev)
+    ex.set_stream(stream.cuda_stream)
+    m.set_stream(stream.cuda_stream)
+
+    d_img = torch.from_numpy(frames).to(dev)
+    d_kps = torch.zeros(B, cap, 28, dtype=torch.uint8, device=dev)
+    d_desc = torch.zeros(B, cap, 32, dtype=torch.uint8, device=dev)
+    d_n = torch.zeros(B, dtype=torch.int32, device=dev)
+    d_qf = torch.arange(B, dtype=torch.int32, device=dev)
+    d_df = (torch.arange(B, dtype=torch.int32, device=dev) - 1) % B
+    d_top2 = torch.zeros(B, cap, 4, dtype=torch.int32, device=dev)
+    d_acc = torch.zeros(B, cap, dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+
+    def step():
+        ex.extract_batch_device(d_img.data_ptr(), W, H, B, d_kps.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
+        m.top2_frames_device(d_desc.data_ptr(), d_n.data_ptr(), cap, d_qf.data_ptr(), d_df.data_ptr(), B, d_top2.data_ptr(),
+                             d_acc.data_ptr(), RATIO, TH_LOW)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        for _ in range(Wm):
+            step()
+    ex.sync()
+    barrier()
+    launches0 = lib().ydorb_kernel_launches()
+    ex.set_profiling(True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+        for _ in range(K):
+            step()
+        e1.record(stream)
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = lib().ydorb_kernel_launches() - launches0
+    stage_ms = ex.stage_ms()
+    ex.set_profiling(False)
+    ex.sync()  # raises if a device-side status flag (capacity overflow) was set
+    n_kp = d_n.cpu().numpy()
+    n_acc = int(d_acc.sum().item())
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    value = world * B * K / (ms_total * 1e-3)
+
+    # ---- e2e: host buffers through the host-pointer C-ABI calls, H2D/D2H inside the timed region
+    from ydorbslam_b200._lib import KP_DTYPE, TOP2_DTYPE, check, ptr
+    import ctypes as C
+
+    ex.set_stream(None)
+    m.set_stream(None)
+    h_img = torch.from_numpy(frames).pin_memory()
+    h_kps = torch.zeros(B, cap, 28, dtype=torch.uint8).pin_memory()
+    h_desc = torch.zeros(B, cap, 32, dtype=torch.uint8).pin_memory()
+    h_n = torch.zeros(B, dtype=torch.int32).pin_memory()
+    h_top2 = torch.zeros(B, cap, 4, dtype=torch.int32).pin_memory()
+    h_acc = torch.zeros(B, cap, dtype=torch.uint8).pin_memory()
+    qf = np.arange(B, dtype=np.int32)
+    df = ((np.arange(B) - 1) % B).astype(np.int32)
+
+    def e2e_step():
+        check(lib().ydorb_extract_batch(ex._h, C.c_void_p(h_img.data_ptr()), W, H, W, C.c_size_t(W * H), B,
+                                        C.c_void_p(h_kps.data_ptr()), C.c_void_p(h_desc.data_ptr()), cap,
+                                        C.c_void_p(h_n.data_ptr())))
+        check(lib().ydorb_match_frames(m._h, ex._h, ptr(qf), ptr(df), B, C.c_float(RATIO), TH_LOW,
+                                       C.c_void_p(h_top2.data_ptr()), C.c_void_p(h_acc.data_ptr())))
+
+    for _ in range(max(Wm, 1)):
+        e2e_step()
+    barrier()
+    ke = max(min(K, 10), 1)
+    t0 = time.perf_counter()
+    for _ in range(ke):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * B * ke / float(t.item())
+    h2d = B * W * H + 2 * 4 * B
+    d2h = B * cap * (28 + 32) + 4 * B + B * cap * (16 + 1)
+    assert np.array_equal(h_n.numpy(), n_kp), "host-API and device-API keypoint counts differ"
+
+    # ---- secondary metric: Hamming top-2, 2000 queries x 1M database rows sharded over the ranks
+    ham = None
+    if not args.skip_hamming:
+        rows = HAMMING_NDB // world
+        base = rank * rows
+        db_np = synth.synth_descriptors(rows, 1000 + rank)
+        q_np = synth.synth_descriptors(HAMMING_NQ, 7)
+        d_db = torch.from_numpy(db_np).to(dev)
+        d_q = torch.from_numpy(q_np).to(dev)
+        d_part = torch.zeros(HAMMING_NQ, 4, dtype=torch.int32, device=dev)
+        d_all = torch.zeros(world, HAMMING_NQ, 4, dtype=torch.int32, device=dev)
+        d_out = torch.zeros(HAMMING_NQ, 4, dtype=torch.int32, device=dev)
+        d_ok = torch.zeros(HAMMING_NQ, dtype=torch.uint8, device=dev)
+        m.set_stream(stream.cuda_stream)
+
+        def ham_step():
+            m.top2_device(d_q.data_ptr(), HAMMING_NQ, d_db.data_ptr(), rows, base, d_part.data_ptr())
+            if world > 1:
+                dist.all_gather_into_tensor(d_all, d_part)  # NCCL: 32 KB per rank
+                m.top2_merge_device(d_all.data_ptr(), world, HAMMING_NQ, d_out.data_ptr())
+                src = d_out
+            else:
+                src = d_part
+            m.ratio_accept_device(src.data_ptr(), HAMMING_NQ, d_ok.data_ptr(), RATIO, TH_LOW)
+
+        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 10
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                ham_step()
+            barrier()
+            h0.record(stream)
+            for _ in range(reps):
+                ham_step()
+            h1.record(stream)
+        barrier()
+        t = torch.tensor([h0.elapsed_time(h1) / reps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ham_ms = float(t.item())
+        ham = {"metric": "Hamming top-2 Gmatch/s", "value": HAMMING_NQ * rows * world / (ham_ms * 1e-3) / 1e9, "unit": "Gpairs/s",
+               "ms": ham_ms, "workload": f"{HAMMING_NQ} queries x {rows * world} database descriptors, {world} shard(s)"
+               + (", NCCL all-gather merge" if world > 1 else ""), "scaling": "strong",
+               "int_ops_per_pair": {"xor": 8, "popc": 8, "iadd": 8}}
+        m.set_stream(None)
+
+    # ---- CPU baseline beside it (rank 0, N=1 only): oracle port on the host cores, bounded sample
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        probe = frames[: min(threads, B)]
+        tp = cpu_extract_match(probe, threads)
+        per_frame = tp / len(probe)
+        sample = int(min(B, max(len(probe), 15.0 / max(per_frame, 1e-6))))
+        ts = cpu_extract_match(frames[:sample], threads)
+        cpu = {"value": sample / ts, "unit": "frames/s", "cores": threads, "kind": "port",
+               "sample": f"first {sample} frames of the batch, extract + match vs previous frame, oracle/ydorb_oracle.cpp with "
+                         f"{threads} threads, {ts:.1f} s"}
+
+    if rank == 0:
+        peak, peak_kind = measured_peak()
+        ab = algorithmic_bytes(W, H)
+        names = ["pyramid", "fast", "quadtree", "describe"]
+        match_ms = ms_total / K - sum(stage_ms)
+        dom = int(np.argmax(stage_ms))
+        dom_bytes = ab[names[dom]] * B
+        achieved = dom_bytes / (stage_ms[dom] * 1e-3) / 1e9 if stage_ms[dom] > 0 else 0.0
+        step_gbs = ab["total"] * B / (ms_total / K * 1e-3) / 1e9
+        line = {
+            "metric": "ORB extract+match frames/s (640x480, 1000 kp)", "value": value, "unit": "frames/s", "n_gpus": world,
+            "steps": K, "warmup": Wm, "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": f"{B} synthetic 640x480 frames/step/GPU: extractAndCompute(1000,1.2,8,20,7) + Hamming top-2 "
+                                   "ratio match vs previous frame (1000x1000 per frame)",
+                       "parallelism": f"frames sharded over {world} GPU(s), no collective",
+                       "l2": f"working set {B} x (input 0.31 MB + pyramid 1.2 MB) > 126 MB L2, no flush"},
+            "clocks": clocks,
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "timing": "host wall clock around the synchronous host-pointer C-ABI calls, pinned buffers"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
+                         "algorithmic_bytes_per_launch": dom_bytes, "launch_ms": stage_ms[dom]},
+            "stage_ms": dict(zip(names, stage_ms), match=match_ms),
+            "roofline_step": {"algorithmic_bytes_per_frame": ab["total"], "achieved": step_gbs, "peak": peak, "unit": "GB/s",
+                              "frac": step_gbs / peak},
+            "keypoints_per_frame": float(n_kp.mean()), "accepted_matches_per_frame": n_acc / B,
+            "hamming": ham, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=256)
+    ap.add_argument("--skip-hamming", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -54,6 +54,8 @@ typedef struct YdExtractor YdExtractor;
 
 const char* ydorb_last_error(void); /* thread-local message of the last failing call */
 int ydorb_device_count(void);
+/* number of CUDA kernels this library has launched in this process (evidence for benchmarks) */
+long long ydorb_kernel_launches(void);
 
 /* ---- OrbExtractor -------------------------------------------------------------------------------------- */
 /* OrbExtractor::OrbExtractor (src/orbExtractor.cpp:315-354).  max_* size the device buffers. */
@@ -82,6 +84,11 @@ int ydorb_extract_batch_device(YdExtractor* ex, const uint8_t* d_images, int wid
                                size_t frame_stride, int batch, YdKeyPoint* d_keypoints, uint8_t* d_descriptors,
                                int capacity, int32_t* d_n_out);
 int ydorb_extractor_sync(YdExtractor* ex);
+/* enqueue on a caller-owned cudaStream_t instead of the handle's own stream (NULL restores it) */
+int ydorb_extractor_set_stream(YdExtractor* ex, void* cuda_stream);
+/* per-stage CUDA-event timing of the last extract call: ms[0..3] = pyramid, FAST, quadtree, describe */
+int ydorb_extractor_set_profiling(YdExtractor* ex, int enable);
+int ydorb_extractor_stage_ms(YdExtractor* ex, float* ms4);
 
 /* m_v_imagePyramid (src/orbExtractor.hpp:50): padded level of the last extract call, device memory.
  * *d_level points at the level's (0,0) pixel; 19 px of REFLECT_101 border are readable around it. */
@@ -110,6 +117,7 @@ int ydorb_matcher_create(int device, YdMatcher** out);
 void ydorb_matcher_destroy(YdMatcher* m);
 void* ydorb_matcher_stream(const YdMatcher* m);
 int ydorb_matcher_sync(YdMatcher* m);
+int ydorb_matcher_set_stream(YdMatcher* m, void* cuda_stream);
 
 /* OrbMatcher::computeDescriptorsDistance (src/orbMatcher.cpp:11-23), n pairs: dist[i] = |a_i xor b_i| */
 int ydorb_hamming_pairs(YdMatcher* m, const uint8_t* a, const uint8_t* b, int n, int32_t* dist);
@@ -119,6 +127,16 @@ int ydorb_hamming_top2(YdMatcher* m, const uint8_t* queries, int nq, const uint8
                        YdTop2* out);
 int ydorb_hamming_top2_device(YdMatcher* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, int ndb, int idx_base,
                               YdTop2* d_out);
+/* batched dense top-2 between frames of one descriptor block d_desc[frame][capacity][32] with per-frame counts
+ * d_n[frame]: pair p matches the descriptors of frame d_q_frame[p] against those of frame d_db_frame[p] (e.g. frame
+ * t against frame t-1).  d_out[p*capacity + i]; d_accept (may be NULL) gets the ratio test of src/orbMatcher.cpp:336. */
+int ydorb_hamming_top2_frames_device(YdMatcher* m, const uint8_t* d_desc, const int32_t* d_n, int capacity,
+                                     const int32_t* d_q_frame, const int32_t* d_db_frame, int npairs, YdTop2* d_out,
+                                     uint8_t* d_accept, float ratio, int th);
+/* same on the descriptors left on the device by the last ydorb_extract_batch (host API) of `ex`; host in/out.
+ * out[p*capacity + i] with capacity = sum of the per-level quotas of `ex` (ydorb_extractor_quotas). */
+int ydorb_match_frames(YdMatcher* m, const YdExtractor* ex, const int32_t* q_frame, const int32_t* db_frame, int npairs,
+                       float ratio, int th, YdTop2* out, uint8_t* accept);
 /* merge per-shard results (shards[s*nq + i]) into the result of one scan over the whole database */
 int ydorb_top2_merge_device(YdMatcher* m, const YdTop2* d_shards, int nshards, int nq, YdTop2* d_out);
 /* accept[i] = best<=th && (float)best < ratio*(float)second   (src/orbMatcher.cpp:336) */

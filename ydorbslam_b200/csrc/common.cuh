@@ -18,6 +18,7 @@ constexpr int kMaxLevels = YDORB_MAX_LEVELS;
 constexpr int kQtDigits = 16;  // quadtree path digits per code (2 bits each)
 
 void set_error(const std::string& msg);
+void count_launches(int n);  // bookkeeping for ydorb_kernel_launches()
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
 #define YD_CUDA(expr)                                                         \
@@ -70,7 +71,12 @@ struct YdExtractor {
   YdExtractorParams params;
   int device;
   int max_w, max_h, max_batch;
-  cudaStream_t stream;
+  cudaStream_t stream;      // stream the stages are enqueued on (own_stream unless the caller set one)
+  cudaStream_t own_stream;
+  int profiling;            // record per-stage events
+  cudaEvent_t ev_ring[64][5];  // per call: pyramid | fast | quadtree | describe boundaries (ring of 64 calls)
+  cudaEvent_t* ev;           // slot of the current call
+  long long prof_calls;      // calls recorded since profiling was enabled
   float sf[ydorb::kMaxLevels], inv_sf[ydorb::kMaxLevels], sf2[ydorb::kMaxLevels], inv_sf2[ydorb::kMaxLevels];
   int quota[ydorb::kMaxLevels];
   int umax[16];

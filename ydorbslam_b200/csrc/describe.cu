@@ -177,6 +177,7 @@ int launch_describe(const YdExtractor* ex, int batch, YdKeyPoint* d_kps, uint8_t
   dim3 grid((ex->geom.n_quota + kDescWarps - 1) / kDescWarps, batch);
   k_describe<<<grid, kDescWarps * 32, 0, s>>>(ex->d_geom, ex->d_pyr, ex->d_sel, ex->d_sel_n, d_kps, d_desc, capacity,
                                               d_nout, ex->d_status);
+  count_launches(1);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
 }

@@ -1,6 +1,7 @@
 // C ABI of the extractor (include/ydorb.h): handle life cycle, per-size geometry and OpenCV-compatible resize
 // tables built on the host, stage orchestration on the handle's stream.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -10,6 +11,9 @@
 namespace ydorb {
 
 static thread_local std::string g_last_error;
+static std::atomic<long long> g_launches{0};
+
+void count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
 void set_error(const std::string& msg) { g_last_error = msg; }
 
@@ -193,16 +197,24 @@ static int run_pipeline(YdExtractor* ex, const uint8_t* d_images, int w, int h, 
   if (rc != YDORB_OK) return rc;
   ex->cur_batch = batch;
   cudaStream_t s = ex->stream;
+  const bool prof = ex->profiling != 0;
+  if (prof) ex->ev = ex->ev_ring[ex->prof_calls++ % 64];
+  if (prof) YD_CUDA(cudaEventRecord(ex->ev[0], s));
   if ((rc = launch_pyramid(ex, d_images, stride, frame_stride, batch, s)) != YDORB_OK) return rc;
+  if (prof) YD_CUDA(cudaEventRecord(ex->ev[1], s));
   if (ex->geom.n_cells == 0 || ex->geom.n_quota == 0) {
+    if (prof) for (int i = 2; i < 5; i++) YD_CUDA(cudaEventRecord(ex->ev[i], s));
     YD_CUDA(cudaMemsetAsync(d_nout, 0, sizeof(int32_t) * batch, s));
     YD_CUDA(cudaMemsetAsync(ex->d_sel_n, 0, sizeof(int) * kMaxLevels * batch, s));
     YD_CUDA(cudaMemsetAsync(ex->d_level_ncand, 0, sizeof(int) * kMaxLevels * batch, s));
     return YDORB_OK;
   }
   if ((rc = launch_fast(ex, batch, s)) != YDORB_OK) return rc;
+  if (prof) YD_CUDA(cudaEventRecord(ex->ev[2], s));
   if ((rc = launch_quadtree(ex, batch, s)) != YDORB_OK) return rc;
+  if (prof) YD_CUDA(cudaEventRecord(ex->ev[3], s));
   if ((rc = launch_describe(ex, batch, d_kps, d_desc, capacity, d_nout, s)) != YDORB_OK) return rc;
+  if (prof) YD_CUDA(cudaEventRecord(ex->ev[4], s));
   return YDORB_OK;
 }
 
@@ -213,6 +225,8 @@ using namespace ydorb;
 extern "C" {
 
 const char* ydorb_last_error(void) { return g_last_error.c_str(); }
+
+long long ydorb_kernel_launches(void) { return g_launches.load(); }
 
 int ydorb_device_count(void) {
   int n = 0;
@@ -250,7 +264,10 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
   const int nq = std::max(hg.g.n_quota, 1);
   ex->out_cap = nq;
   const size_t B = (size_t)max_batch;
-  cudaError_t e = cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking);
+  cudaError_t e = cudaStreamCreateWithFlags(&ex->own_stream, cudaStreamNonBlocking);
+  ex->stream = ex->own_stream;
+  for (int i = 0; i < 64 * 5 && e == cudaSuccess; i++) e = cudaEventCreate(&ex->ev_ring[i / 5][i % 5]);
+  ex->ev = ex->ev_ring[0];
   auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, std::max<size_t>(bytes, 16)); };
   alloc((void**)&ex->d_geom, sizeof(FrameGeomDev));
   alloc((void**)&ex->d_pyr, B * ex->cap_pyr_bytes);
@@ -294,7 +311,9 @@ void ydorb_extractor_destroy(YdExtractor* ex) {
                   ex->d_status, ex->d_images, ex->d_kps, ex->d_desc, ex->d_nout};
   for (void* p : ptrs)
     if (p) cudaFree(p);
-  if (ex->stream) cudaStreamDestroy(ex->stream);
+  for (int i = 0; i < 64 * 5; i++)
+    if (ex->ev_ring[i / 5][i % 5]) cudaEventDestroy(ex->ev_ring[i / 5][i % 5]);
+  if (ex->own_stream) cudaStreamDestroy(ex->own_stream);
   delete ex;
 }
 
@@ -317,6 +336,38 @@ int ydorb_extractor_quotas(const YdExtractor* ex, int32_t* per_level) {
 }
 
 void* ydorb_extractor_stream(const YdExtractor* ex) { return ex ? (void*)ex->stream : nullptr; }
+
+int ydorb_extractor_set_stream(YdExtractor* ex, void* cuda_stream) {
+  YD_REQUIRE(ex, "null extractor");
+  YD_CUDA(cudaSetDevice(ex->device));
+  YD_CUDA(cudaStreamSynchronize(ex->stream));
+  ex->stream = cuda_stream ? (cudaStream_t)cuda_stream : ex->own_stream;
+  return YDORB_OK;
+}
+
+int ydorb_extractor_set_profiling(YdExtractor* ex, int enable) {
+  YD_REQUIRE(ex, "null extractor");
+  ex->profiling = enable ? 1 : 0;
+  ex->prof_calls = 0;
+  return YDORB_OK;
+}
+
+int ydorb_extractor_stage_ms(YdExtractor* ex, float* ms4) {
+  YD_REQUIRE(ex && ms4, "null argument");
+  if (!ex->profiling || ex->prof_calls <= 0) { set_error("profiling not enabled or no extract call since"); return YDORB_E_STATE; }
+  YD_CUDA(cudaSetDevice(ex->device));
+  YD_CUDA(cudaEventSynchronize(ex->ev[4]));
+  // mean over the calls recorded since profiling was switched on (at most the last 64)
+  const int calls = (int)std::min<long long>(ex->prof_calls, 64);
+  for (int i = 0; i < 4; i++) ms4[i] = 0.f;
+  for (int c = 0; c < calls; c++)
+    for (int i = 0; i < 4; i++) {
+      float t = 0.f;
+      YD_CUDA(cudaEventElapsedTime(&t, ex->ev_ring[c][i], ex->ev_ring[c][i + 1]));
+      ms4[i] += t / (float)calls;
+    }
+  return YDORB_OK;
+}
 
 int ydorb_extractor_sync(YdExtractor* ex) {
   YD_REQUIRE(ex, "null extractor");
@@ -350,6 +401,9 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
   YD_CUDA(cudaSetDevice(ex->device));
   cudaStream_t s = ex->stream;
   const size_t dpitch = (size_t)width;
+  if (stride == width && (batch == 1 || frame_stride == (size_t)width * height)) {
+    YD_CUDA(cudaMemcpyAsync(ex->d_images, images, (size_t)batch * width * height, cudaMemcpyHostToDevice, s));
+  } else
   for (int b = 0; b < batch; b++)
     YD_CUDA(cudaMemcpy2DAsync(ex->d_images + (size_t)b * width * height, dpitch, images + (size_t)b * frame_stride,
                               (size_t)stride, (size_t)width, (size_t)height, cudaMemcpyHostToDevice, s));
@@ -362,6 +416,12 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
   rc = check_status(ex);
   if (rc != YDORB_OK) return rc;
   int ret = YDORB_OK;
+  if (capacity == dcap) {  // same layout on both sides: two bulk copies instead of two per frame
+    YD_CUDA(cudaMemcpyAsync(keypoints, ex->d_kps, sizeof(YdKeyPoint) * (size_t)batch * dcap, cudaMemcpyDeviceToHost, s));
+    YD_CUDA(cudaMemcpyAsync(descriptors, ex->d_desc, (size_t)32 * batch * dcap, cudaMemcpyDeviceToHost, s));
+    YD_CUDA(cudaStreamSynchronize(s));
+    return ret;
+  }
   for (int b = 0; b < batch; b++) {
     int n = n_out[b];
     if (n > capacity) { n = capacity; ret = YDORB_E_CAPACITY; set_error("keypoint capacity too small"); }

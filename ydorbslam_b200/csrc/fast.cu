@@ -157,6 +157,7 @@ int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s) {
   dim3 grid((ex->geom.n_cells + kWarpsPerCta - 1) / kWarpsPerCta, batch);
   k_fast_cells<<<grid, kWarpsPerCta * 32, 0, s>>>(ex->d_geom, ex->d_cells, ex->d_pyr, ini, mn, ex->d_raw, ex->d_raw_counter,
                                                   ex->d_cell_count, ex->d_cell_start, ex->d_status);
+  count_launches(1);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
 }

@@ -128,6 +128,68 @@ __global__ void k_ratio_accept(const YdTop2* __restrict__ t, int nq, float ratio
   accept[qi] = (v.best_idx >= 0 && v.best_dist <= th && (float)v.best_dist < __fmul_rn(ratio, (float)v.second_dist)) ? 1 : 0;
 }
 
+// Batched variant for many small problems (frame t vs frame t-1): blockIdx.y = pair, the whole database frame
+// (<= capacity rows) is streamed by every CTA; results are written unpacked, optionally with the ratio test.
+__global__ void __launch_bounds__(kTopThreads)
+k_top2_frames(const uint4* __restrict__ desc, const int32_t* __restrict__ n_of, int capacity,
+              const int32_t* __restrict__ q_frame, const int32_t* __restrict__ db_frame, YdTop2* __restrict__ out,
+              uint8_t* __restrict__ accept, float ratio, int th) {
+  __shared__ uint4 s_db[2 * kTopTile];
+  const int tid = threadIdx.x;
+  const int pair = blockIdx.y;
+  const int qf = q_frame[pair], df = db_frame[pair];
+  const int nq = min(n_of[qf], capacity), ndb = min(n_of[df], capacity);
+  const int q0 = blockIdx.x * kTopQblock;
+  if (q0 >= nq) return;
+  const uint4* q = desc + (size_t)qf * capacity * 2;
+  const uint4* db = desc + (size_t)df * capacity * 2;
+  uint32_t qa[kTopQpt][8];
+  uint32_t best[kTopQpt], second[kTopQpt];
+#pragma unroll
+  for (int k = 0; k < kTopQpt; k++) {
+    const int qi = q0 + k * kTopThreads + tid;
+    uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
+    if (qi < nq) { lo = q[2 * qi]; hi = q[2 * qi + 1]; }
+    qa[k][0] = lo.x; qa[k][1] = lo.y; qa[k][2] = lo.z; qa[k][3] = lo.w;
+    qa[k][4] = hi.x; qa[k][5] = hi.y; qa[k][6] = hi.z; qa[k][7] = hi.w;
+    best[k] = kNoKey;
+    second[k] = kNoKey;
+  }
+  for (int t0 = 0; t0 < ndb; t0 += kTopTile) {
+    const int rows = min(kTopTile, ndb - t0);
+    __syncthreads();
+    for (int i = tid; i < 2 * rows; i += kTopThreads) s_db[i] = db[2 * (size_t)t0 + i];
+    __syncthreads();
+#pragma unroll 2
+    for (int r = 0; r < rows; r++) {
+      const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1];
+#pragma unroll
+      for (int k = 0; k < kTopQpt; k++) {
+        const int d = __popc(qa[k][0] ^ lo.x) + __popc(qa[k][1] ^ lo.y) + __popc(qa[k][2] ^ lo.z) +
+                      __popc(qa[k][3] ^ lo.w) + __popc(qa[k][4] ^ hi.x) + __popc(qa[k][5] ^ hi.y) +
+                      __popc(qa[k][6] ^ hi.z) + __popc(qa[k][7] ^ hi.w);
+        const uint32_t key = ((uint32_t)d << 23) | (uint32_t)(t0 + r);
+        second[k] = min(second[k], max(best[k], key));
+        best[k] = min(best[k], key);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < kTopQpt; k++) {
+    const int qi = q0 + k * kTopThreads + tid;
+    if (qi >= nq) continue;
+    YdTop2 o;
+    o.best_idx = best[k] == kNoKey ? -1 : (int)(best[k] & 0x7FFFFFu);
+    o.best_dist = best[k] == kNoKey ? 256 : (int)(best[k] >> 23);
+    o.second_idx = second[k] == kNoKey ? -1 : (int)(second[k] & 0x7FFFFFu);
+    o.second_dist = second[k] == kNoKey ? 256 : (int)(second[k] >> 23);
+    out[(size_t)pair * capacity + qi] = o;
+    if (accept)
+      accept[(size_t)pair * capacity + qi] =
+          (o.best_idx >= 0 && o.best_dist <= th && (float)o.best_dist < __fmul_rn(ratio, (float)o.second_dist)) ? 1 : 0;
+  }
+}
+
 int matcher_reserve(YdMatcher* m, size_t bytes) {
   if (bytes <= m->scratch_bytes) return YDORB_OK;
   if (m->d_scratch) YD_CUDA(cudaFree(m->d_scratch));
@@ -166,8 +228,9 @@ int ydorb_matcher_create(int device, YdMatcher** out) {
   m->scratch_bytes = 0;
   m->d_io = nullptr;
   m->io_bytes = 0;
-  cudaError_t e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+  cudaError_t e = cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { delete m; return cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__); }
+  m->stream = m->own_stream;
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, device);
   m->sm_count = prop.multiProcessorCount;
@@ -180,7 +243,7 @@ void ydorb_matcher_destroy(YdMatcher* m) {
   cudaSetDevice(m->device);
   if (m->d_scratch) cudaFree(m->d_scratch);
   if (m->d_io) cudaFree(m->d_io);
-  if (m->stream) cudaStreamDestroy(m->stream);
+  if (m->own_stream) cudaStreamDestroy(m->own_stream);
   delete m;
 }
 
@@ -189,6 +252,61 @@ void* ydorb_matcher_stream(const YdMatcher* m) { return m ? (void*)m->stream : n
 int ydorb_matcher_sync(YdMatcher* m) {
   YD_REQUIRE(m, "null matcher");
   YD_CUDA(cudaSetDevice(m->device));
+  YD_CUDA(cudaStreamSynchronize(m->stream));
+  return YDORB_OK;
+}
+
+int ydorb_matcher_set_stream(YdMatcher* m, void* cuda_stream) {
+  YD_REQUIRE(m, "null matcher");
+  YD_CUDA(cudaSetDevice(m->device));
+  YD_CUDA(cudaStreamSynchronize(m->stream));
+  m->stream = cuda_stream ? (cudaStream_t)cuda_stream : m->own_stream;
+  return YDORB_OK;
+}
+
+int ydorb_hamming_top2_frames_device(YdMatcher* m, const uint8_t* d_desc, const int32_t* d_n, int capacity,
+                                     const int32_t* d_q_frame, const int32_t* d_db_frame, int npairs, YdTop2* d_out,
+                                     uint8_t* d_accept, float ratio, int th) {
+  YD_REQUIRE(m && d_desc && d_n && d_q_frame && d_db_frame && d_out, "null argument");
+  YD_REQUIRE(capacity > 0 && capacity < (1 << 23) && npairs >= 0, "bad size");
+  YD_REQUIRE(((uintptr_t)d_desc & 15) == 0, "descriptor block must be 16-byte aligned");
+  if (npairs == 0) return YDORB_OK;
+  YD_CUDA(cudaSetDevice(m->device));
+  dim3 grid((capacity + kTopQblock - 1) / kTopQblock, npairs);
+  k_top2_frames<<<grid, kTopThreads, 0, m->stream>>>(reinterpret_cast<const uint4*>(d_desc), d_n, capacity, d_q_frame,
+                                                     d_db_frame, d_out, d_accept, ratio, th);
+  count_launches(1);
+  YD_CUDA(cudaGetLastError());
+  return YDORB_OK;
+}
+
+int ydorb_match_frames(YdMatcher* m, const YdExtractor* ex, const int32_t* q_frame, const int32_t* db_frame, int npairs,
+                       float ratio, int th, YdTop2* out, uint8_t* accept) {
+  YD_REQUIRE(m && ex && q_frame && db_frame && out && npairs >= 0, "bad argument");
+  if (ex->cur_w <= 0) { set_error("no extract call yet"); return YDORB_E_STATE; }
+  YD_REQUIRE(ex->device == m->device, "handles live on different devices");
+  for (int p = 0; p < npairs; p++)
+    YD_REQUIRE(q_frame[p] >= 0 && q_frame[p] < ex->cur_batch && db_frame[p] >= 0 && db_frame[p] < ex->cur_batch,
+               "frame index out of range");
+  if (npairs == 0) return YDORB_OK;
+  YD_CUDA(cudaSetDevice(m->device));
+  const int cap = ex->out_cap;
+  const size_t nres = (size_t)npairs * cap;
+  const size_t o_q = 0, o_db = (sizeof(int32_t) * npairs + 255) / 256 * 256, o_out = 2 * o_db,
+               o_acc = o_out + (sizeof(YdTop2) * nres + 255) / 256 * 256, total = o_acc + nres;
+  int rc = matcher_reserve_io(m, total);
+  if (rc != YDORB_OK) return rc;
+  uint8_t* io = reinterpret_cast<uint8_t*>(m->d_io);
+  YD_CUDA(cudaStreamSynchronize(ex->stream));  // descriptors were produced on the extractor's stream
+  YD_CUDA(cudaMemcpyAsync(io + o_q, q_frame, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, m->stream));
+  YD_CUDA(cudaMemcpyAsync(io + o_db, db_frame, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, m->stream));
+  YD_CUDA(cudaMemsetAsync(io + o_out, 0xFF, sizeof(YdTop2) * nres, m->stream));  // unused rows read as idx -1
+  rc = ydorb_hamming_top2_frames_device(m, ex->d_desc, ex->d_nout, cap, reinterpret_cast<int32_t*>(io + o_q),
+                                        reinterpret_cast<int32_t*>(io + o_db), npairs, reinterpret_cast<YdTop2*>(io + o_out),
+                                        accept ? io + o_acc : nullptr, ratio, th);
+  if (rc != YDORB_OK) return rc;
+  YD_CUDA(cudaMemcpyAsync(out, io + o_out, sizeof(YdTop2) * nres, cudaMemcpyDeviceToHost, m->stream));
+  if (accept) YD_CUDA(cudaMemcpyAsync(accept, io + o_acc, nres, cudaMemcpyDeviceToHost, m->stream));
   YD_CUDA(cudaStreamSynchronize(m->stream));
   return YDORB_OK;
 }
@@ -215,6 +333,7 @@ int ydorb_hamming_top2_device(YdMatcher* m, const uint8_t* d_queries, int nq, co
   k_top2_chunks<<<grid, kTopThreads, 0, m->stream>>>(reinterpret_cast<const uint4*>(d_queries), nq,
                                                      reinterpret_cast<const uint4*>(d_db), ndb, chunk_rows, partial);
   k_top2_finish<<<(nq + 127) / 128, 128, 0, m->stream>>>(partial, nchunks, nq, chunk_rows, idx_base, d_out);
+  count_launches(2);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
 }
@@ -265,6 +384,7 @@ int ydorb_top2_merge_device(YdMatcher* m, const YdTop2* d_shards, int nshards, i
   if (nq == 0) return YDORB_OK;
   YD_CUDA(cudaSetDevice(m->device));
   k_top2_merge<<<(nq + 127) / 128, 128, 0, m->stream>>>(d_shards, nshards, nq, d_out);
+  count_launches(1);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
 }
@@ -274,6 +394,7 @@ int ydorb_ratio_accept_device(YdMatcher* m, const YdTop2* d_top2, int nq, float 
   if (nq == 0) return YDORB_OK;
   YD_CUDA(cudaSetDevice(m->device));
   k_ratio_accept<<<(nq + 127) / 128, 128, 0, m->stream>>>(d_top2, nq, ratio, th, d_accept);
+  count_launches(1);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
 }

@@ -6,6 +6,7 @@ struct YdMatcher {
   int device;
   int sm_count;
   cudaStream_t stream;
+  cudaStream_t own_stream;
   void* d_scratch;       // kernel scratch (per-chunk partial results, candidate lists)
   size_t scratch_bytes;
   void* d_io;            // staging for host entry points

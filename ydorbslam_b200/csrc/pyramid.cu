@@ -96,6 +96,7 @@ int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, s
       k_pyr_resize<<<grid, block, 0, s>>>(ex->d_geom, l, ex->d_tab_ofs, reinterpret_cast<const short2*>(ex->d_tab_a),
                                           ex->d_pyr);
   }
+  count_launches(g.n_levels);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
 }

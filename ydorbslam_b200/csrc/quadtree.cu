@@ -494,6 +494,7 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
   A.status = ex->d_status;
   dim3 grid(ex->geom.n_levels, batch);
   k_quadtree<<<grid, kQtThreads, 0, s>>>(A);
+  count_launches(2);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
 }

@@ -72,6 +72,19 @@ class OrbExtractor:
     def sync(self):
         check(lib().ydorb_extractor_sync(self._h))
 
+    def set_stream(self, cuda_stream):
+        """Enqueue on a caller-owned cudaStream_t (int); None restores the handle's own stream."""
+        check(lib().ydorb_extractor_set_stream(self._h, C.c_void_p(cuda_stream) if cuda_stream else None))
+
+    def set_profiling(self, enable=True):
+        check(lib().ydorb_extractor_set_profiling(self._h, 1 if enable else 0))
+
+    def stage_ms(self):
+        """CUDA-event durations of the last call: [pyramid, fast, quadtree, describe] in ms."""
+        ms = (C.c_float * 4)()
+        check(lib().ydorb_extractor_stage_ms(self._h, ms))
+        return [float(v) for v in ms]
+
     # ---- extractAndCompute (src/orbExtractor.cpp:355-399)
     def extractAndCompute(self, image):
         """image: HxW uint8.  Returns (keypoints KP_DTYPE[N], descriptors uint8[N,32])."""

@@ -99,6 +99,28 @@ class OrbMatcher:
     def top2_device(self, d_q, nq, d_db, ndb, idx_base, d_out):
         check(lib().ydorb_hamming_top2_device(self._h, ptr(d_q), nq, ptr(d_db), ndb, idx_base, ptr(d_out)))
 
+    def set_stream(self, cuda_stream):
+        check(lib().ydorb_matcher_set_stream(self._h, C.c_void_p(cuda_stream) if cuda_stream else None))
+
+    def top2_frames_device(self, d_desc, d_n, capacity, d_q_frame, d_db_frame, npairs, d_out, d_accept=None, ratio=None,
+                           th=LOW_THD):
+        """Batched dense top-2 between frames of one descriptor block (device pointers, asynchronous)."""
+        check(lib().ydorb_hamming_top2_frames_device(self._h, ptr(d_desc), ptr(d_n), capacity, ptr(d_q_frame), ptr(d_db_frame),
+                                                     npairs, ptr(d_out), ptr(d_accept),
+                                                     C.c_float(self.ratio if ratio is None else ratio), th))
+
+    def match_frames(self, extractor, q_frame, db_frame, ratio=None, th=LOW_THD):
+        """Host API: top-2 + ratio test between frames of the extractor's last host-API batch (descriptors stay on
+        the device).  Returns (top2[npairs, capacity], accept[npairs, capacity])."""
+        qf = np.ascontiguousarray(q_frame, dtype=np.int32)
+        df = np.ascontiguousarray(db_frame, dtype=np.int32)
+        cap = extractor.capacity
+        out = np.zeros((len(qf), cap), TOP2_DTYPE)
+        acc = np.zeros((len(qf), cap), np.uint8)
+        check(lib().ydorb_match_frames(self._h, extractor._h, ptr(qf), ptr(df), len(qf),
+                                       C.c_float(self.ratio if ratio is None else ratio), th, ptr(out), ptr(acc)))
+        return out, acc
+
     def top2_merge_device(self, d_shards, nshards, nq, d_out):
         check(lib().ydorb_top2_merge_device(self._h, ptr(d_shards), nshards, nq, ptr(d_out)))
 
