@@ -82,6 +82,7 @@ struct YdExtractor {
   int umax[16];
   // geometry for the current (w,h)
   int cur_w, cur_h, cur_batch;
+  int max_cell_w, max_cell_h;     // largest FAST cell ROI of the current geometry (sizes the smem tile)
   ydorb::FrameGeomDev geom;       // host copy
   ydorb::FrameGeomDev* d_geom;    // device copy
   // capacities computed for (max_w,max_h)

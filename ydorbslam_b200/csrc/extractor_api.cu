@@ -166,6 +166,11 @@ static int set_size(YdExtractor* ex, int w, int h) {
     return YDORB_E_CAPACITY;
   }
   ex->geom = hg.g;
+  ex->max_cell_w = ex->max_cell_h = 8;
+  for (const int4& c : hg.cells) {
+    ex->max_cell_w = std::max(ex->max_cell_w, c.z - c.x);
+    ex->max_cell_h = std::max(ex->max_cell_h, c.w - c.y);
+  }
   YD_CUDA(cudaMemcpyAsync(ex->d_geom, &ex->geom, sizeof(FrameGeomDev), cudaMemcpyHostToDevice, ex->stream));
   if (!hg.tab_ofs.empty()) {
     YD_CUDA(cudaMemcpyAsync(ex->d_tab_ofs, hg.tab_ofs.data(), hg.tab_ofs.size() * sizeof(int), cudaMemcpyHostToDevice, ex->stream));
