@@ -57,6 +57,11 @@ int ydorb_device_count(void);
 /* number of CUDA kernels this library has launched in this process (evidence for benchmarks) */
 long long ydorb_kernel_launches(void);
 
+/* Diagnostics (no reference counterpart): measured issue rates of the integer pipes, thread-operations per second:
+ * out[0] POPC, [1] LOP3, [2] VIMNMX3.S16x2 (DPX), [3] IMAD, [4] LOP3+IMAD alternating.  Denominators of the integer
+ * roofline bench.py reports for the FAST and Hamming kernels. */
+int ydorb_diag_int_peaks(int device, double* ops_per_s, int n);
+
 /* ---- OrbExtractor -------------------------------------------------------------------------------------- */
 /* OrbExtractor::OrbExtractor (src/orbExtractor.cpp:315-354).  max_* size the device buffers. */
 int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int max_height, int max_batch, int device,

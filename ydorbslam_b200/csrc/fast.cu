@@ -7,18 +7,23 @@
 // a contiguous slice of the frame's candidate buffer with one atomicAdd; the global (cell-major) order is restored
 // later from the per-cell counts.
 //
-// Scoring is branch-free and exact for EVERY tested pixel: with d_k = I(p) - I(circle_k),
-//     m = max( max_arcs min_arc d ,  -min_arcs max_arc d ),   corner <=> m > t,   response = m - 1,
-// which does not depend on the threshold, so one scoring pass serves both thresholds of the fallback.  A thread
-// scores two horizontally adjacent pixels at once on packed s16x2 values with the DPX 3-input min/max
-// (VIMNMX3.S16x2): the tile is stored as 16-bit pixel pairs, d is kept biased by +256 so packed subtraction never
-// borrows across halves, the 9-arc minimum is min3(min3) over a circular array (16+16 ops), the max over arcs 8 ops.
-// This is integer-pipe work (about 75 instructions per pixel), not HBM-bound: the level is read from HBM once.
+// Everything is done on packed s16x2 pixel pairs (two horizontally adjacent pixels per 32-bit word, DPX VIMNMX3):
+//   stage   aligned 32-bit global loads -> two pair words per load (PRMT), tile column 0 is 4-byte aligned in HBM;
+//   reject  necessary condition for a 9-arc: every antipodal pair (k, k+8) of the circle has a member on the arc, so
+//           min_k max(d_k, d_k+8) > t  or  max_k min(d_k, d_k+8) < -t  must hold; tested on k = 0,2,4,6 (8 loads);
+//           pairs that pass are compacted through a small per-warp queue so the exact score runs on full warps;
+//   score   exact and branch-free: with d_k = I(p) - I(circle_k),
+//               m = max( max_arcs min_arc d ,  -min_arcs max_arc d ),   corner <=> m > t,   response = m - 1;
+//           d is kept biased by +256 so packed subtraction never borrows across halves, the 9-arc minimum is
+//           min3(min3) over a circular array (16+16 ops), the max over arcs 8 ops.  Stored value: max(m - t_low, 0);
+//   nms     packed: the 8-neighbour maximum of a pair is 4 funnel shifts + 4 VIMNMX; keep <=> centre > neighbours.
+// This is integer-pipe work, not HBM-bound: the level is read from HBM once.
 #include "kernels.cuh"
 
 namespace ydorb {
 
 constexpr int kWarpsPerCta = 4;
+constexpr int kFastQueue = 64;  // compaction queue entries per warp
 
 // circular 9-arc extremum: r[k] = op3 over D[k..k+8]
 #define YD_ARC_TREE(OP3, D, OUT)                                                   \
@@ -45,34 +50,49 @@ __device__ __forceinline__ uint32_t min16_s16x2(const uint32_t (&v)[16]) {
   return __vmins2(a, d);
 }
 
-// FAST-9/16 score m of the two pixels held in the 16-bit pair word at `row` (tile columns 2j-1+? see k_fast_cells).
-// Returns (m_lo, m_hi) as two ints in [-255, 255].
-__device__ __forceinline__ void fast_score_pair(const uint32_t* __restrict__ row, int wpr, int& m_lo, int& m_hi) {
-  // pair word j covers tile columns (2j-1, 2j); this pair starts at an odd tile column c, word j = (c+1)/2.
-  // even dx: word j + dx/2; odd dx: funnel shift of words j+(dx-1)/2 and j+(dx+1)/2.
-  auto fsr = [](uint32_t lo, uint32_t hi) { return __funnelshift_r(lo, hi, 16); };
+__device__ __forceinline__ uint32_t fsr16(uint32_t lo, uint32_t hi) { return __funnelshift_r(lo, hi, 16); }
+
+// Word j of a tile row holds tile columns (2j, 2j+1).  For the pixel pair at `row` (= &tile[r][j]): an even dx reads
+// word j + dx/2, an odd dx the funnel shift of words j+(dx-1)/2 and j+(dx+1)/2.
+
+// Cheap necessary condition for "one of the two pixels is a corner at threshold t" (see header).
+// k1 = (0x7FFF - (t+256)) * 0x10001,  k2 = (0x8000 + 255 - t) * 0x10001.
+__device__ __forceinline__ bool fast_quick_pair(const uint32_t* __restrict__ row, int wpr, uint32_t k1, uint32_t k2) {
+  const uint32_t cb = row[0] + 0x01000100u;  // centre + 256 in both halves
+  const uint32_t d0 = cb - row[3 * wpr], d8 = cb - row[-3 * wpr];                      // (0,3) (0,-3)
+  const uint32_t d4 = cb - fsr16(row[1], row[2]), d12 = cb - fsr16(row[-2], row[-1]);  // (3,0) (-3,0)
+  const uint32_t d2 = cb - row[2 * wpr + 1], d10 = cb - row[-2 * wpr - 1];             // (2,2) (-2,-2)
+  const uint32_t d6 = cb - row[-2 * wpr + 1], d14 = cb - row[2 * wpr - 1];             // (2,-2) (-2,2)
+  const uint32_t a = __vimin3_s16x2(__vmaxs2(d0, d8), __vmaxs2(d4, d12), __vmins2(__vmaxs2(d2, d10), __vmaxs2(d6, d14)));
+  const uint32_t b = __vimax3_s16x2(__vmins2(d0, d8), __vmins2(d4, d12), __vmaxs2(__vmins2(d2, d10), __vmins2(d6, d14)));
+  // half of a > t+256  <=> bit 15 of (a + k1);  half of b < 256-t  <=> bit 15 of (k2 - b); no carries between halves
+  return (((a + k1) | (k2 - b)) & 0x80008000u) != 0u;
+}
+
+// Exact FAST-9/16 score of both pixels of the pair, returned biased: each half = m + 256, m in [-255, 255].
+__device__ __forceinline__ uint32_t fast_score_pair(const uint32_t* __restrict__ row, int wpr) {
   uint32_t P[16];
   {
     const uint32_t* r = row + 3 * wpr;  // dy = +3: k0 (0,3) k1 (1,3) k15 (-1,3)
     const uint32_t a = r[-1], b = r[0], c = r[1];
-    P[0] = b; P[1] = fsr(b, c); P[15] = fsr(a, b);
+    P[0] = b; P[1] = fsr16(b, c); P[15] = fsr16(a, b);
   }
   {
     const uint32_t* r = row - 3 * wpr;  // dy = -3: k8 (0,-3) k7 (1,-3) k9 (-1,-3)
     const uint32_t a = r[-1], b = r[0], c = r[1];
-    P[8] = b; P[7] = fsr(b, c); P[9] = fsr(a, b);
+    P[8] = b; P[7] = fsr16(b, c); P[9] = fsr16(a, b);
   }
   P[2] = row[2 * wpr + 1];    // (2,2)
   P[14] = row[2 * wpr - 1];   // (-2,2)
   P[6] = row[-2 * wpr + 1];   // (2,-2)
   P[10] = row[-2 * wpr - 1];  // (-2,-2)
-  P[3] = fsr(row[wpr + 1], row[wpr + 2]);      // (3,1)
-  P[13] = fsr(row[wpr - 2], row[wpr - 1]);     // (-3,1)
-  P[5] = fsr(row[-wpr + 1], row[-wpr + 2]);    // (3,-1)
-  P[11] = fsr(row[-wpr - 2], row[-wpr - 1]);   // (-3,-1)
-  P[4] = fsr(row[1], row[2]);                  // (3,0)
-  P[12] = fsr(row[-2], row[-1]);               // (-3,0)
-  const uint32_t cb = row[0] + 0x01000100u;    // centre + 256 in both halves
+  P[3] = fsr16(row[wpr + 1], row[wpr + 2]);      // (3,1)
+  P[13] = fsr16(row[wpr - 2], row[wpr - 1]);     // (-3,1)
+  P[5] = fsr16(row[-wpr + 1], row[-wpr + 2]);    // (3,-1)
+  P[11] = fsr16(row[-wpr - 2], row[-wpr - 1]);   // (-3,-1)
+  P[4] = fsr16(row[1], row[2]);                  // (3,0)
+  P[12] = fsr16(row[-2], row[-1]);               // (-3,0)
+  const uint32_t cb = row[0] + 0x01000100u;      // centre + 256 in both halves
   uint32_t D[16];
 #pragma unroll
   for (int k = 0; k < 16; k++) D[k] = cb - P[k];  // halves in [1, 511]: no borrow between halves
@@ -81,25 +101,23 @@ __device__ __forceinline__ void fast_score_pair(const uint32_t* __restrict__ row
   YD_ARC_TREE(__vimax3_s16x2, D, hi9)
   const uint32_t dark = max16_s16x2(lo9);    // max over arcs of min d (+256)
   const uint32_t bright = min16_s16x2(hi9);  // min over arcs of max d (+256)
-  m_lo = max((int)(dark & 0xFFFFu) - 256, 256 - (int)(bright & 0xFFFFu));
-  m_hi = max((int)(dark >> 16) - 256, 256 - (int)(bright >> 16));
+  return __vmaxs2(dark, 0x02000200u - bright);  // halves of (512 - bright) in [1, 511]: no borrow
 }
 
 struct FastSmemLayout {
-  int wpr;          // pair words per tile row
-  int sstride;      // bytes per score row
-  int tile_words;   // per warp
-  int score_bytes;  // per warp
+  int wpr;          // pair words per tile row (even)
+  int plane_words;  // words of one [max_th][wpr] plane incl. 2 slack words on either side
+  int list_cap;     // NMS survivors per cell (no two are 8-neighbours)
   int warp_bytes;
 };
 
 __host__ __device__ inline FastSmemLayout fast_layout(int max_tw, int max_th) {
   FastSmemLayout L;
-  L.wpr = (max_tw + 1) / 2 + 2;              // word j covers cols (2j-1, 2j); +1 word of slack each side
-  L.sstride = (max_tw + 2 + 3) & ~3;
-  L.tile_words = L.wpr * max_th;
-  L.score_bytes = L.sstride * (max_th + 2);
-  L.warp_bytes = (L.tile_words * 4 + L.score_bytes + 128 * 4 + 15) & ~15;  // + ballot words
+  const int nw4 = (4 + max_tw + 3) / 4;  // aligned 32-bit loads per row, worst-case alignment
+  L.wpr = 2 * nw4;
+  L.plane_words = L.wpr * max_th + 4;
+  L.list_cap = ((max_tw - 6 + 1) / 2 + 1) * ((max_th - 6 + 1) / 2 + 1);
+  L.warp_bytes = ((2 * L.plane_words + L.list_cap) * 4 + kFastQueue * 2 + 15) & ~15;
   return L;
 }
 
@@ -110,6 +128,7 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const FastSmemLayout L = fast_layout(max_tw, max_th);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t lt_mask = (1u << lane) - 1u;
   const int cell = blockIdx.x * kWarpsPerCta + warp;
   const int frame = blockIdx.y;
   if (cell >= g->n_cells) return;
@@ -126,69 +145,134 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
     if (cell >= g->lv[l].cell_base) level = l;
   const LevelGeom lv = g->lv[level];
   const uint8_t* src = pyr + (size_t)frame * g->pyr_bytes + level_origin(lv) + (size_t)roi.y * lv.stride + roi.x;
+  // ROI column 0 is tile column a, a in [1, 4]: tile column 0 is 4-byte aligned in HBM and every word a tested pixel's
+  // LOW half depends on is a staged pixel (<= 255), so packed subtraction never borrows into a tested half.
+  const int a = (int)((reinterpret_cast<uintptr_t>(src) - 1u) & 3u) + 1;
   uint8_t* wbase = smem_raw + (size_t)warp * L.warp_bytes;
-  uint32_t* tile = reinterpret_cast<uint32_t*>(wbase);                 // [th][wpr] pair words, word 1 = cols (-1,0)
-  uint8_t* score = wbase + L.tile_words * 4 + L.sstride;               // [th][sstride], one zero row above
-  uint32_t* ballots = reinterpret_cast<uint32_t*>(wbase + L.tile_words * 4 + L.score_bytes);
-  const int wpr = L.wpr, S = L.sstride;
-  // stage the tile as 16-bit pixel pairs: word (r, 1 + j) = (col 2j-1, col 2j); columns outside the tile read 0
-  const int nwords = (tw + 2) / 2;  // j = 0 .. nwords-1 covers cols -1 .. tw (at most)
-  for (int r = 0; r < th_; r++) {
-    const uint8_t* srow = src + (size_t)r * lv.stride;
-    for (int j = lane; j < nwords; j += 32) {
-      const int c0 = 2 * j - 1, c1 = 2 * j;
-      const uint32_t v0 = (c0 >= 0 && c0 < tw) ? srow[c0] : 0u;
-      const uint32_t v1 = (c1 < tw) ? srow[c1] : 0u;
-      tile[r * wpr + 1 + j] = v0 | (v1 << 16);
+  uint32_t* tile = reinterpret_cast<uint32_t*>(wbase) + 2;                    // [th][wpr] pixel pairs
+  uint32_t* score = tile + L.plane_words;                                      // [th][wpr] stored scores, pairs
+  uint32_t* list = reinterpret_cast<uint32_t*>(wbase) + 2 * L.plane_words;     // survivors, packed output format
+  uint16_t* queue = reinterpret_cast<uint16_t*>(list + L.list_cap);
+  const int wpr = L.wpr;
+
+  // ---- stage: word (r, 2w) = cols (4w, 4w+1), word (r, 2w+1) = cols (4w+2, 4w+3) of the aligned row
+  {
+    const int nw4 = (a + tw + 3) >> 2;
+    const uint8_t* src_al = src - a;
+    int r = 0, w = lane;
+    while (w >= nw4) { w -= nw4; r++; }
+    while (r < th_) {
+      const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src_al + (size_t)r * lv.stride) + w);
+      *reinterpret_cast<uint2*>(tile + r * wpr + 2 * w) = make_uint2(__byte_perm(v, 0, 0x4140), __byte_perm(v, 0, 0x4342));
+      w += 32;
+      while (w >= nw4) { w -= nw4; r++; }
     }
-    for (int c = lane; c < S; c += 32) score[r * S + c] = 0;
   }
-  for (int c = lane; c < S; c += 32) { score[-S + c] = 0; score[th_ * S + c] = 0; }
-  __syncwarp();
-  // score every tested pixel; a lane handles the pair at tile columns (c, c+1), c odd, rows 3..th-4
-  const int iw = tw - 6, ih = th_ - 6;
-  const int ipw = (iw + 1) / 2;  // pairs per row
+  // tested pixels: tile columns [a+3, a+tw-4], rows [3, th-4]
+  const int c_lo = a + 3, c_hi = a + tw - 4;
+  const int j0 = c_lo >> 1, j1 = c_hi >> 1;
+  const int ipw = j1 - j0 + 1, ih = th_ - 6;
   const int npairs = ipw * ih;
+  // zero ring of the score plane around the tested pairs (NMS reads one pair / one row beyond them)
+  for (int j = lane; j < wpr; j += 32) { score[2 * wpr + j] = 0; score[(th_ - 3) * wpr + j] = 0; }
+  for (int r = 3 + lane; r < th_ - 3; r += 32) { score[r * wpr + j0 - 1] = 0; score[r * wpr + j1 + 1] = 0; }
+  __syncwarp();
+
   const int low_th = min(max(min(ini_th, min_th), 0), 255);
   {
-    int r = 0, jj = lane;  // pair (r, jj) without a division per step
+    // ---- reject + exact score
+    const uint32_t k1 = (uint32_t)(0x7FFF - (low_th + 256)) * 0x10001u;
+    const uint32_t k2 = (uint32_t)(0x8000 + 255 - low_th) * 0x10001u;
+    const uint32_t kc = (uint32_t)(256 + low_th) * 0x10001u;
+    auto score_entry = [&](uint32_t e) {
+      const int r = (int)(e >> 8), j = (int)(e & 255u);
+      const uint32_t mm = fast_score_pair(tile + r * wpr + j, wpr);  // m + 256
+      uint32_t s = __vmaxs2(mm, kc) - kc;                            // max(m - low_th, 0), no borrow
+      if (2 * j < c_lo) s &= 0xFFFF0000u;                            // untested half of an edge pair
+      if (2 * j + 1 > c_hi) s &= 0x0000FFFFu;
+      score[r * wpr + j] = s;
+    };
+    int qn = 0;
+    int r = 3, jj = lane;
     while (jj >= ipw) { jj -= ipw; r++; }
-    for (int p = lane; p < npairs; p += 32) {
-      const int c = 3 + 2 * jj, rr = r + 3;
-      int m0, m1;
-      fast_score_pair(tile + rr * wpr + 1 + (c + 1) / 2, wpr, m0, m1);
-      // stored score: m if corner at the lower threshold, else 0 (m <= 255)
-      score[rr * S + c] = (uint8_t)(m0 > low_th ? m0 : 0);
-      if (c + 1 < tw - 3) score[rr * S + c + 1] = (uint8_t)(m1 > low_th ? m1 : 0);
+    for (int base = 0; base < npairs; base += 32) {
+      const bool valid = base + lane < npairs;
+      bool pass = false;
+      if (valid) {
+        pass = fast_quick_pair(tile + r * wpr + j0 + jj, wpr, k1, k2);
+        if (!pass) score[r * wpr + j0 + jj] = 0;
+      }
+      const uint32_t bal = __ballot_sync(0xffffffffu, pass);
+      if (pass) queue[qn + __popc(bal & lt_mask)] = (uint16_t)((r << 8) | (j0 + jj));
+      qn += __popc(bal);
+      __syncwarp();
+      if (qn >= 32) {
+        score_entry(queue[lane]);
+        const int rem = qn - 32;
+        uint16_t t = 0;
+        if (lane < rem) t = queue[32 + lane];
+        __syncwarp();
+        if (lane < rem) queue[lane] = t;
+        qn = rem;
+        __syncwarp();
+      }
       jj += 32;
       while (jj >= ipw) { jj -= ipw; r++; }
     }
+    if (lane < qn) score_entry(queue[lane]);
+    __syncwarp();
   }
-  __syncwarp();
-  // NMS at threshold th: corners are pixels with score > th; strictly greater than all 8 neighbours, where
-  // non-corners (and untested pixels) count 0.  Row-major pixel index i over the tested area.
-  const int total = iw * ih;
-  auto nms_keep = [&](int i, int th, int& r, int& c, int& m) -> bool {
-    if (i >= total) return false;
-    r = i / iw + 3;
-    c = i - (r - 3) * iw + 3;
-    const uint8_t* s = score + r * S + c;
-    m = s[0];
-    if (m <= th) return false;
-    auto e = [&](int v) { return v > th ? v : 0; };
-    return m > e(s[-1]) && m > e(s[1]) && m > e(s[-S - 1]) && m > e(s[-S]) && m > e(s[-S + 1]) && m > e(s[S - 1]) &&
-           m > e(s[S]) && m > e(s[S + 1]);
+
+  // ---- NMS: strictly greater than all 8 neighbours, non-corners (and untested pixels) count 0; row-major emit.
+  // `plane` holds max(m - th, 0) for the threshold th in use, so response = value + th - 1.
+  // (the x term may be negative before the column is added: sum modulo 2^32, never OR)
+  const uint32_t pos_base = ((uint32_t)(roi.y - kBorder) << 20) + ((uint32_t)(roi.x - a - kBorder) << 8);
+  auto nms_pass = [&](const uint32_t* __restrict__ plane, int th) -> int {
+    int count = 0;
+    int r = 3, jj = lane;
+    while (jj >= ipw) { jj -= ipw; r++; }
+    for (int base = 0; base < npairs; base += 32) {
+      const bool valid = base + lane < npairs;
+      const uint32_t* p = plane + r * wpr + j0 + jj;
+      const uint32_t c = valid ? p[0] : 0u;
+      if (__ballot_sync(0xffffffffu, c != 0u) != 0u) {
+        uint32_t flags = 0;
+        if (c != 0u) {
+          const uint32_t cl = p[-1], cr = p[1];
+          const uint32_t ul = p[-wpr - 1], um = p[-wpr], ur = p[-wpr + 1];
+          const uint32_t dl = p[wpr - 1], dm = p[wpr], dr = p[wpr + 1];
+          uint32_t n = __vmaxs2(fsr16(cl, c), fsr16(c, cr));
+          n = __vimax3_s16x2(n, __vimax3_s16x2(fsr16(ul, um), um, fsr16(um, ur)),
+                             __vimax3_s16x2(fsr16(dl, dm), dm, fsr16(dm, dr)));
+          flags = (c + 0x7FFF7FFFu - n) & 0x80008000u;  // half of c > half of n (all values in [0, 255])
+        }
+        const bool k_lo = (flags & 0x8000u) != 0u, k_hi = (flags >> 31) != 0u;
+        const uint32_t b_lo = __ballot_sync(0xffffffffu, k_lo), b_hi = __ballot_sync(0xffffffffu, k_hi);
+        int slot = count + __popc(b_lo & lt_mask) + __popc(b_hi & lt_mask);
+        const uint32_t pos = pos_base + ((uint32_t)r << 20) + ((uint32_t)(2 * (j0 + jj)) << 8) + (uint32_t)(th - 1);
+        if (k_lo) list[slot++] = pos + (c & 0xFFFFu);
+        if (k_hi) list[slot] = pos + 256u + (c >> 16);
+        count += __popc(b_lo) + __popc(b_hi);
+      }
+      jj += 32;
+      while (jj >= ipw) { jj -= ipw; r++; }
+    }
+    return count;
   };
-  int count = 0, th_used = 0;
+  int count = 0;
   for (int attempt = 0; attempt < 2 && count == 0; attempt++) {
     if (attempt == 1 && min_th == ini_th) break;  // same threshold, same (empty) answer (reference: SURVEY F3)
-    th_used = min(max(attempt == 0 ? ini_th : min_th, 0), 255);
+    const int th_used = min(max(attempt == 0 ? ini_th : min_th, 0), 255);
     // keyPointsInCell.empty() is judged after NMS (src/orbExtractor.cpp:582)
-    for (int base = 0, w = 0; base < total; base += 32, w++) {
-      int r, c, m;
-      const uint32_t bal = __ballot_sync(0xffffffffu, nms_keep(base + lane, th_used, r, c, m));
-      if (lane == 0) ballots[w] = bal;
-      count += __popc(bal);
+    if (th_used == low_th) {
+      count = nms_pass(score, th_used);
+    } else {
+      // re-threshold into the (no longer needed) tile plane: max(m - th_used, 0) = max(stored - (th_used-low), 0)
+      const uint32_t kd = (uint32_t)(th_used - low_th) * 0x10001u;
+      for (int i = 2 * wpr + lane; i < (th_ - 2) * wpr; i += 32) tile[i] = __vmaxs2(score[i], kd) - kd;
+      __syncwarp();
+      count = nms_pass(tile, th_used);
+      __syncwarp();
     }
   }
   __syncwarp();
@@ -203,20 +287,9 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
     if (lane == 0) { atomicOr(status, kStatusRawOverflow); *out_count = 0; *out_start = 0; }
     return;
   }
-  int pos = start;
-  for (int base = 0, w = 0; base < total; base += 32, w++) {
-    const uint32_t bal = ballots[w];
-    if (bal & (1u << lane)) {
-      const int i = base + lane;
-      const int r = i / iw + 3, c = i - (r - 3) * iw + 3;
-      const int m = score[r * S + c];
-      const int slot = pos + __popc(bal & ((1u << lane) - 1u));
-      // coordinates relative to the 16 px border, as distributeQuadTree sees them (:586-590); 12 bits each
-      raw[(size_t)frame * g->raw_cap + slot] =
-          ((uint32_t)(r + roi.y - kBorder) << 20) | ((uint32_t)(c + roi.x - kBorder) << 8) | (uint32_t)(m - 1);
-    }
-    pos += __popc(bal);
-  }
+  // y:12 | x:12 | response:8, coordinates relative to the 16 px border as distributeQuadTree sees them (:586-590)
+  uint32_t* dst = raw + (size_t)frame * g->raw_cap + start;
+  for (int i = lane; i < count; i += 32) dst[i] = list[i];
   if (lane == 0) { *out_count = count; *out_start = start; }
 }
 
