@@ -73,6 +73,8 @@ struct YdExtractor {
   int max_w, max_h, max_batch;
   cudaStream_t stream;      // stream the stages are enqueued on (own_stream unless the caller set one)
   cudaStream_t own_stream;
+  cudaStream_t aux_stream;  // second stream of the host entry points: chunk i+1's H2D overlaps chunk i's kernels
+  cudaEvent_t ev_fork, ev_join;
   int profiling;            // record per-stage events
   cudaEvent_t ev_ring[64][5];  // per call: pyramid | fast | quadtree | describe boundaries (ring of 64 calls)
   cudaEvent_t* ev;           // slot of the current call

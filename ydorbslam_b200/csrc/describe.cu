@@ -15,13 +15,14 @@
 namespace ydorb {
 
 constexpr int kDescWarps = 4;
-constexpr int kPatchRows = 43;   // y-21 .. y+21  (18 px pattern reach + 3 px blur reach)
-constexpr int kPatchCols = 53;   // x-26 .. x+26  (IC-angle reach 26)
-constexpr int kPatchStride = 56;
-constexpr int kHbCols = 37;      // x-18 .. x+18
-constexpr int kHbStride = 38;
+constexpr int kPatchRows = 43;    // y-21 .. y+21  (18 px pattern reach + 3 px blur reach)
+constexpr int kPatchStride = 64;  // bytes per staged row: 15 aligned words cover x-26-a .. x+26 (IC-angle reach 26)
+constexpr int kPatchWords = 15;
+constexpr int kHbGroups = 11;     // horizontal-blur outputs per row in groups of 4: patch columns 7 .. 50
+constexpr int kHbStride = 4 * kHbGroups;  // u16 per row
+constexpr int kHbCol0 = 7;        // patch column of hb[.][0]
 
-__constant__ int8_t c_pattern[1024] = {
+__constant__ __align__(16) int8_t c_pattern[1024] = {
 #include "brief_pattern.inc"
 };
 
@@ -53,8 +54,11 @@ k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, 
            int32_t* __restrict__ n_out, int* __restrict__ status) {
   __shared__ __align__(16) uint8_t s_patch[kDescWarps][kPatchRows * kPatchStride];
   __shared__ __align__(16) uint16_t s_hb[kDescWarps][kPatchRows * kHbStride];
-  __shared__ int8_t s_pat[1024];
-  for (int i = threadIdx.x; i < 1024; i += blockDim.x) s_pat[i] = c_pattern[i];
+  __shared__ uint32_t s_pat[256];  // [bit b][lane]: the two pattern points (x0,y0,x1,y1 as s8) of bit b of byte `lane`
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+    const int b = i >> 5, l = i & 31;
+    s_pat[i] = reinterpret_cast<const uint32_t*>(c_pattern)[l * 8 + b];
+  }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slot = blockIdx.x * kDescWarps + warp;
@@ -83,17 +87,19 @@ k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, 
   const uint8_t* img = pyr + (size_t)frame * g->pyr_bytes + level_origin(lv);
   uint8_t* patch = s_patch[warp];
   uint16_t* hb = s_hb[warp];
-  // stage the neighbourhood (the 19 px reflect-101 pad makes every read legal: keypoints are >= 19 px from the edge)
+  // stage the neighbourhood with aligned 32-bit loads (the 19 px reflect-101 pad makes every read legal: keypoints
+  // are >= 19 px from the edge and rows are padded to 16 B); pixel (dx, dy) lands at patch[(dy+21)*64 + dx+26+a]
+  const uint8_t* src = img + (ptrdiff_t)(kp.y - 21) * lv.stride + (kp.x - 26);
+  const int a = (int)(reinterpret_cast<uintptr_t>(src) & 3u);
   {
-    const uint8_t* src = img + (ptrdiff_t)(kp.y - 21) * lv.stride + (kp.x - 26);
-    for (int i = lane; i < kPatchRows * kPatchCols; i += 32) {
-      const int r = i / kPatchCols, c = i - r * kPatchCols;
-      patch[r * kPatchStride + c] = src[(ptrdiff_t)r * lv.stride + c];
-    }
+    const uint32_t* src_al = reinterpret_cast<const uint32_t*>(src - a);
+    const int w = lane & 15, stride_w = lv.stride >> 2;
+    for (int r = lane >> 4; r < kPatchRows; r += 2)
+      if (w < kPatchWords) reinterpret_cast<uint32_t*>(patch)[r * (kPatchStride / 4) + w] = __ldg(src_al + (ptrdiff_t)r * stride_w + w);
   }
   __syncwarp();
   // ---- E5 IC angle
-  const uint8_t* ctr = patch + 21 * kPatchStride + 26;
+  const uint8_t* ctr = patch + 21 * kPatchStride + 26 + a;
   int m10 = 0, m01 = 0;
   if (lane < 31) m10 += (lane - 15) * ctr[lane - 15];                       // v = 0 row, u = -15..15  (:404-406)
   if (lane < 10) {                                                          // v = 1..10: half width 0 (F4)
@@ -120,28 +126,35 @@ k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, 
     m01 += __shfl_xor_sync(0xffffffffu, m01, o);
   }
   const float angle = fast_atan2_deg((float)m01, (float)m10);               // :419
-  // ---- E6 horizontal blur pass over rows y-21..y+21, columns x-18..x+18 (exact, <= 65280)
-  for (int i = lane; i < kPatchRows * kHbCols; i += 32) {
-    const int r = i / kHbCols, c = i - r * kHbCols;
-    const uint8_t* p = patch + r * kPatchStride + (c + 26 - 18 - 3);
-    const int acc = 18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3];
-    hb[r * kHbStride + c] = (uint16_t)acc;
+  // ---- E6 horizontal blur pass over rows y-21..y+21 (exact, <= 65280).  A task = 4 adjacent outputs at patch
+  // columns c0..c0+3 with c0 = 7 + 4*grp, i.e. c0-3 word aligned: taps [18 34 48 56 | 48 34 18 0] as two DP4A.
+  for (int t = lane; t < kPatchRows * kHbGroups; t += 32) {
+    const int r = t / kHbGroups, grp = t - r * kHbGroups;
+    const uint32_t* pw = reinterpret_cast<const uint32_t*>(patch) + r * (kPatchStride / 4) + 1 + grp;
+    const uint32_t A = pw[0], B = pw[1], C = pw[2];
+    const uint32_t k_lo = 0x38302212u, k_hi = 0x00122230u;  // (18,34,48,56), (48,34,18,0) little endian
+    const uint32_t o0 = __dp4a(A, k_lo, __dp4a(B, k_hi, 0u));
+    const uint32_t o1 = __dp4a(__funnelshift_r(A, B, 8), k_lo, __dp4a(__funnelshift_r(B, C, 8), k_hi, 0u));
+    const uint32_t o2 = __dp4a(__funnelshift_r(A, B, 16), k_lo, __dp4a(__funnelshift_r(B, C, 16), k_hi, 0u));
+    const uint32_t o3 = __dp4a(__funnelshift_r(A, B, 24), k_lo, __dp4a(__funnelshift_r(B, C, 24), k_hi, 0u));
+    *reinterpret_cast<uint2*>(hb + r * kHbStride + 4 * grp) = make_uint2(o0 | (o1 << 16), o2 | (o3 << 16));
   }
   __syncwarp();
   // ---- E7 rBRIEF
   const float a_rad = __fmul_rn(angle, (float)(3.14159265358979323846 / 180.0));  // :425
   const float cosA = (float)cos((double)a_rad), sinB = (float)sin((double)a_rad);    // :426
+  const uint16_t* hctr = hb + (21 - 3) * kHbStride + (26 + a - kHbCol0);  // hb position of (dx = 0, dy = -3)
   uint32_t byte = 0;
 #pragma unroll
   for (int b = 0; b < 8; b++) {
+    const uint32_t pp = s_pat[b * 32 + lane];
     int val[2];
 #pragma unroll
     for (int e = 0; e < 2; e++) {
-      const int idx = lane * 16 + 2 * b + e;
-      const float px = (float)s_pat[2 * idx], py = (float)s_pat[2 * idx + 1];
+      const float px = (float)(int8_t)(pp >> (16 * e)), py = (float)(int8_t)(pp >> (16 * e + 8));
       const int rr = __float2int_rn(__fadd_rn(__fmul_rn(px, sinB), __fmul_rn(py, cosA)));  // :428
       const int cc = __float2int_rn(__fsub_rn(__fmul_rn(px, cosA), __fmul_rn(py, sinB)));  // :429
-      const uint16_t* h = hb + (rr + 21 - 3) * kHbStride + (cc + 18);
+      const uint16_t* h = hctr + rr * kHbStride + cc;
       const uint32_t acc = 18u * (h[0] + h[6 * kHbStride]) + 34u * (h[kHbStride] + h[5 * kHbStride]) +
                            48u * (h[2 * kHbStride] + h[4 * kHbStride]) + 56u * h[3 * kHbStride];
       val[e] = (int)((acc + 32768u) >> 16);

@@ -196,6 +196,42 @@ static int check_status(YdExtractor* ex) {
   return YDORB_OK;
 }
 
+// A handle whose per-frame buffers start at frame f0 and whose work goes to stream s: lets the stage launchers run
+// on a sub-batch without knowing about it (every kernel indexes its buffers by blockIdx = frame within the launch).
+static YdExtractor frame_view(const YdExtractor* ex, int f0, cudaStream_t s) {
+  YdExtractor v = *ex;
+  const FrameGeomDev& g = ex->geom;
+  v.stream = s;
+  v.d_pyr += (size_t)f0 * g.pyr_bytes;
+  v.d_cell_count += (size_t)f0 * g.n_cells;
+  v.d_cell_start += (size_t)f0 * g.n_cells;
+  v.d_cell_rank += (size_t)f0 * (g.n_cells + 1);
+  v.d_raw += (size_t)f0 * g.raw_cap;
+  v.d_raw_counter += f0;
+  for (int i = 0; i < 3; i++) { v.d_qt_keys[i] += (size_t)f0 * g.raw_cap; v.d_qt_vals[i] += (size_t)f0 * g.raw_cap; }
+  v.d_level_ncand += (size_t)f0 * kMaxLevels;
+  v.d_sel += (size_t)f0 * g.n_quota;
+  v.d_sel_n += (size_t)f0 * kMaxLevels;
+  return v;
+}
+
+// stages of frames [f0, f0+n) on stream s, no profiling events (used by the chunked host entry point)
+static int run_stages(const YdExtractor* ex, int f0, int n, cudaStream_t s, const uint8_t* d_images, int stride,
+                      size_t frame_stride, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity, int32_t* d_nout) {
+  const YdExtractor v = frame_view(ex, f0, s);
+  int rc;
+  if ((rc = launch_pyramid(&v, d_images, stride, frame_stride, n, s)) != YDORB_OK) return rc;
+  if (ex->geom.n_cells == 0 || ex->geom.n_quota == 0) {
+    YD_CUDA(cudaMemsetAsync(d_nout, 0, sizeof(int32_t) * n, s));
+    YD_CUDA(cudaMemsetAsync(v.d_sel_n, 0, sizeof(int) * kMaxLevels * n, s));
+    YD_CUDA(cudaMemsetAsync(v.d_level_ncand, 0, sizeof(int) * kMaxLevels * n, s));
+    return YDORB_OK;
+  }
+  if ((rc = launch_fast(&v, n, s)) != YDORB_OK) return rc;
+  if ((rc = launch_quadtree(&v, n, s)) != YDORB_OK) return rc;
+  return launch_describe(&v, n, d_kps, d_desc, capacity, d_nout, s);
+}
+
 static int run_pipeline(YdExtractor* ex, const uint8_t* d_images, int w, int h, int stride, size_t frame_stride,
                         int batch, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity, int32_t* d_nout) {
   int rc = set_size(ex, w, h);
@@ -271,6 +307,9 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
   const size_t B = (size_t)max_batch;
   cudaError_t e = cudaStreamCreateWithFlags(&ex->own_stream, cudaStreamNonBlocking);
   ex->stream = ex->own_stream;
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->aux_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ex->ev_fork, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ex->ev_join, cudaEventDisableTiming);
   for (int i = 0; i < 64 * 5 && e == cudaSuccess; i++) e = cudaEventCreate(&ex->ev_ring[i / 5][i % 5]);
   ex->ev = ex->ev_ring[0];
   auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, std::max<size_t>(bytes, 16)); };
@@ -318,6 +357,9 @@ void ydorb_extractor_destroy(YdExtractor* ex) {
     if (p) cudaFree(p);
   for (int i = 0; i < 64 * 5; i++)
     if (ex->ev_ring[i / 5][i % 5]) cudaEventDestroy(ex->ev_ring[i / 5][i % 5]);
+  if (ex->ev_fork) cudaEventDestroy(ex->ev_fork);
+  if (ex->ev_join) cudaEventDestroy(ex->ev_join);
+  if (ex->aux_stream) cudaStreamDestroy(ex->aux_stream);
   if (ex->own_stream) cudaStreamDestroy(ex->own_stream);
   delete ex;
 }
@@ -406,15 +448,51 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
   YD_CUDA(cudaSetDevice(ex->device));
   cudaStream_t s = ex->stream;
   const size_t dpitch = (size_t)width;
-  if (stride == width && (batch == 1 || frame_stride == (size_t)width * height)) {
-    YD_CUDA(cudaMemcpyAsync(ex->d_images, images, (size_t)batch * width * height, cudaMemcpyHostToDevice, s));
-  } else
-  for (int b = 0; b < batch; b++)
-    YD_CUDA(cudaMemcpy2DAsync(ex->d_images + (size_t)b * width * height, dpitch, images + (size_t)b * frame_stride,
-                              (size_t)stride, (size_t)width, (size_t)height, cudaMemcpyHostToDevice, s));
   const int dcap = ex->out_cap;
-  int rc = run_pipeline(ex, ex->d_images, width, height, width, (size_t)width * height, batch, ex->d_kps, ex->d_desc,
-                        dcap, ex->d_nout);
+  int rc = set_size(ex, width, height);
+  if (rc != YDORB_OK) return rc;
+  ex->cur_batch = batch;
+  const bool bulk_in = stride == width && (batch == 1 || frame_stride == (size_t)width * height);
+  auto upload = [&](int f0, int n, cudaStream_t st) -> int {
+    if (bulk_in) {
+      YD_CUDA(cudaMemcpyAsync(ex->d_images + (size_t)f0 * width * height, images + (size_t)f0 * width * height,
+                              (size_t)n * width * height, cudaMemcpyHostToDevice, st));
+    } else {
+      for (int b = f0; b < f0 + n; b++)
+        YD_CUDA(cudaMemcpy2DAsync(ex->d_images + (size_t)b * width * height, dpitch, images + (size_t)b * frame_stride,
+                                  (size_t)stride, (size_t)width, (size_t)height, cudaMemcpyHostToDevice, st));
+    }
+    return YDORB_OK;
+  };
+  if (!ex->profiling && capacity == dcap && batch >= 8) {
+    // Chunked: sub-batches alternate between the handle's stream and an internal one, each doing
+    // H2D -> stages -> D2H in order, so one chunk's copies overlap the other chunk's kernels.  Outputs have the
+    // caller's layout (capacity == quota sum), so results are copied back in bulk without knowing the counts.
+    const int chunk = std::max(4, (batch + 7) / 8);
+    YD_CUDA(cudaEventRecord(ex->ev_fork, s));
+    YD_CUDA(cudaStreamWaitEvent(ex->aux_stream, ex->ev_fork, 0));
+    int k = 0;
+    for (int f0 = 0; f0 < batch; f0 += chunk, k++) {
+      const int n = std::min(chunk, batch - f0);
+      cudaStream_t st = (k & 1) ? ex->aux_stream : s;
+      if ((rc = upload(f0, n, st)) != YDORB_OK) return rc;
+      rc = run_stages(ex, f0, n, st, ex->d_images + (size_t)f0 * width * height, width, (size_t)width * height,
+                      ex->d_kps + (size_t)f0 * dcap, ex->d_desc + (size_t)f0 * dcap * 32, dcap, ex->d_nout + f0);
+      if (rc != YDORB_OK) return rc;
+      YD_CUDA(cudaMemcpyAsync(n_out + f0, ex->d_nout + f0, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st));
+      YD_CUDA(cudaMemcpyAsync(keypoints + (size_t)f0 * dcap, ex->d_kps + (size_t)f0 * dcap, sizeof(YdKeyPoint) * (size_t)n * dcap,
+                              cudaMemcpyDeviceToHost, st));
+      YD_CUDA(cudaMemcpyAsync(descriptors + (size_t)f0 * dcap * 32, ex->d_desc + (size_t)f0 * dcap * 32, (size_t)32 * n * dcap,
+                              cudaMemcpyDeviceToHost, st));
+    }
+    YD_CUDA(cudaEventRecord(ex->ev_join, ex->aux_stream));
+    YD_CUDA(cudaStreamWaitEvent(s, ex->ev_join, 0));
+    YD_CUDA(cudaStreamSynchronize(s));
+    return check_status(ex);
+  }
+  if ((rc = upload(0, batch, s)) != YDORB_OK) return rc;
+  rc = run_pipeline(ex, ex->d_images, width, height, width, (size_t)width * height, batch, ex->d_kps, ex->d_desc,
+                    dcap, ex->d_nout);
   if (rc != YDORB_OK) return rc;
   YD_CUDA(cudaMemcpyAsync(n_out, ex->d_nout, sizeof(int32_t) * batch, cudaMemcpyDeviceToHost, s));
   YD_CUDA(cudaStreamSynchronize(s));
