@@ -179,6 +179,76 @@ int ydorb_search_by_projection(YdFrame* f, const YdMapPointProj* map_points, con
                                const uint8_t* mp_obs_positive, int n_map_points, const uint8_t* kp_occupied, float th,
                                float ratio, int32_t* match_out, int32_t* n_matches);
 
+/* ---- Projection searches after M1 ------------------------------------------------------------------------
+ * OrbMatcher::searchByProjectionInLastAndCurrentFrame (src/orbMatcher.cpp:65-155), ...InKeyFrameAndCurrentFrame
+ * (:156-239), searchByProjectionInSim (:240-302), both directions of searchBySim3 (:566-681), and the candidate
+ * search of fuseByProjection (:682-745) / fuseBySim3 (:746-807) share one loop: project, getKeyPointsInArea,
+ * best-1 over the window, threshold, greedy claim, rotation histogram (:120-153, computeThreeMaxima :827-854).
+ * The projection (the reference's own cv::Mat arithmetic, e.g. :84-93) stays in the caller's shim, which fills one
+ * YdWindowQuery per map point; the library runs everything from the getKeyPointsInArea call on. */
+#define YDORB_Q_ACTIVE 1 /* all gates before `!vIndices.empty()` passed (z>=0, isInImage, distance range, normal) */
+#define YDORB_Q_BLOCKS 2 /* a claim by this query blocks later queries (observations>0 in :106-107; always in :194, :284) */
+typedef struct {
+  float x, y;                   /* projection in the searched frame */
+  float r;                      /* radius handed to getKeyPointsInArea */
+  int32_t min_level, max_level; /* level arguments of getKeyPointsInArea, -1 = defaulted */
+  int32_t oct_lo, oct_hi;       /* caller-side gate oct_lo <= octave <= oct_hi (:285-286, :616, :716-717, :782) */
+  float right_x;                /* projected right-image x (stereo gate :108-109, chi2 :715) */
+  float right_r;                /* stereo gate radius; < 0: no stereo gate */
+  float angle;                  /* angle of the source keypoint (rotation histogram, :121, :206) */
+  int32_t flags;                /* YDORB_Q_* */
+} YdWindowQuery;
+
+typedef struct {
+  int32_t max_dist;          /* m_int_highThd / m_int_lowThd / _orbDist */
+  int32_t strict;            /* 1: best < max_dist (:117); 0: best <= max_dist */
+  int32_t exclusive;         /* 1: keypoints held before the call (kp_occupied) or claimed by an earlier blocking query are skipped */
+  int32_t check_orientation; /* m_b_isToCheckOrientation */
+  int32_t chi2_gate;         /* 1: fuseByProjection's 5.99 / 7.81 reprojection gates (:713-719) */
+  float inv_sf2[YDORB_MAX_LEVELS]; /* m_v_invScaleFactorSquares, read by the chi2 gate only */
+} YdWindowParams;
+
+/* best_of[j] (may be NULL) = keypoint chosen by query j or -1.  match_out[i] (may be NULL) = last accepted query that
+ * claimed keypoint i; -1 = untouched; -2 = cleared by the orientation check.  *n_matches = the reference function's
+ * return value.  Host pointers. */
+int ydorb_search_windows(YdFrame* f, const YdWindowQuery* queries, const uint8_t* q_descriptors, int nq,
+                         const YdWindowParams* prm, const uint8_t* kp_occupied, int32_t* best_of, int32_t* match_out,
+                         int32_t* n_matches);
+
+/* ---- BoW matchers ---------------------------------------------------------------------------------------
+ * DBoW3::FeatureVector (std::map<NodeId, std::vector<unsigned>>, thirdParty/DBow3/src/FeatureVector.h:19-21) in CSR
+ * form: node_ids ascending (= std::map order), node_start[n_nodes+1], items in push_back order.  Every feature index
+ * appears in at most one node (DBoW3 assigns each feature to one node at `levelsup`). */
+typedef struct {
+  const int32_t* node_ids;
+  const int32_t* node_start;
+  const int32_t* items;
+  int32_t n_nodes;
+} YdFeatureVector;
+
+/* mode 0: OrbMatcher::searchByBowInKeyFrameAndFrame (src/orbMatcher.cpp:303-379): side 1 = key frame (valid1[i] =
+ *         matched map point present and not bad), side 2 = frame; match_out[n2]: frame index -> key-frame index or -1.
+ * mode 1: OrbMatcher::searchByBowInTwoKeyFrames (:380-462): valid2 required too; match_out[n1]: first -> second or -1.
+ * Host pointers. */
+int ydorb_search_by_bow(YdMatcher* m, const YdKeyPoint* kps1, const uint8_t* desc1, const uint8_t* valid1, int n1,
+                        const YdFeatureVector* fv1, const YdKeyPoint* kps2, const uint8_t* desc2, const uint8_t* valid2,
+                        int n2, const YdFeatureVector* fv2, int mode, float ratio, int check_orientation,
+                        int32_t* match_out, int32_t* n_matches);
+
+/* OrbMatcher::searchForTriangulation (src/orbMatcher.cpp:463-565) with isEpipolarLineDistCorrect (:808-819).
+ * has_mp*[i]: getMapPoint(i) != null.  F: _fMatrix_first2second, row-major 3x3.  epipole: (xCord, yCord) of :469-470.
+ * sf / sf2: second key frame's m_v_scaleFactors / m_v_scaleFactorSquares (n_levels entries).
+ * match_out[n1]: first index -> second index or -1 (the reference emits them as pairs in ascending first index). */
+int ydorb_search_for_triangulation(YdMatcher* m, const YdKeyPoint* kps1, const uint8_t* desc1, const float* right_x1,
+                                   const uint8_t* has_mp1, int n1, const YdFeatureVector* fv1, const YdKeyPoint* kps2,
+                                   const uint8_t* desc2, const float* right_x2, const uint8_t* has_mp2, int n2,
+                                   const YdFeatureVector* fv2, const float* F, float epipole_x, float epipole_y,
+                                   const float* sf, const float* sf2, int n_levels, int stereo_only,
+                                   int check_orientation, int32_t* match_out, int32_t* n_matches);
+
+/* OrbMatcher::computeThreeMaxima (src/orbMatcher.cpp:827-854) on the bin sizes; host helper, no device work. */
+void ydorb_three_maxima(const int32_t* sizes, int len, int32_t* idx1, int32_t* idx2, int32_t* idx3);
+
 /* Frame::computeStereoMatches (src/frame.cpp:362-472) on the pyramids held by two extractor handles
  * (frame index = position in their last batch).  mode 0 = reference (leftIdx lag etc.),
  * 1 = corrected (descriptor row and output slot follow the keypoint).  max_d = bf/baseline (+inf on the

@@ -269,3 +269,100 @@ def stereo_match(p, w, h, pyr_l, pyr_r, kpl, dl, kpr, dr, bf, max_d, mode=0):
         C.c_float(bf), C.c_float(max_d), mode, _p(rx), _p(dp),
     )
     return rx, dp
+
+
+# ---- M2/M3/M4/M7 window searches, M5/M6 BoW matchers -------------------------------------------------------
+WINDOW_QUERY_DTYPE = np.dtype(
+    [("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"), ("oct_lo", "<i4"), ("oct_hi", "<i4"),
+     ("right_x", "<f4"), ("right_r", "<f4"), ("angle", "<f4"), ("flags", "<i4")]
+)
+
+
+class WindowParams(C.Structure):
+    _fields_ = [("max_dist", C.c_int32), ("strict", C.c_int32), ("exclusive", C.c_int32), ("check_orientation", C.c_int32),
+                ("chi2_gate", C.c_int32), ("inv_sf2", C.c_float * 16)]
+
+
+class FeatureVector(C.Structure):
+    _fields_ = [("node_ids", C.c_void_p), ("node_start", C.c_void_p), ("items", C.c_void_p), ("n_nodes", C.c_int32)]
+
+    @classmethod
+    def from_arrays(cls, node_ids, node_start, items):
+        fv = cls()
+        fv._keep = (np.ascontiguousarray(node_ids, np.int32), np.ascontiguousarray(node_start, np.int32),
+                    np.ascontiguousarray(items, np.int32))
+        fv.node_ids, fv.node_start, fv.items = (a.ctypes.data for a in fv._keep)
+        fv.n_nodes = len(fv._keep[0])
+        return fv
+
+
+def _window_params(prm):
+    """Accepts the product's ctypes WindowParams (same layout) or an oracle one."""
+    p = WindowParams()
+    for name, _ in WindowParams._fields_[:5]:
+        setattr(p, name, getattr(prm, name))
+    for i in range(16):
+        p.inv_sf2[i] = prm.inv_sf2[i]
+    return p
+
+
+def search_windows(g, kps, desc, right_x, kp_occupied, queries, q_desc, prm):
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+    desc = np.ascontiguousarray(desc, dtype=np.uint8)
+    right_x = np.ascontiguousarray(right_x, dtype=np.float32)
+    occ = None if kp_occupied is None else np.ascontiguousarray(kp_occupied, dtype=np.uint8)
+    q = np.ascontiguousarray(queries, dtype=WINDOW_QUERY_DTYPE)
+    qd = np.ascontiguousarray(q_desc, dtype=np.uint8)
+    best = np.full(max(len(q), 1), -1, np.int32)
+    match = np.full(max(len(kps), 1), -1, np.int32)
+    p = _window_params(prm)
+    n = lib().orc_search_windows(C.byref(g), _p(kps), _p(desc), _p(right_x), len(kps), _p(occ) if occ is not None else None,
+                                 _p(q), _p(qd), len(q), C.byref(p), _p(best), _p(match))
+    return n, best[: len(q)], match[: len(kps)]
+
+
+def three_maxima(sizes):
+    sz = np.ascontiguousarray(sizes, dtype=np.int32)
+    a, b, c = C.c_int32(), C.c_int32(), C.c_int32()
+    lib().orc_three_maxima(_p(sz), len(sz), C.byref(a), C.byref(b), C.byref(c))
+    return a.value, b.value, c.value
+
+
+def search_by_bow(mode, kps1, desc1, valid1, fv1, kps2, desc2, valid2, fv2, ratio, check_orientation):
+    k1 = np.ascontiguousarray(kps1, dtype=KP_DTYPE)
+    k2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+    d1 = np.ascontiguousarray(desc1, dtype=np.uint8)
+    d2 = np.ascontiguousarray(desc2, dtype=np.uint8)
+    v1 = np.ascontiguousarray(valid1, dtype=np.uint8)
+    v2 = np.ascontiguousarray(valid2 if valid2 is not None else np.ones(len(k2)), dtype=np.uint8)
+    f1, f2 = FeatureVector.from_arrays(*fv1), FeatureVector.from_arrays(*fv2)
+    n_out = len(k2) if mode == 0 else len(k1)
+    out = np.full(max(n_out, 1), -1, np.int32)
+    n = lib().orc_search_by_bow(_p(k1), _p(d1), _p(v1), len(k1), C.byref(f1), _p(k2), _p(d2), _p(v2), len(k2), C.byref(f2),
+                                mode, C.c_float(ratio), int(check_orientation), _p(out))
+    return n, out[:n_out]
+
+
+def search_for_triangulation(kps1, desc1, right_x1, has_mp1, fv1, kps2, desc2, right_x2, has_mp2, fv2, F, epipole, sf, sf2,
+                             stereo_only, check_orientation):
+    k1 = np.ascontiguousarray(kps1, dtype=KP_DTYPE)
+    k2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+    d1 = np.ascontiguousarray(desc1, dtype=np.uint8)
+    d2 = np.ascontiguousarray(desc2, dtype=np.uint8)
+    r1 = np.ascontiguousarray(right_x1, dtype=np.float32)
+    r2 = np.ascontiguousarray(right_x2, dtype=np.float32)
+    h1 = np.ascontiguousarray(has_mp1, dtype=np.uint8)
+    h2 = np.ascontiguousarray(has_mp2, dtype=np.uint8)
+    f1, f2 = FeatureVector.from_arrays(*fv1), FeatureVector.from_arrays(*fv2)
+    Fm = np.ascontiguousarray(F, dtype=np.float32).reshape(9)
+    sfa = np.zeros(16, np.float32)
+    sf2a = np.zeros(16, np.float32)
+    sfa[: len(sf)] = sf
+    sf2a[: len(sf2)] = sf2
+    out = np.full(max(len(k1), 1), -1, np.int32)
+    n = lib().orc_search_for_triangulation(_p(k1), _p(d1), _p(r1), _p(h1), len(k1), C.byref(f1), _p(k2), _p(d2), _p(r2), _p(h2),
+                                           len(k2), C.byref(f2), _p(Fm), C.c_float(epipole[0]), C.c_float(epipole[1]), _p(sfa),
+                                           _p(sf2a), int(stereo_only), int(check_orientation), _p(out))
+    out = out[: len(k1)]
+    first = np.nonzero(out >= 0)[0]
+    return n, np.stack([first, out[first]], axis=1).astype(np.int32)

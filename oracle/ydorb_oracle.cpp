@@ -910,4 +910,239 @@ void orc_stereo_match(const OrcParams* p, int w, int h, const uint8_t* pyr_l, co
   }
 }
 
+
+/* ------------------------------------------------------------------------------------------------
+ * M7  computeThreeMaxima  src/orbMatcher.cpp:827-854
+ * ---------------------------------------------------------------------------------------------- */
+void orc_three_maxima(const int32_t* sizes, int len, int32_t* idx1, int32_t* idx2, int32_t* idx3) {
+  int max1 = 0, max2 = 0, max3 = 0;
+  int i1 = -1, i2 = -1, i3 = -1;  // callers initialise to -1 (:139-141)
+  for (int i = 0; i < len; i++) {
+    const int n = sizes[i];
+    if (n > max1) {
+      max3 = max2; max2 = max1; max1 = n; i3 = i2; i2 = i1; i1 = i;
+    } else if (n > max2) {
+      max3 = max2; max2 = n; i3 = i2; i2 = i;
+    } else if (n > max3) {
+      max3 = n; i3 = i;
+    }
+  }
+  if (max2 < max1 / 10) {  // integer division, as written (:848)
+    i3 = -1; i2 = -1;
+  } else if (max3 < max1 / 10) {
+    i3 = -1;
+  }
+  *idx1 = i1; *idx2 = i2; *idx3 = i3;
+}
+
+}  // extern "C"
+
+namespace {
+const int kHistLen = 30;  // OrbMatcher::m_int_histLen src/orbMatcher.cpp:9
+
+// bin of the rotation histogram (:121-129).  add_is_float: searchForTriangulation adds 360.0f (:521), the others 360.0
+int rotation_bin(float angle_a, float angle_b, bool add_is_float) {
+  const float factor = 1.0 / kHistLen;  // :78 (double 1/30 rounded to float)
+  float rotation = angle_a - angle_b;
+  if (rotation < 0.0) {
+    if (add_is_float) rotation += 360.0f; else rotation += 360.0;
+  }
+  int bin = (int)round(rotation * factor);
+  if (bin == kHistLen) bin = 0;
+  return bin;
+}
+
+struct FvIter {  // DBoW3::FeatureVector::const_iterator over the CSR form
+  const OrcFeatureVector* fv;
+  int pos;
+  bool end() const { return pos >= fv->n_nodes; }
+  int id() const { return fv->node_ids[pos]; }
+  void lower_bound(int id) { pos = (int)(std::lower_bound(fv->node_ids, fv->node_ids + fv->n_nodes, id) - fv->node_ids); }
+};
+}  // namespace
+
+extern "C" {
+
+/* ------------------------------------------------------------------------------------------------
+ * M2 / M3 / M4  window searches  src/orbMatcher.cpp:65-302, :566-807 (see ydorb_oracle.h)
+ * ---------------------------------------------------------------------------------------------- */
+int orc_search_windows(const OrcFrameGeom* g, const OrcKeyPoint* kps, const uint8_t* desc, const float* right_x, int nkp,
+                       const uint8_t* kp_occupied, const OrcWindowQuery* queries, const uint8_t* q_desc, int nq,
+                       const OrcWindowParams* prm, int32_t* best_of, int32_t* match_out) {
+  Grid* grid = new Grid();
+  build_grid(g, kps, nkp, *grid);
+  // slot state: -3 cleared by the orientation check, -2 blocked before the call, -1 untouched, >= 0 last claimant
+  std::vector<int> slot(nkp);
+  for (int i = 0; i < nkp; i++) slot[i] = (kp_occupied && kp_occupied[i]) ? -2 : -1;
+  std::vector<std::vector<int>> hist(kHistLen);
+  int matches = 0;
+  std::vector<int> cands;
+  for (int j = 0; j < nq; j++) {
+    const OrcWindowQuery& q = queries[j];
+    best_of[j] = -1;
+    if (!(q.flags & 1)) continue;
+    keypoints_in_area(g, *grid, kps, q.x, q.y, q.r, q.min_level, q.max_level, cands);
+    if (cands.empty()) continue;  // :102, :190
+    int bestDist = 256, bestIdx = -1;
+    for (int idx : cands) {
+      if (prm->exclusive) {  // :106-107, :194, :284
+        const bool blocked = slot[idx] == -2 || (slot[idx] >= 0 && (queries[slot[idx]].flags & 2));
+        if (blocked) continue;
+      }
+      if (q.right_r >= 0 && !(right_x[idx] <= 0.0 || fabs(q.right_x - right_x[idx]) <= q.right_r)) continue;  // :108-109
+      const int oct = kps[idx].octave;
+      if (oct < q.oct_lo || oct > q.oct_hi) continue;  // :285-286, :616, :716-717, :782
+      if (prm->chi2_gate) {                            // :713-719
+        const float mono = pow(kps[idx].x - q.x, 2.0) + pow(kps[idx].y - q.y, 2.0);
+        const float stereo = mono + pow(right_x[idx] - q.right_x, 2.0);
+        const bool ok = (right_x[idx] >= 0 && stereo * prm->inv_sf2[oct] <= 7.81) ||
+                        (right_x[idx] < 0 && mono * prm->inv_sf2[oct] <= 5.99);
+        if (!ok) continue;
+      }
+      const int d = orc_hamming(q_desc + (size_t)j * 32, desc + (size_t)idx * 32);
+      if (d < bestDist) { bestDist = d; bestIdx = idx; }  // :111-114
+    }
+    const bool accept = prm->strict ? (bestDist < prm->max_dist) : (bestDist <= prm->max_dist);
+    if (!accept || bestIdx < 0) continue;
+    best_of[j] = bestIdx;
+    slot[bestIdx] = j;  // :118 (overwrites a non-blocking earlier claimant)
+    matches++;
+    if (prm->check_orientation) hist[rotation_bin(q.angle, kps[bestIdx].angle, false)].push_back(bestIdx);  // :120-131
+  }
+  if (prm->check_orientation) {  // :138-153
+    int32_t sizes[kHistLen], i1, i2, i3;
+    for (int b = 0; b < kHistLen; b++) sizes[b] = (int32_t)hist[b].size();
+    orc_three_maxima(sizes, kHistLen, &i1, &i2, &i3);
+    for (int b = 0; b < kHistLen; b++)
+      if (b != i1 && b != i2 && b != i3)
+        for (int idx : hist[b]) { slot[idx] = -3; matches--; }
+  }
+  for (int i = 0; i < nkp; i++) match_out[i] = slot[i] >= 0 ? slot[i] : (slot[i] == -3 ? -2 : -1);
+  delete grid;
+  return matches;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * M5  searchByBowInKeyFrameAndFrame :303-379 (mode 0), searchByBowInTwoKeyFrames :380-462 (mode 1)
+ * ---------------------------------------------------------------------------------------------- */
+int orc_search_by_bow(const OrcKeyPoint* kps1, const uint8_t* desc1, const uint8_t* valid1, int n1,
+                      const OrcFeatureVector* fv1, const OrcKeyPoint* kps2, const uint8_t* desc2, const uint8_t* valid2,
+                      int n2, const OrcFeatureVector* fv2, int mode, float ratio, int check_orientation,
+                      int32_t* match_out) {
+  const int n_out = mode == 0 ? n2 : n1;
+  for (int i = 0; i < n_out; i++) match_out[i] = -1;  // :305, :385
+  std::vector<char> matched2(n2, 0);                   // mode 0: _vSptrMatchedMapPoints[frameIdx] != null; mode 1: :386
+  std::vector<std::vector<int>> hist(kHistLen);
+  int matches = 0;
+  FvIter it1{fv1, 0}, it2{fv2, 0};
+  while (!it1.end() && !it2.end()) {  // :317, :397
+    if (it1.id() == it2.id()) {
+      for (int a = fv1->node_start[it1.pos]; a < fv1->node_start[it1.pos + 1]; a++) {
+        const int i1 = fv1->items[a];
+        if (!valid1[i1]) continue;  // :320, :400
+        int bestDist = 256, secondDist = 256, bestIdx = -1;
+        for (int b = fv2->node_start[it2.pos]; b < fv2->node_start[it2.pos + 1]; b++) {
+          const int i2 = fv2->items[b];
+          if (matched2[i2]) continue;                       // :325, :405
+          if (mode == 1 && !valid2[i2]) continue;           // :406-407
+          const int d = orc_hamming(desc1 + (size_t)i1 * 32, desc2 + (size_t)i2 * 32);
+          if (d < bestDist) { secondDist = bestDist; bestDist = d; bestIdx = i2; }
+          else if (d < secondDist) { secondDist = d; }
+        }
+        if (bestDist <= 50 && static_cast<float>(bestDist) < ratio * static_cast<float>(secondDist)) {  // :336, :418
+          matched2[bestIdx] = 1;
+          const int out_idx = mode == 0 ? bestIdx : i1;
+          match_out[out_idx] = mode == 0 ? i1 : bestIdx;  // :337, :419
+          if (check_orientation) hist[rotation_bin(kps1[i1].angle, kps2[bestIdx].angle, false)].push_back(out_idx);
+          matches++;
+        }
+      }
+      it1.pos++; it2.pos++;
+    } else if (it1.id() < it2.id()) {
+      it1.lower_bound(it2.id());  // :357
+    } else {
+      it2.lower_bound(it1.id());  // :359
+    }
+  }
+  if (check_orientation) {  // :362-377
+    int32_t sizes[kHistLen], i1, i2, i3;
+    for (int b = 0; b < kHistLen; b++) sizes[b] = (int32_t)hist[b].size();
+    orc_three_maxima(sizes, kHistLen, &i1, &i2, &i3);
+    for (int b = 0; b < kHistLen; b++)
+      if (b != i1 && b != i2 && b != i3)
+        for (int idx : hist[b]) { match_out[idx] = -1; matches--; }
+  }
+  return matches;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * M6  searchForTriangulation :463-565, isEpipolarLineDistCorrect :808-819
+ * ---------------------------------------------------------------------------------------------- */
+static bool epipolar_ok(const OrcKeyPoint& k1, const OrcKeyPoint& k2, const float* F, const float* sf2) {
+  const float a = F[0] * k1.x + F[3] * k1.y + F[6];  // :810 (column 0 of F: at(0,0), at(1,0), at(2,0))
+  const float b = F[1] * k1.x + F[4] * k1.y + F[7];  // :811
+  const float c = F[2] * k1.x + F[5] * k1.y + F[8];  // :812
+  if ((a * a + b * b) > 0) {
+    return ((((a * k2.x + b * k2.y + c) * (a * k2.x + b * k2.y + c)) / ((a * a + b * b) * (a * a + b * b))) <
+            (3.841 * sf2[k2.octave]));  // :814-815 (squared denominator, as written)
+  }
+  return false;
+}
+
+int orc_search_for_triangulation(const OrcKeyPoint* kps1, const uint8_t* desc1, const float* right_x1,
+                                 const uint8_t* has_mp1, int n1, const OrcFeatureVector* fv1, const OrcKeyPoint* kps2,
+                                 const uint8_t* desc2, const float* right_x2, const uint8_t* has_mp2, int n2,
+                                 const OrcFeatureVector* fv2, const float* F, float epipole_x, float epipole_y,
+                                 const float* sf, const float* sf2, int stereo_only, int check_orientation,
+                                 int32_t* match_out) {
+  const float xCord = epipole_x, yCord = epipole_y;  // :469-470
+  for (int i = 0; i < n1; i++) match_out[i] = -1;    // :476
+  std::vector<char> matched2(n2, 0);                 // :475
+  std::vector<std::vector<int>> hist(kHistLen);
+  int matches = 0;
+  FvIter it1{fv1, 0}, it2{fv2, 0};
+  while (!it1.end() && !it2.end()) {
+    if (it1.id() == it2.id()) {
+      for (int a = fv1->node_start[it1.pos]; a < fv1->node_start[it1.pos + 1]; a++) {
+        const int i1 = fv1->items[a];
+        const bool stereo1 = right_x1[i1] >= 0;  // :489
+        if (has_mp1[i1] || (stereo_only && !stereo1)) continue;  // :491
+        int bestDist = 50, bestIdx = -1;  // :493-494
+        for (int b = fv2->node_start[it2.pos]; b < fv2->node_start[it2.pos + 1]; b++) {
+          const int i2 = fv2->items[b];
+          const bool stereo2 = right_x2[i2] >= 0;  // :496
+          if (matched2[i2] || has_mp2[i2] || (stereo_only && !stereo2)) continue;  // :497-499
+          const int d = orc_hamming(desc1 + (size_t)i1 * 32, desc2 + (size_t)i2 * 32);
+          if (d <= 50 && d <= bestDist &&
+              (stereo1 || stereo2 ||
+               pow((float)xCord - (float)(kps2[i2].x), 2.0) + pow((float)yCord - (float)(kps2[i2].y), 2.0) >=
+                   100 * sf[kps2[i2].octave])) {  // :502-505
+            if (epipolar_ok(kps1[i1], kps2[i2], F, sf2)) { bestIdx = i2; bestDist = d; }  // :506-509
+          }
+        }
+        if (bestIdx >= 0) {  // :513-527
+          matched2[bestIdx] = 1;
+          match_out[i1] = bestIdx;
+          matches++;
+          if (check_orientation) hist[rotation_bin(kps1[i1].angle, kps2[bestIdx].angle, true)].push_back(i1);
+        }
+      }
+      it1.pos++; it2.pos++;
+    } else if (it1.id() < it2.id()) {
+      it1.lower_bound(it2.id());
+    } else {
+      it2.lower_bound(it1.id());
+    }
+  }
+  if (check_orientation) {  // :539-554
+    int32_t sizes[kHistLen], i1, i2, i3;
+    for (int b = 0; b < kHistLen; b++) sizes[b] = (int32_t)hist[b].size();
+    orc_three_maxima(sizes, kHistLen, &i1, &i2, &i3);
+    for (int b = 0; b < kHistLen; b++)
+      if (b != i1 && b != i2 && b != i3)
+        for (int idx : hist[b]) { match_out[idx] = -1; matches--; }
+  }
+  return matches;
+}
+
 }  // extern "C"

@@ -15,6 +15,37 @@ TOP2_DTYPE = np.dtype([("best_idx", "<i4"), ("best_dist", "<i4"), ("second_dist"
 MPPROJ_DTYPE = np.dtype(
     [("proj_x", "<f4"), ("proj_y", "<f4"), ("proj_right_x", "<f4"), ("view_cos", "<f4"), ("level", "<i4"), ("active", "<i4")]
 )
+WINDOW_QUERY_DTYPE = np.dtype(
+    [("x", "<f4"), ("y", "<f4"), ("r", "<f4"), ("min_level", "<i4"), ("max_level", "<i4"), ("oct_lo", "<i4"), ("oct_hi", "<i4"),
+     ("right_x", "<f4"), ("right_r", "<f4"), ("angle", "<f4"), ("flags", "<i4")]
+)
+Q_ACTIVE, Q_BLOCKS = 1, 2
+
+
+class WindowParams(C.Structure):
+    _fields_ = [
+        ("max_dist", C.c_int32),
+        ("strict", C.c_int32),
+        ("exclusive", C.c_int32),
+        ("check_orientation", C.c_int32),
+        ("chi2_gate", C.c_int32),
+        ("inv_sf2", C.c_float * MAX_LEVELS),
+    ]
+
+
+class FeatureVector(C.Structure):
+    """DBoW3::FeatureVector in CSR form (include/ydorb.h YdFeatureVector)."""
+
+    _fields_ = [("node_ids", C.c_void_p), ("node_start", C.c_void_p), ("items", C.c_void_p), ("n_nodes", C.c_int32)]
+
+    @classmethod
+    def from_arrays(cls, node_ids, node_start, items):
+        fv = cls()
+        fv._keep = (np.ascontiguousarray(node_ids, np.int32), np.ascontiguousarray(node_start, np.int32),
+                    np.ascontiguousarray(items, np.int32))
+        fv.node_ids, fv.node_start, fv.items = (a.ctypes.data for a in fv._keep)
+        fv.n_nodes = len(fv._keep[0])
+        return fv
 
 
 class ExtractorParams(C.Structure):
@@ -61,7 +92,7 @@ def lib():
         _lib.ydorb_extractor_stream.restype = C.c_void_p
         _lib.ydorb_matcher_stream.restype = C.c_void_p
         _lib.ydorb_kernel_launches.restype = C.c_longlong
-        for name in ("ydorb_extractor_destroy", "ydorb_matcher_destroy", "ydorb_frame_destroy"):
+        for name in ("ydorb_extractor_destroy", "ydorb_matcher_destroy", "ydorb_frame_destroy", "ydorb_three_maxima"):
             getattr(_lib, name).restype = None
     return _lib
 

@@ -6,7 +6,8 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from ._lib import KP_DTYPE, MPPROJ_DTYPE, TOP2_DTYPE, check, lib, ptr
+from . import queries as Q
+from ._lib import KP_DTYPE, MPPROJ_DTYPE, TOP2_DTYPE, WINDOW_QUERY_DTYPE, FeatureVector, check, lib, ptr
 
 HIGH_THD = 100  # OrbMatcher::m_int_highThd  src/orbMatcher.cpp:7
 LOW_THD = 50    # OrbMatcher::m_int_lowThd   src/orbMatcher.cpp:8
@@ -145,6 +146,125 @@ class OrbMatcher:
         check(lib().ydorb_search_by_projection(frame._h, ptr(mps), ptr(md), ptr(obs), len(mps), ptr(occ), C.c_float(thd),
                                                C.c_float(self.ratio), ptr(out), C.byref(n)))
         return n.value, out[: frame.n]
+
+    # ---- M2/M3/M4: everything after the projection (include/ydorb.h ydorb_search_windows)
+    def searchWindows(self, frame, queries, q_descriptors, params, kp_occupied=None):
+        """Returns (n_matches, best_of[nq], match_of_keypoint[n_kp]); match codes: >=0 query, -1 untouched, -2 cleared."""
+        q = np.ascontiguousarray(queries, dtype=WINDOW_QUERY_DTYPE)
+        qd = np.ascontiguousarray(q_descriptors, dtype=np.uint8).reshape(-1, 32)
+        assert len(qd) == len(q)
+        occ = None if kp_occupied is None else np.ascontiguousarray(kp_occupied, dtype=np.uint8)
+        best = np.full(max(len(q), 1), -1, np.int32)
+        match = np.full(max(frame.n, 1), -1, np.int32)
+        n = C.c_int32()
+        check(lib().ydorb_search_windows(frame._h, ptr(q), ptr(qd), len(q), C.byref(params), ptr(occ), ptr(best), ptr(match),
+                                         C.byref(n)))
+        return n.value, best[: len(q)], match[: frame.n]
+
+    def searchByProjectionInLastAndCurrentFrame(self, cur_frame, proj_x, proj_y, proj_right_x, octave, angle, active,
+                                                obs_positive, q_descriptors, scale_factors, thd, motion="none",
+                                                kp_occupied=None):
+        """src/orbMatcher.cpp:65-155.  kp_occupied[i]: the current frame's slot i holds a map point with observations>0."""
+        q, prm = Q.last_and_current_frame(proj_x, proj_y, proj_right_x, octave, angle, active, obs_positive, scale_factors,
+                                          thd, motion, self.check_orientation)
+        n, _, match = self.searchWindows(cur_frame, q, q_descriptors, prm, kp_occupied)
+        return n, match
+
+    def searchByProjectionInKeyFrameAndCurrentFrame(self, cur_frame, proj_x, proj_y, predicted_level, angle, active,
+                                                    q_descriptors, scale_factors, thd, orb_dist, kp_occupied=None):
+        """src/orbMatcher.cpp:156-239.  kp_occupied[i]: the current frame's slot i is non-null."""
+        q, prm = Q.keyframe_and_current_frame(proj_x, proj_y, predicted_level, angle, active, scale_factors, thd, orb_dist,
+                                              self.check_orientation)
+        n, _, match = self.searchWindows(cur_frame, q, q_descriptors, prm, kp_occupied)
+        return n, match
+
+    def searchByProjectionInSim(self, kf_frame, proj_x, proj_y, predicted_level, active, q_descriptors, scale_factors, thd,
+                                matched=None):
+        """src/orbMatcher.cpp:240-302.  matched[i]: _vSptrMatchedMapPoints[i] non-null on entry."""
+        q, prm = Q.in_sim(proj_x, proj_y, predicted_level, active, scale_factors, thd)
+        n, _, match = self.searchWindows(kf_frame, q, q_descriptors, prm, matched)
+        return n, match
+
+    def searchBySim3(self, first_frame, second_frame, first_to_second, second_to_first, scale_factors, thd):
+        """src/orbMatcher.cpp:566-681.  first_to_second = (proj_x, proj_y, predicted_level, active, descriptors) of the
+        first key frame's map points projected into the second (active already excludes :583-590's matched points), and
+        vice versa.  Returns (foundNum, second index per first index or -1)."""
+        q12, p12 = Q.sim3_direction(*first_to_second[:4], scale_factors, thd)
+        q21, p21 = Q.sim3_direction(*second_to_first[:4], scale_factors, thd)
+        _, best12, _ = self.searchWindows(second_frame, q12, first_to_second[4], p12)
+        _, best21, _ = self.searchWindows(first_frame, q21, second_to_first[4], p21)
+        return Q.sim3_agreement(best12, best21)
+
+    def fuseByProjectionCandidates(self, kf_frame, proj_x, proj_y, proj_right_x, predicted_level, active, q_descriptors,
+                                   scale_factors, inv_sf2, thd):
+        """Candidate search of fuseByProjection (src/orbMatcher.cpp:682-727): best key point per map point or -1."""
+        q, prm = Q.fuse_by_projection(proj_x, proj_y, proj_right_x, predicted_level, active, scale_factors, inv_sf2, thd)
+        n, best, _ = self.searchWindows(kf_frame, q, q_descriptors, prm)
+        return n, best
+
+    def fuseBySim3Candidates(self, kf_frame, proj_x, proj_y, predicted_level, active, q_descriptors, scale_factors, thd):
+        """Candidate search of fuseBySim3 (src/orbMatcher.cpp:746-790)."""
+        q, prm = Q.fuse_by_sim3(proj_x, proj_y, predicted_level, active, scale_factors, thd)
+        n, best, _ = self.searchWindows(kf_frame, q, q_descriptors, prm)
+        return n, best
+
+    # ---- M5 BoW matchers (src/orbMatcher.cpp:303-462); feature vectors as (node_ids, node_start, items) CSR triples
+    def _bow(self, mode, kps1, desc1, valid1, fv1, kps2, desc2, valid2, fv2):
+        k1 = np.ascontiguousarray(kps1, dtype=KP_DTYPE)
+        k2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+        d1 = np.ascontiguousarray(desc1, dtype=np.uint8).reshape(-1, 32)
+        d2 = np.ascontiguousarray(desc2, dtype=np.uint8).reshape(-1, 32)
+        v1 = np.ascontiguousarray(valid1, dtype=np.uint8)
+        v2 = None if valid2 is None else np.ascontiguousarray(valid2, dtype=np.uint8)
+        f1, f2 = FeatureVector.from_arrays(*fv1), FeatureVector.from_arrays(*fv2)
+        out = np.full(max(len(k2) if mode == 0 else len(k1), 1), -1, np.int32)
+        n = C.c_int32()
+        check(lib().ydorb_search_by_bow(self._h, ptr(k1), ptr(d1), ptr(v1), len(k1), C.byref(f1), ptr(k2), ptr(d2), ptr(v2),
+                                        len(k2), C.byref(f2), mode, C.c_float(self.ratio), int(self.check_orientation),
+                                        ptr(out), C.byref(n)))
+        return n.value, out[: (len(k2) if mode == 0 else len(k1))]
+
+    def searchByBowInKeyFrameAndFrame(self, kf_kps, kf_desc, kf_valid, kf_fv, fr_kps, fr_desc, fr_fv):
+        """src/orbMatcher.cpp:303-379: returns (matchNum, key-frame index per frame key point or -1)."""
+        return self._bow(0, kf_kps, kf_desc, kf_valid, kf_fv, fr_kps, fr_desc, None, fr_fv)
+
+    def searchByBowInTwoKeyFrames(self, kps1, desc1, valid1, fv1, kps2, desc2, valid2, fv2):
+        """src/orbMatcher.cpp:380-462: returns (matchNum, second index per first key point or -1)."""
+        return self._bow(1, kps1, desc1, valid1, fv1, kps2, desc2, valid2, fv2)
+
+    # ---- M6 searchForTriangulation (src/orbMatcher.cpp:463-565)
+    def searchForTriangulation(self, kps1, desc1, right_x1, has_mp1, fv1, kps2, desc2, right_x2, has_mp2, fv2, F, epipole,
+                               scale_factors, scale_factor_squares, stereo_only=False):
+        """Returns (matchNum, pairs[k, 2]) with pairs in ascending first index as :555-563 emits them."""
+        k1 = np.ascontiguousarray(kps1, dtype=KP_DTYPE)
+        k2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+        d1 = np.ascontiguousarray(desc1, dtype=np.uint8).reshape(-1, 32)
+        d2 = np.ascontiguousarray(desc2, dtype=np.uint8).reshape(-1, 32)
+        r1 = np.ascontiguousarray(right_x1, dtype=np.float32)
+        r2 = np.ascontiguousarray(right_x2, dtype=np.float32)
+        h1 = np.ascontiguousarray(has_mp1, dtype=np.uint8)
+        h2 = np.ascontiguousarray(has_mp2, dtype=np.uint8)
+        f1, f2 = FeatureVector.from_arrays(*fv1), FeatureVector.from_arrays(*fv2)
+        Fm = np.ascontiguousarray(F, dtype=np.float32).reshape(9)
+        sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+        sf2 = np.ascontiguousarray(scale_factor_squares, dtype=np.float32)
+        out = np.full(max(len(k1), 1), -1, np.int32)
+        n = C.c_int32()
+        check(lib().ydorb_search_for_triangulation(self._h, ptr(k1), ptr(d1), ptr(r1), ptr(h1), len(k1), C.byref(f1), ptr(k2),
+                                                   ptr(d2), ptr(r2), ptr(h2), len(k2), C.byref(f2), ptr(Fm),
+                                                   C.c_float(epipole[0]), C.c_float(epipole[1]), ptr(sf), ptr(sf2), len(sf),
+                                                   int(stereo_only), int(self.check_orientation), ptr(out), C.byref(n)))
+        out = out[: len(k1)]
+        first = np.nonzero(out >= 0)[0]
+        return n.value, np.stack([first, out[first]], axis=1).astype(np.int32)
+
+    @staticmethod
+    def computeThreeMaxima(sizes):
+        """src/orbMatcher.cpp:827-854 on the histogram bin sizes."""
+        sz = np.ascontiguousarray(sizes, dtype=np.int32)
+        a, b, c = C.c_int32(), C.c_int32(), C.c_int32()
+        lib().ydorb_three_maxima(ptr(sz), len(sz), C.byref(a), C.byref(b), C.byref(c))
+        return a.value, b.value, c.value
 
     # ---- S1 Frame::computeStereoMatches (src/frame.cpp:362-472)
     def computeStereoMatches(self, left_ex, left_frame, right_ex, right_frame, kp_left, desc_left, kp_right, desc_right, bf,

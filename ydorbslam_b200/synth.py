@@ -142,5 +142,38 @@ def synth_map_points(kps, desc, n_mp, w, h, n_levels, seed):
     obs_pos = ((r2[1::2] % np.uint64(8)) != 0).astype(np.uint8)  # 1/8 have no observations yet
     return dict(
         proj_x=px, proj_y=py, proj_right_x=(px - 10.0).astype(np.float32), view_cos=vc, level=level, active=active,
-        desc=np.ascontiguousarray(d), obs_positive=obs_pos,
+        desc=np.ascontiguousarray(d), obs_positive=obs_pos, src=src,
     )
+
+
+def synth_source_angles(kps, src, seed):
+    """Angles of the source key points behind projected map points: mostly the matched key point's angle plus a small
+    rotation (one dominant histogram bin), some with an arbitrary rotation (the bins the orientation check clears)."""
+    n = len(src)
+    r = rand_u64(seed, 11, n * 2)
+    small = ((r[0::2] >> np.uint64(11)).astype(np.float64) / float(1 << 53) - 0.5) * 40.0
+    big = (r[1::2] >> np.uint64(11)).astype(np.float64) / float(1 << 53) * 360.0
+    base = kps["angle"][src].astype(np.float64) if len(kps) else np.zeros(n)
+    rot = np.where((r[0::2] % np.uint64(5)) == 0, big, small)
+    return np.mod(base + rot, 360.0).astype(np.float32)
+
+
+def synth_feature_vector(desc, seed, bits=6, drop_every=5):
+    """A DBoW3-like FeatureVector for `desc` without a vocabulary: node id = hash of the descriptor's first `bits` bits
+    (so perturbed copies of a descriptor mostly land in the same node), ids sparse and ascending, features in
+    ascending index inside a node (DBoW3 transform pushes them in feature order); every `drop_every`-th node of the
+    id space (chosen by seed) is absent so the two sides of a match have unshared nodes (lower_bound path).
+
+    Returns (node_ids, node_start, items) int32 arrays."""
+    n = len(desc)
+    word = desc[:, 0].astype(np.int64) & ((1 << bits) - 1)
+    node = word * 7 + 3
+    keep = (word + seed) % drop_every != 0
+    ids = np.unique(node[keep]) if n else np.zeros(0, np.int64)
+    start = [0]
+    items = []
+    for i in ids:
+        members = np.nonzero(keep & (node == i))[0]
+        items.extend(members.tolist())
+        start.append(len(items))
+    return ids.astype(np.int32), np.asarray(start, np.int32), np.asarray(items, np.int32)
