@@ -322,18 +322,32 @@ def run_gpu(args):
                "int_ops_per_pair": {"xor": 8, "popc": 8, "iadd": 8}}
         m.set_stream(None)
 
-    # ---- CPU baseline beside it (rank 0, N=1 only): oracle port on the host cores, bounded sample
+    # ---- integer-pipe peaks measured live on this device (tools/int_peaks.py, csrc/diag.cu): roofline denominators
+    # of the kernels that are issue-bound rather than HBM-bound (DESIGN.md "Integer roofline")
+    int_peaks = None
+    if rank == 0:
+        import ctypes as C2
+
+        rates = (C2.c_double * 5)()
+        check(lib().ydorb_diag_int_peaks(local, rates, 5))
+        int_peaks = dict(zip(["popc", "lop3", "vimnmx3_s16x2", "imad", "lop3_imad_mix"], [r / 1e9 for r in rates]))
+
+    # ---- CPU baseline beside it (rank 0, N=1 only): oracle port on the host cores, bounded sample of ~12 s
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         probe = frames[: min(threads, B)]
         tp = cpu_extract_match(probe, threads)
         per_frame = tp / len(probe)
-        sample = int(min(B, max(len(probe), 15.0 / max(per_frame, 1e-6))))
-        ts = cpu_extract_match(frames[:sample], threads)
-        cpu = {"value": sample / ts, "unit": "frames/s", "cores": threads, "kind": "port",
-               "sample": f"first {sample} frames of the batch, extract + match vs previous frame, oracle/ydorb_oracle.cpp with "
-                         f"{threads} threads, {ts:.1f} s"}
+        want = max(len(probe), int(12.0 / max(per_frame, 1e-6)))
+        done, ts = 0, 0.0
+        while done < want and ts < 30.0:
+            chunk = frames[: min(B, want - done)]
+            ts += cpu_extract_match(chunk, threads)
+            done += len(chunk)
+        cpu = {"value": done / ts, "unit": "frames/s", "cores": threads, "kind": "port",
+               "sample": f"{done} frames (the batch's frames, repeated) extract + match vs previous frame, "
+                         f"oracle/ydorb_oracle.cpp with {threads} threads, {ts:.1f} s"}
 
     if rank == 0:
         peak, peak_kind = measured_peak()
@@ -363,8 +377,25 @@ def run_gpu(args):
             "roofline_step": {"algorithmic_bytes_per_frame": ab["total"], "achieved": step_gbs, "peak": peak, "unit": "GB/s",
                               "frac": step_gbs / peak},
             "keypoints_per_frame": float(n_kp.mean()), "accepted_matches_per_frame": n_acc / B,
-            "hamming": ham, "cpu_baseline": cpu,
+            "hamming": ham, "cpu_baseline": cpu, "int_peaks_gops": int_peaks,
         }
+        if ham and int_peaks:
+            # 8 POPC per descriptor pair; the POPC pipe issues 16 thread-ops/clk/SM
+            ham["int_roofline"] = {"bound": "popc pipe", "achieved": ham["value"] * 8, "peak": int_peaks["popc"],
+                                   "unit": "G POPC/s", "frac": ham["value"] * 8 / int_peaks["popc"]}
+        if int_peaks:
+            pairs = float(n_kp.astype(np.float64).dot(np.roll(n_kp, 1).astype(np.float64)))  # frame b vs frame b-1
+            line["int_roofline"] = {"kernel": "k_top2_frames", "bound": "popc pipe", "achieved": pairs * 8 / (match_ms * 1e-3) / 1e9,
+                                    "peak": int_peaks["popc"], "unit": "G POPC/s",
+                                    "frac": pairs * 8 / (match_ms * 1e-3) / 1e9 / int_peaks["popc"]}
+        traffic_path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if os.path.exists(traffic_path):
+            # dram__bytes_read.sum + dram__bytes_write.sum per frame of each stage kernel, from the committed
+            # `ncu --set full` capture (profiles/): scaled to this launch's batch
+            tr = json.load(open(traffic_path))
+            if names[dom] in tr.get("bytes_per_frame", {}):
+                line["roofline"]["traffic"] = tr["bytes_per_frame"][names[dom]] * B
+                line["roofline"]["traffic_source"] = tr.get("source")
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
