@@ -10,6 +10,7 @@
 // The database is split into chunks across blockIdx.y so the grid fills 148 SMs; per-chunk top-2 pairs are merged
 // by a second kernel with the same order-free rule, which is also the cross-GPU shard merge.
 #include <algorithm>
+#include <cstdlib>
 
 #include "matcher.cuh"
 
@@ -20,6 +21,42 @@ constexpr int kTopQpt = 4;                          // queries per thread
 constexpr int kTopQblock = kTopThreads * kTopQpt;   // queries per CTA
 constexpr int kTopTile = 256;                       // database rows per shared-memory tile
 constexpr uint32_t kNoKey = 0xFFFFFFFFu;
+#ifndef YD_TOP_CTAS_PER_SM
+#define YD_TOP_CTAS_PER_SM 6
+#endif
+constexpr int kTopCtasPerSm = YD_TOP_CTAS_PER_SM;   // 6 x 4 warps per SM hide the POPC (XU) latency
+
+// 256-bit Hamming distance with a carry-save adder tree: the 8 XOR words are compressed by four 3:2 compressors
+// (sum = a^b^c, carry = maj(a,b,c), one LOP3 each) into words of weight 1,1,2,4, so a pair costs 4 POPC (XU pipe,
+// 16 thread-ops/clk/SM) + 16 LOP3 (ALU pipe, 64/clk/SM) instead of 8 POPC + 8 LOP3.  Same integer result as
+// src/orbMatcher.cpp:11-23.
+__device__ __forceinline__ uint32_t csa_sum(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;  // inline PTX keeps the compiler from re-associating the XOR tree into more, narrower LOP3s
+  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+__device__ __forceinline__ uint32_t csa_carry(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+  return r;
+}
+// returns distance << 23, ready to be added to a row index below 2^23
+__device__ __forceinline__ uint32_t ham256_key(const uint32_t (&q)[8], const uint4& lo, const uint4& hi, uint32_t row) {
+  const uint32_t x0 = q[0] ^ lo.x, x1 = q[1] ^ lo.y, x2 = q[2] ^ lo.z, x3 = q[3] ^ lo.w;
+  const uint32_t x4 = q[4] ^ hi.x, x5 = q[5] ^ hi.y, x6 = q[6] ^ hi.z, x7 = q[7] ^ hi.w;
+  const uint32_t sA = csa_sum(x0, x1, x2), cA = csa_carry(x0, x1, x2);
+  const uint32_t sB = csa_sum(x3, x4, x5), cB = csa_carry(x3, x4, x5);
+  const uint32_t sC = csa_sum(sA, sB, x6), cC = csa_carry(sA, sB, x6);
+  const uint32_t sD = csa_sum(cA, cB, cC), cD = csa_carry(cA, cB, cC);
+  // weights 1,1,2,4 folded with the << 23 into multiply-adds (FMA pipe, off the ALU pipe the LOP3s use)
+  uint32_t d = __popc(sC) + __popc(x7);
+  d = __popc(sD) * 2u + d;
+  d = __popc(cD) * 4u + d;
+  return d * 0x800000u + row;
+}
+__device__ __forceinline__ uint32_t ham256(const uint32_t (&q)[8], const uint4& lo, const uint4& hi) {
+  return ham256_key(q, lo, hi, 0) >> 23;
+}
 
 __global__ void k_hamming_pairs(const uint4* __restrict__ a, const uint4* __restrict__ b, int n, int32_t* __restrict__ dist) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -61,10 +98,7 @@ k_top2_chunks(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db,
       const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1];
 #pragma unroll
       for (int k = 0; k < kTopQpt; k++) {
-        const int d = __popc(qa[k][0] ^ lo.x) + __popc(qa[k][1] ^ lo.y) + __popc(qa[k][2] ^ lo.z) +
-                      __popc(qa[k][3] ^ lo.w) + __popc(qa[k][4] ^ hi.x) + __popc(qa[k][5] ^ hi.y) +
-                      __popc(qa[k][6] ^ hi.z) + __popc(qa[k][7] ^ hi.w);
-        const uint32_t key = ((uint32_t)d << 23) | (local0 + (uint32_t)r);
+        const uint32_t key = ham256_key(qa[k], lo, hi, local0 + (uint32_t)r);
         second[k] = min(second[k], max(best[k], key));
         best[k] = min(best[k], key);
       }
@@ -165,10 +199,7 @@ k_top2_frames(const uint4* __restrict__ desc, const int32_t* __restrict__ n_of, 
       const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1];
 #pragma unroll
       for (int k = 0; k < kTopQpt; k++) {
-        const int d = __popc(qa[k][0] ^ lo.x) + __popc(qa[k][1] ^ lo.y) + __popc(qa[k][2] ^ lo.z) +
-                      __popc(qa[k][3] ^ lo.w) + __popc(qa[k][4] ^ hi.x) + __popc(qa[k][5] ^ hi.y) +
-                      __popc(qa[k][6] ^ hi.z) + __popc(qa[k][7] ^ hi.w);
-        const uint32_t key = ((uint32_t)d << 23) | (uint32_t)(t0 + r);
+        const uint32_t key = ham256_key(qa[k], lo, hi, (uint32_t)(t0 + r));
         second[k] = min(second[k], max(best[k], key));
         best[k] = min(best[k], key);
       }
@@ -234,6 +265,8 @@ int ydorb_matcher_create(int device, YdMatcher** out) {
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, device);
   m->sm_count = prop.multiProcessorCount;
+  m->top_ctas_per_sm = kTopCtasPerSm;
+  if (const char* e = getenv("YDORB_TOP_CTAS_PER_SM")) m->top_ctas_per_sm = std::max(1, atoi(e));  // tuning knob
   *out = m;
   return YDORB_OK;
 }
@@ -320,7 +353,7 @@ int ydorb_hamming_top2_device(YdMatcher* m, const uint8_t* d_queries, int nq, co
   YD_REQUIRE(((uintptr_t)d_queries & 15) == 0 && ((uintptr_t)d_db & 15) == 0, "descriptor matrices must be 16-byte aligned");
   YD_CUDA(cudaSetDevice(m->device));
   const int qblocks = (nq + kTopQblock - 1) / kTopQblock;
-  int nchunks = std::max(1, (2 * m->sm_count + qblocks - 1) / qblocks);
+  int nchunks = std::max(1, (m->top_ctas_per_sm * m->sm_count + qblocks - 1) / qblocks);
   nchunks = std::min(nchunks, std::max(1, (ndb + 1023) / 1024));
   int chunk_rows = (ndb + nchunks - 1) / nchunks;
   chunk_rows = std::max((chunk_rows + kTopTile - 1) / kTopTile * kTopTile, kTopTile);

@@ -5,6 +5,7 @@
 struct YdMatcher {
   int device;
   int sm_count;
+  int top_ctas_per_sm;   // grid size of the chunked top-2 kernel, in CTAs per SM
   cudaStream_t stream;
   cudaStream_t own_stream;
   void* d_scratch;       // kernel scratch (per-chunk partial results, candidate lists)
