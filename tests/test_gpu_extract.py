@@ -58,6 +58,19 @@ def test_extract_matches_oracle(shape, nf, seed):
     ex.close()
 
 
+@pytest.mark.parametrize("scale,levels,shape", [(1.5, 5, (480, 640)), (2.0, 4, (376, 1241)), (1.1, 6, (333, 517))])
+def test_extract_other_scale_factors(scale, levels, shape):
+    """The resize tiles size their shared buffers from the scale factor; check pyramids and results away from 1.2."""
+    h, w = shape
+    img = synth.synth_frame(w, h, 77)
+    p = orc.make_params(800, scale, levels, 20)
+    ok, od, _ = orc.extract(p, img, cap=900)
+    ex = OrbExtractor(800, scale, levels, 20, 7, max_width=w, max_height=h, max_batch=1)
+    kps, desc = ex.extractAndCompute(img)
+    _check_against(ex, img, kps, desc, ok, od)
+    ex.close()
+
+
 def test_batch_and_reuse():
     """Batch of different frames == frame-by-frame; a reused handle gives fresh-extractor results."""
     imgs = synth.synth_batch(640, 480, 5, seed0=100)

@@ -46,6 +46,7 @@ struct LevelGeom {
   int quota_base;      // prefix sum of quotas
   int root_w, root_h;  // quadtree root extents (maxBorder - minBorder)
   int tab_base;        // offset of this level's resize tables (x then y) in the table arrays; level 0 unused
+  int tile_base;       // offset of this level's resize tile descriptors in the int table array (pyramid.cu)
   float sf;            // m_v_scaleFactors[level]
   float size;          // (float)(int)(31*sf)
 };

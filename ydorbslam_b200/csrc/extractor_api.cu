@@ -147,6 +147,10 @@ static int build_geom(const YdExtractor* ex, int w, int h, HostGeom* out) {
       tab_base += lv.w + lv.h;
     }
   }
+  {
+    const int rc = pyramid_tile_tables(&g, &out->tab_ofs);
+    if (rc != YDORB_OK) return rc;
+  }
   g.n_cells = cell_base;
   g.n_quota = quota_base;
   g.pyr_bytes = off;

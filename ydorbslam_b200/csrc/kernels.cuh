@@ -7,6 +7,8 @@ namespace ydorb {
 // E2 computePyramid (src/orbExtractor.cpp:605-621)
 int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, size_t frame_stride, int batch,
                    cudaStream_t s);
+// appends the resize tile descriptors to the int table array (host side of the geometry set-up)
+int pyramid_tile_tables(FrameGeomDev* g, std::vector<int>* tab);
 // E3 per-cell FAST with threshold fallback (src/orbExtractor.cpp:562-593)
 int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s);
 // E4 distributeQuadTree (src/orbExtractor.cpp:455-544)

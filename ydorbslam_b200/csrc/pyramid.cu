@@ -14,7 +14,7 @@
 
 namespace ydorb {
 
-__device__ __forceinline__ int reflect101(int i, int n) {
+__host__ __device__ __forceinline__ int reflect101(int i, int n) {
   // |pad| < n is guaranteed by the host (levels narrower than the pad are rejected)
   if (i < 0) i = -i;
   if (i >= n) i = 2 * (n - 1) - i;
@@ -22,129 +22,192 @@ __device__ __forceinline__ int reflect101(int i, int n) {
 }
 
 // Inclusive range [lo, hi] of reflect101(i, n) over i in [a, b] (a <= b, |pad| < n).
-__device__ __forceinline__ void reflect_range(int a, int b, int n, int& lo, int& hi) {
+static void reflect_range(int a, int b, int n, int& lo, int& hi) {
   const int ra = reflect101(a, n), rb = reflect101(b, n);
-  lo = (a < 0 && b >= 0) ? 0 : min(ra, rb);
-  hi = (a <= n - 1 && b >= n - 1) ? n - 1 : max(ra, rb);
+  lo = (a < 0 && b >= 0) ? 0 : std::min(ra, rb);
+  hi = (a <= n - 1 && b >= n - 1) ? n - 1 : std::max(ra, rb);
 }
 
 // level 0: copy the input image into the centre of the padded buffer and synthesise the border.
-// A thread owns 4 padded bytes (one aligned store).  When all four are interior pixels and the source rows are
-// 4-byte aligned (`aligned4`), they come from two aligned 32-bit loads and a funnel shift; otherwise byte by byte.
-__global__ void __launch_bounds__(256) k_pyr_level0(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ images,
-                                                    int in_stride, size_t frame_stride, int aligned4,
-                                                    uint8_t* __restrict__ pyr) {
-  const LevelGeom lv = g->lv[0];
+// A thread owns 16 padded bytes of kPy0Rows consecutive rows (one aligned 128-bit store per row).
+//   interior role (blockIdx.x < gridDim.x-1): 16-byte groups made only of image pixels -- five aligned 32-bit loads
+//     and four funnel shifts (any row stride; needs a 4-byte aligned frame base, `aligned4`);
+//   border role (last blockIdx.x): the few groups per row that touch the pad go byte by byte through reflect101.
+// Keeping the two roles in different CTAs keeps every warp on one path.
+constexpr int kPy0Rows = 8;
+__global__ void __launch_bounds__(256) k_pyr_level0(const uint8_t* __restrict__ images, int in_stride, size_t frame_stride,
+                                                    int aligned4, int w, int h, int dstride, long long doff,
+                                                    long long pyr_bytes, uint8_t* __restrict__ pyr) {
   const int frame = blockIdx.z;
-  const int py = blockIdx.y;                                    // padded row
-  const int px4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;  // padded column of the first of 4 bytes
-  const int pw = lv.w + 2 * kPad;
-  if (px4 >= lv.stride) return;
+  const int pw = w + 2 * kPad, ph = h + 2 * kPad;
   const uint8_t* src = images + (size_t)frame * frame_stride;
-  const int sy = reflect101(py - kPad, lv.h);
-  const uint8_t* srow = src + (size_t)sy * in_stride;
-  const int x = px4 - kPad;
-  uint32_t out = 0;
-  if (aligned4 && x >= 0 && ((x >> 2) + 2) * 4 <= lv.w) {
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(srow) + (x >> 2);
-    out = __funnelshift_r(__ldg(w), __ldg(w + 1), 8 * (x & 3));
-  } else {
+  uint8_t* dst = pyr + (size_t)frame * pyr_bytes + doff;
+  // groups g_lo..g_hi are interior: x = 16 g - 19 >= 0 and x + 15 <= w - 1
+  const int ngroups = dstride / 16, g_lo = 2, g_hi = aligned4 ? (w + 3) / 16 : 1;
+  if (blockIdx.x + 1 < gridDim.x) {
+    const int grp = g_lo + blockIdx.x * 64 + (threadIdx.x & 63);
+    const int py0 = (blockIdx.y * 4 + (threadIdx.x >> 6)) * kPy0Rows;
+    if (grp > g_hi) return;
+    const int x = grp * 16 - kPad;
+    const long long frame_bytes = (long long)(h - 1) * in_stride + w;
+#pragma unroll 2
+    for (int i = 0; i < kPy0Rows; i++) {
+      const int py = py0 + i;
+      if (py >= ph) break;
+      const int sy = reflect101(py - kPad, h);
+      const long long fo = (long long)sy * in_stride + x;  // byte offset of the first source pixel in the frame
+      uint4 out;
+      if ((fo & ~3ll) + 20 <= frame_bytes) {
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(src + (fo & ~3ll));
+        const uint32_t w0 = __ldg(wp), w1 = __ldg(wp + 1), w2 = __ldg(wp + 2), w3 = __ldg(wp + 3), w4 = __ldg(wp + 4);
+        const int sh = 8 * (int)(fo & 3);
+        out = make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh),
+                         __funnelshift_r(w3, w4, sh));
+      } else {  // the last few bytes of a frame: stay inside the caller's buffer
+        const uint8_t* sp = src + fo;
+        uint32_t o[4] = {0, 0, 0, 0};
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-      const int px = px4 + k;
-      uint32_t v = 0;
-      if (px < pw) v = srow[reflect101(px - kPad, lv.w)];
-      out |= v << (8 * k);
+        for (int k = 0; k < 16; k++) o[k >> 2] |= (uint32_t)sp[k] << (8 * (k & 3));
+        out = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+      *reinterpret_cast<uint4*>(dst + (size_t)py * dstride + grp * 16) = out;
+    }
+  } else {
+    // border groups: 0, 1 and g_hi+1 .. ngroups-1; a thread owns one 4-byte word of one group of one row
+    const int nb = 2 + (ngroups - 1 - g_hi);
+    const int nwords = nb * 4;
+    const int rows_per_cta = 4 * kPy0Rows;
+    for (int idx = threadIdx.x; idx < nwords * rows_per_cta; idx += 256) {
+      const int r = idx / nwords, wd = idx - r * nwords;
+      const int py = blockIdx.y * rows_per_cta + r;
+      if (py >= ph) break;
+      const int b = wd >> 2;
+      const int grp = b < 2 ? b : g_hi + 1 + (b - 2);
+      const int px4 = grp * 16 + (wd & 3) * 4;
+      const uint8_t* srow = src + (size_t)reflect101(py - kPad, h) * in_stride;
+      uint32_t o = 0;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int px = px4 + k;
+        if (px < pw) o |= (uint32_t)srow[reflect101(px - kPad, w)] << (8 * k);
+      }
+      *reinterpret_cast<uint32_t*>(dst + (size_t)py * dstride + px4) = o;
     }
   }
-  uint8_t* drow = pyr + (size_t)frame * g->pyr_bytes + lv.offset + (size_t)py * lv.stride;
-  *reinterpret_cast<uint32_t*>(drow + px4) = out;
 }
 
 // level l >= 1 from level l-1, separable like OpenCV's own resize (hresize into an int row buffer, then vresize):
 // a CTA owns a kPyTW x th tile of the PADDED destination.
-//   phase A  every source row the tile needs is interpolated horizontally ONCE for the tile's destination columns
-//            into shared memory as (S[sx0]*a0 + S[sx1]*a1) >> 4 (the value the vertical pass consumes); a thread
-//            keeps its column's (sx0, sx1, a0, a1) in registers and walks down the source rows.
-//   phase B  a thread produces 4 adjacent padded bytes per row: two LDS.128 (rows r0, r1 of the buffer), 4 x
+//   stage    the source rows/columns the tile needs are copied to shared memory with aligned 128-bit loads, twice:
+//            copy A as is and copy B shifted by one byte, so that the pixel pair (S[sx], S[sx+1]) of any sx is ONE
+//            aligned 16-bit shared load (from A when sx is even, from B when it is odd).
+//   phase A  every staged source row is interpolated horizontally ONCE for the tile's destination columns into the
+//            int buffer H as (S[sx0]*a0 + S[sx0+1]*a1) >> 4 -- one LDS.U16 + one DP2A per value; a thread keeps its
+//            column's offset and packed weights in registers and walks down the rows.  (Where OpenCV clamps
+//            sx1 = sx0 the weight a1 is 0, so reading the pad byte at sx0+1 is harmless.)
+//   phase B  a thread produces 4 adjacent padded bytes per row: two LDS.128 (rows r0, r1 of H), 4 x
 //            (((b0*H0)>>16) + ((b1*H1)>>16) + 2) >> 2, one aligned 32-bit store.  Pad pixels read the reflected
-//            column/row of the same buffer (REFLECT_101 of the resized level == resize evaluated at the reflected
-//            coordinate), so the border costs no second pass over memory.
-// The buffer's column origin is chosen = 1 (mod 4) so that interior 4-byte groups are 16-byte aligned in it.
+//            column/row of H (REFLECT_101 of the resized level == resize evaluated at the reflected coordinate),
+//            so the border costs no second pass over memory.
+// H's column origin is chosen = 1 (mod 4) so that interior 4-byte groups are 16-byte aligned in it; H column
+// kPyHS-1 is kept zero and stands in for the stride padding beyond the padded width.
 constexpr int kPyTW = 128;             // padded destination columns per CTA
-constexpr int kPyHS = kPyTW + 4;       // row stride of the horizontal-pass buffer (ints)
-constexpr int kPyMaxSrcRows = 48;      // source rows held per tile; the host picks th so that they fit
-constexpr int kPyMaxTH = 32;
+constexpr int kPyHS = kPyTW + 4;       // row stride of H (ints)
+constexpr int kPyMaxTH = 32;           // destination rows per CTA (the host shrinks it for large scale factors)
 
-__global__ void __launch_bounds__(256) k_pyr_resize(const FrameGeomDev* __restrict__ g, int level, int th,
-                                                    const int* __restrict__ tab_ofs, const short2* __restrict__ tab_a,
-                                                    uint8_t* __restrict__ pyr) {
-  __shared__ __align__(16) int s_h[kPyMaxSrcRows * kPyHS];
-  __shared__ int4 s_row[kPyMaxTH];  // per tile row: {r0*kPyHS, r1*kPyHS, b0, b1}
-  const LevelGeom lv = g->lv[level];
-  const LevelGeom sv = g->lv[level - 1];
+struct PyrArgs {
+  int dw, dh, dstride;   // destination level
+  int sw, sh, sstride;   // source level
+  long long doff;        // byte offset of the destination padded buffer in a frame's pyramid block
+  long long sorg;        // byte offset of source pixel (0,0)
+  long long pyr_bytes;
+  int xb, yb;            // table bases (x then y)
+  int th;                // destination rows per tile
+  int nsr_cap;           // source rows the shared buffers hold
+  int tile_base;         // index (in the int table array) of this level's tile descriptors, see pyramid_tile_tables
+};
+
+template <int SS>  // SS: row stride (bytes) of the staged source copies
+__global__ void __launch_bounds__(256) k_pyr_resize(const PyrArgs a, const int* __restrict__ tab_ofs,
+                                                    const short2* __restrict__ tab_a, uint8_t* __restrict__ pyr) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  int* s_h = reinterpret_cast<int*>(smem);                                   // [nsr_cap][kPyHS]
+  int4* s_row = reinterpret_cast<int4*>(s_h + a.nsr_cap * kPyHS);            // [kPyMaxTH] {r0*kPyHS, r1*kPyHS, b0, b1}
+  uint8_t* s_a = reinterpret_cast<uint8_t*>(s_row + kPyMaxTH);               // [nsr_cap][SS]
+  uint8_t* s_b = s_a + a.nsr_cap * SS;                                       // [nsr_cap][SS], s_b[j] = s_a[j+1]
   const int tid = threadIdx.x;
-  const int frame = blockIdx.z;
-  const int px0 = blockIdx.x * kPyTW, py0 = blockIdx.y * th;
-  const int pw = lv.w + 2 * kPad, ph = lv.h + 2 * kPad;
-  uint8_t* fbase = pyr + (size_t)frame * g->pyr_bytes;
-  const uint8_t* s = fbase + level_origin(sv);
-  const int xb = lv.tab_base, yb = lv.tab_base + lv.w;
+  const int px0 = blockIdx.x * kPyTW, py0 = blockIdx.y * a.th;
+  const int pw = a.dw + 2 * kPad, ph = a.dh + 2 * kPad;
+  uint8_t* fbase = pyr + (size_t)blockIdx.z * a.pyr_bytes;
+  const uint8_t* src0 = fbase + a.sorg;
 
-  int lo, hi, rlo, rhi;
-  reflect_range(px0 - kPad, max(min(px0 + kPyTW, pw) - 1, px0) - kPad, lv.w, lo, hi);
-  reflect_range(py0 - kPad, min(py0 + th, ph) - 1 - kPad, lv.h, rlo, rhi);
-  const int org = lo - ((lo - 1) & 3);  // buffer column 0 <-> destination column org, org = 1 (mod 4)
-  const int sy_lo = tab_ofs[yb + rlo];
-  const int nsr = min(tab_ofs[yb + rhi] + 1, sv.h - 1) - sy_lo + 1;
+  // tile geometry precomputed on the host (pyramid_tile_tables): nothing below depends on the thread
+  const int4* td = reinterpret_cast<const int4*>(tab_ofs + a.tile_base);
+  const int4 X0 = __ldg(td + 2 * blockIdx.x), X1 = __ldg(td + 2 * blockIdx.x + 1), Y = __ldg(td + 2 * gridDim.x + blockIdx.y);
+  const int lo = X0.x, hi = X0.y, org = X0.z, sxa = X0.w, nchunk = X1.x;
+  const int sy_lo = Y.x, nsr = Y.y;
 
-  if (tid < th) {
+  if (tid < a.th) {
     const int py = py0 + tid;
     int4 r = make_int4(0, 0, 0, 0);
     if (py < ph) {
-      const int dy = reflect101(py - kPad, lv.h);
-      const int sy0 = tab_ofs[yb + dy];
-      const short2 b = tab_a[yb + dy];
-      r = make_int4((sy0 - sy_lo) * kPyHS, (min(sy0 + 1, sv.h - 1) - sy_lo) * kPyHS, b.x, b.y);
+      const int dy = reflect101(py - kPad, a.dh);
+      const int sy0 = tab_ofs[a.yb + dy];
+      const short2 b = tab_a[a.yb + dy];
+      r = make_int4((sy0 - sy_lo) * kPyHS, (min(sy0 + 1, a.sh - 1) - sy_lo) * kPyHS, b.x, b.y);
     }
     s_row[tid] = r;
   }
+  if (tid < nsr) s_h[tid * kPyHS + kPyHS - 1] = 0;
+  // ---- stage
+  for (int c = tid & 15; c < nchunk; c += 16) {
+    for (int r = tid >> 4; r < nsr; r += 16) {
+      const uint8_t* gp = src0 + (long long)(sy_lo + r) * a.sstride + sxa + 16 * c;
+      const uint4 v = *reinterpret_cast<const uint4*>(gp);
+      const uint32_t nx = (c + 1 < nchunk) ? *reinterpret_cast<const uint32_t*>(gp + 16) : 0u;
+      *reinterpret_cast<uint4*>(s_a + r * SS + 16 * c) = v;
+      *reinterpret_cast<uint4*>(s_b + r * SS + 16 * c) =
+          make_uint4(__funnelshift_r(v.x, v.y, 8), __funnelshift_r(v.y, v.z, 8), __funnelshift_r(v.z, v.w, 8),
+                     __funnelshift_r(v.w, nx, 8));
+    }
+  }
+  __syncthreads();
   // ---- phase A
   {
     const int c = tid & (kPyTW - 1);
     const int dx = org + c;
     if (dx >= lo && dx <= hi) {
-      const int sx0 = tab_ofs[xb + dx];
-      const short2 a = tab_a[xb + dx];
-      const int sx1 = min(sx0 + 1, sv.w - 1);
-      const uint8_t* p = s + (size_t)sy_lo * sv.stride;
+      const int o0 = tab_ofs[a.xb + dx] - sxa;
+      const short2 wa = tab_a[a.xb + dx];
+      const uint32_t wpk = ((uint32_t)(uint16_t)wa.y << 16) | (uint16_t)wa.x;
+      const uint8_t* sp = ((o0 & 1) ? s_b : s_a) + (o0 & ~1) + (tid >> 7) * SS;
+      int* hp = s_h + (tid >> 7) * kPyHS + c;
+      const int n = (nsr - (tid >> 7) + 1) >> 1;  // rows tid>>7, +2, +4, ...
 #pragma unroll 4
-      for (int sr = tid >> 7; sr < nsr; sr += 2) {
-        const uint8_t* q = p + (size_t)sr * sv.stride;
-        s_h[sr * kPyHS + c] = (q[sx0] * a.x + q[sx1] * a.y) >> 4;
-      }
+      for (int i = 0; i < n; i++)
+        hp[i * 2 * kPyHS] = (int)(__dp2a_lo(wpk, (uint32_t) * reinterpret_cast<const uint16_t*>(sp + i * 2 * SS), 0u) >> 4);
     }
-    const int c2 = kPyTW + (tid & 3), dx2 = org + c2;  // the up to 3 columns the alignment shift adds
-    if (dx2 <= hi) {
-      const int sx0 = tab_ofs[xb + dx2];
-      const short2 a = tab_a[xb + dx2];
-      const int sx1 = min(sx0 + 1, sv.w - 1);
-      for (int sr = tid >> 2; sr < nsr; sr += 64) {
-        const uint8_t* q = s + (size_t)(sy_lo + sr) * sv.stride;
-        s_h[sr * kPyHS + c2] = (q[sx0] * a.x + q[sx1] * a.y) >> 4;
-      }
+    const int c2 = kPyTW + (tid >> 5), dx2 = org + c2;  // the up to 3 columns the alignment shift adds: warps 0..2
+    if (tid < 96 && dx2 <= hi) {
+      const int o0 = tab_ofs[a.xb + dx2] - sxa;
+      const short2 wa = tab_a[a.xb + dx2];
+      const uint32_t wpk = ((uint32_t)(uint16_t)wa.y << 16) | (uint16_t)wa.x;
+      const uint8_t* sp = ((o0 & 1) ? s_b : s_a) + (o0 & ~1);
+#pragma unroll 1
+      for (int sr = tid & 31; sr < nsr; sr += 32)
+        s_h[sr * kPyHS + c2] = (int)(__dp2a_lo(wpk, (uint32_t) * reinterpret_cast<const uint16_t*>(sp + sr * SS), 0u) >> 4);
     }
   }
   __syncthreads();
   // ---- phase B
   const int px4 = px0 + 4 * (tid & 31);
-  if (px4 >= lv.stride) return;
-  const bool straight = px4 - kPad >= 0 && px4 + 3 - kPad <= lv.w - 1;
+  if (px4 >= a.dstride) return;
+  const bool straight = px4 - kPad >= 0 && px4 + 3 - kPad <= a.dw - 1;
   int c[4];
 #pragma unroll
-  for (int k = 0; k < 4; k++) c[k] = (px4 + k < pw) ? reflect101(px4 + k - kPad, lv.w) - org : -1;
-  uint8_t* dcol = fbase + lv.offset + px4;
-  for (int i = tid >> 5; i < th; i += 8) {
+  for (int k = 0; k < 4; k++) c[k] = (px4 + k < pw) ? reflect101(px4 + k - kPad, a.dw) - org : kPyHS - 1;
+  uint8_t* dcol = fbase + a.doff + px4;
+  for (int i = tid >> 5; i < a.th; i += 8) {
     const int py = py0 + i;
     if (py >= ph) break;
     const int4 r = s_row[i];
@@ -157,42 +220,113 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const FrameGeomDev* __restri
     } else {
 #pragma unroll
       for (int k = 0; k < 4; k++) {
-        h0[k] = c[k] >= 0 ? s_h[r.x + c[k]] : 0;
-        h1[k] = c[k] >= 0 ? s_h[r.y + c[k]] : 0;
+        h0[k] = s_h[r.x + c[k]];
+        h1[k] = s_h[r.y + c[k]];
       }
     }
-    uint32_t out = 0;
+    uint32_t v[4];
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-      uint32_t v = (uint32_t)((((r.z * h0[k]) >> 16) + ((r.w * h1[k]) >> 16) + 2) >> 2);
-      if (c[k] < 0) v = 0;
-      out |= v << (8 * k);
-    }
-    *reinterpret_cast<uint32_t*>(dcol + (size_t)py * lv.stride) = out;
+    for (int k = 0; k < 4; k++)  // the "+2" rides on the first product as 2 << 16
+      v[k] = (uint32_t)((((r.z * h0[k] + 0x20000) >> 16) + ((r.w * h1[k]) >> 16)) >> 2);
+    const uint32_t out = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+    *reinterpret_cast<uint32_t*>(dcol + (size_t)py * a.dstride) = out;
   }
 }
 
-// rows of the destination tile such that the source rows it needs fit the shared buffer (any scale factor)
-static int resize_tile_rows(const LevelGeom& sv, const LevelGeom& lv) {
-  const double scale = (double)sv.h / (double)lv.h;
-  int th = (int)((kPyMaxSrcRows - 4) / scale);
-  return std::max(1, std::min(th, kPyMaxTH));
+// tile rows and shared-memory sizing of one resize launch (any scale factor up to kPyMaxScale)
+struct ResizePlan {
+  int th, nsr_cap, ss;
+  size_t smem;
+};
+static bool plan_resize(const LevelGeom& sv, const LevelGeom& lv, ResizePlan* p) {
+  const double sy = (double)sv.h / (double)lv.h, sx = (double)sv.w / (double)lv.w;
+  int th = kPyMaxTH;
+  while (th > 1 && (int)((th - 1) * sy) + 4 > 48) th--;
+  p->th = th;
+  p->nsr_cap = (int)((th - 1) * sy) + 4;
+  // bytes staged per row: <= 15 (alignment) + floor(127*sx) + 3 source columns, in whole 16-byte chunks
+  const int need = ((int)((kPyTW - 1) * sx) + 19 + 15) / 16 * 16;
+  p->ss = need <= 192 ? 192 : 512;
+  p->smem = (size_t)p->nsr_cap * kPyHS * 4 + sizeof(int4) * kPyMaxTH + 2 * (size_t)p->nsr_cap * p->ss;
+  return need <= 512;
+}
+
+// Appends the per-tile descriptors of every resize launch to the int table array and records their base per level.
+//   per tile column bx: {lo, hi, org, sxa} {nchunk, 0, 0, 0}   then per tile row by: {sy_lo, nsr, 0, 0}
+// lo..hi = destination columns (after REFLECT_101) the tile needs, org = H column origin (= 1 mod 4),
+// sxa = first staged source column (16-byte aligned address), nchunk = 16-byte chunks staged per source row,
+// sy_lo/nsr = staged source rows.
+int pyramid_tile_tables(FrameGeomDev* g, std::vector<int>* tab) {
+  for (int l = 1; l < g->n_levels; l++) {
+    LevelGeom& lv = g->lv[l];
+    const LevelGeom& sv = g->lv[l - 1];
+    ResizePlan p;
+    YD_REQUIRE(plan_resize(sv, lv, &p), "scale factor too large for the resize kernel (max ~3.5)");
+    const int pw = lv.w + 2 * kPad, ph = lv.h + 2 * kPad;
+    const int nbx = (lv.stride + kPyTW - 1) / kPyTW, nby = (ph + p.th - 1) / p.th;
+    const int mis = (int)(level_origin(sv) & 15);
+    tab->resize((tab->size() + 3) / 4 * 4);
+    lv.tile_base = (int)tab->size();
+    const int* xo = tab->data() + lv.tab_base;
+    std::vector<int> d;
+    for (int bx = 0; bx < nbx; bx++) {
+      const int px0 = bx * kPyTW;
+      int lo, hi;
+      reflect_range(px0 - kPad, std::max(std::min(px0 + kPyTW, pw) - 1, px0) - kPad, lv.w, lo, hi);
+      const int org = lo - ((lo - 1) & 3);
+      const int sx_lo = xo[lo], sx_hi = xo[hi] + 1;
+      const int sxa = sx_lo - ((sx_lo + mis) & 15);
+      const int nchunk = (sx_hi - sxa) / 16 + 1;
+      YD_REQUIRE(nchunk * 16 <= p.ss && hi - org < kPyHS - 1, "internal: resize tile exceeds its shared buffers");
+      const int v[8] = {lo, hi, org, sxa, nchunk, 0, 0, 0};
+      d.insert(d.end(), v, v + 8);
+    }
+    for (int by = 0; by < nby; by++) {
+      const int py0 = by * p.th;
+      int rlo, rhi;
+      reflect_range(py0 - kPad, std::min(py0 + p.th, ph) - 1 - kPad, lv.h, rlo, rhi);
+      const int sy_lo = xo[lv.w + rlo];
+      const int nsr = std::min(xo[lv.w + rhi] + 1, sv.h - 1) - sy_lo + 1;
+      YD_REQUIRE(nsr <= p.nsr_cap, "internal: resize tile exceeds its shared buffers");
+      const int v[4] = {sy_lo, nsr, 0, 0};
+      d.insert(d.end(), v, v + 4);
+    }
+    tab->insert(tab->end(), d.begin(), d.end());  // (xo is dead from here: the vector may have moved)
+  }
+  return YDORB_OK;
 }
 
 int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, size_t frame_stride, int batch,
                    cudaStream_t s) {
   const FrameGeomDev& g = ex->geom;
-  const int aligned4 = ((uintptr_t)d_images % 4 == 0 && stride % 4 == 0 && frame_stride % 4 == 0) ? 1 : 0;
+  const int aligned4 = ((uintptr_t)d_images % 4 == 0 && frame_stride % 4 == 0) ? 1 : 0;
+  YD_REQUIRE(g.pyr_bytes % 16 == 0, "pyramid block must be a multiple of 16 bytes");
   for (int l = 0; l < g.n_levels; l++) {
     const LevelGeom& lv = g.lv[l];
     if (l == 0) {
-      dim3 grid((lv.stride / 4 + 255) / 256, lv.h + 2 * kPad, batch);
-      k_pyr_level0<<<grid, 256, 0, s>>>(ex->d_geom, d_images, stride, frame_stride, aligned4, ex->d_pyr);
+      const int n_int = std::max(aligned4 ? (lv.w + 3) / 16 - 1 : 0, 0);  // interior 16-byte groups per row
+      dim3 grid((n_int + 63) / 64 + 1, (lv.h + 2 * kPad + 4 * kPy0Rows - 1) / (4 * kPy0Rows), batch);
+      k_pyr_level0<<<grid, 256, 0, s>>>(d_images, stride, frame_stride, aligned4, lv.w, lv.h, lv.stride, lv.offset,
+                                        g.pyr_bytes, ex->d_pyr);
     } else {
-      const int th = resize_tile_rows(g.lv[l - 1], lv);
-      dim3 grid((lv.stride + kPyTW - 1) / kPyTW, (lv.h + 2 * kPad + th - 1) / th, batch);
-      k_pyr_resize<<<grid, 256, 0, s>>>(ex->d_geom, l, th, ex->d_tab_ofs, reinterpret_cast<const short2*>(ex->d_tab_a),
-                                        ex->d_pyr);
+      const LevelGeom& sv = g.lv[l - 1];
+      ResizePlan p;
+      YD_REQUIRE(plan_resize(sv, lv, &p), "scale factor too large for the resize kernel (max ~3.5)");
+      YD_REQUIRE(sv.stride % 16 == 0 && lv.offset % 16 == 0 && sv.offset % 16 == 0, "pyramid levels must be 16-byte aligned");
+      PyrArgs a;
+      a.dw = lv.w; a.dh = lv.h; a.dstride = lv.stride;
+      a.sw = sv.w; a.sh = sv.h; a.sstride = sv.stride;
+      a.doff = lv.offset; a.sorg = level_origin(sv); a.pyr_bytes = g.pyr_bytes;
+      a.xb = lv.tab_base; a.yb = lv.tab_base + lv.w;
+      a.th = p.th; a.nsr_cap = p.nsr_cap; a.tile_base = lv.tile_base;
+      dim3 grid((lv.stride + kPyTW - 1) / kPyTW, (lv.h + 2 * kPad + p.th - 1) / p.th, batch);
+      const short2* ta = reinterpret_cast<const short2*>(ex->d_tab_a);
+      if (p.smem > 48 * 1024)  // only reached with scale factors well above the reference's 1.2
+        YD_CUDA(cudaFuncSetAttribute(k_pyr_resize<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      if (p.ss == 192)
+        k_pyr_resize<192><<<grid, 256, p.smem, s>>>(a, ex->d_tab_ofs, ta, ex->d_pyr);
+      else
+        k_pyr_resize<512><<<grid, 256, p.smem, s>>>(a, ex->d_tab_ofs, ta, ex->d_pyr);
     }
   }
   count_launches(g.n_levels);
