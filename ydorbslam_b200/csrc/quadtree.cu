@@ -26,7 +26,13 @@ constexpr int kQtItems = 8;                  // elements per thread and chunk in
 constexpr int kQtDig = 14;                   // digits per path code (28 bits): roots up to 16384 px
 constexpr int kQtBits = 2 * kQtDig;
 
+constexpr int kQtMapDig = 8;                 // depth covered by the occupancy bitmap (4^8 cells)
+constexpr int kQtMapWords = (1 << (2 * kQtMapDig)) / 32;
+
 struct QtSmem {
+  uint32_t bitmap[kQtMapWords];  // bit p set <=> some candidate's path starts with the 8-digit prefix p
+  int cnt[kQtMapDig + 1];        // number of distinct d-digit prefixes, d = 0..8
+  uint32_t ballots[kQtThreads / 32];
   int hist[256];
   int warp_cnt[kQtWarps][256];
   int scan_tmp[kQtWarps];
@@ -139,11 +145,11 @@ __device__ bool qt_radix_pass(QtSmem& sm, const uint32_t* __restrict__ kin, cons
   return true;
 }
 
-// CTA-wide stable sort of (keys, vals) on bits [0, nbits).  Buffers ping-pong; returns index (0/1) of the buffer
+// CTA-wide stable sort of (keys, vals) on bits [lo, nbits) (bits at and above nbits must be zero).  Buffers ping-pong; returns index (0/1) of the buffer
 // holding the result.
-__device__ int qt_sort(QtSmem& sm, uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int n, int nbits) {
+__device__ int qt_sort(QtSmem& sm, uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int n, int nbits, int lo = 0) {
   int cur = 0;
-  for (int shift = 0; shift < nbits; shift += 8) {
+  for (int shift = lo; shift < nbits; shift += 8) {
     const bool moved = cur == 0 ? qt_radix_pass(sm, k0, v0, k1, v1, n, shift) : qt_radix_pass(sm, k1, v1, k0, v0, n, shift);
     if (moved) cur ^= 1;
   }
@@ -337,8 +343,8 @@ struct QtArgs {
 };
 
 // writes (key, packed candidate) of every candidate of the level at its candidate-order position
-__device__ void qt_fill(const QtArgs& A, const LevelGeom& lv, int frame, int level_base, int code_shift, uint32_t* keys,
-                        uint32_t* vals) {
+__device__ void qt_fill(const QtArgs& A, const LevelGeom& lv, int frame, int level_base, uint32_t* keys, uint32_t* vals,
+                        uint32_t* bitmap) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int ncell = lv.cell_cols * lv.cell_rows;
   const size_t cbase = (size_t)frame * A.g->n_cells + lv.cell_base;
@@ -351,8 +357,12 @@ __device__ void qt_fill(const QtArgs& A, const LevelGeom& lv, int frame, int lev
     const int pos0 = rank[c] - level_base;
     for (int e = lane; e < cnt; e += 32) {
       const uint32_t r = raw[start + e];  // y:12 | x:12 | response:8, border-relative coordinates
-      keys[pos0 + e] = qt_code((int)((r >> 8) & 4095u), (int)(r >> 20), lv.root_w, lv.root_h) >> code_shift;
+      const uint32_t code = qt_code((int)((r >> 8) & 4095u), (int)(r >> 20), lv.root_w, lv.root_h);
+      keys[pos0 + e] = code;
       vals[pos0 + e] = r;
+      const uint32_t p8 = code >> (kQtBits - 2 * kQtMapDig);
+      const uint32_t bit = 1u << (p8 & 31u);
+      if (!(bitmap[p8 >> 5] & bit)) atomicOr(&bitmap[p8 >> 5], bit);
     }
   }
 }
@@ -377,35 +387,95 @@ __global__ void __launch_bounds__(kQtThreads) k_quadtree(QtArgs A) {
   uint32_t* K[3] = {A.keys[0] + seg, A.keys[1] + seg, A.keys[2] + seg};
   uint32_t* V[3] = {A.vals[0] + seg, A.vals[1] + seg, A.vals[2] + seg};
 
-  // (1)+(2) full path codes in candidate order, sorted; distinct-prefix counts; depth D (loop condition :479)
-  qt_fill(A, lv, frame, level_base, 0, K[0], V[0]);
+  // (1) path codes in candidate order + occupancy bitmap of their 8-digit prefixes
+  for (int i = tid; i < kQtMapWords; i += kQtThreads) sm.bitmap[i] = 0;
+  if (tid <= kQtMapDig) sm.cnt[tid] = 0;
   __syncthreads();
-  int cur = qt_sort(sm, K[0], V[0], K[1], V[1], n, kQtBits);
-  for (int d = tid; d < kQtDig + 2; d += kQtThreads) sm.lcp_hist[d] = 0;
+  qt_fill(A, lv, frame, level_base, K[0], V[0], sm.bitmap);
   __syncthreads();
+  // (2) #nodes after d passes = #distinct d-digit prefixes (d = 1..8): fold the bitmap.  Thread t < 256 owns the
+  // 8 words under the 4-digit prefix t; deeper levels fold inside a word, shallower ones across lanes by ballot.
   {
-    const uint32_t* ks = K[cur];
-    for (int i = tid + 1; i < n; i += kQtThreads) atomicAdd(&sm.lcp_hist[lcp_digits(ks[i - 1], ks[i], kQtDig)], 1);
+    int c8 = 0, c7 = 0, c6 = 0, c5 = 0;
+    bool any = false;
+    if (tid < 256) {
+      uint32_t pair = 0;
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        const uint32_t w = sm.bitmap[tid * 8 + k];
+        c8 += __popc(w);
+        const uint32_t m7 = (w | (w >> 1) | (w >> 2) | (w >> 3)) & 0x11111111u;
+        c7 += __popc(m7);
+        c6 += __popc((m7 | (m7 >> 4) | (m7 >> 8) | (m7 >> 12)) & 0x00010001u);
+        pair |= w;
+        if (k & 1) { c5 += pair != 0; any |= pair != 0; pair = 0; }
+      }
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, any);
+    c8 = __reduce_add_sync(0xffffffffu, c8);
+    c7 = __reduce_add_sync(0xffffffffu, c7);
+    c6 = __reduce_add_sync(0xffffffffu, c6);
+    c5 = __reduce_add_sync(0xffffffffu, c5);
+    if ((tid & 31) == 0) {
+      if (c8) { atomicAdd(&sm.cnt[8], c8); atomicAdd(&sm.cnt[7], c7); atomicAdd(&sm.cnt[6], c6); atomicAdd(&sm.cnt[5], c5); }
+      if (bal) {
+        atomicAdd(&sm.cnt[4], __popc(bal));
+        atomicAdd(&sm.cnt[3], __popc((bal | (bal >> 1) | (bal >> 2) | (bal >> 3)) & 0x11111111u));
+        atomicAdd(&sm.cnt[2], ((bal & 0xffffu) != 0) + ((bal >> 16) != 0));
+      }
+      sm.ballots[tid >> 5] = bal;
+    }
   }
   __syncthreads();
   if (tid == 0) {
-    // cnt(d) = 1 + #adjacent pairs with lcp < d
-    int D = 0, last = 0, size = 1, below = 0;
+    int c1 = 0;
+    for (int k = 0; k < 4; k++) c1 += (sm.ballots[2 * k] | sm.ballots[2 * k + 1]) != 0;
+    sm.cnt[1] = c1;
+    // the reference's loop condition (:479): split again while the list grew and is still shorter than `want`
+    int D = 0, last = 0, size = 1, deep = 0;
     while (size > last && size < want && D < kQtDig) {
       last = size;
-      below += sm.lcp_hist[D];
       D++;
-      size = 1 + below;
+      if (D > kQtMapDig) { deep = 1; break; }
+      size = sm.cnt[D];
     }
     sm.misc[1] = D;
+    sm.misc[3] = deep;
   }
   __syncthreads();
+  int cur;
+  if (sm.misc[3]) {
+    // rare: more than 8 passes (tightly clustered points).  Sort the full codes, count distinct prefixes of every
+    // depth from the common-prefix lengths of neighbours, then restore candidate order.
+    __syncthreads();
+    cur = qt_sort(sm, K[0], V[0], K[1], V[1], n, kQtBits);
+    for (int d = tid; d < kQtDig + 2; d += kQtThreads) sm.lcp_hist[d] = 0;
+    __syncthreads();
+    {
+      const uint32_t* ks = K[cur];
+      for (int i = tid + 1; i < n; i += kQtThreads) atomicAdd(&sm.lcp_hist[lcp_digits(ks[i - 1], ks[i], kQtDig)], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      // cnt(d) = 1 + #adjacent pairs with lcp < d
+      int D = 0, last = 0, size = 1, below = 0;
+      while (size > last && size < want && D < kQtDig) {
+        last = size;
+        below += sm.lcp_hist[D];
+        D++;
+        size = 1 + below;
+      }
+      sm.misc[1] = D;
+    }
+    __syncthreads();
+    qt_fill(A, lv, frame, level_base, K[0], V[0], sm.bitmap);
+    __syncthreads();
+  }
   const int D = sm.misc[1];
+  const int sh = kQtBits - 2 * D;  // D-digit prefix of a code = code >> sh
 
-  // (3) stable sort of candidate-ordered points by D-digit prefix
-  qt_fill(A, lv, frame, level_base, kQtBits - 2 * D, K[0], V[0]);
-  __syncthreads();
-  cur = (D == 0) ? 0 : qt_sort(sm, K[0], V[0], K[1], V[1], n, 2 * D);
+  // (3) stable sort of the candidate-ordered points by their D-digit prefix (members of a node stay in candidate order)
+  cur = (D == 0) ? 0 : qt_sort(sm, K[0], V[0], K[1], V[1], n, kQtBits, sh);
   const uint32_t* PK = K[cur];
   const uint32_t* PV = V[cur];
   uint32_t* node_start = K[cur ^ 1];   // free ping-pong buffer
@@ -416,7 +486,7 @@ __global__ void __launch_bounds__(kQtThreads) k_quadtree(QtArgs A) {
   __syncthreads();
   for (int base = 0; base < n; base += kQtThreads) {
     const int i = base + tid;
-    const int head = (i < n) && (i == 0 || PK[i] != PK[i - 1]);
+    const int head = (i < n) && (i == 0 || (PK[i] >> sh) != (PK[i - 1] >> sh));
     int total;
     const int ex = qt_block_scan(sm, head, &total);
     const int off = sm.misc[2];
@@ -433,12 +503,12 @@ __global__ void __launch_bounds__(kQtThreads) k_quadtree(QtArgs A) {
   for (int m = tid; m < M; m += kQtThreads) {
     const int beg = (int)node_start[m];
     const int end = (m + 1 < M) ? (int)node_start[m + 1] : n;
-    const uint32_t pre = PK[beg];
+    const uint32_t pre = PK[beg] >> sh;
     int s = D;
     if (end - beg == 1) {
       int l = 0;
-      if (m > 0) l = max(l, lcp_digits(pre, PK[node_start[m - 1]], D));
-      if (m + 1 < M) l = max(l, lcp_digits(pre, PK[end], D));
+      if (m > 0) l = max(l, lcp_digits(pre, PK[node_start[m - 1]] >> sh, D));
+      if (m + 1 < M) l = max(l, lcp_digits(pre, PK[end] >> sh, D));
       s = (n == 1) ? 0 : min(D, l + 1);
     }
     // best response, first maximum in candidate order, number of maxima
@@ -459,13 +529,13 @@ __global__ void __launch_bounds__(kQtThreads) k_quadtree(QtArgs A) {
     const uint32_t ps = (s == 0) ? 0u : (pre >> (2 * (D - s)));
     uint32_t mask = 0;
     for (int k = s; k >= 1; k -= 2) mask |= 3u << (2 * (s - k));
-    NK[m] = ((uint32_t)(D - s) << kQtBits) | (ps ^ mask);
+    NK[m] = ((uint32_t)(D - s) << (2 * D)) | (ps ^ mask);  // 2D + 4 significant bits
     NV[m] = best_val;
   }
   __syncthreads();
 
   // (5) list order
-  const int ncur = qt_sort(sm, NK, NV, K[cur ^ 1], V[cur ^ 1], M, 32);
+  const int ncur = qt_sort(sm, NK, NV, K[cur ^ 1], V[cur ^ 1], M, 2 * D + 4);
   const uint32_t* OV = (ncur == 0) ? NV : V[cur ^ 1];
 
   // (6) emit the first min(M, want) winners (:541-543), coordinates back in level space (:597-598)
