@@ -107,7 +107,7 @@ __device__ __forceinline__ uint32_t fast_score_pair(const uint32_t* __restrict__
 struct FastSmemLayout {
   int wpr;          // pair words per tile row (even)
   int plane_words;  // words of one [max_th][wpr] plane incl. 2 slack words on either side
-  int list_cap;     // NMS survivors per cell (no two are 8-neighbours)
+  int nz_cap;       // tested pairs per cell (entries of the non-zero-score list, 2 bytes each)
   int warp_bytes;
 };
 
@@ -116,8 +116,8 @@ __host__ __device__ inline FastSmemLayout fast_layout(int max_tw, int max_th) {
   const int nw4 = (4 + max_tw + 3) / 4;  // aligned 32-bit loads per row, worst-case alignment
   L.wpr = 2 * nw4;
   L.plane_words = L.wpr * max_th + 4;
-  L.list_cap = ((max_tw - 6 + 1) / 2 + 1) * ((max_th - 6 + 1) / 2 + 1);
-  L.warp_bytes = ((2 * L.plane_words + L.list_cap) * 4 + kFastQueue * 2 + 15) & ~15;
+  L.nz_cap = ((max_tw - 6) / 2 + 2) * (max_th - 6) + 32;
+  L.warp_bytes = (2 * L.plane_words * 4 + L.nz_cap * 2 + kFastQueue * 2 + 15) & ~15;
   return L;
 }
 
@@ -151,21 +151,22 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
   uint8_t* wbase = smem_raw + (size_t)warp * L.warp_bytes;
   uint32_t* tile = reinterpret_cast<uint32_t*>(wbase) + 2;                    // [th][wpr] pixel pairs
   uint32_t* score = tile + L.plane_words;                                      // [th][wpr] stored scores, pairs
-  uint32_t* list = reinterpret_cast<uint32_t*>(wbase) + 2 * L.plane_words;     // survivors, packed output format
-  uint16_t* queue = reinterpret_cast<uint16_t*>(list + L.list_cap);
+  uint16_t* nz = reinterpret_cast<uint16_t*>(reinterpret_cast<uint32_t*>(wbase) + 2 * L.plane_words);  // see below
+  uint16_t* queue = nz + L.nz_cap;
   const int wpr = L.wpr;
 
   // ---- stage: word (r, 2w) = cols (4w, 4w+1), word (r, 2w+1) = cols (4w+2, 4w+3) of the aligned row
   {
     const int nw4 = (a + tw + 3) >> 2;
     const uint8_t* src_al = src - a;
-    int r = 0, w = lane;
-    while (w >= nw4) { w -= nw4; r++; }
+    const int sr = 32 / nw4, sw = 32 - sr * nw4;
+    int r = lane / nw4, w = lane - r * nw4;
     while (r < th_) {
       const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src_al + (size_t)r * lv.stride) + w);
       *reinterpret_cast<uint2*>(tile + r * wpr + 2 * w) = make_uint2(__byte_perm(v, 0, 0x4140), __byte_perm(v, 0, 0x4342));
-      w += 32;
-      while (w >= nw4) { w -= nw4; r++; }
+      r += sr;
+      w += sw;
+      if (w >= nw4) { w -= nw4; r++; }
     }
   }
   // tested pixels: tile columns [a+3, a+tw-4], rows [3, th-4]
@@ -173,41 +174,51 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
   const int j0 = c_lo >> 1, j1 = c_hi >> 1;
   const int ipw = j1 - j0 + 1, ih = th_ - 6;
   const int npairs = ipw * ih;
-  // zero ring of the score plane around the tested pairs (NMS reads one pair / one row beyond them)
-  for (int j = lane; j < wpr; j += 32) { score[2 * wpr + j] = 0; score[(th_ - 3) * wpr + j] = 0; }
-  for (int r = 3 + lane; r < th_ - 3; r += 32) { score[r * wpr + j0 - 1] = 0; score[r * wpr + j1 + 1] = 0; }
+  // lane's walk over the tested pairs in row-major order, 32 pairs per step
+  const int step_r = 32 / ipw, step_j = 32 - step_r * ipw;
+  const int r_first = 3 + lane / ipw, j_first = lane - (lane / ipw) * ipw;
+  // score plane := 0 (only pairs that hold a corner are written; NMS reads one pair / one row around them)
+  {
+    uint2* z = reinterpret_cast<uint2*>(score - 2);
+    for (int i = lane; i < L.plane_words / 2; i += 32) z[i] = make_uint2(0u, 0u);
+  }
   __syncwarp();
 
   const int low_th = min(max(min(ini_th, min_th), 0), 255);
+  int nzn = 0;  // pairs with a non-zero stored score, in row-major order: nz[i] = r << 6 | j
   {
     // ---- reject + exact score
     const uint32_t k1 = (uint32_t)(0x7FFF - (low_th + 256)) * 0x10001u;
     const uint32_t k2 = (uint32_t)(0x8000 + 255 - low_th) * 0x10001u;
     const uint32_t kc = (uint32_t)(256 + low_th) * 0x10001u;
-    auto score_entry = [&](uint32_t e) {
-      const int r = (int)(e >> 8), j = (int)(e & 255u);
-      const uint32_t mm = fast_score_pair(tile + r * wpr + j, wpr);  // m + 256
-      uint32_t s = __vmaxs2(mm, kc) - kc;                            // max(m - low_th, 0), no borrow
-      if (2 * j < c_lo) s &= 0xFFFF0000u;                            // untested half of an edge pair
-      if (2 * j + 1 > c_hi) s &= 0x0000FFFFu;
-      score[r * wpr + j] = s;
+    auto score_batch = [&](int nvalid) {
+      uint32_t s = 0;
+      int r = 0, j = 0;
+      if (lane < nvalid) {
+        const uint32_t e = queue[lane];
+        r = (int)(e >> 8);
+        j = (int)(e & 255u);
+        const uint32_t mm = fast_score_pair(tile + r * wpr + j, wpr);  // m + 256
+        s = __vmaxs2(mm, kc) - kc;                                     // max(m - low_th, 0), no borrow
+        if (2 * j < c_lo) s &= 0xFFFF0000u;                            // untested half of an edge pair
+        if (2 * j + 1 > c_hi) s &= 0x0000FFFFu;
+        if (s != 0u) score[r * wpr + j] = s;
+      }
+      const uint32_t bal = __ballot_sync(0xffffffffu, s != 0u);
+      if (s != 0u) nz[nzn + __popc(bal & lt_mask)] = (uint16_t)((r << 6) | j);
+      nzn += __popc(bal);
     };
     int qn = 0;
-    int r = 3, jj = lane;
-    while (jj >= ipw) { jj -= ipw; r++; }
+    int r = r_first, jj = j_first;
     for (int base = 0; base < npairs; base += 32) {
-      const bool valid = base + lane < npairs;
       bool pass = false;
-      if (valid) {
-        pass = fast_quick_pair(tile + r * wpr + j0 + jj, wpr, k1, k2);
-        if (!pass) score[r * wpr + j0 + jj] = 0;
-      }
+      if (base + lane < npairs) pass = fast_quick_pair(tile + r * wpr + j0 + jj, wpr, k1, k2);
       const uint32_t bal = __ballot_sync(0xffffffffu, pass);
       if (pass) queue[qn + __popc(bal & lt_mask)] = (uint16_t)((r << 8) | (j0 + jj));
       qn += __popc(bal);
       __syncwarp();
       if (qn >= 32) {
-        score_entry(queue[lane]);
+        score_batch(32);
         const int rem = qn - 32;
         uint16_t t = 0;
         if (lane < rem) t = queue[32 + lane];
@@ -216,66 +227,54 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
         qn = rem;
         __syncwarp();
       }
-      jj += 32;
-      while (jj >= ipw) { jj -= ipw; r++; }
+      r += step_r;
+      jj += step_j;
+      if (jj >= ipw) { jj -= ipw; r++; }
     }
-    if (lane < qn) score_entry(queue[lane]);
+    score_batch(qn);
     __syncwarp();
   }
 
-  // ---- NMS: strictly greater than all 8 neighbours, non-corners (and untested pixels) count 0; row-major emit.
-  // `plane` holds max(m - th, 0) for the threshold th in use, so response = value + th - 1.
-  // (the x term may be negative before the column is added: sum modulo 2^32, never OR)
-  const uint32_t pos_base = ((uint32_t)(roi.y - kBorder) << 20) + ((uint32_t)(roi.x - a - kBorder) << 8);
-  auto nms_pass = [&](const uint32_t* __restrict__ plane, int th) -> int {
+  // ---- NMS over the non-zero pairs only: strictly greater than all 8 neighbours, non-corners (and untested pixels)
+  // count 0.  The plane holds max(m - low_th, 0); for a threshold th >= low_th the values max(m - th, 0) are
+  // max(v, kd) - kd with kd = th - low_th, which commutes with the neighbourhood maximum.  Two neighbouring pixels
+  // cannot both survive, so a pair keeps at most one: flag bits 13 (low half) / 14 (high half) of the nz entry.
+  auto nms_pass = [&](int th) -> int {
+    const uint32_t kd = (uint32_t)(th - low_th) * 0x10001u;
     int count = 0;
-    int r = 3, jj = lane;
-    while (jj >= ipw) { jj -= ipw; r++; }
-    for (int base = 0; base < npairs; base += 32) {
-      const bool valid = base + lane < npairs;
-      const uint32_t* p = plane + r * wpr + j0 + jj;
-      const uint32_t c = valid ? p[0] : 0u;
-      if (__ballot_sync(0xffffffffu, c != 0u) != 0u) {
-        uint32_t flags = 0;
+    for (int base = 0; base < nzn; base += 32) {
+      uint32_t flags = 0;
+      uint32_t e = 0;
+      if (base + lane < nzn) {
+        e = nz[base + lane] & 0x1FFFu;
+        const uint32_t* p = score + (int)(e >> 6) * wpr + (int)(e & 63u);
+        const uint32_t c = __vmaxs2(p[0], kd) - kd;
         if (c != 0u) {
           const uint32_t cl = p[-1], cr = p[1];
           const uint32_t ul = p[-wpr - 1], um = p[-wpr], ur = p[-wpr + 1];
           const uint32_t dl = p[wpr - 1], dm = p[wpr], dr = p[wpr + 1];
-          uint32_t n = __vmaxs2(fsr16(cl, c), fsr16(c, cr));
+          uint32_t n = __vmaxs2(fsr16(cl, p[0]), fsr16(p[0], cr));
           n = __vimax3_s16x2(n, __vimax3_s16x2(fsr16(ul, um), um, fsr16(um, ur)),
                              __vimax3_s16x2(fsr16(dl, dm), dm, fsr16(dm, dr)));
+          n = __vmaxs2(n, kd) - kd;
           flags = (c + 0x7FFF7FFFu - n) & 0x80008000u;  // half of c > half of n (all values in [0, 255])
+          if ((c & 0xFFFFu) == 0u) flags &= 0x80000000u;  // a zero half is not a corner at this threshold
+          if ((c >> 16) == 0u) flags &= 0x00008000u;
         }
-        const bool k_lo = (flags & 0x8000u) != 0u, k_hi = (flags >> 31) != 0u;
-        const uint32_t b_lo = __ballot_sync(0xffffffffu, k_lo), b_hi = __ballot_sync(0xffffffffu, k_hi);
-        int slot = count + __popc(b_lo & lt_mask) + __popc(b_hi & lt_mask);
-        const uint32_t pos = pos_base + ((uint32_t)r << 20) + ((uint32_t)(2 * (j0 + jj)) << 8) + (uint32_t)(th - 1);
-        if (k_lo) list[slot++] = pos + (c & 0xFFFFu);
-        if (k_hi) list[slot] = pos + 256u + (c >> 16);
-        count += __popc(b_lo) + __popc(b_hi);
+        nz[base + lane] = (uint16_t)(e | ((flags & 0x8000u) >> 2) | ((flags >> 31) << 14));
       }
-      jj += 32;
-      while (jj >= ipw) { jj -= ipw; r++; }
+      count += __popc(__ballot_sync(0xffffffffu, flags != 0u));
     }
     return count;
   };
-  int count = 0;
+  int count = 0, th_used = low_th;
   for (int attempt = 0; attempt < 2 && count == 0; attempt++) {
     if (attempt == 1 && min_th == ini_th) break;  // same threshold, same (empty) answer (reference: SURVEY F3)
-    const int th_used = min(max(attempt == 0 ? ini_th : min_th, 0), 255);
+    th_used = min(max(attempt == 0 ? ini_th : min_th, 0), 255);
     // keyPointsInCell.empty() is judged after NMS (src/orbExtractor.cpp:582)
-    if (th_used == low_th) {
-      count = nms_pass(score, th_used);
-    } else {
-      // re-threshold into the (no longer needed) tile plane: max(m - th_used, 0) = max(stored - (th_used-low), 0)
-      const uint32_t kd = (uint32_t)(th_used - low_th) * 0x10001u;
-      for (int i = 2 * wpr + lane; i < (th_ - 2) * wpr; i += 32) tile[i] = __vmaxs2(score[i], kd) - kd;
-      __syncwarp();
-      count = nms_pass(tile, th_used);
-      __syncwarp();
-    }
+    count = nms_pass(th_used);
+    __syncwarp();
   }
-  __syncwarp();
   if (count == 0) {
     if (lane == 0) { *out_count = 0; *out_start = 0; }
     return;
@@ -287,9 +286,28 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
     if (lane == 0) { atomicOr(status, kStatusRawOverflow); *out_count = 0; *out_start = 0; }
     return;
   }
-  // y:12 | x:12 | response:8, coordinates relative to the 16 px border as distributeQuadTree sees them (:586-590)
-  uint32_t* dst = raw + (size_t)frame * g->raw_cap + start;
-  for (int i = lane; i < count; i += 32) dst[i] = list[i];
+  // ---- emit in row-major order.  y:12 | x:12 | response:8, coordinates relative to the 16 px border as
+  // distributeQuadTree sees them (:586-590); response = m - 1 = stored + low_th - 1.
+  // (the x term may be negative before the column is added: sum modulo 2^32, never OR)
+  {
+    const uint32_t pos_base = ((uint32_t)(roi.y - kBorder) << 20) + ((uint32_t)(roi.x - a - kBorder) << 8) + (uint32_t)(low_th - 1);
+    uint32_t* dst = raw + (size_t)frame * g->raw_cap + start;
+    int done = 0;
+    for (int base = 0; base < nzn; base += 32) {
+      uint32_t e = 0;
+      if (base + lane < nzn) e = nz[base + lane];
+      const bool keep = (e & 0x6000u) != 0u;
+      const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+      if (keep) {
+        const int r = (int)((e >> 6) & 127u), j = (int)(e & 63u);
+        const uint32_t v = score[r * wpr + j];
+        const bool hi = (e & 0x4000u) != 0u;
+        dst[done + __popc(bal & lt_mask)] =
+            pos_base + ((uint32_t)r << 20) + ((uint32_t)(2 * j + (hi ? 1 : 0)) << 8) + (hi ? (v >> 16) : (v & 0xFFFFu));
+      }
+      done += __popc(bal);
+    }
+  }
   if (lane == 0) { *out_count = count; *out_start = start; }
 }
 
