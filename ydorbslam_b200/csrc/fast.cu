@@ -121,54 +121,108 @@ __host__ __device__ inline FastSmemLayout fast_layout(int max_tw, int max_th) {
   return L;
 }
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
-k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells, const uint8_t* __restrict__ pyr,
-             int ini_th, int min_th, int max_tw, int max_th, uint32_t* __restrict__ raw, int* __restrict__ raw_counter,
-             int* __restrict__ cell_count, int* __restrict__ cell_start, int* __restrict__ status) {
-  extern __shared__ __align__(16) uint8_t smem_raw[];
-  const FastSmemLayout L = fast_layout(max_tw, max_th);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t lt_mask = (1u << lane) - 1u;
-  const int cell = blockIdx.x * kWarpsPerCta + warp;
-  const int frame = blockIdx.y;
-  if (cell >= g->n_cells) return;
-  const int4 roi = cells[cell];
-  const int tw = roi.z - roi.x, th_ = roi.w - roi.y;
-  int* out_count = cell_count + (size_t)frame * g->n_cells + cell;
-  int* out_start = cell_start + (size_t)frame * g->n_cells + cell;
-  if (tw < 7 || th_ < 7) {  // skipped cell or nothing testable
-    if (lane == 0) { *out_count = 0; *out_start = 0; }
-    return;
+constexpr int kCellsPerWarp = 4;  // consecutive cells a warp works through
+constexpr int kFastPf = 14;       // 32-bit words per lane prefetched for the next cell (covers 36 x 36 px cells)
+
+struct FastCell {
+  int valid;
+  int cell;
+  int4 roi;
+  int tw, th, a, nw4;      // ROI extents, tile column of ROI column 0, aligned 32-bit loads per row
+  const uint8_t* src_al;   // 4-byte aligned address of tile (0, 0)
+  int stride;
+};
+
+__device__ __forceinline__ FastCell fast_cell_setup(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
+                                                    const uint8_t* __restrict__ pyr, int cell, int frame, int lane,
+                                                    int* __restrict__ cell_count, int* __restrict__ cell_start) {
+  FastCell c;
+  c.valid = 0;
+  c.cell = cell;
+  if (cell >= g->n_cells) return c;
+  c.roi = cells[cell];
+  c.tw = c.roi.z - c.roi.x;
+  c.th = c.roi.w - c.roi.y;
+  if (c.tw < 7 || c.th < 7) {  // skipped cell or nothing testable
+    if (lane == 0) {
+      cell_count[(size_t)frame * g->n_cells + cell] = 0;
+      cell_start[(size_t)frame * g->n_cells + cell] = 0;
+    }
+    return c;
   }
   int level = 0;
   for (int l = 1; l < g->n_levels; l++)
     if (cell >= g->lv[l].cell_base) level = l;
-  const LevelGeom lv = g->lv[level];
-  const uint8_t* src = pyr + (size_t)frame * g->pyr_bytes + level_origin(lv) + (size_t)roi.y * lv.stride + roi.x;
+  c.stride = g->lv[level].stride;
+  const uint8_t* src = pyr + (size_t)frame * g->pyr_bytes + g->lv[level].offset + (size_t)(kPad + c.roi.y) * c.stride + kPad + c.roi.x;
   // ROI column 0 is tile column a, a in [1, 4]: tile column 0 is 4-byte aligned in HBM and every word a tested pixel's
   // LOW half depends on is a staged pixel (<= 255), so packed subtraction never borrows into a tested half.
-  const int a = (int)((reinterpret_cast<uintptr_t>(src) - 1u) & 3u) + 1;
-  uint8_t* wbase = smem_raw + (size_t)warp * L.warp_bytes;
-  uint32_t* tile = reinterpret_cast<uint32_t*>(wbase) + 2;                    // [th][wpr] pixel pairs
-  uint32_t* score = tile + L.plane_words;                                      // [th][wpr] stored scores, pairs
-  uint16_t* nz = reinterpret_cast<uint16_t*>(reinterpret_cast<uint32_t*>(wbase) + 2 * L.plane_words);  // see below
-  uint16_t* queue = nz + L.nz_cap;
-  const int wpr = L.wpr;
+  c.a = (int)((reinterpret_cast<uintptr_t>(src) - 1u) & 3u) + 1;
+  c.nw4 = (c.a + c.tw + 3) >> 2;
+  c.src_al = src - c.a;
+  c.valid = 1;
+  return c;
+}
 
-  // ---- stage: word (r, 2w) = cols (4w, 4w+1), word (r, 2w+1) = cols (4w+2, 4w+3) of the aligned row
-  {
-    const int nw4 = (a + tw + 3) >> 2;
-    const uint8_t* src_al = src - a;
-    const int sr = 32 / nw4, sw = 32 - sr * nw4;
-    int r = lane / nw4, w = lane - r * nw4;
-    while (r < th_) {
-      const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(src_al + (size_t)r * lv.stride) + w);
-      *reinterpret_cast<uint2*>(tile + r * wpr + 2 * w) = make_uint2(__byte_perm(v, 0, 0x4140), __byte_perm(v, 0, 0x4342));
-      r += sr;
-      w += sw;
-      if (w >= nw4) { w -= nw4; r++; }
-    }
+// issue the global loads of a cell's tile into registers (lane i takes words i, i+32, ... in row-major order)
+__device__ __forceinline__ void fast_prefetch(const FastCell& c, int lane, uint32_t (&v)[kFastPf]) {
+  const int sr = 32 / c.nw4, sw = 32 - sr * c.nw4;
+  int r = lane / c.nw4, w = lane - r * c.nw4;
+#pragma unroll
+  for (int i = 0; i < kFastPf; i++) {
+    v[i] = 0;
+    if (r < c.th) v[i] = __ldg(reinterpret_cast<const uint32_t*>(c.src_al + (size_t)r * c.stride) + w);
+    r += sr;
+    w += sw;
+    if (w >= c.nw4) { w -= c.nw4; r++; }
   }
+}
+
+// registers -> shared tile: word (r, 2w) = cols (4w, 4w+1), word (r, 2w+1) = cols (4w+2, 4w+3) of the aligned row;
+// words beyond the prefetch depth (cells larger than usual) are loaded here
+__device__ __forceinline__ void fast_stage(const FastCell& c, int lane, const uint32_t (&v)[kFastPf], uint32_t* __restrict__ tile,
+                                           int wpr) {
+  const int sr = 32 / c.nw4, sw = 32 - sr * c.nw4;
+  int r = lane / c.nw4, w = lane - r * c.nw4;
+#pragma unroll
+  for (int i = 0; i < kFastPf; i++) {
+    if (r < c.th)
+      *reinterpret_cast<uint2*>(tile + r * wpr + 2 * w) = make_uint2(__byte_perm(v[i], 0, 0x4140), __byte_perm(v[i], 0, 0x4342));
+    r += sr;
+    w += sw;
+    if (w >= c.nw4) { w -= c.nw4; r++; }
+  }
+  while (r < c.th) {
+    const uint32_t x = __ldg(reinterpret_cast<const uint32_t*>(c.src_al + (size_t)r * c.stride) + w);
+    *reinterpret_cast<uint2*>(tile + r * wpr + 2 * w) = make_uint2(__byte_perm(x, 0, 0x4140), __byte_perm(x, 0, 0x4342));
+    r += sr;
+    w += sw;
+    if (w >= c.nw4) { w -= c.nw4; r++; }
+  }
+}
+
+struct FastOut {
+  const FrameGeomDev* g;
+  uint32_t* raw;
+  int* raw_counter;
+  int* cell_count;
+  int* cell_start;
+  int* status;
+};
+
+// reject, score, NMS and emit of one staged cell (all 32 lanes)
+__device__ void fast_cell_compute(const FastCell& fc, int frame, int lane, int ini_th, int min_th, const FastSmemLayout& L,
+                                  uint32_t* __restrict__ tile, uint32_t* __restrict__ score, uint16_t* __restrict__ nz,
+                                  uint16_t* __restrict__ queue, const FastOut& O) {
+  const FrameGeomDev* g = O.g;
+  uint32_t* raw = O.raw;
+  int* raw_counter = O.raw_counter;
+  int* status = O.status;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const int4 roi = fc.roi;
+  const int tw = fc.tw, th_ = fc.th, a = fc.a, wpr = L.wpr;
+  int* out_count = O.cell_count + (size_t)frame * g->n_cells + fc.cell;
+  int* out_start = O.cell_start + (size_t)frame * g->n_cells + fc.cell;
   // tested pixels: tile columns [a+3, a+tw-4], rows [3, th-4]
   const int c_lo = a + 3, c_hi = a + tw - 4;
   const int j0 = c_lo >> 1, j1 = c_hi >> 1;
@@ -311,6 +365,39 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
   if (lane == 0) { *out_count = count; *out_start = start; }
 }
 
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells, const uint8_t* __restrict__ pyr,
+             int ini_th, int min_th, int max_tw, int max_th, uint32_t* __restrict__ raw, int* __restrict__ raw_counter,
+             int* __restrict__ cell_count, int* __restrict__ cell_start, int* __restrict__ status) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  const FastSmemLayout L = fast_layout(max_tw, max_th);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int frame = blockIdx.y;
+  uint8_t* wbase = smem_raw + (size_t)warp * L.warp_bytes;
+  uint32_t* tile = reinterpret_cast<uint32_t*>(wbase) + 2;                    // [th][wpr] pixel pairs
+  uint32_t* score = tile + L.plane_words;                                      // [th][wpr] stored scores, pairs
+  uint16_t* nz = reinterpret_cast<uint16_t*>(reinterpret_cast<uint32_t*>(wbase) + 2 * L.plane_words);
+  uint16_t* queue = nz + L.nz_cap;
+  const FastOut O{g, raw, raw_counter, cell_count, cell_start, status};
+  // software pipeline over the warp's cells: the next cell's pixels travel HBM -> registers while this one computes
+  const int cell0 = (blockIdx.x * kWarpsPerCta + warp) * kCellsPerWarp;
+  uint32_t v[kFastPf];
+  FastCell cur = fast_cell_setup(g, cells, pyr, cell0, frame, lane, cell_count, cell_start);
+  if (cur.valid) fast_prefetch(cur, lane, v);
+  for (int k = 0; k < kCellsPerWarp; k++) {
+    if (cur.valid) fast_stage(cur, lane, v, tile, L.wpr);
+    FastCell nxt;
+    nxt.valid = 0;
+    if (k + 1 < kCellsPerWarp) {
+      nxt = fast_cell_setup(g, cells, pyr, cell0 + k + 1, frame, lane, cell_count, cell_start);
+      if (nxt.valid) fast_prefetch(nxt, lane, v);
+    }
+    if (cur.valid) fast_cell_compute(cur, frame, lane, ini_th, min_th, L, tile, score, nz, queue, O);
+    __syncwarp();
+    cur = nxt;
+  }
+}
+
 int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s) {
   YD_CUDA(cudaMemsetAsync(ex->d_raw_counter, 0, sizeof(int) * batch, s));
   const int ini = ex->params.ini_th_fast;
@@ -318,7 +405,8 @@ int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s) {
   const FastSmemLayout L = fast_layout(ex->max_cell_w, ex->max_cell_h);
   const size_t smem = (size_t)L.warp_bytes * kWarpsPerCta;
   if (smem > 48 * 1024) YD_CUDA(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid((ex->geom.n_cells + kWarpsPerCta - 1) / kWarpsPerCta, batch);
+  const int per_cta = kWarpsPerCta * kCellsPerWarp;
+  dim3 grid((ex->geom.n_cells + per_cta - 1) / per_cta, batch);
   k_fast_cells<<<grid, kWarpsPerCta * 32, smem, s>>>(ex->d_geom, ex->d_cells, ex->d_pyr, ini, mn, ex->max_cell_w,
                                                      ex->max_cell_h, ex->d_raw, ex->d_raw_counter, ex->d_cell_count,
                                                      ex->d_cell_start, ex->d_status);
