@@ -16,10 +16,12 @@ namespace ydorb {
 
 constexpr int kDescWarps = 4;
 constexpr int kPatchRows = 43;    // y-21 .. y+21  (18 px pattern reach + 3 px blur reach)
-constexpr int kPatchStride = 64;  // bytes per staged row: 15 aligned words cover x-26-a .. x+26 (IC-angle reach 26)
+constexpr int kPatchStride = 68;  // bytes per staged row (15 aligned words cover x-26-a .. x+26, IC-angle reach 26);
+                                  // 17 words: lanes walking down a column hit 32 different banks
 constexpr int kPatchWords = 15;
 constexpr int kHbGroups = 11;     // horizontal-blur outputs per row in groups of 4: patch columns 7 .. 50
-constexpr int kHbStride = 4 * kHbGroups;  // u16 per row
+constexpr int kHbCols = 4 * kHbGroups;    // horizontal-blur columns kept
+constexpr int kHbColStride = 44;          // u16 per COLUMN: the buffer is stored transposed, hb[col][row], rows 0..42 (+1 pad)
 constexpr int kHbCol0 = 7;        // patch column of hb[.][0]
 
 __constant__ __align__(16) int8_t c_pattern[1024] = {
@@ -48,56 +50,134 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
   return a;
 }
 
-__global__ void __launch_bounds__(kDescWarps * 32)
+constexpr int kKpPerWarp = 8;                               // consecutive keypoint slots a warp works through
+constexpr int kDescPf = (kPatchRows * kPatchWords + 31) / 32;  // 32-bit words per lane of one staged neighbourhood
+
+struct DescLevel {      // per-level facts of this frame, built once per CTA
+  int quota_base, cnt, out_base, stride;
+  long long origin;     // byte offset of level pixel (0,0) in the frame's pyramid block
+  float sf, size;
+};
+
+struct DescKp {
+  int valid, level, oi, a;
+  int4 kp;              // x, y (level coords), response, level
+  const uint32_t* src_al;
+  int stride_w;
+};
+
+__device__ __forceinline__ DescKp desc_setup(const DescLevel* __restrict__ lvl, int n_levels, int n_quota, int slot,
+                                             const int4* __restrict__ sel_frame, const uint8_t* __restrict__ pyr_frame,
+                                             int capacity) {
+  DescKp d;
+  d.valid = 0;
+  if (slot >= n_quota) return d;
+  int level = 0;
+  for (int l = 1; l < n_levels; l++)
+    if (slot >= lvl[l].quota_base) level = l;
+  const DescLevel L = lvl[level];
+  const int j = slot - L.quota_base;
+  if (j >= L.cnt) return d;
+  d.oi = L.out_base + j;
+  if (d.oi >= capacity) return d;
+  d.level = level;
+  d.kp = sel_frame[slot];
+  // the 19 px reflect-101 pad makes every read legal: keypoints are >= 19 px from the edge, rows are padded to 16 B
+  const uint8_t* src = pyr_frame + L.origin + (ptrdiff_t)(d.kp.y - 21) * L.stride + (d.kp.x - 26);
+  d.a = (int)(reinterpret_cast<uintptr_t>(src) & 3u);
+  d.src_al = reinterpret_cast<const uint32_t*>(src - d.a);
+  d.stride_w = L.stride >> 2;
+  d.valid = 1;
+  return d;
+}
+
+// Asynchronous copy HBM -> shared of one 43 x 15-word neighbourhood (cp.async, 4 bytes per request because the source
+// is only word aligned); lane i owns words i, i+32, ... in row-major order.  No registers are held across the copy.
+__device__ __forceinline__ void desc_prefetch(const DescKp& d, int lane, uint8_t* __restrict__ patch) {
+  int r = lane / kPatchWords, w = lane - r * kPatchWords;
+  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(patch);
+#pragma unroll
+  for (int i = 0; i < kDescPf; i++) {
+    if (r < kPatchRows)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sbase + (uint32_t)(r * kPatchStride + 4 * w)),
+                   "l"(d.src_al + (ptrdiff_t)r * d.stride_w + w)
+                   : "memory");
+    r += 2;
+    w += 2;
+    if (w >= kPatchWords) { w -= kPatchWords; r++; }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void desc_wait_patch() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+__device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, int lane, uint8_t* __restrict__ patch,
+                             uint16_t* __restrict__ hb, const uint32_t* __restrict__ s_pat, YdKeyPoint* __restrict__ kps,
+                             uint8_t* __restrict__ desc, int capacity);
+
+__global__ void __launch_bounds__(kDescWarps * 32, 5)
 k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, const int4* __restrict__ sel,
            const int* __restrict__ sel_n, YdKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc, int capacity,
            int32_t* __restrict__ n_out, int* __restrict__ status) {
-  __shared__ __align__(16) uint8_t s_patch[kDescWarps][kPatchRows * kPatchStride];
-  __shared__ __align__(16) uint16_t s_hb[kDescWarps][kPatchRows * kHbStride];
+  __shared__ __align__(16) uint8_t s_patch[kDescWarps][2][kPatchRows * kPatchStride];  // double buffered
+  __shared__ __align__(16) uint16_t s_hb[kDescWarps][kHbCols * kHbColStride];
   __shared__ uint32_t s_pat[256];  // [bit b][lane]: the two pattern points (x0,y0,x1,y1 as s8) of bit b of byte `lane`
+  __shared__ DescLevel s_lvl[kMaxLevels];
+  const int frame = blockIdx.y;
+  const int n_levels = g->n_levels, n_quota = g->n_quota;
   for (int i = threadIdx.x; i < 256; i += blockDim.x) {
     const int b = i >> 5, l = i & 31;
     s_pat[i] = reinterpret_cast<const uint32_t*>(c_pattern)[l * 8 + b];
   }
+  if (threadIdx.x < n_levels) {
+    const int l = threadIdx.x;
+    const int* cnt = sel_n + (size_t)frame * kMaxLevels;
+    DescLevel L;
+    L.quota_base = g->lv[l].quota_base;
+    L.cnt = cnt[l];
+    L.out_base = 0;
+    for (int k = 0; k < l; k++) L.out_base += cnt[k];
+    L.stride = g->lv[l].stride;
+    L.origin = level_origin(g->lv[l]);
+    L.sf = g->lv[l].sf;
+    L.size = g->lv[l].size;
+    s_lvl[l] = L;
+    if (l == n_levels - 1 && blockIdx.x == 0) {
+      const int total = L.out_base + L.cnt;
+      n_out[frame] = min(total, capacity);
+      if (total > capacity) atomicOr(status, kStatusOutOverflow);
+    }
+  }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int slot = blockIdx.x * kDescWarps + warp;
-  const int frame = blockIdx.y;
-  if (slot >= g->n_quota) return;
-  int level = 0;
-  for (int l = 1; l < g->n_levels; l++)
-    if (slot >= g->lv[l].quota_base) level = l;
-  const LevelGeom lv = g->lv[level];
-  const int j = slot - lv.quota_base;
-  const int* cnt = sel_n + (size_t)frame * kMaxLevels;
-  int out_base = 0, total = 0;
-  for (int l = 0; l < g->n_levels; l++) {
-    const int c = cnt[l];
-    if (l < level) out_base += c;
-    total += c;
-  }
-  if (slot == 0 && lane == 0) {
-    n_out[frame] = min(total, capacity);
-    if (total > capacity) atomicOr(status, kStatusOutOverflow);
-  }
-  if (j >= cnt[level]) return;
-  const int oi = out_base + j;
-  if (oi >= capacity) return;
-  const int4 kp = sel[(size_t)frame * g->n_quota + slot];  // x, y (level coords), response, level
-  const uint8_t* img = pyr + (size_t)frame * g->pyr_bytes + level_origin(lv);
-  uint8_t* patch = s_patch[warp];
+  const int slot0 = (blockIdx.x * kDescWarps + warp) * kKpPerWarp;
+  const int4* sel_frame = sel + (size_t)frame * n_quota;
+  const uint8_t* pyr_frame = pyr + (size_t)frame * g->pyr_bytes;
   uint16_t* hb = s_hb[warp];
-  // stage the neighbourhood with aligned 32-bit loads (the 19 px reflect-101 pad makes every read legal: keypoints
-  // are >= 19 px from the edge and rows are padded to 16 B); pixel (dx, dy) lands at patch[(dy+21)*64 + dx+26+a]
-  const uint8_t* src = img + (ptrdiff_t)(kp.y - 21) * lv.stride + (kp.x - 26);
-  const int a = (int)(reinterpret_cast<uintptr_t>(src) & 3u);
-  {
-    const uint32_t* src_al = reinterpret_cast<const uint32_t*>(src - a);
-    const int w = lane & 15, stride_w = lv.stride >> 2;
-    for (int r = lane >> 4; r < kPatchRows; r += 2)
-      if (w < kPatchWords) reinterpret_cast<uint32_t*>(patch)[r * (kPatchStride / 4) + w] = __ldg(src_al + (ptrdiff_t)r * stride_w + w);
+  // software pipeline over the warp's keypoints: the next neighbourhood is copied HBM -> shared asynchronously into
+  // the other patch buffer while this one computes
+  DescKp cur = desc_setup(s_lvl, n_levels, n_quota, slot0, sel_frame, pyr_frame, capacity);
+  if (cur.valid) desc_prefetch(cur, lane, s_patch[warp][0]);
+  for (int k = 0; k < kKpPerWarp; k++) {
+    desc_wait_patch();
+    __syncwarp();
+    DescKp nxt;
+    nxt.valid = 0;
+    if (k + 1 < kKpPerWarp) {
+      nxt = desc_setup(s_lvl, n_levels, n_quota, slot0 + k + 1, sel_frame, pyr_frame, capacity);
+      if (nxt.valid) desc_prefetch(nxt, lane, s_patch[warp][(k + 1) & 1]);
+    }
+    if (cur.valid) desc_compute(cur, s_lvl[cur.level], frame, lane, s_patch[warp][k & 1], hb, s_pat, kps, desc, capacity);
+    __syncwarp();
+    cur = nxt;
   }
-  __syncwarp();
+}
+
+// pixel (dx, dy) of the keypoint's neighbourhood sits at patch[(dy+21)*64 + dx+26+a]
+__device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, int lane, uint8_t* __restrict__ patch,
+                             uint16_t* __restrict__ hb, const uint32_t* __restrict__ s_pat, YdKeyPoint* __restrict__ kps,
+                             uint8_t* __restrict__ desc, int capacity) {
+  const int a = d.a, oi = d.oi, level = d.level;
+  const int4 kp = d.kp;
   // ---- E5 IC angle
   const uint8_t* ctr = patch + 21 * kPatchStride + 26 + a;
   int m10 = 0, m01 = 0;
@@ -128,22 +208,26 @@ k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, 
   const float angle = fast_atan2_deg((float)m01, (float)m10);               // :419
   // ---- E6 horizontal blur pass over rows y-21..y+21 (exact, <= 65280).  A task = 4 adjacent outputs at patch
   // columns c0..c0+3 with c0 = 7 + 4*grp, i.e. c0-3 word aligned: taps [18 34 48 56 | 48 34 18 0] as two DP4A.
+  // Tasks run down the rows first (conflict-free loads thanks to the 17-word patch stride) and the results are stored
+  // TRANSPOSED, hb[col][row], so that the 7 vertical taps of a sample are 7 consecutive u16.
   for (int t = lane; t < kPatchRows * kHbGroups; t += 32) {
-    const int r = t / kHbGroups, grp = t - r * kHbGroups;
+    const int grp = t / kPatchRows, r = t - grp * kPatchRows;
     const uint32_t* pw = reinterpret_cast<const uint32_t*>(patch) + r * (kPatchStride / 4) + 1 + grp;
     const uint32_t A = pw[0], B = pw[1], C = pw[2];
     const uint32_t k_lo = 0x38302212u, k_hi = 0x00122230u;  // (18,34,48,56), (48,34,18,0) little endian
-    const uint32_t o0 = __dp4a(A, k_lo, __dp4a(B, k_hi, 0u));
-    const uint32_t o1 = __dp4a(__funnelshift_r(A, B, 8), k_lo, __dp4a(__funnelshift_r(B, C, 8), k_hi, 0u));
-    const uint32_t o2 = __dp4a(__funnelshift_r(A, B, 16), k_lo, __dp4a(__funnelshift_r(B, C, 16), k_hi, 0u));
-    const uint32_t o3 = __dp4a(__funnelshift_r(A, B, 24), k_lo, __dp4a(__funnelshift_r(B, C, 24), k_hi, 0u));
-    *reinterpret_cast<uint2*>(hb + r * kHbStride + 4 * grp) = make_uint2(o0 | (o1 << 16), o2 | (o3 << 16));
+    uint16_t* o = hb + (4 * grp) * kHbColStride + r;
+    o[0] = (uint16_t)__dp4a(A, k_lo, __dp4a(B, k_hi, 0u));
+    o[kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 8), k_lo, __dp4a(__funnelshift_r(B, C, 8), k_hi, 0u));
+    o[2 * kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 16), k_lo, __dp4a(__funnelshift_r(B, C, 16), k_hi, 0u));
+    o[3 * kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 24), k_lo, __dp4a(__funnelshift_r(B, C, 24), k_hi, 0u));
   }
   __syncwarp();
   // ---- E7 rBRIEF
   const float a_rad = __fmul_rn(angle, (float)(3.14159265358979323846 / 180.0));  // :425
   const float cosA = (float)cos((double)a_rad), sinB = (float)sin((double)a_rad);    // :426
-  const uint16_t* hctr = hb + (21 - 3) * kHbStride + (26 + a - kHbCol0);  // hb position of (dx = 0, dy = -3)
+  // 32-bit view of hb; a sample at (rr, cc) reads rows 18+rr .. 24+rr of column 19+a+cc: four consecutive words,
+  // realigned by a funnel shift when the first row is odd, then 4 x DP2A with the tap pairs (18,34)(48,56)(48,34)(18,0)
+  const uint32_t* hw32 = reinterpret_cast<const uint32_t*>(hb) + (26 + a - kHbCol0) * (kHbColStride / 2);
   uint32_t byte = 0;
 #pragma unroll
   for (int b = 0; b < 8; b++) {
@@ -154,9 +238,14 @@ k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, 
       const float px = (float)(int8_t)(pp >> (16 * e)), py = (float)(int8_t)(pp >> (16 * e + 8));
       const int rr = __float2int_rn(__fadd_rn(__fmul_rn(px, sinB), __fmul_rn(py, cosA)));  // :428
       const int cc = __float2int_rn(__fsub_rn(__fmul_rn(px, cosA), __fmul_rn(py, sinB)));  // :429
-      const uint16_t* h = hctr + rr * kHbStride + cc;
-      const uint32_t acc = 18u * (h[0] + h[6 * kHbStride]) + 34u * (h[kHbStride] + h[5 * kHbStride]) +
-                           48u * (h[2 * kHbStride] + h[4 * kHbStride]) + 56u * h[3 * kHbStride];
+      const int row0 = rr + 18;
+      const uint32_t* h = hw32 + cc * (kHbColStride / 2) + (row0 >> 1);
+      const int sh = (row0 & 1) * 16;
+      const uint32_t w0 = h[0], w1 = h[1], w2 = h[2], w3 = h[3];
+      uint32_t acc = __dp2a_lo(__funnelshift_r(w0, w1, sh), 0x2212u, 0u);
+      acc = __dp2a_lo(__funnelshift_r(w1, w2, sh), 0x3830u, acc);
+      acc = __dp2a_lo(__funnelshift_r(w2, w3, sh), 0x2230u, acc);
+      acc = __dp2a_lo(w3 >> sh, 0x0012u, acc);
       val[e] = (int)((acc + 32768u) >> 16);
     }
     byte |= (uint32_t)(val[0] < val[1]) << b;
@@ -187,7 +276,8 @@ k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, 
 
 int launch_describe(const YdExtractor* ex, int batch, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity,
                     int32_t* d_nout, cudaStream_t s) {
-  dim3 grid((ex->geom.n_quota + kDescWarps - 1) / kDescWarps, batch);
+  const int per_cta = kDescWarps * kKpPerWarp;
+  dim3 grid((ex->geom.n_quota + per_cta - 1) / per_cta, batch);
   k_describe<<<grid, kDescWarps * 32, 0, s>>>(ex->d_geom, ex->d_pyr, ex->d_sel, ex->d_sel_n, d_kps, d_desc, capacity,
                                               d_nout, ex->d_status);
   count_launches(1);
