@@ -76,6 +76,8 @@ struct YdExtractor {
   cudaStream_t own_stream;
   cudaStream_t aux_stream;  // second stream of the host entry points: chunk i+1's H2D overlaps chunk i's kernels
   cudaEvent_t ev_fork, ev_join;
+  cudaStream_t in_stream, out_stream;   // H2D and D2H copy streams of the chunked host entry point
+  cudaEvent_t ev_in[16], ev_done[16];   // per chunk: input resident / results ready
   int profiling;            // record per-stage events
   cudaEvent_t ev_ring[64][5];  // per call: pyramid | fast | quadtree | describe boundaries (ring of 64 calls)
   cudaEvent_t* ev;           // slot of the current call

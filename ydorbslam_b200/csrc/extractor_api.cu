@@ -1,6 +1,7 @@
 // C ABI of the extractor (include/ydorb.h): handle life cycle, per-size geometry and OpenCV-compatible resize
 // tables built on the host, stage orchestration on the handle's stream.
 #include <algorithm>
+#include <cstdlib>
 #include <atomic>
 #include <cmath>
 #include <cstdio>
@@ -314,6 +315,12 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->aux_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ex->ev_fork, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ex->ev_join, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->in_stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->out_stream, cudaStreamNonBlocking);
+  for (int i = 0; i < 16 && e == cudaSuccess; i++) {
+    e = cudaEventCreateWithFlags(&ex->ev_in[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ex->ev_done[i], cudaEventDisableTiming);
+  }
   for (int i = 0; i < 64 * 5 && e == cudaSuccess; i++) e = cudaEventCreate(&ex->ev_ring[i / 5][i % 5]);
   ex->ev = ex->ev_ring[0];
   auto alloc = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, std::max<size_t>(bytes, 16)); };
@@ -364,6 +371,12 @@ void ydorb_extractor_destroy(YdExtractor* ex) {
   if (ex->ev_fork) cudaEventDestroy(ex->ev_fork);
   if (ex->ev_join) cudaEventDestroy(ex->ev_join);
   if (ex->aux_stream) cudaStreamDestroy(ex->aux_stream);
+  if (ex->in_stream) cudaStreamDestroy(ex->in_stream);
+  if (ex->out_stream) cudaStreamDestroy(ex->out_stream);
+  for (int i = 0; i < 16; i++) {
+    if (ex->ev_in[i]) cudaEventDestroy(ex->ev_in[i]);
+    if (ex->ev_done[i]) cudaEventDestroy(ex->ev_done[i]);
+  }
   if (ex->own_stream) cudaStreamDestroy(ex->own_stream);
   delete ex;
 }
@@ -469,27 +482,37 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
     return YDORB_OK;
   };
   if (!ex->profiling && capacity == dcap && batch >= 8) {
-    // Chunked: sub-batches alternate between the handle's stream and an internal one, each doing
-    // H2D -> stages -> D2H in order, so one chunk's copies overlap the other chunk's kernels.  Outputs have the
-    // caller's layout (capacity == quota sum), so results are copied back in bulk without knowing the counts.
-    const int chunk = std::max(4, (batch + 7) / 8);
+    // Chunked, four streams: a copy-in stream uploads sub-batch after sub-batch without waiting for any kernel, two
+    // compute streams take the sub-batches alternately (one's small tail kernels overlap the other's wide ones), a
+    // copy-out stream returns each sub-batch's results as soon as they exist.  Outputs have the caller's layout
+    // (capacity == quota sum), so results are copied back in bulk without knowing the counts.
+    int nchunks = std::min(8, std::max(2, batch / 32));
+    if (const char* e = getenv("YDORB_HOST_CHUNKS")) nchunks = std::min(16, std::max(1, atoi(e)));  // tuning knob
+    const int chunk = (batch + nchunks - 1) / nchunks;
     YD_CUDA(cudaEventRecord(ex->ev_fork, s));
     YD_CUDA(cudaStreamWaitEvent(ex->aux_stream, ex->ev_fork, 0));
+    YD_CUDA(cudaStreamWaitEvent(ex->in_stream, ex->ev_fork, 0));
+    YD_CUDA(cudaStreamWaitEvent(ex->out_stream, ex->ev_fork, 0));
     int k = 0;
     for (int f0 = 0; f0 < batch; f0 += chunk, k++) {
       const int n = std::min(chunk, batch - f0);
       cudaStream_t st = (k & 1) ? ex->aux_stream : s;
-      if ((rc = upload(f0, n, st)) != YDORB_OK) return rc;
+      if ((rc = upload(f0, n, ex->in_stream)) != YDORB_OK) return rc;
+      YD_CUDA(cudaEventRecord(ex->ev_in[k], ex->in_stream));
+      YD_CUDA(cudaStreamWaitEvent(st, ex->ev_in[k], 0));
       rc = run_stages(ex, f0, n, st, ex->d_images + (size_t)f0 * width * height, width, (size_t)width * height,
                       ex->d_kps + (size_t)f0 * dcap, ex->d_desc + (size_t)f0 * dcap * 32, dcap, ex->d_nout + f0);
       if (rc != YDORB_OK) return rc;
-      YD_CUDA(cudaMemcpyAsync(n_out + f0, ex->d_nout + f0, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, st));
+      YD_CUDA(cudaEventRecord(ex->ev_done[k], st));
+      YD_CUDA(cudaStreamWaitEvent(ex->out_stream, ex->ev_done[k], 0));
+      YD_CUDA(cudaMemcpyAsync(n_out + f0, ex->d_nout + f0, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, ex->out_stream));
       YD_CUDA(cudaMemcpyAsync(keypoints + (size_t)f0 * dcap, ex->d_kps + (size_t)f0 * dcap, sizeof(YdKeyPoint) * (size_t)n * dcap,
-                              cudaMemcpyDeviceToHost, st));
+                              cudaMemcpyDeviceToHost, ex->out_stream));
       YD_CUDA(cudaMemcpyAsync(descriptors + (size_t)f0 * dcap * 32, ex->d_desc + (size_t)f0 * dcap * 32, (size_t)32 * n * dcap,
-                              cudaMemcpyDeviceToHost, st));
+                              cudaMemcpyDeviceToHost, ex->out_stream));
     }
-    YD_CUDA(cudaEventRecord(ex->ev_join, ex->aux_stream));
+    // the copy-out stream has waited for every sub-batch of both compute streams: joining it joins everything
+    YD_CUDA(cudaEventRecord(ex->ev_join, ex->out_stream));
     YD_CUDA(cudaStreamWaitEvent(s, ex->ev_join, 0));
     YD_CUDA(cudaStreamSynchronize(s));
     return check_status(ex);
