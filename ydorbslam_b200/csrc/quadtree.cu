@@ -67,15 +67,23 @@ __device__ __forceinline__ int lcp_digits(uint32_t a, uint32_t b, int ndig) {
   return ndig - 1 - (hb >> 1);
 }
 
-// ---- CTA-wide stable LSD radix pass on bits [shift, shift+8).  Returns false (nothing moved) if every key
-// has the same digit.  All threads must call it.
+// ---- CTA-wide stable LSD radix pass on bits [shift, shift+bits), bits <= 8.  Returns false (nothing moved) if every
+// key has the same digit.  All threads must call it.  Counting is warp-aggregated (__match_any_sync, one shared-memory
+// atomic per distinct digit and warp instruction): the digits of quadtree prefixes are few and heavily repeated, so
+// per-element atomics would serialise on a handful of addresses.
 __device__ bool qt_radix_pass(QtSmem& sm, const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin,
-                              uint32_t* __restrict__ kout, uint32_t* __restrict__ vout, int n, int shift) {
+                              uint32_t* __restrict__ kout, uint32_t* __restrict__ vout, int n, int shift, int bits) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t dmask = (1u << bits) - 1u;
   for (int b = tid; b < 256; b += kQtThreads) sm.hist[b] = 0;
   if (tid == 0) sm.misc[0] = 0;
   __syncthreads();
-  for (int i = tid; i < n; i += kQtThreads) atomicAdd(&sm.hist[(kin[i] >> shift) & 255], 1);
+  for (int base = 0; base < n; base += kQtThreads) {
+    const int i = base + tid;
+    const uint32_t dgt = i < n ? ((kin[i] >> shift) & dmask) : 256u + lane;
+    const uint32_t peers = __match_any_sync(0xffffffffu, dgt);
+    if (i < n && lane == __ffs(peers) - 1) atomicAdd(&sm.hist[dgt], __popc(peers));
+  }
   __syncthreads();
   if (tid < 256 && sm.hist[tid] == n) sm.misc[0] = 1;
   __syncthreads();
@@ -98,18 +106,23 @@ __device__ bool qt_radix_pass(QtSmem& sm, const uint32_t* __restrict__ kin, cons
     for (int k = 0; k < 8; k++) { sm.hist[lane * 8 + k] = run; run += v[k]; }
   }
   __syncthreads();
+  const int nbins = 1 << bits;
   constexpr int kChunk = kQtThreads * kQtItems;
   for (int base = 0; base < n; base += kChunk) {
     const int wbase = base + warp * 32 * kQtItems;
-    for (int b = lane; b < 256; b += 32) sm.warp_cnt[warp][b] = 0;
+    for (int b = lane; b < nbins; b += 32) sm.warp_cnt[warp][b] = 0;
     __syncwarp();
+    uint32_t key[kQtItems], peers[kQtItems];
 #pragma unroll
     for (int it = 0; it < kQtItems; it++) {
       const int i = wbase + it * 32 + lane;
-      if (i < n) atomicAdd(&sm.warp_cnt[warp][(kin[i] >> shift) & 255], 1);
+      key[it] = i < n ? kin[i] : 0u;
+      const uint32_t dgt = i < n ? ((key[it] >> shift) & dmask) : 256u + lane;  // invalid lanes: singleton groups
+      peers[it] = __match_any_sync(0xffffffffu, dgt);
+      if (i < n && lane == __ffs(peers[it]) - 1) atomicAdd(&sm.warp_cnt[warp][dgt], __popc(peers[it]));
     }
     __syncthreads();
-    if (tid < 256) {
+    if (tid < nbins) {
       int run = sm.hist[tid];
 #pragma unroll
       for (int w = 0; w < kQtWarps; w++) {
@@ -124,18 +137,15 @@ __device__ bool qt_radix_pass(QtSmem& sm, const uint32_t* __restrict__ kin, cons
     for (int it = 0; it < kQtItems; it++) {
       const int i = wbase + it * 32 + lane;
       const bool valid = i < n;
-      uint32_t key = 0, val = 0;
-      uint32_t dgt = 256u + lane;  // invalid lanes: unique pseudo-digits so they form singleton groups
-      if (valid) { key = kin[i]; val = vin[i]; dgt = (key >> shift) & 255; }
-      const uint32_t peers = __match_any_sync(0xffffffffu, dgt);
+      const uint32_t dgt = (key[it] >> shift) & dmask;
       int off = 0;
       if (valid) off = sm.warp_cnt[warp][dgt];
       __syncwarp();
       if (valid) {
-        const int rank = __popc(peers & ((1u << lane) - 1u));
-        if (rank == 0) sm.warp_cnt[warp][dgt] = off + __popc(peers);
-        kout[off + rank] = key;
-        vout[off + rank] = val;
+        const int rank = __popc(peers[it] & ((1u << lane) - 1u));
+        if (rank == 0) sm.warp_cnt[warp][dgt] = off + __popc(peers[it]);
+        kout[off + rank] = key[it];
+        vout[off + rank] = vin[i];
       }
       __syncwarp();
     }
@@ -145,12 +155,17 @@ __device__ bool qt_radix_pass(QtSmem& sm, const uint32_t* __restrict__ kin, cons
   return true;
 }
 
-// CTA-wide stable sort of (keys, vals) on bits [lo, nbits) (bits at and above nbits must be zero).  Buffers ping-pong; returns index (0/1) of the buffer
-// holding the result.
+// CTA-wide stable sort of (keys, vals) on bits [lo, nbits) (bits at and above nbits must be zero), in the fewest
+// passes of at most 8 bits, digit widths balanced.  Buffers ping-pong; returns index (0/1) of the buffer holding the
+// result.
 __device__ int qt_sort(QtSmem& sm, uint32_t* k0, uint32_t* v0, uint32_t* k1, uint32_t* v1, int n, int nbits, int lo = 0) {
   int cur = 0;
-  for (int shift = lo; shift < nbits; shift += 8) {
-    const bool moved = cur == 0 ? qt_radix_pass(sm, k0, v0, k1, v1, n, shift) : qt_radix_pass(sm, k1, v1, k0, v0, n, shift);
+  const int total = nbits - lo;
+  if (total <= 0) return 0;
+  const int npass = (total + 7) / 8, width = (total + npass - 1) / npass;
+  for (int p = 0; p < npass; p++) {
+    const int shift = lo + p * width, bits = min(width, nbits - shift);
+    const bool moved = cur == 0 ? qt_radix_pass(sm, k0, v0, k1, v1, n, shift, bits) : qt_radix_pass(sm, k1, v1, k0, v0, n, shift, bits);
     if (moved) cur ^= 1;
   }
   return cur;
@@ -263,6 +278,22 @@ struct StdSortEmu {
         unguarded_linear_insert(i);
       }
     }
+  }
+  // What std::sort leaves in FRONT depends only on the leftmost chain of introsort partitions: the recursion into a
+  // right part [cut, last) never touches anything left of cut, every element right of the leftmost segment is <= all
+  // of its members, and the final insertion sort moves an element forward only past strictly smaller ones.  So the
+  // front is the first maximum, in array order, of the leftmost segment once it is <= 16 long (or a[0] after the
+  // depth-limit heap sort).  Runs the chain on a[0..n) and returns the length of that segment.
+  __device__ int leftmost_segment(int n) {
+    int first = 0, last = n, depth = 2 * (31 - __clz(n));
+    while (last - first > 16) {
+      if (depth == 0) { heap_sort(first, last); return 1; }
+      --depth;
+      const int mid = first + (last - first) / 2;
+      move_median_to_first(first, first + 1, mid, last - 1);
+      last = unguarded_partition(first + 1, last, first);
+    }
+    return last;
   }
   // returns false if the explicit stack overflowed (never for n < 2^31)
   __device__ bool sort(int n) {
@@ -500,6 +531,9 @@ __global__ void __launch_bounds__(kQtThreads) k_quadtree(QtArgs A) {
   // (4b) node records: order key + winner
   uint32_t* NK = K[2];
   uint32_t* NV = V[2];
+  uint32_t* flagged = node_start + M;  // M + #nodes with > 16 members <= n, so the list fits behind node_start
+  if (tid == 0) sm.misc[4] = 0;
+  __syncthreads();
   for (int m = tid; m < M; m += kQtThreads) {
     const int beg = (int)node_start[m];
     const int end = (m + 1 < M) ? (int)node_start[m + 1] : n;
@@ -520,17 +554,38 @@ __global__ void __launch_bounds__(kQtThreads) k_quadtree(QtArgs A) {
       if (i == beg || r > best_resp) { best_resp = r; best_val = v; ties = 1; }
       else if (r == best_resp) ties++;
     }
-    if (end - beg > 16 && ties > 1) {  // introsort decides among tied maxima
-      for (int i = beg; i < end; i++) scratch[i] = ((PV[i] & 255u) << 24) | (uint32_t)(i - beg);
-      StdSortEmu emu{scratch + beg};
-      if (!emu.sort(end - beg)) atomicOr(A.status, kStatusSortDepth);
-      best_val = PV[beg + (int)(scratch[beg] & 0xFFFFFFu)];
-    }
+    if (end - beg > 16 && ties > 1)  // introsort decides among tied maxima: queued for the warps below
+      flagged[atomicAdd(&sm.misc[4], 1)] = (uint32_t)m;
     const uint32_t ps = (s == 0) ? 0u : (pre >> (2 * (D - s)));
     uint32_t mask = 0;
     for (int k = s; k >= 1; k -= 2) mask |= 3u << (2 * (s - k));
     NK[m] = ((uint32_t)(D - s) << (2 * D)) | (ps ^ mask);  // 2D + 4 significant bits
     NV[m] = best_val;
+  }
+  __syncthreads();
+  // (4c) nodes whose winner std::sort decides: one warp per node, members packed (response << 24 | position) into the
+  // warp's slice of shared memory (the radix counters are idle here), lane 0 runs the leftmost partition chain.
+  {
+    const int nflag = sm.misc[4];
+    const int lane = tid & 31, warp = tid >> 5;
+    for (int f = warp; f < nflag; f += kQtWarps) {
+      const int m = (int)flagged[f];
+      const int beg = (int)node_start[m];
+      const int end = (m + 1 < M) ? (int)node_start[m + 1] : n;
+      const int len = end - beg;
+      uint32_t* buf = (len <= 256) ? reinterpret_cast<uint32_t*>(sm.warp_cnt[warp]) : scratch + beg;
+      for (int i = lane; i < len; i += 32) buf[i] = ((PV[beg + i] & 255u) << 24) | (uint32_t)i;
+      __syncwarp();
+      if (lane == 0) {
+        StdSortEmu emu{buf};
+        const int seg = emu.leftmost_segment(len);
+        uint32_t best = buf[0];
+        for (int i = 1; i < seg; i++)
+          if (StdSortEmu::comp(buf[i], best)) best = buf[i];
+        NV[m] = PV[beg + (int)(best & 0xFFFFFFu)];
+      }
+      __syncwarp();
+    }
   }
   __syncthreads();
 
