@@ -447,8 +447,31 @@ int ydorb_extract_batch_device(YdExtractor* ex, const uint8_t* d_images, int wid
   YD_REQUIRE(batch >= 1 && batch <= ex->max_batch, "batch exceeds max_batch");
   YD_REQUIRE(width > 0 && height > 0 && stride >= width && capacity > 0, "bad image geometry");
   YD_CUDA(cudaSetDevice(ex->device));
-  return run_pipeline(ex, d_images, width, height, stride, frame_stride, batch, d_keypoints, d_descriptors, capacity,
-                      d_n_out);
+  int split = (batch >= 64) ? 2 : 1;
+  if (const char* e = getenv("YDORB_DEVICE_SPLIT")) split = std::max(1, std::min(atoi(e), std::min(batch, 16)));  // tuning knob
+  if (ex->profiling || split == 1)
+    return run_pipeline(ex, d_images, width, height, stride, frame_stride, batch, d_keypoints, d_descriptors, capacity,
+                        d_n_out);
+  // Sub-batches alternate between the handle's stream and its second stream: the latency-bound stages of one
+  // (quadtree, small pyramid levels) overlap the issue-bound stages of the other (FAST, describe).  Per-stage events
+  // make no sense here, so profiling mode keeps the serial path above.
+  int rc = set_size(ex, width, height);
+  if (rc != YDORB_OK) return rc;
+  ex->cur_batch = batch;
+  cudaStream_t s = ex->stream;
+  YD_CUDA(cudaEventRecord(ex->ev_fork, s));
+  YD_CUDA(cudaStreamWaitEvent(ex->aux_stream, ex->ev_fork, 0));
+  const int chunk = (batch + split - 1) / split;
+  int k = 0;
+  for (int f0 = 0; f0 < batch; f0 += chunk, k++) {
+    const int n = std::min(chunk, batch - f0);
+    rc = run_stages(ex, f0, n, (k & 1) ? ex->aux_stream : s, d_images + (size_t)f0 * frame_stride, stride, frame_stride,
+                    d_keypoints + (size_t)f0 * capacity, d_descriptors + (size_t)f0 * capacity * 32, capacity, d_n_out + f0);
+    if (rc != YDORB_OK) return rc;
+  }
+  YD_CUDA(cudaEventRecord(ex->ev_join, ex->aux_stream));
+  YD_CUDA(cudaStreamWaitEvent(s, ex->ev_join, 0));
+  return YDORB_OK;
 }
 
 int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int height, int stride, size_t frame_stride,
