@@ -258,6 +258,44 @@ int ydorb_stereo_match(YdMatcher* m, const YdExtractor* left, int left_frame, co
                        const uint8_t* desc_right, int n_right, float bf, float max_d, int mode, float* right_x,
                        float* depth);
 
+/* ---- Map-point side of the front-end (SURVEY 8f "next" rows) --------------------------------------------------- */
+/* MapPoint::computeDistinctiveDescriptors (src/mapPoint.cpp:169-218), batched over map points.  Point p owns the
+ * descriptor rows [start[p], start[p+1]) of desc (what :183-187 collects from the observing key frames).  best[p] =
+ * relative row whose sorted distance vector is least at index int(0.5*n) (first minimum wins, :203-210); -1 if the
+ * point has no rows.  Host pointers; the _device variant takes device pointers and runs on the matcher's stream. */
+int ydorb_distinctive_descriptors(YdMatcher* m, const uint8_t* desc, const int32_t* start, int n_points, int32_t* best);
+int ydorb_distinctive_descriptors_device(YdMatcher* m, const uint8_t* d_desc, const int32_t* d_start, int n_points,
+                                         int32_t* d_best);
+
+/* Camera state Frame::isInCameraFrustum reads (src/frame.cpp:295-326; members set at :273-290 and :60-130) */
+typedef struct {
+  float R[9];             /* m_cvMat_R_c2w, row-major */
+  float t[3];             /* m_cvMat_t_c2w */
+  float origin[3];        /* m_cvMat_origin */
+  float fx, fy, cx, cy;
+  float min_x, max_x, min_y, max_y;
+  float bf;               /* m_flt_baseLineTimesFx */
+  float log_scale_factor; /* m_flt_logScaleFactor */
+  int32_t n_levels;       /* m_int_scaleLevelsNum */
+} YdCamera;
+
+/* what the frustum test reads of one map point: getPosInWorld(), getNormal(), m_flt_maxDistance, m_flt_minDistance */
+typedef struct {
+  float pos[3];
+  float normal[3];
+  float max_distance;
+  float min_distance;
+} YdMapPoint3d;
+
+/* Frame::isInCameraFrustum + MapPoint::predictScaleLevel (src/mapPoint.cpp:265-277) for n map points: out[i] is the
+ * tracking state the reference stores in the map point (m_flt_trackProjX/Y/RightX, m_int_trackScaleLevel,
+ * m_flt_trackViewCos, m_b_isTrackInView), i.e. exactly the input of ydorb_search_by_projection.  Callers filter bad /
+ * already-seen points first (src/tracking.cpp:586-587) or clear `active` afterwards. */
+int ydorb_frustum(YdMatcher* m, const YdCamera* cam, const YdMapPoint3d* map_points, int n, float view_cos_limit,
+                  YdMapPointProj* out);
+int ydorb_frustum_device(YdMatcher* m, const YdCamera* cam, const YdMapPoint3d* d_map_points, int n, float view_cos_limit,
+                         YdMapPointProj* d_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -366,3 +366,29 @@ def search_for_triangulation(kps1, desc1, right_x1, has_mp1, fv1, kps2, desc2, r
     out = out[: len(k1)]
     first = np.nonzero(out >= 0)[0]
     return n, np.stack([first, out[first]], axis=1).astype(np.int32)
+
+
+# ---- SURVEY 8(f) "next" rows (ydorb_oracle_map.cpp)
+MAPPOINT3D_DTYPE = np.dtype([("pos", "<f4", 3), ("normal", "<f4", 3), ("max_distance", "<f4"), ("min_distance", "<f4")])
+
+
+class Camera(C.Structure):
+    _fields_ = [("R", C.c_float * 9), ("t", C.c_float * 3), ("origin", C.c_float * 3), ("fx", C.c_float), ("fy", C.c_float),
+                ("cx", C.c_float), ("cy", C.c_float), ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float),
+                ("max_y", C.c_float), ("bf", C.c_float), ("log_scale_factor", C.c_float), ("n_levels", C.c_int32)]
+
+
+def distinctive_descriptors(desc, start):
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    s = np.ascontiguousarray(start, np.int32)
+    best = np.zeros(len(s) - 1, np.int32)
+    lib().orc_distinctive_descriptors(_p(d), _p(s), len(best), _p(best))
+    return best
+
+
+def frustum(cam, map_points, view_cos_limit=0.5):
+    """cam: any ctypes struct with YdCamera's layout."""
+    mp = np.ascontiguousarray(map_points, MAPPOINT3D_DTYPE)
+    out = np.zeros(len(mp), MPPROJ_DTYPE)
+    lib().orc_frustum(C.byref(cam), _p(mp), len(mp), C.c_float(view_cos_limit), _p(out))
+    return out
