@@ -296,6 +296,65 @@ int ydorb_frustum(YdMatcher* m, const YdCamera* cam, const YdMapPoint3d* map_poi
 int ydorb_frustum_device(YdMatcher* m, const YdCamera* cam, const YdMapPoint3d* d_map_points, int n, float view_cos_limit,
                          YdMapPointProj* d_out);
 
+/* ---- DBoW3 vocabulary transform ------------------------------------------------------------------
+ * Frame::computeBoW (src/frame.cpp:265-272) calls DBoW3::Vocabulary::transform(features, BowVector&, FeatureVector&,
+ * levelsup = 4) (thirdParty/DBow3/src/Vocabulary.cpp:752-816), which descends the k-ary tree once per descriptor
+ * (:836-873: strict `d < best_d`, first child wins ties, node id captured at level L - levelsup). */
+typedef struct YdVocabulary YdVocabulary;
+
+/* The tree as DBoW3 holds it in m_nodes (Vocabulary.h: Node {id, weight, children, parent, descriptor, word_id}).
+ * Node 0 is the root.  children of node i = children[child_start[i] .. child_start[i+1]) in the order of
+ * Node::children (the order the descent visits them); a node without children is a leaf (a word). */
+typedef struct {
+  int32_t n_nodes;
+  int32_t k, L;                /* m_k, m_L */
+  int32_t weighting;           /* DBoW3::WeightingType: 0 TF_IDF, 1 TF, 2 IDF, 3 BINARY (BowVector.h:38-44) */
+  int32_t scoring;             /* DBoW3::ScoringType: 0 L1_NORM, 1 L2_NORM, 2 CHI_SQUARE, 3 KL, 4 BHATTACHARYYA,
+                                  5 DOT_PRODUCT (BowVector.h:47-55) */
+  const int32_t* child_start;  /* [n_nodes + 1] */
+  const int32_t* children;     /* [n_nodes - 1] */
+  const uint8_t* descriptors;  /* [n_nodes][32]; the root's row is never read */
+  const double* weights;       /* [n_nodes] Node::weight */
+  const int32_t* word_ids;     /* [n_nodes] Node::word_id (meaningful for leaves) */
+} YdVocabularyDesc;
+
+/* Result of one transform of n descriptors.  Caller-owned arrays; capacity of the bow_* and fv_node_* arrays is n
+ * (fv_node_start: n + 1).  Per-feature arrays may be NULL when not wanted. */
+typedef struct {
+  int32_t* word_id;      /* [n] WordId of each descriptor (Vocabulary.cpp:870) */
+  int32_t* node_id;      /* [n] NodeId at level L - levelsup (0 = root when L - levelsup <= 0, or when the leaf is
+                            reached above that level, where the reference leaves it uninitialised) */
+  double* weight;        /* [n] Node::weight of the word (:871) */
+  int32_t* bow_ids;      /* BowVector (std::map<WordId, WordValue>) in ascending key order */
+  double* bow_values;
+  int32_t n_bow;
+  int32_t* fv_node_ids;  /* FeatureVector in the CSR form of YdFeatureVector: directly usable by ydorb_search_by_bow */
+  int32_t* fv_node_start;
+  int32_t* fv_items;     /* [n] */
+  int32_t n_fv_nodes;
+} YdBowResult;
+
+#define YDORB_VOC_MAX_FEATURES 16384 /* descriptors per frame one transform accepts */
+
+int ydorb_vocabulary_create(YdMatcher* m, const YdVocabularyDesc* desc, YdVocabulary** out);
+/* Reads the uncompressed binary stream Vocabulary::toStream writes (Vocabulary.cpp:1180-1226; parsed as
+ * Vocabulary::fromStream does, :1335-1409).  QuickLZ-compressed files are refused with YDORB_E_INVALID. */
+int ydorb_vocabulary_load(YdMatcher* m, const char* path, YdVocabulary** out);
+void ydorb_vocabulary_destroy(YdVocabulary* v);
+/* n_nodes, k, L, weighting, scoring, number of words (leaves) */
+int ydorb_vocabulary_info(const YdVocabulary* v, int32_t* info6);
+/* Vocabulary::transform(features, v, fv, levelsup) for one frame; host pointers, n <= YDORB_VOC_MAX_FEATURES. */
+int ydorb_vocabulary_transform(YdVocabulary* v, const uint8_t* descriptors, int n, int levels_up, YdBowResult* out);
+/* Batched, device-resident: frame b owns rows [b*capacity, b*capacity + d_n[b]) of d_desc (the layout
+ * ydorb_extract_batch_device writes) and the same slice of every output array (bow/fv arrays have per-frame stride
+ * `capacity`, d_fv_node_start capacity + 1); d_counts[b] = {n_bow, n_fv_nodes}.  Per-feature outputs may be NULL.
+ * Runs on the matcher's stream without synchronising. */
+int ydorb_vocabulary_transform_batch_device(YdVocabulary* v, const uint8_t* d_desc, const int32_t* d_n, int capacity,
+                                            int batch, int levels_up, int32_t* d_word_id, int32_t* d_node_id,
+                                            double* d_weight, int32_t* d_bow_ids, double* d_bow_values,
+                                            int32_t* d_fv_node_ids, int32_t* d_fv_node_start, int32_t* d_fv_items,
+                                            int32_t* d_counts);
+
 #ifdef __cplusplus
 }
 #endif

@@ -54,7 +54,8 @@ class FrameGeom(C.Structure):
 
 
 def build(force=False):
-    if force or not _SO.exists() or _SO.stat().st_mtime < (_HERE / "ydorb_oracle.cpp").stat().st_mtime:
+    srcs = [_HERE / f for f in ("ydorb_oracle.cpp", "ydorb_oracle_map.cpp", "ydorb_oracle_bow.cpp", "ydorb_oracle.h")]
+    if force or not _SO.exists() or _SO.stat().st_mtime < max(f.stat().st_mtime for f in srcs):
         subprocess.check_call(["make", "-C", str(_HERE)], stdout=subprocess.DEVNULL)
     return _SO
 
@@ -392,3 +393,37 @@ def frustum(cam, map_points, view_cos_limit=0.5):
     out = np.zeros(len(mp), MPPROJ_DTYPE)
     lib().orc_frustum(C.byref(cam), _p(mp), len(mp), C.c_float(view_cos_limit), _p(out))
     return out
+
+
+class Vocabulary(C.Structure):
+    """OrcVocabulary: the DBoW3 tree in flat form (same layout as include/ydorb.h YdVocabularyDesc)."""
+
+    _fields_ = [("n_nodes", C.c_int32), ("k", C.c_int32), ("L", C.c_int32), ("weighting", C.c_int32), ("scoring", C.c_int32),
+                ("child_start", C.c_void_p), ("children", C.c_void_p), ("descriptors", C.c_void_p), ("weights", C.c_void_p),
+                ("word_ids", C.c_void_p)]
+
+    @classmethod
+    def from_arrays(cls, k, L, weighting, scoring, child_start, children, descriptors, weights, word_ids):
+        v = cls()
+        v._keep = (np.ascontiguousarray(child_start, np.int32), np.ascontiguousarray(children, np.int32),
+                   np.ascontiguousarray(descriptors, np.uint8), np.ascontiguousarray(weights, np.float64),
+                   np.ascontiguousarray(word_ids, np.int32))
+        v.n_nodes = len(v._keep[3])
+        v.k, v.L, v.weighting, v.scoring = k, L, weighting, scoring
+        v.child_start, v.children, v.descriptors, v.weights, v.word_ids = (a.ctypes.data for a in v._keep)
+        return v
+
+
+def voc_transform(voc, desc, levels_up=4):
+    """DBoW3::Vocabulary::transform(features, v, fv, levelsup).  Returns a dict with the per-feature (word_id, node_id,
+    weight), the BowVector (bow_ids, bow_values) and the FeatureVector in CSR form (fv_node_ids, fv_node_start, fv_items)."""
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    n = len(d)
+    word, node, wgt = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n, np.float64)
+    bi, bv = np.zeros(n, np.int32), np.zeros(n, np.float64)
+    fi, fs, ft = np.zeros(n, np.int32), np.zeros(n + 1, np.int32), np.zeros(n, np.int32)
+    nb, nf = C.c_int32(0), C.c_int32(0)
+    lib().orc_voc_transform(C.byref(voc), _p(d), n, levels_up, _p(word), _p(node), _p(wgt), _p(bi), _p(bv), C.byref(nb),
+                            _p(fi), _p(fs), _p(ft), C.byref(nf))
+    return dict(word_id=word, node_id=node, weight=wgt, bow_ids=bi[: nb.value], bow_values=bv[: nb.value],
+                fv_node_ids=fi[: nf.value], fv_node_start=fs[: nf.value + 1], fv_items=ft[: int(fs[nf.value])])

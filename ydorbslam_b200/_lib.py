@@ -92,7 +92,8 @@ def lib():
         _lib.ydorb_extractor_stream.restype = C.c_void_p
         _lib.ydorb_matcher_stream.restype = C.c_void_p
         _lib.ydorb_kernel_launches.restype = C.c_longlong
-        for name in ("ydorb_extractor_destroy", "ydorb_matcher_destroy", "ydorb_frame_destroy", "ydorb_three_maxima"):
+        for name in ("ydorb_extractor_destroy", "ydorb_matcher_destroy", "ydorb_frame_destroy", "ydorb_three_maxima",
+                     "ydorb_vocabulary_destroy"):
             getattr(_lib, name).restype = None
     return _lib
 

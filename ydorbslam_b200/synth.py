@@ -177,3 +177,104 @@ def synth_feature_vector(desc, seed, bits=6, drop_every=5):
         items.extend(members.tolist())
         start.append(len(items))
     return ids.astype(np.int32), np.asarray(start, np.int32), np.asarray(items, np.int32)
+
+
+def synth_vocabulary(k=10, L=6, seed=11, flip=0.18, stop_fraction=0.02, prune=0.0, shuffle_children=False):
+    """A DBoW3-shaped vocabulary tree in the flat form of include/ydorb.h YdVocabularyDesc.
+
+    Nodes are numbered breadth-first (root 0).  A child's descriptor is its parent's with every bit flipped with
+    probability `flip` (what hierarchical k-medians leaves behind: siblings close to each other, far from other
+    subtrees).  `prune` makes that fraction of interior nodes leaves (ragged depth); `shuffle_children` permutes each
+    node's child order so that it differs from id order (a tree loaded from a stream, Vocabulary.cpp:1382-1393).
+    Words are numbered in ascending node id (Vocabulary.cpp createWords); a leaf's weight is an idf-like positive double,
+    0 for `stop_fraction` of them (stopped words, `if (w > 0)` at :781)."""
+    parent = [0]
+    level = [0]
+    desc = [np.zeros(32, np.uint8)]
+    desc[0][:] = rand_bytes(seed, 1, 32)
+    frontier = [0]
+    u = lambda stream, n: rand_u64(seed, stream, n).astype(np.float64) / 2.0**64
+    for lv in range(1, L + 1):
+        pr = u(100 + lv, len(frontier))
+        keep = [p for j, p in enumerate(frontier) if lv == 1 or pr[j] >= prune]
+        if not keep:
+            break
+        nk = len(keep) * k
+        bits = (rand_u64(seed, 200 + lv, nk * 256).astype(np.float64) / 2.0**64 < flip).reshape(nk, 256)
+        masks = np.packbits(bits, axis=1, bitorder="little")
+        base = len(parent)
+        pd = np.stack([desc[p] for p in keep]).repeat(k, axis=0)
+        cd = pd ^ masks
+        for j in range(nk):
+            parent.append(keep[j // k])
+            level.append(lv)
+            desc.append(cd[j])
+        frontier = list(range(base, base + nk))
+    n = len(parent)
+    parent = np.asarray(parent, np.int32)
+    descriptors = np.stack(desc).astype(np.uint8)
+    order = np.arange(1, n)
+    if shuffle_children:
+        order = order[np.argsort(rand_u64(seed, 3, n - 1), kind="stable")]
+    order = order[np.argsort(parent[order], kind="stable")]  # grouped by parent, shuffled (or id) order inside
+    counts = np.bincount(parent[1:], minlength=n)
+    child_start = np.zeros(n + 1, np.int32)
+    child_start[1:] = np.cumsum(counts)
+    children = order.astype(np.int32)
+    leaf = counts == 0
+    word_ids = np.zeros(n, np.int32)
+    word_ids[leaf] = np.arange(int(leaf.sum()), dtype=np.int32)
+    weights = np.zeros(n, np.float64)
+    w = np.log(1.0 + 1.0 / (u(4, n) + 1e-3))
+    w[u(5, n) < stop_fraction] = 0.0
+    weights[leaf] = w[leaf]
+    return dict(k=k, L=L, child_start=child_start, children=children, descriptors=descriptors, weights=weights,
+                word_ids=word_ids, parent=parent)
+
+
+def synth_vocabulary_full(k=10, L=6, seed=11, flip=0.18, stop_fraction=0.02):
+    """synth_vocabulary without pruning/shuffling, fully vectorised: the 1 111 111-node k=10, L=6 tree takes seconds."""
+    starts = [0]
+    for lv in range(1, L + 2):
+        starts.append(starts[-1] + k ** (lv - 1))
+    n = starts[L + 1]
+    descriptors = np.zeros((n, 32), np.uint8)
+    descriptors[0] = rand_bytes(seed, 1, 32)
+    for lv in range(1, L + 1):
+        a, b = starts[lv], starts[lv + 1]
+        nk = b - a
+        out = np.empty((nk, 32), np.uint8)
+        step = 1 << 16
+        for c in range(0, nk, step):
+            m = min(step, nk - c)
+            bits = (rand_u64(seed * 1000003 + lv, c, m * 256) >> np.uint64(40)).astype(np.float64) / 2.0**24 < flip
+            out[c : c + m] = np.packbits(bits.reshape(m, 256), axis=1, bitorder="little")
+        par = descriptors[starts[lv - 1] : starts[lv]].repeat(k, axis=0)
+        descriptors[a:b] = par ^ out
+    child_start = np.zeros(n + 1, np.int64)
+    interior = starts[L]
+    child_start[1 : interior + 1] = np.arange(1, interior + 1, dtype=np.int64) * k
+    child_start[interior + 1 :] = n - 1
+    children = np.arange(1, n, dtype=np.int32)
+    word_ids = np.zeros(n, np.int32)
+    word_ids[interior:] = np.arange(n - interior, dtype=np.int32)
+    uu = lambda stream: rand_u64(seed, stream, n).astype(np.float64) / 2.0**64
+    weights = np.zeros(n, np.float64)
+    w = np.log(1.0 + 1.0 / (uu(4) + 1e-3))
+    w[uu(5) < stop_fraction] = 0.0
+    weights[interior:] = w[interior:]
+    return dict(k=k, L=L, child_start=child_start.astype(np.int32), children=children, descriptors=descriptors,
+                weights=weights, word_ids=word_ids)
+
+
+def synth_vocabulary_queries(voc, n, seed=12, flip=0.06):
+    """n descriptors near random words of `voc` (leaf descriptor with `flip` of its bits toggled), half of them plain
+    uniform noise so that the descent also sees far-from-everything inputs and ties."""
+    leaves = np.flatnonzero(np.diff(voc["child_start"]) == 0)
+    pick = leaves[(rand_u64(seed, 1, n) % np.uint64(len(leaves))).astype(np.int64)]
+    bits = (rand_u64(seed, 2, n * 256).astype(np.float64) / 2.0**64 < flip).reshape(n, 256)
+    q = voc["descriptors"][pick] ^ np.packbits(bits, axis=1, bitorder="little")
+    noise = rand_bytes(seed, 3, n * 32).reshape(n, 32)
+    use_noise = (rand_u64(seed, 4, n) & np.uint64(1)).astype(bool)
+    q[use_noise] = noise[use_noise]
+    return np.ascontiguousarray(q, np.uint8)
