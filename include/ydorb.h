@@ -355,6 +355,49 @@ int ydorb_vocabulary_transform_batch_device(YdVocabulary* v, const uint8_t* d_de
                                             int32_t* d_fv_node_ids, int32_t* d_fv_node_start, int32_t* d_fv_items,
                                             int32_t* d_counts);
 
+/* ---- Input pre-processing around extraction -----------------------------------------------------
+ * The steps Tracking::grabImageStereo / grabImageRGBD and the Frame constructors run right before and after
+ * extractAndCompute.  They use a YdMatcher handle only as the owner of a device and a stream. */
+#define YDORB_RGB2GRAY 0  /* cv::COLOR_RGB2GRAY  (src/tracking.cpp:75, :99)  */
+#define YDORB_BGR2GRAY 1  /* cv::COLOR_BGR2GRAY  (:83, :105)                 */
+#define YDORB_RGBA2GRAY 2 /* cv::COLOR_RGBA2GRAY (:78, :101)                 */
+#define YDORB_BGRA2GRAY 3 /* cv::COLOR_BGRA2GRAY (:86, :107)                 */
+
+/* cv::cvtColor(src, dst, code) on 8-bit images: gray = (R*9798 + G*19235 + B*3735 + 2^14) >> 15 (OpenCV's 8-bit
+ * fixed-point path; pinned against cv2 4.13.0).  Host pointers, strides in bytes. */
+int ydorb_cvt_gray(YdMatcher* m, const uint8_t* src, int width, int height, int src_stride, int code, uint8_t* dst,
+                   int dst_stride);
+/* batched, device pointers, asynchronous on the matcher's stream; dst can be handed to ydorb_extract_batch_device */
+int ydorb_cvt_gray_device(YdMatcher* m, const uint8_t* d_src, int width, int height, int src_stride, size_t src_frame_stride,
+                          int code, uint8_t* d_dst, int dst_stride, size_t dst_frame_stride, int batch);
+
+/* cv::undistortPoints(pts, pts, K, dist, cv::Mat(), P) as Frame::undistortKeyPoints and Frame::computeImageBounds call it
+ * (src/frame.cpp:193-213, :224-248): 5 fixed-point iterations in double, result rounded to float.  K, P: row-major
+ * 3x3 CV_32F; dist: k1 k2 p1 p2 [k3 [k4 k5 k6 [s1 s2 s3 s4]]] (n_dist in {4, 5, 8, 12}).  xy / xy_out: n (x, y) pairs
+ * (may alias).  The caller keeps the reference's `if (dist[0] != 0)` guard.  Host pointers. */
+int ydorb_undistort_points(YdMatcher* m, const float* xy, int n, const float* K, const float* dist, int n_dist,
+                           const float* P, float* xy_out);
+/* Frame::undistortKeyPoints in place on the layout ydorb_extract_batch_device writes (pt.x, pt.y of the first d_n[b]
+ * key points of every frame); a no-op when dist[0] == 0, like the reference (:194).  Device pointers, asynchronous. */
+int ydorb_undistort_keypoints_device(YdMatcher* m, YdKeyPoint* d_keypoints, const int32_t* d_n, int capacity, int batch,
+                                     const float* K, const float* dist, int n_dist, const float* P);
+
+#define YDORB_DEPTH_U16 0 /* CV_16U depth map (TUM RGB-D) */
+#define YDORB_DEPTH_F32 1 /* CV_32F depth map */
+/* Frame::computeStereoFromRGBD (src/frame.cpp:214-223) fused with the depthImage.convertTo(CV_32F, depth_map_factor) of
+ * Tracking::grabImageRGBD (src/tracking.cpp:109-111): instead of converting the whole depth map, only the n pixels
+ * under the (already undistorted) key points are read: d = (float)raw * factor (the factor is skipped for a CV_32F map
+ * when |factor - 1| <= 1e-5, as at :109); d > 0 -> depth[i] = d, right_x[i] = pt.x - bf / d; else both -1.  The pixel
+ * is ((int)pt.y, (int)pt.x) as `at<float>(float, float)` truncates; a key point undistorted to outside the map (where
+ * the reference reads out of bounds) gets -1.  Host pointers; depth_stride in bytes. */
+int ydorb_stereo_from_rgbd(YdMatcher* m, const YdKeyPoint* keypoints, int n, const void* depth_map, int depth_type,
+                           int width, int height, int depth_stride, float depth_map_factor, float bf, float* right_x,
+                           float* depth);
+int ydorb_stereo_from_rgbd_device(YdMatcher* m, const YdKeyPoint* d_keypoints, const int32_t* d_n, int capacity, int batch,
+                                  const void* d_depth_maps, int depth_type, int width, int height, int depth_stride,
+                                  size_t depth_frame_stride, float depth_map_factor, float bf, float* d_right_x,
+                                  float* d_depth);
+
 #ifdef __cplusplus
 }
 #endif

@@ -54,7 +54,7 @@ class FrameGeom(C.Structure):
 
 
 def build(force=False):
-    srcs = [_HERE / f for f in ("ydorb_oracle.cpp", "ydorb_oracle_map.cpp", "ydorb_oracle_bow.cpp", "ydorb_oracle.h")]
+    srcs = [_HERE / f for f in ("ydorb_oracle.cpp", "ydorb_oracle_map.cpp", "ydorb_oracle_bow.cpp", "ydorb_oracle_pre.cpp", "ydorb_oracle.h")]
     if force or not _SO.exists() or _SO.stat().st_mtime < max(f.stat().st_mtime for f in srcs):
         subprocess.check_call(["make", "-C", str(_HERE)], stdout=subprocess.DEVNULL)
     return _SO
@@ -427,3 +427,31 @@ def voc_transform(voc, desc, levels_up=4):
                             _p(fi), _p(fs), _p(ft), C.byref(nf))
     return dict(word_id=word, node_id=node, weight=wgt, bow_ids=bi[: nb.value], bow_values=bv[: nb.value],
                 fv_node_ids=fi[: nf.value], fv_node_start=fs[: nf.value + 1], fv_items=ft[: int(fs[nf.value])])
+
+
+def cvt_gray(img, code):
+    """cv::cvtColor(img, code) for code 0 RGB2GRAY, 1 BGR2GRAY, 2 RGBA2GRAY, 3 BGRA2GRAY on (h, w, 3|4) uint8."""
+    a = np.ascontiguousarray(img, np.uint8)
+    h, w, ch = a.shape
+    assert ch == (4 if code >= 2 else 3)
+    out = np.zeros((h, w), np.uint8)
+    lib().orc_cvt_gray(_p(a), w, h, w * ch, code, _p(out), w)
+    return out
+
+
+def undistort_points(xy, K, dist, P):
+    pts = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    Kf, Pf, df = (np.ascontiguousarray(v, np.float32).ravel() for v in (K, P, dist))
+    out = np.zeros_like(pts)
+    lib().orc_undistort_points(_p(pts), len(pts), _p(Kf), _p(df), len(df), _p(Pf), _p(out))
+    return out
+
+
+def stereo_from_rgbd(kps, depth_map, factor, bf):
+    k = np.ascontiguousarray(kps, KP_DTYPE)
+    d = np.ascontiguousarray(depth_map)
+    assert d.dtype in (np.uint16, np.float32)
+    rx, dz = np.zeros(len(k), np.float32), np.zeros(len(k), np.float32)
+    lib().orc_stereo_from_rgbd(_p(k), len(k), _p(d), 0 if d.dtype == np.uint16 else 1, d.shape[1], d.shape[0], d.strides[0],
+                               C.c_float(factor), C.c_float(bf), _p(rx), _p(dz))
+    return rx, dz

@@ -40,7 +40,7 @@ fi = torch.zeros((B, cap), dtype=torch.int32, device=dev)
 fs = torch.zeros((B, cap + 1), dtype=torch.int32, device=dev)
 ft = torch.zeros((B, cap), dtype=torch.int32, device=dev)
 cnt = torch.zeros((B, 2), dtype=torch.int32, device=dev)
-stream = torch.cuda.ExternalStream(m.stream())
+stream = torch.cuda.ExternalStream(m.stream)
 torch.cuda.synchronize()
 
 
