@@ -171,6 +171,11 @@ def run_gpu(args):
     from ydorbslam_b200._lib import lib
 
     rank, world, local = dist_env()
+    # stdout carries exactly one JSON line: anything libraries print there (NCCL's version banner under NCCL_DEBUG) goes
+    # to stderr instead while the run lasts
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     torch.cuda.set_device(local)
@@ -414,7 +419,8 @@ def run_gpu(args):
             if names[dom] in tr.get("bytes_per_frame", {}):
                 line["roofline"]["traffic"] = tr["bytes_per_frame"][names[dom]] * B
                 line["roofline"]["traffic_source"] = tr.get("source")
-        print(json.dumps(line))
+        real_stdout.write(json.dumps(line) + "\n")
+        real_stdout.flush()
     if world > 1:
         dist.destroy_process_group()
     return 0
