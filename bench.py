@@ -27,6 +27,7 @@ W, H, NFEAT = 640, 480, 1000
 EXTRACTOR_ARGS = (NFEAT, 1.2, 8, 20, 7)
 RATIO, TH_LOW = 0.6, 50
 HAMMING_NQ, HAMMING_NDB = 2000, 1_000_000
+E2E_THREADS = int(os.environ.get("YDORB_E2E_THREADS", "4"))  # host threads (one extractor + matcher handle each) of the e2e leg
 
 
 def level_sizes(w, h, n_levels=8, scale=1.2):
@@ -252,9 +253,13 @@ def run_gpu(args):
     ms_total = float(t.item())
     value = world * B * K / (ms_total * 1e-3)
 
-    # ---- e2e: host buffers through the host-pointer C-ABI calls, H2D/D2H inside the timed region
+    # ---- e2e: host buffers through the host-pointer C-ABI calls, H2D/D2H inside the timed region.
+    # E2E_THREADS host threads each own an extractor + matcher handle and a contiguous share of every step's frames and
+    # run their K steps back to back (the reference drives its left and right extractor from two concurrent threads,
+    # src/frame.cpp:84-87): one handle's upload overlaps another's kernels.  The single-thread figure is reported too.
     from ydorbslam_b200._lib import KP_DTYPE, TOP2_DTYPE, check, ptr
     import ctypes as C
+    import threading
 
     ex.set_stream(None)
     m.set_stream(None)
@@ -264,32 +269,64 @@ def run_gpu(args):
     h_n = torch.zeros(B, dtype=torch.int32).pin_memory()
     h_top2 = torch.zeros(B, cap, 4, dtype=torch.int32).pin_memory()
     h_acc = torch.zeros(B, cap, dtype=torch.uint8).pin_memory()
-    qf = np.arange(B, dtype=np.int32)
-    df = ((np.arange(B) - 1) % B).astype(np.int32)
 
-    def e2e_step():
-        check(lib().ydorb_extract_batch(ex._h, C.c_void_p(h_img.data_ptr()), W, H, W, C.c_size_t(W * H), B,
-                                        C.c_void_p(h_kps.data_ptr()), C.c_void_p(h_desc.data_ptr()), cap,
-                                        C.c_void_p(h_n.data_ptr())))
-        check(lib().ydorb_match_frames(m._h, ex._h, ptr(qf), ptr(df), B, C.c_float(RATIO), TH_LOW,
-                                       C.c_void_p(h_top2.data_ptr()), C.c_void_p(h_acc.data_ptr())))
+    def make_worker(exh, mh, f0, n):
+        qf = np.arange(n, dtype=np.int32)
+        df = ((np.arange(n) - 1) % n).astype(np.int32)
 
-    for _ in range(max(Wm, 1)):
-        e2e_step()
-    barrier()
+        def run(steps):
+            for _ in range(steps):
+                check(lib().ydorb_extract_batch(exh._h, C.c_void_p(h_img[f0:].data_ptr()), W, H, W, C.c_size_t(W * H), n,
+                                                C.c_void_p(h_kps[f0:].data_ptr()), C.c_void_p(h_desc[f0:].data_ptr()), cap,
+                                                C.c_void_p(h_n[f0:].data_ptr())))
+                check(lib().ydorb_match_frames(mh._h, exh._h, ptr(qf), ptr(df), n, C.c_float(RATIO), TH_LOW,
+                                               C.c_void_p(h_top2[f0:].data_ptr()), C.c_void_p(h_acc[f0:].data_ptr())))
+
+        return run
+
+    def timed(workers, steps):
+        errs = []
+
+        def guard(w):
+            try:
+                w(steps)
+            except Exception as e:  # noqa: BLE001
+                errs.append(e)
+
+        th = [threading.Thread(target=guard, args=(w,)) for w in workers]
+        t0 = time.perf_counter()
+        for x in th:
+            x.start()
+        for x in th:
+            x.join()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if errs:
+            raise errs[0]
+        return dt
+
     ke = max(min(K, 10), 1)
-    t0 = time.perf_counter()
-    for _ in range(ke):
-        e2e_step()
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * B * ke / float(t.item())
+
+    def e2e_measure(workers):
+        timed(workers, max(Wm, 1))
+        barrier()
+        t = torch.tensor([timed(workers, ke)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return world * B * ke / float(t.item())
+
+    e2e_single = e2e_measure([make_worker(ex, m, 0, B)])
+    assert np.array_equal(h_n.numpy(), n_kp), "host-API and device-API keypoint counts differ"
+    T = max(1, min(E2E_THREADS, B // 8))
+    bounds = [B * t // T for t in range(T + 1)]
+    handles = [(OrbExtractor(*EXTRACTOR_ARGS, max_width=W, max_height=H, max_batch=bounds[t + 1] - bounds[t], device=local),
+                OrbMatcher(RATIO, device=local)) for t in range(T)]
+    h_n.zero_()
+    e2e_value = e2e_measure([make_worker(handles[t][0], handles[t][1], bounds[t], bounds[t + 1] - bounds[t]) for t in range(T)])
+    assert np.array_equal(h_n.numpy(), n_kp), "threaded host-API and device-API keypoint counts differ"
+    del handles
     h2d = B * W * H + 2 * 4 * B
     d2h = B * cap * (28 + 32) + 4 * B + B * cap * (16 + 1)
-    assert np.array_equal(h_n.numpy(), n_kp), "host-API and device-API keypoint counts differ"
 
     # ---- secondary metric: Hamming top-2, 2000 queries x 1M database rows sharded over the ranks
     ham = None
@@ -383,7 +420,10 @@ def run_gpu(args):
                        "l2": f"working set {B} x (input 0.31 MB + pyramid 1.2 MB) > 126 MB L2, no flush"},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "timing": "host wall clock around the synchronous host-pointer C-ABI calls, pinned buffers"},
+                    "timing": f"host wall clock around the synchronous host-pointer C-ABI calls (ydorb_extract_batch + "
+                              f"ydorb_match_frames), pinned buffers; {T} host threads, each with its own extractor + matcher "
+                              "handle and 1/T of every step's frames, steps back to back per thread",
+                    "host_threads": T, "single_thread_value": e2e_single},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,

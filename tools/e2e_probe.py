@@ -57,3 +57,28 @@ print("match_frames   ms", timeit(mat))
 print("both           ms", timeit(lambda: (ext(), mat())))
 print("H2D 78.6MB     ms", timeit(lambda: d_img.copy_(h_img, non_blocking=True)))
 print("D2H 15.4MB     ms", timeit(lambda: h_out.copy_(d_out, non_blocking=True)))
+
+# ---- two handles driven from two host threads (the reference runs its left and right extractor concurrently on two
+# instances, src/frame.cpp:84-87): each thread owns half of the step's frames; one pipeline's fill/drain overlaps the
+# other's kernels
+from concurrent.futures import ThreadPoolExecutor
+
+for T in (2, 4):
+    Bh = B // T
+    exs = [OrbExtractor(*bench.EXTRACTOR_ARGS, max_width=W, max_height=H, max_batch=Bh, device=0) for _ in range(T)]
+    ms = [OrbMatcher(0.6, device=0) for _ in range(T)]
+    qh = np.arange(Bh, dtype=np.int32)
+    dh = ((np.arange(Bh) - 1) % Bh).astype(np.int32)
+
+    def half(t):
+        o = t * Bh
+        check(lib().ydorb_extract_batch(exs[t]._h, C.c_void_p(h_img[o:].data_ptr()), W, H, W, C.c_size_t(W * H), Bh,
+                                        C.c_void_p(h_kps[o:].data_ptr()), C.c_void_p(h_desc[o:].data_ptr()), cap,
+                                        C.c_void_p(h_n[o:].data_ptr())))
+        check(lib().ydorb_match_frames(ms[t]._h, exs[t]._h, ptr(qh), ptr(dh), Bh, C.c_float(0.6), 50,
+                                       C.c_void_p(h_top2[o:].data_ptr()), C.c_void_p(h_acc[o:].data_ptr())))
+
+    pool = ThreadPoolExecutor(T)
+    print(f"{T} handles / {T} threads, both  ms", timeit(lambda: list(pool.map(half, range(T)))))
+    pool.shutdown()
+    del exs, ms

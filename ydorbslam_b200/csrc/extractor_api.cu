@@ -1,6 +1,7 @@
 // C ABI of the extractor (include/ydorb.h): handle life cycle, per-size geometry and OpenCV-compatible resize
 // tables built on the host, stage orchestration on the handle's stream.
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <atomic>
 #include <cmath>
@@ -509,16 +510,35 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
     // compute streams take the sub-batches alternately (one's small tail kernels overlap the other's wide ones), a
     // copy-out stream returns each sub-batch's results as soon as they exist.  Outputs have the caller's layout
     // (capacity == quota sum), so results are copied back in bulk without knowing the counts.
-    int nchunks = std::min(8, std::max(2, batch / 32));
-    if (const char* e = getenv("YDORB_HOST_CHUNKS")) nchunks = std::min(16, std::max(1, atoi(e)));  // tuning knob
-    const int chunk = (batch + nchunks - 1) / nchunks;
+    // Sub-batch plan (measured on a B200, tools/chunk_probe.py and tools/e2e_threads_probe.py): sub-batches of 32-64
+    // frames keep the grids wide enough while the first upload stays short; a handle that is one of several driven
+    // from concurrent host threads (small batch each) does best with two sub-batches.
+    // YDORB_HOST_PLAN="16,48,64,..." (frames per sub-batch, last value repeats) and YDORB_HOST_CHUNKS=n (n equal
+    // sub-batches) are tuning knobs.
+    int plan[16], nplan = 0;
+    if (const char* e = getenv("YDORB_HOST_PLAN")) {
+      for (const char* q = e; *q && nplan < 16;) {
+        const int v = atoi(q);
+        if (v > 0) plan[nplan++] = v;
+        while (*q && *q != ',') q++;
+        if (*q == ',') q++;
+      }
+    }
+    if (nplan == 0) {
+      int nchunks = batch >= 192 ? 6 : 2;
+      if (const char* e = getenv("YDORB_HOST_CHUNKS")) nchunks = std::min(16, std::max(1, atoi(e)));
+      plan[nplan++] = (batch + nchunks - 1) / nchunks;
+    }
+    static const bool trace = getenv("YDORB_HOST_TRACE") != nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
     YD_CUDA(cudaEventRecord(ex->ev_fork, s));
     YD_CUDA(cudaStreamWaitEvent(ex->aux_stream, ex->ev_fork, 0));
     YD_CUDA(cudaStreamWaitEvent(ex->in_stream, ex->ev_fork, 0));
     YD_CUDA(cudaStreamWaitEvent(ex->out_stream, ex->ev_fork, 0));
     int k = 0;
-    for (int f0 = 0; f0 < batch; f0 += chunk, k++) {
-      const int n = std::min(chunk, batch - f0);
+    for (int f0 = 0; f0 < batch; k++) {
+      int n = std::min(plan[std::min(k, nplan - 1)], batch - f0);
+      if (k == 15) n = batch - f0;  // event slots: at most 16 sub-batches
       cudaStream_t st = (k & 1) ? ex->aux_stream : s;
       if ((rc = upload(f0, n, ex->in_stream)) != YDORB_OK) return rc;
       YD_CUDA(cudaEventRecord(ex->ev_in[k], ex->in_stream));
@@ -533,11 +553,19 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
                               cudaMemcpyDeviceToHost, ex->out_stream));
       YD_CUDA(cudaMemcpyAsync(descriptors + (size_t)f0 * dcap * 32, ex->d_desc + (size_t)f0 * dcap * 32, (size_t)32 * n * dcap,
                               cudaMemcpyDeviceToHost, ex->out_stream));
+      f0 += n;
     }
     // the copy-out stream has waited for every sub-batch of both compute streams: joining it joins everything
     YD_CUDA(cudaEventRecord(ex->ev_join, ex->out_stream));
     YD_CUDA(cudaStreamWaitEvent(s, ex->ev_join, 0));
+    const auto t_issued = std::chrono::steady_clock::now();
     YD_CUDA(cudaStreamSynchronize(s));
+    if (trace) {
+      const auto t_end = std::chrono::steady_clock::now();
+      fprintf(stderr, "[ydorb] extract_batch: %d sub-batches, issue %.3f ms, total %.3f ms\n", k,
+              std::chrono::duration<double, std::milli>(t_issued - t_begin).count(),
+              std::chrono::duration<double, std::milli>(t_end - t_begin).count());
+    }
     return check_status(ex);
   }
   if ((rc = upload(0, batch, s)) != YDORB_OK) return rc;
