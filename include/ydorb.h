@@ -7,7 +7,8 @@
  *   YDORBSLAM::Frame hooks    (src/frame.hpp:83,96,166: computeStereoMatches, getKeyPointsInArea,
  *                              assignKeyPointsToGrid)
  * Each entry point below names the reference member it replaces.  INTEGRATION.md shows the C++ shim a
- * maintainer adds on the reference side (ydorbslam_b200/cpp/ydorb.hpp is that shim without OpenCV types).
+ * maintainer adds on the reference side (include/ydorb.hpp is that shim without OpenCV types; tests/cpp/shim_check.cpp
+ * drives it and tests/test_cpp_shim.py checks its outputs against the oracle).
  *
  * Conventions: plain pointers and sizes, no exceptions, int status return (0 = ok, <0 = YDORB_E_*),
  * caller-owned output buffers.  "host" entry points take host memory and synchronise before returning;
