@@ -40,12 +40,14 @@ struct QtSmem {
   int misc[8];
 };
 
-// path code of a point (coordinates relative to the 16 px border), divideNode geometry :7-33
+// path code of a point (coordinates relative to the 16 px border), divideNode geometry :7-33.  NDIG leading digits are
+// computed; the result is always aligned like a full kQtDig-digit code (missing low digits are zero).
+template <int NDIG = kQtDig>
 __device__ __forceinline__ uint32_t qt_code(int x, int y, int rootw, int rooth) {
   int tlx = 0, trx = rootw, tly = 0, bly = rooth;
   uint32_t code = 0;
 #pragma unroll
-  for (int d = 0; d < kQtDig; d++) {
+  for (int d = 0; d < NDIG; d++) {
     const int cx = (trx + tlx + 1) >> 1;  // ceil(float(a+b)/2.0), a+b >= 0
     const int cy = (bly + tly + 1) >> 1;
     const bool right = x >= cx, low = y >= cy;
@@ -56,7 +58,7 @@ __device__ __forceinline__ uint32_t qt_code(int x, int y, int rootw, int rooth) 
     else { q = 3; const int t = tly; tlx = cx; tly = cy; bly = t; }  // F6: child-4 bl.y := parent tl.y
     code = (code << 2) | q;
   }
-  return code;
+  return code << (2 * (kQtDig - NDIG));
 }
 
 // number of common leading digits of two ndig-digit values
@@ -388,7 +390,7 @@ __device__ void qt_fill(const QtArgs& A, const LevelGeom& lv, int frame, int lev
     const int pos0 = rank[c] - level_base;
     for (int e = lane; e < cnt; e += 32) {
       const uint32_t r = raw[start + e];  // y:12 | x:12 | response:8, border-relative coordinates
-      const uint32_t code = qt_code((int)((r >> 8) & 4095u), (int)(r >> 20), lv.root_w, lv.root_h);
+      const uint32_t code = qt_code<kQtDig>((int)((r >> 8) & 4095u), (int)(r >> 20), lv.root_w, lv.root_h);
       keys[pos0 + e] = code;
       vals[pos0 + e] = r;
       const uint32_t p8 = code >> (kQtBits - 2 * kQtMapDig);
@@ -398,7 +400,33 @@ __device__ void qt_fill(const QtArgs& A, const LevelGeom& lv, int frame, int lev
   }
 }
 
-__global__ void __launch_bounds__(kQtThreads) k_quadtree(QtArgs A) {
+// Path codes of every candidate of every frame, written at the candidate-order position the quadtree CTA expects
+// (keys[0] / vals[0]).  One warp per (frame, cell); only the kQtMapDig leading digits are computed here -- all the
+// common case needs (depth <= 8) -- so this instruction-heavy step runs across the whole GPU instead of inside the one
+// CTA that owns a (level, frame) segment.  The rare deeper case recomputes full codes inside k_quadtree (qt_fill).
+constexpr int kCodeWarps = 8;
+__global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
+  const FrameGeomDev* g = A.g;
+  const int frame = blockIdx.y, lane = threadIdx.x & 31;
+  const int c = blockIdx.x * kCodeWarps + (threadIdx.x >> 5);  // cell index within the frame
+  if (c >= g->n_cells) return;
+  const int cnt = A.cell_count[(size_t)frame * g->n_cells + c];
+  if (cnt == 0) return;
+  int level = 0;
+  for (int l = 1; l < g->n_levels; l++)
+    if (c >= g->lv[l].cell_base) level = l;
+  const int root_w = g->lv[level].root_w, root_h = g->lv[level].root_h;
+  const int start = A.cell_start[(size_t)frame * g->n_cells + c];
+  const size_t pos0 = (size_t)frame * g->raw_cap + A.cell_rank[(size_t)frame * (g->n_cells + 1) + c];
+  const uint32_t* raw = A.raw + (size_t)frame * g->raw_cap;
+  for (int e = lane; e < cnt; e += 32) {
+    const uint32_t r = raw[start + e];  // y:12 | x:12 | response:8, border-relative coordinates
+    A.keys[0][pos0 + e] = qt_code<kQtMapDig>((int)((r >> 8) & 4095u), (int)(r >> 20), root_w, root_h);
+    A.vals[0][pos0 + e] = r;
+  }
+}
+
+__global__ void __launch_bounds__(kQtThreads, 3) k_quadtree(QtArgs A) {
   __shared__ QtSmem sm;
   const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
   const FrameGeomDev* g = A.g;
@@ -422,7 +450,11 @@ __global__ void __launch_bounds__(kQtThreads) k_quadtree(QtArgs A) {
   for (int i = tid; i < kQtMapWords; i += kQtThreads) sm.bitmap[i] = 0;
   if (tid <= kQtMapDig) sm.cnt[tid] = 0;
   __syncthreads();
-  qt_fill(A, lv, frame, level_base, K[0], V[0], sm.bitmap);
+  for (int i = tid; i < n; i += kQtThreads) {  // codes come from k_qt_codes
+    const uint32_t p8 = K[0][i] >> (kQtBits - 2 * kQtMapDig);
+    const uint32_t bit = 1u << (p8 & 31u);
+    if (!(sm.bitmap[p8 >> 5] & bit)) atomicOr(&sm.bitmap[p8 >> 5], bit);
+  }
   __syncthreads();
   // (2) #nodes after d passes = #distinct d-digit prefixes (d = 1..8): fold the bitmap.  Thread t < 256 owns the
   // 8 words under the 4-digit prefix t; deeper levels fold inside a word, shallower ones across lanes by ballot.
@@ -478,6 +510,8 @@ __global__ void __launch_bounds__(kQtThreads) k_quadtree(QtArgs A) {
   if (sm.misc[3]) {
     // rare: more than 8 passes (tightly clustered points).  Sort the full codes, count distinct prefixes of every
     // depth from the common-prefix lengths of neighbours, then restore candidate order.
+    __syncthreads();
+    qt_fill(A, lv, frame, level_base, K[0], V[0], sm.bitmap);  // full kQtDig-digit codes
     __syncthreads();
     cur = qt_sort(sm, K[0], V[0], K[1], V[1], n, kQtBits);
     for (int d = tid; d < kQtDig + 2; d += kQtThreads) sm.lcp_hist[d] = 0;
@@ -617,9 +651,11 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
   A.sel_n = ex->d_sel_n;
   A.level_ncand = ex->d_level_ncand;
   A.status = ex->d_status;
+  if (ex->geom.n_cells > 0)
+    k_qt_codes<<<dim3((ex->geom.n_cells + kCodeWarps - 1) / kCodeWarps, batch), kCodeWarps * 32, 0, s>>>(A);
   dim3 grid(ex->geom.n_levels, batch);
   k_quadtree<<<grid, kQtThreads, 0, s>>>(A);
-  count_launches(2);
+  count_launches(3);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
 }
