@@ -80,11 +80,21 @@ __device__ bool qt_radix_pass(QtSmem& sm, const uint32_t* __restrict__ kin, cons
   for (int b = tid; b < 256; b += kQtThreads) sm.hist[b] = 0;
   if (tid == 0) sm.misc[0] = 0;
   __syncthreads();
-  for (int base = 0; base < n; base += kQtThreads) {
-    const int i = base + tid;
-    const uint32_t dgt = i < n ? ((kin[i] >> shift) & dmask) : 256u + lane;
-    const uint32_t peers = __match_any_sync(0xffffffffu, dgt);
-    if (i < n && lane == __ffs(peers) - 1) atomicAdd(&sm.hist[dgt], __popc(peers));
+  for (int base = 0; base < n; base += 4 * kQtThreads) {
+    uint32_t k4[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {  // four independent loads in flight before the first vote
+      const int i = base + u * kQtThreads + tid;
+      k4[u] = i < n ? kin[i] : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int i = base + u * kQtThreads + tid;
+      if (base + u * kQtThreads >= n) break;  // uniform over the CTA
+      const uint32_t dgt = i < n ? ((k4[u] >> shift) & dmask) : 256u + lane;
+      const uint32_t peers = __match_any_sync(0xffffffffu, dgt);
+      if (i < n && lane == __ffs(peers) - 1) atomicAdd(&sm.hist[dgt], __popc(peers));
+    }
   }
   __syncthreads();
   if (tid < 256 && sm.hist[tid] == n) sm.misc[0] = 1;
@@ -114,11 +124,16 @@ __device__ bool qt_radix_pass(QtSmem& sm, const uint32_t* __restrict__ kin, cons
     const int wbase = base + warp * 32 * kQtItems;
     for (int b = lane; b < nbins; b += 32) sm.warp_cnt[warp][b] = 0;
     __syncwarp();
-    uint32_t key[kQtItems], peers[kQtItems];
+    uint32_t key[kQtItems], val[kQtItems], peers[kQtItems];
+#pragma unroll
+    for (int it = 0; it < kQtItems; it++) {  // all loads of the chunk in flight before the first vote
+      const int i = wbase + it * 32 + lane;
+      key[it] = i < n ? kin[i] : 0u;
+      val[it] = i < n ? vin[i] : 0u;
+    }
 #pragma unroll
     for (int it = 0; it < kQtItems; it++) {
       const int i = wbase + it * 32 + lane;
-      key[it] = i < n ? kin[i] : 0u;
       const uint32_t dgt = i < n ? ((key[it] >> shift) & dmask) : 256u + lane;  // invalid lanes: singleton groups
       peers[it] = __match_any_sync(0xffffffffu, dgt);
       if (i < n && lane == __ffs(peers[it]) - 1) atomicAdd(&sm.warp_cnt[warp][dgt], __popc(peers[it]));
@@ -147,7 +162,7 @@ __device__ bool qt_radix_pass(QtSmem& sm, const uint32_t* __restrict__ kin, cons
         const int rank = __popc(peers[it] & ((1u << lane) - 1u));
         if (rank == 0) sm.warp_cnt[warp][dgt] = off + __popc(peers[it]);
         kout[off + rank] = key[it];
-        vout[off + rank] = vin[i];
+        vout[off + rank] = val[it];
       }
       __syncwarp();
     }
@@ -450,10 +465,20 @@ __global__ void __launch_bounds__(kQtThreads, 3) k_quadtree(QtArgs A) {
   for (int i = tid; i < kQtMapWords; i += kQtThreads) sm.bitmap[i] = 0;
   if (tid <= kQtMapDig) sm.cnt[tid] = 0;
   __syncthreads();
-  for (int i = tid; i < n; i += kQtThreads) {  // codes come from k_qt_codes
-    const uint32_t p8 = K[0][i] >> (kQtBits - 2 * kQtMapDig);
-    const uint32_t bit = 1u << (p8 & 31u);
-    if (!(sm.bitmap[p8 >> 5] & bit)) atomicOr(&sm.bitmap[p8 >> 5], bit);
+  for (int base = 0; base < n; base += 4 * kQtThreads) {  // codes come from k_qt_codes
+    uint32_t c4[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int i = base + u * kQtThreads + tid;
+      c4[u] = i < n ? K[0][i] : 0xffffffffu;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      if (c4[u] == 0xffffffffu) continue;  // codes have kQtBits = 28 significant bits
+      const uint32_t p8 = c4[u] >> (kQtBits - 2 * kQtMapDig);
+      const uint32_t bit = 1u << (p8 & 31u);
+      if (!(sm.bitmap[p8 >> 5] & bit)) atomicOr(&sm.bitmap[p8 >> 5], bit);
+    }
   }
   __syncthreads();
   // (2) #nodes after d passes = #distinct d-digit prefixes (d = 1..8): fold the bitmap.  Thread t < 256 owns the
@@ -549,13 +574,29 @@ __global__ void __launch_bounds__(kQtThreads, 3) k_quadtree(QtArgs A) {
   // (4a) node boundaries
   if (tid == 0) sm.misc[2] = 0;
   __syncthreads();
-  for (int base = 0; base < n; base += kQtThreads) {
-    const int i = base + tid;
-    const int head = (i < n) && (i == 0 || (PK[i] >> sh) != (PK[i - 1] >> sh));
+  for (int base = 0; base < n; base += 4 * kQtThreads) {  // thread = 4 consecutive points per CTA-wide scan
+    const int i0 = base + 4 * tid;
+    uint32_t pk[5];
+#pragma unroll
+    for (int u = 0; u < 5; u++) {
+      const int i = i0 - 1 + u;
+      pk[u] = (i >= 0 && i < n) ? (PK[i] >> sh) : 0xffffffffu;
+    }
+    int heads = 0;
+    uint32_t hm = 0;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const int i = i0 + u;
+      const bool head = (i < n) && (i == 0 || pk[u + 1] != pk[u]);
+      hm |= (uint32_t)head << u;
+      heads += head;
+    }
     int total;
-    const int ex = qt_block_scan(sm, head, &total);
+    int ex = qt_block_scan(sm, heads, &total);
     const int off = sm.misc[2];
-    if (head) node_start[off + ex] = (uint32_t)i;
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if ((hm >> u) & 1u) node_start[off + ex++] = (uint32_t)(i0 + u);
     __syncthreads();
     if (tid == 0) sm.misc[2] = off + total;
     __syncthreads();
