@@ -353,10 +353,16 @@ __global__ void __launch_bounds__(256) k_cell_scan(const FrameGeomDev* __restric
   int* rank = cell_rank + (size_t)frame * (nc + 1);
   if (tid == 0) s_carry = 0;
   __syncthreads();
-  for (int base = 0; base < nc; base += 256) {
-    const int i = base + tid;
-    const int v = i < nc ? cnt[i] : 0;
-    int incl = v;
+  constexpr int kPer = 8;  // consecutive cells per thread and chunk: 2048 cells per CTA-wide scan
+  for (int base = 0; base < nc; base += 256 * kPer) {
+    const int i0 = base + tid * kPer;
+    int v[kPer], sum = 0;
+#pragma unroll
+    for (int k = 0; k < kPer; k++) {
+      v[k] = (i0 + k < nc) ? cnt[i0 + k] : 0;
+      sum += v[k];
+    }
+    int incl = sum;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
       const int t = __shfl_up_sync(0xffffffffu, incl, o);
@@ -367,7 +373,12 @@ __global__ void __launch_bounds__(256) k_cell_scan(const FrameGeomDev* __restric
     int woff = 0;
     for (int w = 0; w < warp; w++) woff += s_warp[w];
     const int carry = s_carry;
-    if (i < nc) rank[i] = carry + woff + incl - v;
+    int run = carry + woff + incl - sum;
+#pragma unroll
+    for (int k = 0; k < kPer; k++) {
+      if (i0 + k < nc) rank[i0 + k] = run;
+      run += v[k];
+    }
     __syncthreads();
     if (tid == 255) s_carry = carry + woff + incl;
     __syncthreads();
