@@ -16,6 +16,7 @@ constexpr int kHalfPatch = 15; // m_int_halfPatchSize src/orbExtractor.hpp:71
 constexpr int kPatch = 31;     // m_int_patchSize     src/orbExtractor.hpp:70
 constexpr int kMaxLevels = YDORB_MAX_LEVELS;
 constexpr int kQtDigits = 16;  // quadtree path digits per code (2 bits each)
+constexpr int kQtMapWords = 2048;  // 4^8 bits: occupancy bitmap of the 8 leading path digits (quadtree.cu)
 
 void set_error(const std::string& msg);
 void count_launches(int n);  // bookkeeping for ydorb_kernel_launches()
@@ -105,6 +106,9 @@ struct YdExtractor {
   int* d_raw_counter;    // [max_batch]
   uint32_t* d_qt_keys[3];  // [max_batch][cap_raw] quadtree sort scratch
   uint32_t* d_qt_vals[3];
+  uint32_t* d_qt_bitmap; // [max_batch][kMaxLevels][kQtMapWords] occupancy of 8-digit path prefixes (zero between calls)
+  uint32_t* d_qt_fold;   // [max_batch][kMaxLevels][2][kQtMapWords] D-digit occupancy + exclusive popcount prefix per word
+  int* d_qt_meta;        // [max_batch][kMaxLevels][8] per segment: n, D, M, deep, level_base
   int* d_level_ncand;    // [max_batch][kMaxLevels]
   int4* d_sel;           // [max_batch][n_quota] selected keypoints {x,y (level coords), response bits, level}
   int* d_sel_n;          // [max_batch][kMaxLevels]

@@ -215,6 +215,9 @@ static YdExtractor frame_view(const YdExtractor* ex, int f0, cudaStream_t s) {
   v.d_raw += (size_t)f0 * g.raw_cap;
   v.d_raw_counter += f0;
   for (int i = 0; i < 3; i++) { v.d_qt_keys[i] += (size_t)f0 * g.raw_cap; v.d_qt_vals[i] += (size_t)f0 * g.raw_cap; }
+  v.d_qt_bitmap += (size_t)f0 * kMaxLevels * kQtMapWords;
+  v.d_qt_fold += (size_t)f0 * kMaxLevels * 2 * kQtMapWords;
+  v.d_qt_meta += (size_t)f0 * kMaxLevels * 8;
   v.d_level_ncand += (size_t)f0 * kMaxLevels;
   v.d_sel += (size_t)f0 * g.n_quota;
   v.d_sel_n += (size_t)f0 * kMaxLevels;
@@ -339,6 +342,10 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
     alloc((void**)&ex->d_qt_keys[i], sizeof(uint32_t) * B * ex->cap_raw);
     alloc((void**)&ex->d_qt_vals[i], sizeof(uint32_t) * B * ex->cap_raw);
   }
+  alloc((void**)&ex->d_qt_bitmap, sizeof(uint32_t) * B * kMaxLevels * kQtMapWords);
+  alloc((void**)&ex->d_qt_fold, sizeof(uint32_t) * B * kMaxLevels * 2 * kQtMapWords);
+  alloc((void**)&ex->d_qt_meta, sizeof(int) * B * kMaxLevels * 8);
+  if (e == cudaSuccess) e = cudaMemset(ex->d_qt_bitmap, 0, sizeof(uint32_t) * B * kMaxLevels * kQtMapWords);
   alloc((void**)&ex->d_level_ncand, sizeof(int) * B * kMaxLevels);
   alloc((void**)&ex->d_sel, sizeof(int4) * B * nq);
   alloc((void**)&ex->d_sel_n, sizeof(int) * B * kMaxLevels);
@@ -363,7 +370,7 @@ void ydorb_extractor_destroy(YdExtractor* ex) {
   cudaSetDevice(ex->device);
   void* ptrs[] = {ex->d_geom, ex->d_pyr, ex->d_tab_ofs, ex->d_tab_a, ex->d_cells, ex->d_cell_count, ex->d_cell_start,
                   ex->d_cell_rank, ex->d_raw, ex->d_raw_counter, ex->d_qt_keys[0], ex->d_qt_keys[1], ex->d_qt_keys[2],
-                  ex->d_qt_vals[0], ex->d_qt_vals[1], ex->d_qt_vals[2], ex->d_level_ncand, ex->d_sel, ex->d_sel_n,
+                  ex->d_qt_vals[0], ex->d_qt_vals[1], ex->d_qt_vals[2], ex->d_qt_bitmap, ex->d_qt_fold, ex->d_qt_meta, ex->d_level_ncand, ex->d_sel, ex->d_sel_n,
                   ex->d_status, ex->d_images, ex->d_kps, ex->d_desc, ex->d_nout};
   for (void* p : ptrs)
     if (p) cudaFree(p);

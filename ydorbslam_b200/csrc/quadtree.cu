@@ -27,14 +27,14 @@ constexpr int kQtDig = 14;                   // digits per path code (28 bits): 
 constexpr int kQtBits = 2 * kQtDig;
 
 constexpr int kQtMapDig = 8;                 // depth covered by the occupancy bitmap (4^8 cells)
-constexpr int kQtMapWords = (1 << (2 * kQtMapDig)) / 32;
+static_assert(kQtMapWords == (1 << (2 * kQtMapDig)) / 32, "kQtMapWords (common.cuh) must cover 4^kQtMapDig bits");
 
 struct QtSmem {
   uint32_t bitmap[kQtMapWords];  // bit p set <=> some candidate's path starts with the 8-digit prefix p
   int cnt[kQtMapDig + 1];        // number of distinct d-digit prefixes, d = 0..8
   uint32_t ballots[kQtThreads / 32];
   int hist[256];
-  int warp_cnt[kQtWarps][256];
+  alignas(8) int warp_cnt[kQtWarps][256];
   int scan_tmp[kQtWarps];
   int lcp_hist[kQtDig + 2];
   int misc[8];
@@ -395,6 +395,9 @@ struct QtArgs {
   const uint32_t* raw;
   uint32_t* keys[3];
   uint32_t* vals[3];
+  uint32_t* bitmap;  // [frame][kMaxLevels][kQtMapWords]
+  uint32_t* fold;    // [frame][kMaxLevels][2][kQtMapWords]
+  int* meta;         // [frame][kMaxLevels][8]
   int4* sel;
   int* sel_n;
   int* level_ncand;
@@ -439,17 +442,473 @@ __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
   const int cnt = A.cell_count[(size_t)frame * g->n_cells + c];
   if (cnt == 0) return;
   int level = 0;
-  for (int l = 1; l < g->n_levels; l++)
-    if (c >= g->lv[l].cell_base) level = l;
+  for (int l = 1; l < g->n_levels && c >= g->lv[l].cell_base; l++) level = l;  // cell bases ascend with the level
   const int root_w = g->lv[level].root_w, root_h = g->lv[level].root_h;
   const int start = A.cell_start[(size_t)frame * g->n_cells + c];
   const size_t pos0 = (size_t)frame * g->raw_cap + A.cell_rank[(size_t)frame * (g->n_cells + 1) + c];
   const uint32_t* raw = A.raw + (size_t)frame * g->raw_cap;
+  uint32_t* bitmap = A.bitmap + ((size_t)frame * kMaxLevels + level) * kQtMapWords;
   for (int e = lane; e < cnt; e += 32) {
     const uint32_t r = raw[start + e];  // y:12 | x:12 | response:8, border-relative coordinates
-    A.keys[0][pos0 + e] = qt_code<kQtMapDig>((int)((r >> 8) & 4095u), (int)(r >> 20), root_w, root_h);
+    const uint32_t code = qt_code<kQtMapDig>((int)((r >> 8) & 4095u), (int)(r >> 20), root_w, root_h);
+    A.keys[0][pos0 + e] = code;
     A.vals[0][pos0 + e] = r;
+    const uint32_t p8 = code >> (kQtBits - 2 * kQtMapDig);
+    const uint32_t bit = 1u << (p8 & 31u);
+    if (!(bitmap[p8 >> 5] & bit)) atomicOr(&bitmap[p8 >> 5], bit);  // occupancy of the 8-digit prefixes (k_qt_depth)
   }
+}
+
+// ======================================================================================================================
+// Node-table path (the common case, depth <= kQtMapDig).  Only the winner of every node matters, and which node a
+// candidate falls into is a rank query into the occupancy bitmap, so the per-candidate work needs no sort at all and
+// runs GPU-wide with order-free atomics; the CTA that owns a (level, frame) segment only touches the M nodes:
+//   k_qt_codes   (GPU-wide)   path codes + occupancy bitmap of the 8-digit prefixes
+//   k_qt_depth   (CTA/segment) depth D from the bitmap, D-digit occupancy + popcount prefix = node index of a prefix
+//   k_qt_pass1/2 (GPU-wide)   per node: member count, first maximum in candidate order (atomicMax on
+//                             response << 24 | ~position), number of members that tie with it
+//   k_qt_finish  (CTA/segment) node records, std::sort emulation for the nodes that need it (members gathered in
+//                             candidate order through the FAST cell grid), list-order sort, truncate, emit
+// Segments that need more than kQtMapDig passes (tightly clustered points) keep the sort-based k_quadtree below.
+enum { kMetaN = 0, kMetaD = 1, kMetaM = 2, kMetaDeep = 3, kMetaBase = 4 };
+
+__global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
+  __shared__ uint32_t s_map[kQtMapWords];
+  __shared__ uint32_t s_fold[kQtMapWords];
+  __shared__ int s_cnt[kQtMapDig + 1];
+  __shared__ uint32_t s_ballots[kQtThreads / 32];
+  __shared__ int s_scan[kQtWarps];
+  __shared__ int s_misc[4];
+  const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const FrameGeomDev* g = A.g;
+  const LevelGeom lv = g->lv[level];
+  const int* rank = A.cell_rank + (size_t)frame * (g->n_cells + 1);
+  const int level_base = rank[lv.cell_base];
+  const int n = rank[lv.cell_base + lv.cell_cols * lv.cell_rows] - level_base;
+  const int want = lv.quota;
+  int* meta = A.meta + ((size_t)frame * kMaxLevels + level) * 8;
+  uint32_t* gmap = A.bitmap + ((size_t)frame * kMaxLevels + level) * kQtMapWords;
+  if (tid == 0) {
+    A.level_ncand[(size_t)frame * kMaxLevels + level] = n;
+    meta[kMetaBase] = level_base;
+  }
+  if (n == 0 || want <= 0) {
+    if (tid == 0) {
+      A.sel_n[(size_t)frame * kMaxLevels + level] = 0;
+      meta[kMetaN] = 0; meta[kMetaD] = 0; meta[kMetaM] = 0; meta[kMetaDeep] = 0;
+    }
+    // the bitmap is all zero when n == 0; with n > 0 and no quota it must be cleared for the next call
+    if (n != 0)
+      for (int i = tid; i < kQtMapWords; i += kQtThreads) gmap[i] = 0;
+    return;
+  }
+  for (int i = tid; i < kQtMapWords; i += kQtThreads) {
+    s_map[i] = gmap[i];
+    gmap[i] = 0;  // zero between calls
+    s_fold[i] = 0;
+  }
+  if (tid <= kQtMapDig) s_cnt[tid] = 0;
+  __syncthreads();
+  // #nodes after d passes = #distinct d-digit prefixes (d = 1..8): fold the bitmap.  Thread t < 256 owns the 8 words
+  // under the 4-digit prefix t; deeper levels fold inside a word, shallower ones across lanes by ballot.
+  {
+    int c8 = 0, c7 = 0, c6 = 0, c5 = 0;
+    bool any = false;
+    if (tid < 256) {
+      uint32_t pair = 0;
+#pragma unroll
+      for (int k = 0; k < 8; k++) {
+        const uint32_t w = s_map[tid * 8 + k];
+        c8 += __popc(w);
+        const uint32_t m7 = (w | (w >> 1) | (w >> 2) | (w >> 3)) & 0x11111111u;
+        c7 += __popc(m7);
+        c6 += __popc((m7 | (m7 >> 4) | (m7 >> 8) | (m7 >> 12)) & 0x00010001u);
+        pair |= w;
+        if (k & 1) { c5 += pair != 0; any |= pair != 0; pair = 0; }
+      }
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, any);
+    c8 = __reduce_add_sync(0xffffffffu, c8);
+    c7 = __reduce_add_sync(0xffffffffu, c7);
+    c6 = __reduce_add_sync(0xffffffffu, c6);
+    c5 = __reduce_add_sync(0xffffffffu, c5);
+    if (lane == 0) {
+      if (c8) { atomicAdd(&s_cnt[8], c8); atomicAdd(&s_cnt[7], c7); atomicAdd(&s_cnt[6], c6); atomicAdd(&s_cnt[5], c5); }
+      if (bal) {
+        atomicAdd(&s_cnt[4], __popc(bal));
+        atomicAdd(&s_cnt[3], __popc((bal | (bal >> 1) | (bal >> 2) | (bal >> 3)) & 0x11111111u));
+        atomicAdd(&s_cnt[2], ((bal & 0xffffu) != 0) + ((bal >> 16) != 0));
+      }
+      s_ballots[warp] = bal;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int c1 = 0;
+    for (int k = 0; k < 4; k++) c1 += (s_ballots[2 * k] | s_ballots[2 * k + 1]) != 0;
+    s_cnt[1] = c1;
+    // the reference's loop condition (:479): split again while the list grew and is still shorter than `want`
+    int D = 0, last = 0, size = 1, deep = 0;
+    while (size > last && size < want && D < kQtDig) {
+      last = size;
+      D++;
+      if (D > kQtMapDig) { deep = 1; break; }
+      size = s_cnt[D];
+    }
+    s_misc[0] = D;
+    s_misc[1] = deep;
+  }
+  __syncthreads();
+  const int D = s_misc[0];
+  if (s_misc[1]) {  // k_quadtree handles the segment
+    if (tid == 0) { meta[kMetaN] = n; meta[kMetaD] = D; meta[kMetaM] = 0; meta[kMetaDeep] = 1; }
+    return;
+  }
+  // D-digit occupancy: bit p set <=> some 8-digit prefix below p is occupied
+  const int drop = 2 * (kQtMapDig - D);
+  for (int w = tid; w < kQtMapWords; w += kQtThreads) {
+    uint32_t bits = s_map[w];
+    if (drop == 0) { s_fold[w] = bits; continue; }
+    while (bits) {
+      const int b = __ffs(bits) - 1;
+      // all 8-digit prefixes that share the D-digit prefix of this one sit in the next (1 << drop) positions: skip them
+      const uint32_t p8 = (uint32_t)w * 32u + (uint32_t)b, pd = p8 >> drop;
+      atomicOr(&s_fold[pd >> 5], 1u << (pd & 31u));
+      const uint32_t next = ((pd + 1u) << drop);  // first 8-digit prefix of the next D-digit group
+      if (next >= (uint32_t)(w + 1) * 32u) break;
+      bits &= ~((1u << (next - (uint32_t)w * 32u)) - 1u);
+    }
+  }
+  __syncthreads();
+  // exclusive popcount prefix per word: node index of prefix p = prefix[p >> 5] + popc(fold[p >> 5] & below(p))
+  uint32_t* gfold = A.fold + ((size_t)frame * kMaxLevels + level) * 2 * kQtMapWords;
+  {
+    constexpr int kPer = kQtMapWords / kQtThreads;  // 4 consecutive words per thread
+    int c[kPer], sum = 0;
+#pragma unroll
+    for (int k = 0; k < kPer; k++) { c[k] = __popc(s_fold[tid * kPer + k]); sum += c[k]; }
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_scan[warp] = incl;
+    __syncthreads();
+    int woff = 0;
+    for (int w = 0; w < warp; w++) woff += s_scan[w];
+    int run = woff + incl - sum;
+#pragma unroll
+    for (int k = 0; k < kPer; k++) {
+      gfold[tid * kPer + k] = s_fold[tid * kPer + k];
+      gfold[kQtMapWords + tid * kPer + k] = (uint32_t)run;
+      run += c[k];
+    }
+    if (tid == kQtThreads - 1) s_misc[2] = run;
+  }
+  __syncthreads();
+  const int M = s_misc[2];
+  // node tables of the segment: best key, member count, tie count
+  const size_t seg = (size_t)frame * g->raw_cap + level_base;
+  uint32_t *best = A.keys[1] + seg, *cnt = A.vals[1] + seg, *ties = A.keys[2] + seg;
+  for (int m = tid; m < M; m += kQtThreads) { best[m] = 0; cnt[m] = 0; ties[m] = 0; }
+  if (tid == 0) { meta[kMetaN] = n; meta[kMetaD] = D; meta[kMetaM] = M; meta[kMetaDeep] = 0; }
+}
+
+// segment of a candidate position and its node index; returns false for positions past the frame's candidates or in
+// segments the node-table path does not handle
+struct QtWhere { int level, i, D; size_t seg; uint32_t m; };
+__device__ __forceinline__ bool qt_locate(const QtArgs& A, int frame, int pos, QtWhere* w) {
+  const FrameGeomDev* g = A.g;
+  if (pos >= A.cell_rank[(size_t)frame * (g->n_cells + 1) + g->n_cells]) return false;
+  const int* meta = A.meta + (size_t)frame * kMaxLevels * 8;
+  int level = 0;
+  for (int l = 1; l < g->n_levels; l++)
+    if (pos >= meta[l * 8 + kMetaBase]) level = l;
+  meta += level * 8;
+  if (meta[kMetaDeep] || meta[kMetaN] == 0) return false;
+  const int base = meta[kMetaBase], D = meta[kMetaD];
+  const uint32_t code = A.keys[0][(size_t)frame * g->raw_cap + pos];
+  const uint32_t p = D == 0 ? 0u : code >> (kQtBits - 2 * D);
+  const uint32_t* fold = A.fold + ((size_t)frame * kMaxLevels + level) * 2 * kQtMapWords;
+  w->level = level;
+  w->i = pos - base;
+  w->D = D;
+  w->seg = (size_t)frame * g->raw_cap + base;
+  w->m = fold[kQtMapWords + (p >> 5)] + __popc(fold[p >> 5] & ((1u << (p & 31u)) - 1u));
+  return true;
+}
+
+// Candidates that follow each other in candidate order come from the same FAST cell and mostly fall into the same node:
+// the lanes of a warp that hit the same node combine their contribution (MATCH.ANY + REDUX) and one of them issues the
+// atomics, instead of up to 32 same-address atomics serialising in L2.
+__global__ void __launch_bounds__(256) k_qt_pass1(QtArgs A) {
+  const int frame = blockIdx.y, lane = threadIdx.x & 31;
+  const int total = A.cell_rank[(size_t)frame * (A.g->n_cells + 1) + A.g->n_cells];
+  for (int base = blockIdx.x * 256 + (threadIdx.x & ~31); base < total; base += gridDim.x * 256) {  // warp-uniform
+    const int pos = base + lane;
+    QtWhere w;
+    const bool ok = qt_locate(A, frame, pos, &w);
+    uint32_t key = 0;
+    if (ok) {
+      const uint32_t r = A.vals[0][(size_t)frame * A.g->raw_cap + pos];
+      A.vals[2][(size_t)frame * A.g->raw_cap + pos] = w.m;  // node index, reused by pass 2
+      key = ((r & 255u) << 24) | (0xFFFFFFu - (uint32_t)w.i);  // max response, then first position
+    }
+    const uint32_t group = ok ? ((uint32_t)w.level << 16) | w.m : 0x80000000u | (uint32_t)lane;
+    const uint32_t peers = __match_any_sync(0xffffffffu, group);
+    const uint32_t top = __reduce_max_sync(peers, key);
+    if (ok && lane == __ffs(peers) - 1) {
+      atomicMax(&A.keys[1][w.seg + w.m], top);
+      atomicAdd(&A.vals[1][w.seg + w.m], (uint32_t)__popc(peers));
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) k_qt_pass2(QtArgs A) {
+  const int frame = blockIdx.y, lane = threadIdx.x & 31;
+  const FrameGeomDev* g = A.g;
+  const int total = A.cell_rank[(size_t)frame * (g->n_cells + 1) + g->n_cells];
+  const int* fmeta = A.meta + (size_t)frame * kMaxLevels * 8;
+  for (int base = blockIdx.x * 256 + (threadIdx.x & ~31); base < total; base += gridDim.x * 256) {  // warp-uniform
+    const int pos = base + lane;
+    bool tie = false;
+    uint32_t group = 0x80000000u | (uint32_t)lane;
+    size_t slot = 0;
+    if (pos < total) {
+      int level = 0;
+      for (int l = 1; l < g->n_levels; l++)
+        if (pos >= fmeta[l * 8 + kMetaBase]) level = l;
+      const int* meta = fmeta + level * 8;
+      if (!meta[kMetaDeep] && meta[kMetaN] != 0) {
+        const uint32_t r = A.vals[0][(size_t)frame * g->raw_cap + pos];
+        const uint32_t m = A.vals[2][(size_t)frame * g->raw_cap + pos];
+        slot = (size_t)frame * g->raw_cap + meta[kMetaBase] + m;
+        tie = (r & 255u) == (A.keys[1][slot] >> 24);
+        group = ((uint32_t)level << 16) | m;
+      }
+    }
+    const uint32_t peers = __match_any_sync(0xffffffffu, group);
+    const uint32_t tb = __ballot_sync(0xffffffffu, tie) & peers;  // lanes of this node that tie with its maximum
+    if (tie && lane == __ffs(tb) - 1) atomicAdd(&A.keys[2][slot], (uint32_t)__popc(tb));
+  }
+}
+
+// previous / next occupied D-digit prefix around bit b of word w (or -1)
+__device__ __forceinline__ int qt_prev_prefix(const uint32_t* fold, int w, int b) {
+  uint32_t below = fold[w] & ((1u << b) - 1u);
+  while (below == 0u) {
+    if (--w < 0) return -1;
+    below = fold[w];
+  }
+  return w * 32 + 31 - __clz(below);
+}
+__device__ __forceinline__ int qt_next_prefix(const uint32_t* fold, int nwords, int w, int b) {
+  uint32_t above = b == 31 ? 0u : (fold[w] & ~((2u << b) - 1u));
+  while (above == 0u) {
+    if (++w >= nwords) return -1;
+    above = fold[w];
+  }
+  return w * 32 + __ffs(above) - 1;
+}
+
+struct QtFinSmem {
+  QtSmem q;                     // radix-sort workspace (q.bitmap holds the D-digit occupancy here)
+  uint32_t prefix[kQtMapWords]; // exclusive popcount prefix per word
+};
+
+__global__ void __launch_bounds__(kQtThreads) k_qt_finish(QtArgs A) {
+  __shared__ QtFinSmem fs;
+  QtSmem& sm = fs.q;
+  const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
+  const FrameGeomDev* g = A.g;
+  const int* meta = A.meta + ((size_t)frame * kMaxLevels + level) * 8;
+  const int n = meta[kMetaN];
+  if (n == 0 || meta[kMetaDeep]) return;
+  const LevelGeom lv = g->lv[level];
+  const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase], want = lv.quota;
+  const int sh = kQtBits - 2 * D;
+  const size_t seg = (size_t)frame * g->raw_cap + level_base;
+  const uint32_t* CK = A.keys[0] + seg;   // path codes, candidate order
+  const uint32_t* CV = A.vals[0] + seg;   // packed candidates, candidate order
+  uint32_t* best = A.keys[1] + seg;       // node winners (NV) once the records are written
+  uint32_t* cnt = A.vals[1] + seg;
+  uint32_t* ties = A.keys[2] + seg;
+  uint32_t* NK = A.vals[2] + seg;         // order keys [0, M), then the flagged list (3 words per entry)
+  uint32_t* NV = best;
+  uint32_t* flagged = NK + M;             // M + 3 * #(nodes with > 16 members) <= n
+  const uint32_t* gfold = A.fold + ((size_t)frame * kMaxLevels + level) * 2 * kQtMapWords;
+  const int nbits = 1 << (2 * D), nwords = (nbits + 31) >> 5;
+  for (int w = tid; w < nwords; w += kQtThreads) {
+    sm.bitmap[w] = gfold[w];
+    fs.prefix[w] = gfold[kQtMapWords + w];
+  }
+  if (tid == 0) sm.misc[4] = 0;
+  __syncthreads();
+
+  // node records: order key + winner (first maximum in candidate order); nodes std::sort decides are queued.
+  // Thread = one D-digit prefix; its node index is a rank query.
+  for (int p = tid; p < nbits; p += kQtThreads) {
+    const int w = p >> 5, b = p & 31;
+    const uint32_t word = sm.bitmap[w];
+    if (!((word >> b) & 1u)) continue;
+    const int m = (int)fs.prefix[w] + __popc(word & ((1u << b) - 1u));
+    const uint32_t pre = (uint32_t)p;
+    const int len = (int)cnt[m];
+    int s = D;
+    if (len == 1) {
+      int l = 0;
+      const int pp = qt_prev_prefix(sm.bitmap, w, b), pn = qt_next_prefix(sm.bitmap, nwords, w, b);
+      if (pp >= 0) l = max(l, lcp_digits(pre, (uint32_t)pp, D));
+      if (pn >= 0) l = max(l, lcp_digits(pre, (uint32_t)pn, D));
+      s = (n == 1) ? 0 : min(D, l + 1);
+    }
+    const uint32_t bk = best[m];
+    const int first_max = (int)(0xFFFFFFu - (bk & 0xFFFFFFu));
+    if (len > 16 && ties[m] > 1u) {  // introsort decides among tied maxima
+      const int f = atomicAdd(&sm.misc[4], 1);
+      flagged[3 * f] = (uint32_t)m;
+      flagged[3 * f + 1] = pre;
+      flagged[3 * f + 2] = (uint32_t)len;
+    }
+    const uint32_t ps = (s == 0) ? 0u : (pre >> (2 * (D - s)));
+    uint32_t mask = 0;
+    for (int k = s; k >= 1; k -= 2) mask |= 3u << (2 * (s - k));
+    NK[m] = ((uint32_t)(D - s) << (2 * D)) | (ps ^ mask);  // 2D + 4 significant bits
+    NV[m] = CV[first_max];
+  }
+  __syncthreads();
+  // nodes whose winner std::sort decides: one warp per node.  Its members, in candidate order, are the candidates with
+  // the node's prefix found by walking the FAST cells (candidate order = cell-major) that overlap the node's rectangle.
+  {
+    const int nflag = sm.misc[4];
+    const int lane = tid & 31, warp = tid >> 5;
+    uint32_t* big_buf = ties;  // node tables are dead from here on: scratch for nodes with more than 128 members
+    uint32_t* big_pos = cnt;
+    if (tid == 0) sm.misc[5] = 0;
+    __syncthreads();
+    const size_t cbase = (size_t)frame * g->n_cells + lv.cell_base;
+    const int* rank = A.cell_rank + (size_t)frame * (g->n_cells + 1) + lv.cell_base;
+    for (int f = warp; f < nflag; f += kQtWarps) {
+      const int m = (int)flagged[3 * f], len = (int)flagged[3 * f + 2];
+      const uint32_t pre = flagged[3 * f + 1];
+      // rectangle of the node: replay divideNode on the prefix digits, tracking the true bounds of the members
+      int tlx = 0, trx = lv.root_w, tly = 0, bly = lv.root_h;
+      int xlo = 0, xhi = lv.root_w, ylo = 0, yhi = lv.root_h;
+      for (int d = D - 1; d >= 0; d--) {
+        const uint32_t q = (pre >> (2 * d)) & 3u;
+        const int cx = (trx + tlx + 1) >> 1, cy = (bly + tly + 1) >> 1;
+        if (q & 1u) xlo = max(xlo, cx); else xhi = min(xhi, cx);
+        if (q & 2u) ylo = max(ylo, cy); else yhi = min(yhi, cy);
+        if (q == 0u) { trx = cx; bly = cy; }
+        else if (q == 1u) { tlx = cx; bly = cy; }
+        else if (q == 2u) { trx = cx; tly = cy; }
+        else { const int t = tly; tlx = cx; tly = cy; bly = t; }
+      }
+      // a candidate at border-relative (x, y) was found by cell ((x - 3) / cell_w, (y - 3) / cell_h): the detection
+      // areas [j * cell_w + 3, (j + 1) * cell_w + 3) tile the level exactly (src/orbExtractor.cpp:563-579)
+      const int j0 = max(0, (max(xlo, 3) - 3) / lv.cell_w), j1 = min(lv.cell_cols - 1, (max(xhi - 1, 3) - 3) / lv.cell_w);
+      const int i0 = max(0, (max(ylo, 3) - 3) / lv.cell_h), i1 = min(lv.cell_rows - 1, (max(yhi - 1, 3) - 3) / lv.cell_h);
+      uint32_t *buf, *pos;
+      if (len <= 128) {
+        buf = reinterpret_cast<uint32_t*>(sm.warp_cnt[warp]);
+        pos = buf + 128;
+      } else {
+        int o = 0;
+        if (lane == 0) o = atomicAdd(&sm.misc[5], len);
+        o = __shfl_sync(0xffffffffu, o, 0);
+        buf = big_buf + o;
+        pos = big_pos + o;
+      }
+      // the cells of the rectangle in cell-major order, 32 at a time: lane = cell (count, first position), then the
+      // candidates of those cells as one flat list, 32 per step (lane finds its cell by bisection over the prefix sums)
+      const int ncx = j1 - j0 + 1, ncell = max(0, i1 - i0 + 1) * max(0, ncx);
+      int k = 0;
+      for (int cb = 0; cb < ncell; cb += 32) {
+        const int ci = cb + lane;
+        int cc = 0, p0 = 0;
+        if (ci < ncell) {
+          const int c = (i0 + ci / ncx) * lv.cell_cols + j0 + ci % ncx;
+          cc = A.cell_count[cbase + c];
+          p0 = rank[c] - level_base;
+        }
+        int incl = cc;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += t;
+        }
+        const int excl = incl - cc, T = __shfl_sync(0xffffffffu, incl, 31);
+        for (int t0 = 0; t0 < T; t0 += 32) {
+          const int t = t0 + lane;
+          int lo = 0;
+#pragma unroll
+          for (int step = 16; step >= 1; step >>= 1) {
+            const int e = __shfl_sync(0xffffffffu, excl, (lo + step) & 31);
+            if (lo + step < 32 && e <= t) lo += step;
+          }
+          const int pc = __shfl_sync(0xffffffffu, p0, lo), ec = __shfl_sync(0xffffffffu, excl, lo);
+          const int idx = pc + (t - ec);
+          const bool is = t < T && (D == 0 || (CK[idx] >> sh) == pre);
+          const uint32_t bal = __ballot_sync(0xffffffffu, is);
+          if (is) {
+            const int o = k + __popc(bal & ((1u << lane) - 1u));
+            if (o < len) {
+              buf[o] = ((CV[idx] & 255u) << 24) | (uint32_t)o;
+              pos[o] = (uint32_t)idx;
+            }
+          }
+          k += __popc(bal);
+        }
+      }
+      __syncwarp();
+      if (lane == 0) {
+        if (k != len) atomicOr(A.status, kStatusSortDepth);  // the cell walk missed a member: never expected
+        StdSortEmu emu{buf};
+        const int sg = emu.leftmost_segment(len);
+        uint32_t bst = buf[0];
+        for (int i = 1; i < sg; i++)
+          if (StdSortEmu::comp(buf[i], bst)) bst = buf[i];
+        NV[m] = CV[pos[bst & 0xFFFFFFu]];
+      }
+      __syncwarp();
+    }
+  }
+  __syncthreads();
+
+  // list order, then the first min(M, want) winners (:541-543), coordinates back in level space (:597-598)
+  const int m_out = min(M, want);
+  int4* sel = A.sel + (size_t)frame * g->n_quota + lv.quota_base;
+  constexpr int kSmemSort = kQtWarps * 256 / 2;  // 64-bit (order key, winner) pairs that fit the radix counters' space
+  if (M <= kSmemSort) {
+    // few nodes: bitonic sort of the pairs in shared memory (order keys are unique)
+    unsigned long long* sk = reinterpret_cast<unsigned long long*>(&sm.warp_cnt[0][0]);
+    int P = 2;
+    while (P < M) P <<= 1;
+    for (int i = tid; i < P; i += kQtThreads) sk[i] = i < M ? ((unsigned long long)NK[i] << 32) | NV[i] : ~0ull;
+    __syncthreads();
+    for (int k = 2; k <= P; k <<= 1)
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int t = tid; t < (P >> 1); t += kQtThreads) {
+          const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), q = i | j;
+          const unsigned long long a = sk[i], b = sk[q];
+          if ((a > b) == ((i & k) == 0)) { sk[i] = b; sk[q] = a; }
+        }
+        __syncthreads();
+      }
+    for (int i = tid; i < m_out; i += kQtThreads) {
+      const uint32_t r = (uint32_t)sk[i];
+      sel[i] = make_int4((int)((r >> 8) & 4095u) + kBorder, (int)(r >> 20) + kBorder, (int)(r & 255u), level);
+    }
+  } else {
+    const int ncur = qt_sort(sm, NK, NV, cnt, ties, M, 2 * D + 4);
+    const uint32_t* OV = (ncur == 0) ? NV : ties;
+    for (int i = tid; i < m_out; i += kQtThreads) {
+      const uint32_t r = OV[i];
+      sel[i] = make_int4((int)((r >> 8) & 4095u) + kBorder, (int)(r >> 20) + kBorder, (int)(r & 255u), level);
+    }
+  }
+  if (tid == 0) A.sel_n[(size_t)frame * kMaxLevels + level] = m_out;
 }
 
 __global__ void __launch_bounds__(kQtThreads, 3) k_quadtree(QtArgs A) {
@@ -463,7 +922,7 @@ __global__ void __launch_bounds__(kQtThreads, 3) k_quadtree(QtArgs A) {
   const int n = level_end - level_base;
   const int want = lv.quota;
   int* sel_n = A.sel_n + (size_t)frame * kMaxLevels + level;
-  if (tid == 0) A.level_ncand[(size_t)frame * kMaxLevels + level] = n;
+  if (!A.meta[((size_t)frame * kMaxLevels + level) * 8 + kMetaDeep]) return;  // the node-table path did this segment
   if (n == 0 || want <= 0) {
     if (tid == 0) *sel_n = 0;
     return;
@@ -699,15 +1158,25 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
   A.cell_rank = ex->d_cell_rank;
   A.raw = ex->d_raw;
   for (int i = 0; i < 3; i++) { A.keys[i] = ex->d_qt_keys[i]; A.vals[i] = ex->d_qt_vals[i]; }
+  A.bitmap = ex->d_qt_bitmap;
+  A.fold = ex->d_qt_fold;
+  A.meta = ex->d_qt_meta;
   A.sel = ex->d_sel;
   A.sel_n = ex->d_sel_n;
   A.level_ncand = ex->d_level_ncand;
   A.status = ex->d_status;
   if (ex->geom.n_cells > 0)
     k_qt_codes<<<dim3((ex->geom.n_cells + kCodeWarps - 1) / kCodeWarps, batch), kCodeWarps * 32, 0, s>>>(A);
-  dim3 grid(ex->geom.n_levels, batch);
-  k_quadtree<<<grid, kQtThreads, 0, s>>>(A);
-  count_launches(3);
+  // candidate passes: grid-stride over the frame's candidates (their number is only known on the device); enough CTAs per
+  // frame to fill the GPU when the batch is small, few when it is large
+  const int per_frame = std::max(1, std::min((ex->geom.raw_cap + 255) / 256, (148 * 8 + batch - 1) / batch));
+  dim3 grid(ex->geom.n_levels, batch), cgrid(per_frame, batch);
+  k_qt_depth<<<grid, kQtThreads, 0, s>>>(A);
+  k_qt_pass1<<<cgrid, 256, 0, s>>>(A);
+  k_qt_pass2<<<cgrid, 256, 0, s>>>(A);
+  k_qt_finish<<<grid, kQtThreads, 0, s>>>(A);
+  k_quadtree<<<grid, kQtThreads, 0, s>>>(A);  // segments deeper than kQtMapDig only
+  count_launches(7);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
 }
