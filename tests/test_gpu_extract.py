@@ -116,3 +116,19 @@ def test_empty_image_and_errors():
     with pytest.raises(YdorbError):
         ex.extractAndCompute(np.zeros((480, 640), np.uint8))  # larger than max
     ex.close()
+
+
+@pytest.mark.parametrize("patch,nf", [(48, 1000), (90, 2000), (24, 500)])
+def test_clustered_corners_deep_quadtree(patch, nf):
+    """All corners inside one small textured patch of a flat image: far fewer candidates than the quota, so the
+    reference keeps splitting until every point is alone (more than 8 passes: the sort-based deep path of the quadtree),
+    while the upper pyramid levels, where the patch shrinks, take the node-table path."""
+    img = np.full((480, 640), 90, np.uint8)
+    tex = synth.synth_frame(patch, patch, 123 + patch)
+    img[200 : 200 + patch, 300 : 300 + patch] = tex
+    img[37 : 37 + patch // 2, 41 : 41 + patch // 2] = tex[: patch // 2, : patch // 2]
+    ex = OrbExtractor(nf, 1.2, 8, 20, 7, max_width=640, max_height=480)
+    kps, desc = ex.extractAndCompute(img)
+    ok, od, _ = orc.extract(orc.make_params(nf, 1.2, 8, 20), img)
+    assert len(kps) == len(ok) and len(kps) > 20
+    assert np.array_equal(kps, ok) and np.array_equal(desc, od)
