@@ -894,7 +894,9 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_finish(QtArgs A) {
           const unsigned long long a = sk[i], b = sk[q];
           if ((a > b) == ((i & k) == 0)) { sk[i] = b; sk[q] = a; }
         }
-        __syncthreads();
+        // strides up to 32 keep a warp inside its own 64 elements (for every round of the t loop): the next such
+        // stride only needs the warp's own writes
+        if (j > 32 || j == 1) __syncthreads(); else __syncwarp();
       }
     for (int i = tid; i < m_out; i += kQtThreads) {
       const uint32_t r = (uint32_t)sk[i];
