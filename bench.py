@@ -317,7 +317,8 @@ def run_gpu(args):
 
     e2e_single = e2e_measure([make_worker(ex, m, 0, B)])
     assert np.array_equal(h_n.numpy(), n_kp), "host-API and device-API keypoint counts differ"
-    T = max(1, min(E2E_THREADS, B // 8))
+    # the synchronous entry points spin while they wait: keep the ranks' threads within the host's cores
+    T = max(1, min(E2E_THREADS, B // 8, max(1, (os.cpu_count() or 4) // world)))
     bounds = [B * t // T for t in range(T + 1)]
     handles = [(OrbExtractor(*EXTRACTOR_ARGS, max_width=W, max_height=H, max_batch=bounds[t + 1] - bounds[t], device=local),
                 OrbMatcher(RATIO, device=local)) for t in range(T)]
