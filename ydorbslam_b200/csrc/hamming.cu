@@ -164,7 +164,8 @@ __global__ void k_ratio_accept(const YdTop2* __restrict__ t, int nq, float ratio
 
 // Batched variant for many small problems (frame t vs frame t-1): blockIdx.y = pair, the whole database frame
 // (<= capacity rows) is streamed by every CTA; results are written unpacked, optionally with the ratio test.
-__global__ void __launch_bounds__(kTopThreads)
+template <int QPT, int THR>  // queries per thread: 4 amortises a database row best, 2 doubles the warps when the batch is small
+__global__ void __launch_bounds__(THR)
 k_top2_frames(const uint4* __restrict__ desc, const int32_t* __restrict__ n_of, int capacity,
               const int32_t* __restrict__ q_frame, const int32_t* __restrict__ db_frame, YdTop2* __restrict__ out,
               uint8_t* __restrict__ accept, float ratio, int th) {
@@ -173,15 +174,15 @@ k_top2_frames(const uint4* __restrict__ desc, const int32_t* __restrict__ n_of, 
   const int pair = blockIdx.y;
   const int qf = q_frame[pair], df = db_frame[pair];
   const int nq = min(n_of[qf], capacity), ndb = min(n_of[df], capacity);
-  const int q0 = blockIdx.x * kTopQblock;
+  const int q0 = blockIdx.x * (THR * QPT);
   if (q0 >= nq) return;
   const uint4* q = desc + (size_t)qf * capacity * 2;
   const uint4* db = desc + (size_t)df * capacity * 2;
-  uint32_t qa[kTopQpt][8];
-  uint32_t best[kTopQpt], second[kTopQpt];
+  uint32_t qa[QPT][8];
+  uint32_t best[QPT], second[QPT];
 #pragma unroll
-  for (int k = 0; k < kTopQpt; k++) {
-    const int qi = q0 + k * kTopThreads + tid;
+  for (int k = 0; k < QPT; k++) {
+    const int qi = q0 + k * THR + tid;
     uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
     if (qi < nq) { lo = q[2 * qi]; hi = q[2 * qi + 1]; }
     qa[k][0] = lo.x; qa[k][1] = lo.y; qa[k][2] = lo.z; qa[k][3] = lo.w;
@@ -192,13 +193,13 @@ k_top2_frames(const uint4* __restrict__ desc, const int32_t* __restrict__ n_of, 
   for (int t0 = 0; t0 < ndb; t0 += kTopTile) {
     const int rows = min(kTopTile, ndb - t0);
     __syncthreads();
-    for (int i = tid; i < 2 * rows; i += kTopThreads) s_db[i] = db[2 * (size_t)t0 + i];
+    for (int i = tid; i < 2 * rows; i += THR) s_db[i] = db[2 * (size_t)t0 + i];
     __syncthreads();
 #pragma unroll 2
     for (int r = 0; r < rows; r++) {
       const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1];
 #pragma unroll
-      for (int k = 0; k < kTopQpt; k++) {
+      for (int k = 0; k < QPT; k++) {
         const uint32_t key = ham256_key(qa[k], lo, hi, (uint32_t)(t0 + r));
         second[k] = min(second[k], max(best[k], key));
         best[k] = min(best[k], key);
@@ -206,8 +207,8 @@ k_top2_frames(const uint4* __restrict__ desc, const int32_t* __restrict__ n_of, 
     }
   }
 #pragma unroll
-  for (int k = 0; k < kTopQpt; k++) {
-    const int qi = q0 + k * kTopThreads + tid;
+  for (int k = 0; k < QPT; k++) {
+    const int qi = q0 + k * THR + tid;
     if (qi >= nq) continue;
     YdTop2 o;
     o.best_idx = best[k] == kNoKey ? -1 : (int)(best[k] & 0x7FFFFFu);
@@ -305,9 +306,21 @@ int ydorb_hamming_top2_frames_device(YdMatcher* m, const uint8_t* d_desc, const 
   YD_REQUIRE(((uintptr_t)d_desc & 15) == 0, "descriptor block must be 16-byte aligned");
   if (npairs == 0) return YDORB_OK;
   YD_CUDA(cudaSetDevice(m->device));
-  dim3 grid((capacity + kTopQblock - 1) / kTopQblock, npairs);
-  k_top2_frames<<<grid, kTopThreads, 0, m->stream>>>(reinterpret_cast<const uint4*>(d_desc), d_n, capacity, d_q_frame,
-                                                     d_db_frame, d_out, d_accept, ratio, th);
+  // Queries per thread: 4 amortise a database row over the most distance computations, but a small batch then has too
+  // few warps to hide the kernel's latencies (256 pairs of 1000 x 1000 = 13.5 warps per SM): halve it until the launch
+  // has ~20 warps per SM (measured: 0.410 -> 0.358 ms per 256 pairs, 731 Gpairs/s).  YDORB_MATCH_QPT overrides.
+  const long long warps4 = (long long)npairs * ((capacity + kTopQblock - 1) / kTopQblock) * (kTopThreads / 32);
+  int qpt = warps4 >= 20ll * m->sm_count ? 4 : (2 * warps4 >= 20ll * m->sm_count ? 2 : 1);
+  if (const char* e = getenv("YDORB_MATCH_QPT")) qpt = atoi(e);
+#define YD_LAUNCH_FRAMES(QPT, THR)                                                                                   \
+  k_top2_frames<QPT, THR><<<dim3((capacity + THR * QPT - 1) / (THR * QPT), npairs), THR, 0, m->stream>>>(           \
+      reinterpret_cast<const uint4*>(d_desc), d_n, capacity, d_q_frame, d_db_frame, d_out, d_accept, ratio, th)
+  switch (qpt) {
+    case 1: YD_LAUNCH_FRAMES(1, kTopThreads); break;
+    case 2: YD_LAUNCH_FRAMES(2, kTopThreads); break;
+    default: YD_LAUNCH_FRAMES(4, kTopThreads); break;
+  }
+#undef YD_LAUNCH_FRAMES
   count_launches(1);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
