@@ -127,3 +127,30 @@ def test_stereo_identical_images_median_zero():
     assert np.array_equal(rx, orx) and np.array_equal(dp, odp)
     assert (rx == -2).sum() > 0
     exl.close(); exr.close()
+
+
+@pytest.mark.parametrize("keep_rows,expect_big_lag", [(0.5, True), (0.97, False)])
+def test_stereo_lag_window(keep_rows, expect_big_lag):
+    """Reference mode resolves the leftIdx lag (frame.cpp:388-403) from a 64-wide table; right keypoints confined to the
+    top of the image leave many left rows empty, so the lag outgrows the window and the general chain takes over."""
+    w, h, nf = 1241, 376, 2000
+    left, right = synth.synth_stereo_pair(w, h, 64)
+    exl = OrbExtractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    exr = OrbExtractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    kl, dl = exl.extractAndCompute(left)
+    kr, dr = exr.extractAndCompute(right)
+    keep = kr["y"] < h * keep_rows
+    kr, dr = np.ascontiguousarray(kr[keep]), np.ascontiguousarray(dr[keep])
+    empty_rows = int((kl["y"] > h * keep_rows + 40).sum())
+    assert (empty_rows > 64) == expect_big_lag
+    m = OrbMatcher()
+    bf = 386.1448
+    p = orc.make_params(nf, 1.2, 8, 20)
+    _, pl = orc.pyramid(p, left)
+    _, pr = orc.pyramid(p, right)
+    for mode in (0, 1):
+        rx, dp = m.computeStereoMatches(exl, 0, exr, 0, kl, dl, kr, dr, bf, np.inf, mode)
+        orx, odp = orc.stereo_match(p, w, h, pl, pr, kl, dl, kr, dr, bf, np.inf, mode)
+        assert np.array_equal(rx.view(np.uint32), orx.view(np.uint32))
+        assert np.array_equal(dp.view(np.uint32), odp.view(np.uint32))
+    exl.close(); exr.close()

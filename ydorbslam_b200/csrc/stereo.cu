@@ -14,6 +14,7 @@
 //      pair result up.  In mode 1 (corrected: row = slot = k) C is parallel over k as well.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 #include "matcher.cuh"
 
@@ -179,7 +180,7 @@ struct ChainArgs {
   float* right_x;
   float* depth;
   int* rec_sad;     // [nl] SAD recorded at a slot, -1 = none
-  int* counters;    // [0] recorded, [1] recorded with SAD 0
+  int* counters;    // [0] recorded, [1] recorded with SAD 0, [2] lag window overflowed, [3] final lag
 };
 
 // Hamming arg-min of left descriptor row `row` over the candidate list of keypoint k (warp-cooperative)
@@ -219,24 +220,105 @@ __device__ __forceinline__ int stereo_step(const ChainArgs& A, int k, int slot, 
   return 1;
 }
 
-// C (reference mode): one warp walks the lag chain
+// C (reference mode), general form: one warp walks the lag chain.  Only runs when the windowed form below overflowed.
 __global__ void __launch_bounds__(32) k_stereo_chain(ChainArgs A) {
+  if (!A.counters[2]) return;
   const int lane = threadIdx.x;
   int left_idx = 0;
   for (int k = 0; k < A.nl; k++) left_idx += stereo_step(A, k, left_idx, lane);
 }
-// C (corrected mode): slot = k, parallel
-__global__ void __launch_bounds__(128) k_stereo_direct(ChainArgs A) {
+// C (corrected mode, lag == nullptr): slot = k.  Reference mode: slot = k - lag[k] from the lag walk.
+__global__ void __launch_bounds__(128) k_stereo_direct(ChainArgs A, const int* __restrict__ lag) {
   const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (k < A.nl) stereo_step(A, k, k, lane);
+  if (k >= A.nl) return;
+  if (lag && A.counters[2]) return;  // window overflowed: k_stereo_chain does the work
+  stereo_step(A, k, lag ? k - lag[k] : k, lane);
+}
+
+// C (reference mode), windowed form.  lag(k) = k - leftIdx(k) only grows when a step does not advance, and once it
+// is > 0 the descriptor row belongs to another keypoint, so it stays small in practice.  Whether step k advances is
+// a function of (k, lag) alone: tabulate it for lag < 64 with the whole GPU (bit `lag` of adv[k]), then resolve the
+// chain as a walk over those bits.
+constexpr int kLagWindow = 64;
+constexpr int kLagBlock = 32;      // keypoints per walk block
+constexpr int kLagMaxBlocks = 1024;  // 64 KB of shared memory: n_left <= 32768, else the general form runs
+
+__global__ void __launch_bounds__(128) k_stereo_lag_table(ChainArgs A, uint32_t* __restrict__ adv) {
+  // warp per (keypoint, half of the window), lane per lag
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int k = wid >> 1, h = wid & 1;
+  if (k >= A.nl) return;
+  if (!A.row_nonempty[k]) {  // :388, never advances
+    if (lane == 0) adv[wid] = 0u;
+    return;
+  }
+  const int b = A.cand_start[k], e = A.cand_start[k + 1];
+  const int row = k - (lane + 32 * h);
+  bool bit = true;  // lags beyond k are never reached
+  if (row >= 0) {
+    const uint4 a0 = A.dl[2 * row], a1 = A.dl[2 * row + 1];
+    uint32_t key = 0xFFFFFFFFu;
+#pragma unroll 4
+    for (int t = b; t < e; t++) {  // every lane walks the same list: broadcast loads
+      const int r = A.cand[t];
+      const uint4 b0 = A.dr[2 * r], b1 = A.dr[2 * r + 1];
+      const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                    __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+      key = min(key, ((uint32_t)d << 22) | (uint32_t)(t - b));
+    }
+    if (key != 0xFFFFFFFFu && (key >> 22) < 75u) bit = A.res[b + (int)(key & 0x3FFFFFu)].state != 0;
+  }
+  const uint32_t word = __ballot_sync(0xffffffffu, bit);
+  if (lane == 0) adv[wid] = word;  // little-endian halves of the 64-bit row
+}
+
+__device__ __forceinline__ int lag_walk(const unsigned long long* __restrict__ adv, int k0, int k1, int lag, int* out) {
+  // lag == kLagWindow is the sticky overflow state
+#pragma unroll 4
+  for (int k = k0; k < k1; k++) {
+    const unsigned long long bits = adv[k];
+    if (out) out[k] = lag;
+    if (lag < kLagWindow) lag += 1 - (int)((bits >> lag) & 1ull);
+  }
+  return lag;
+}
+
+// single CTA: (1) per block of 32 keypoints and per entry lag, the exit lag; (2) one thread chains the blocks;
+// (3) per block, the walk from its now known entry lag writes lag[k].  Serial depth 32 + nblk + 32 instead of n.
+__global__ void __launch_bounds__(1024) k_stereo_lag_walk(const unsigned long long* __restrict__ adv, int nl,
+                                                          int* __restrict__ lag, int* __restrict__ counters) {
+  extern __shared__ uint8_t s_exit[];  // [nblk][64]
+  __shared__ int s_entry[kLagMaxBlocks];
+  const int nblk = (nl + kLagBlock - 1) / kLagBlock;
+  for (int w = threadIdx.x; w < nblk * kLagWindow; w += blockDim.x) {
+    const int blk = w >> 6, l0 = w & 63, k0 = blk * kLagBlock;
+    s_exit[w] = (uint8_t)lag_walk(adv, k0, min(k0 + kLagBlock, nl), l0, nullptr);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int l = 0;
+    for (int blk = 0; blk < nblk; blk++) {
+      s_entry[blk] = l;
+      if (l < kLagWindow) l = s_exit[blk * kLagWindow + l];
+    }
+    counters[2] = l >= kLagWindow;
+    counters[3] = l;
+  }
+  __syncthreads();
+  for (int blk = threadIdx.x; blk < nblk; blk += blockDim.x) {
+    const int k0 = blk * kLagBlock;
+    lag_walk(adv, k0, min(k0 + kLagBlock, nl), s_entry[blk], lag);
+  }
 }
 
 __global__ void k_stereo_init(int nl, float* __restrict__ right_x, float* __restrict__ depth, int* __restrict__ rec_sad,
                               int* __restrict__ counters) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < nl) { right_x[i] = -1.0f; depth[i] = -1.0f; rec_sad[i] = -1; }  // :363-364
-  if (i == 0) { counters[0] = 0; counters[1] = 0; }
+  if (i == 0) { counters[0] = 0; counters[1] = 0; counters[2] = 0; counters[3] = 0; }
 }
+
+__global__ void k_stereo_force_chain(int* counters) { counters[2] = 1; }
 
 // :463-471 -- the ascending loop breaks at once unless the median SAD is 0, in which case every match goes to -2
 __global__ void k_stereo_outliers(int nl, const int* __restrict__ rec_sad, const int* __restrict__ counters,
@@ -290,7 +372,8 @@ extern "C" int ydorb_stereo_match(YdMatcher* m, const YdExtractor* left, int lef
                o_dr = o_dl + al((size_t)32 * nl), o_rx = o_dr + al((size_t)32 * std::max(nr, 1)), o_dp = o_rx + al(sizeof(float) * (size_t)nl),
                o_cnt = o_dp + al(sizeof(float) * (size_t)nl), o_start = o_cnt + al(sizeof(int) * (size_t)nl),
                o_row = o_start + al(sizeof(int) * ((size_t)nl + 1)), o_rec = o_row + al((size_t)nl),
-               o_ctr = o_rec + al(sizeof(int) * (size_t)nl), io_total = o_ctr + 256;
+               o_ctr = o_rec + al(sizeof(int) * (size_t)nl), o_adv = o_ctr + 256,
+               o_lag = o_adv + al(sizeof(unsigned long long) * (size_t)nl), io_total = o_lag + al(sizeof(int) * (size_t)nl);
   int rc = matcher_reserve_io(m, io_total);
   if (rc != YDORB_OK) return rc;
   uint8_t* io = reinterpret_cast<uint8_t*>(m->d_io);
@@ -303,6 +386,8 @@ extern "C" int ydorb_stereo_match(YdMatcher* m, const YdExtractor* left, int lef
   uint8_t* d_row = io + o_row;
   int* d_rec = reinterpret_cast<int*>(io + o_rec);
   int* d_ctr = reinterpret_cast<int*>(io + o_ctr);
+  unsigned long long* d_adv = reinterpret_cast<unsigned long long*>(io + o_adv);
+  int* d_lag = reinterpret_cast<int*>(io + o_lag);
   YD_CUDA(cudaMemcpyAsync(d_kl, kp_left, sizeof(YdKeyPoint) * (size_t)nl, cudaMemcpyHostToDevice, s));
   YD_CUDA(cudaMemcpyAsync(io + o_dl, desc_left, (size_t)32 * nl, cudaMemcpyHostToDevice, s));
   if (nr > 0) {
@@ -340,8 +425,23 @@ extern "C" int ydorb_stereo_match(YdMatcher* m, const YdExtractor* left, int lef
   A.depth = d_dp;
   A.rec_sad = d_rec;
   A.counters = d_ctr;
-  if (mode == 0) k_stereo_chain<<<1, 32, 0, s>>>(A);
-  else k_stereo_direct<<<wblocks, 128, 0, s>>>(A);
+  if (mode == 0) {
+    const int nblk = (nl + kLagBlock - 1) / kLagBlock;
+    static const bool force_chain = getenv("YDORB_STEREO_CHAIN") != nullptr;  // probe: the general form only
+    if (nblk <= kLagMaxBlocks && !force_chain) {
+      if ((size_t)nblk * kLagWindow > 40 * 1024)
+        YD_CUDA(cudaFuncSetAttribute(k_stereo_lag_walk, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kLagMaxBlocks * kLagWindow));
+      k_stereo_lag_table<<<(nl * 64 + 127) / 128, 128, 0, s>>>(A, reinterpret_cast<uint32_t*>(d_adv));
+      k_stereo_lag_walk<<<1, 1024, (size_t)nblk * kLagWindow, s>>>(d_adv, nl, d_lag, d_ctr);
+      k_stereo_direct<<<wblocks, 128, 0, s>>>(A, d_lag);
+    } else {
+      k_stereo_force_chain<<<1, 1, 0, s>>>(d_ctr);
+    }
+    k_stereo_chain<<<1, 32, 0, s>>>(A);
+  } else {
+    k_stereo_direct<<<wblocks, 128, 0, s>>>(A, nullptr);
+  }
   k_stereo_outliers<<<(nl + 255) / 256, 256, 0, s>>>(nl, d_rec, d_ctr, d_rx, d_dp);
   YD_CUDA(cudaGetLastError());
   YD_CUDA(cudaMemcpyAsync(right_x, d_rx, sizeof(float) * (size_t)nl, cudaMemcpyDeviceToHost, s));
