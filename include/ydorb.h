@@ -179,6 +179,12 @@ int ydorb_frame_keypoints_in_area(YdFrame* f, float x, float y, float r, int min
 int ydorb_search_by_projection(YdFrame* f, const YdMapPointProj* map_points, const uint8_t* mp_descriptors,
                                const uint8_t* mp_obs_positive, int n_map_points, const uint8_t* kp_occupied, float th,
                                float ratio, int32_t* match_out, int32_t* n_matches);
+/* Same search with the map point arrays, kp_occupied and match_out resident in device memory (a local map kept on the
+ * GPU between frames); mp_descriptors 16-byte aligned.  *n_matches is a host int; returns after the matcher's stream
+ * has drained, match_out is complete by then. */
+int ydorb_search_by_projection_device(YdFrame* f, const YdMapPointProj* map_points, const uint8_t* mp_descriptors,
+                                      const uint8_t* mp_obs_positive, int n_map_points, const uint8_t* kp_occupied,
+                                      float th, float ratio, int32_t* match_out, int32_t* n_matches);
 
 /* ---- Projection searches after M1 ------------------------------------------------------------------------
  * OrbMatcher::searchByProjectionInLastAndCurrentFrame (src/orbMatcher.cpp:65-155), ...InKeyFrameAndCurrentFrame

@@ -66,6 +66,18 @@ def test_search_by_projection(frame640, nmp, th, occupied):
     assert np.array_equal(match, rmatch)
     if nmp >= 3000:
         assert n > 50
+    # the same search with the local map resident on the device
+    import torch
+
+    dev = torch.device("cuda:0")
+    d_mps = torch.from_numpy(mps.view(np.uint8).reshape(-1).copy() if nmp else np.zeros(16, np.uint8)).to(dev)
+    d_mpd = torch.from_numpy(np.ascontiguousarray(mpd).reshape(-1).copy() if nmp else np.zeros(32, np.uint8)).to(dev)
+    d_obs = torch.from_numpy(np.ascontiguousarray(obs, dtype=np.uint8).copy() if nmp else np.zeros(1, np.uint8)).to(dev)
+    d_occ = torch.from_numpy(occ).to(dev)
+    d_out = torch.full((len(kps),), 7, dtype=torch.int32, device=dev)
+    dn = m.searchByProjectionInFrameAndMapPoint_device(fr, d_mps.data_ptr(), d_mpd.data_ptr(), d_obs.data_ptr(), nmp,
+                                                       d_out.data_ptr(), th, d_occ.data_ptr() if occupied else None)
+    assert dn == rn and np.array_equal(d_out.cpu().numpy(), rmatch)
     fr.close()
 
 

@@ -13,6 +13,9 @@
 // the map point index the fixed point is unique and equals the sequential result.
 #include <algorithm>
 #include <vector>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 #include "frame.cuh"
 
@@ -102,76 +105,225 @@ struct SearchArgs {
   const uint8_t* mp_obs;
   int nmp;
   float th, ratio;
-  const int* blocker;   // B[idx]: first blocking claimant (-1: occupied before the call)
-  int* blocker_next;    // B'[idx]
-  int* last_writer;     // max accepted claimant per keypoint
-  int* best_of;         // [nmp] best keypoint of each map point or -1
-  int* flags;           // [0] changed, [1] match count
+  const uint8_t* occupied;  // [n] or nullptr: slot held before the call (blocks every map point)
+  // candidate lists built by the one window walk
+  uint32_t* pool;           // packed {idx:19, octave:4, dist:9} in walk order
+  int pool_cap;
+  int3* live;               // {map point, first pool slot, count}; count < 0: list did not fit, walk again each round
+  int* best_prev;           // [live slot] best keypoint in the previous round (-2 before the first)
+  int* blockers;            // 3 x [n]: round r reads r%3, claims into (r+1)%3, resets (r+2)%3
+  int n;
+  int* last_writer;         // [n] largest accepted claimant per keypoint
+  int* ctr;                 // [0] live count, [1] pool cursor, [2] matches, [3] done, [4..19] changed flag of round r&15
 };
 
-// one thread per map point: body of the loop at src/orbMatcher.cpp:26-61
-__global__ void __launch_bounds__(128) k_search_projection(SearchArgs A) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= A.nmp) return;
-  const YdMapPointProj mp = A.mps[j];
-  int best_idx = -1;
-  if (mp.active) {                                                                   // :27
-    const int L = mp.level;
-    const float radius = __fmul_rn(A.th, ((double)mp.view_cos > 0.998) ? 2.5f : 4.0f);  // :30, :820-826
-    const float r = __fmul_rn(radius, A.gp.sf[L]);
-    const uint4 q0 = A.mp_desc[2 * j], q1 = A.mp_desc[2 * j + 1];
-    int bestDist = 256, bestLevel = -1, secondDist = 256, secondLevel = -1;
-    CellRange cr;
-    if (cell_range(A.gp, mp.proj_x, mp.proj_y, r, cr)) {
-      for (int ix = cr.x0; ix <= cr.x1; ix++)
-        for (int iy = cr.y0; iy <= cr.y1; iy++) {
-          const int c = ix * kGridRows + iy;
-          const int e = A.cell_start[c + 1];
-          for (int t = A.cell_start[c]; t < e; t++) {
-            const int idx = A.items[t];
-            const YdKeyPoint kp = A.kps[idx];
-            if (!in_window(kp, mp.proj_x, mp.proj_y, r, L - 1, L)) continue;         // :31
-            if (A.blocker[idx] < j) continue;                                        // :40 slot held, observations>0
-            const float rx = A.right_x[idx];
-            if (!(rx <= 0.f || fabsf(__fsub_rn(mp.proj_right_x, rx)) <= r)) continue;  // :41
-            const int d = hamming256(q0, q1, A.desc[2 * idx], A.desc[2 * idx + 1]);
-            if (d < bestDist) {                                                      // :43-52
-              secondDist = bestDist; bestDist = d; secondLevel = bestLevel; bestLevel = kp.octave; best_idx = idx;
-            } else if (d < secondDist) {
-              secondLevel = kp.octave; secondDist = d;
-            }
-          }
-        }
+constexpr int kCtrChanged = 4;
+
+__device__ __forceinline__ float search_radius(const SearchArgs& A, const YdMapPointProj& mp) {
+  const float radius = __fmul_rn(A.th, ((double)mp.view_cos > 0.998) ? 2.5f : 4.0f);  // :30, :820-826
+  return __fmul_rn(radius, A.gp.sf[mp.level]);
+}
+
+// the window walk of map point j (:31 getKeyPointsInArea order, then the gates of :41): f(idx, octave, dist)
+template <class F>
+__device__ __forceinline__ void search_walk(const SearchArgs& A, int j, const YdMapPointProj& mp, F&& f) {
+  const int L = mp.level;
+  const float r = search_radius(A, mp);
+  const uint4 q0 = A.mp_desc[2 * j], q1 = A.mp_desc[2 * j + 1];
+  CellRange cr;
+  if (!cell_range(A.gp, mp.proj_x, mp.proj_y, r, cr)) return;
+  for (int ix = cr.x0; ix <= cr.x1; ix++) {
+    // cells (ix, y0..y1) are adjacent in the CSR table: one item range per column
+    const int e = A.cell_start[ix * kGridRows + cr.y1 + 1];
+    for (int t = A.cell_start[ix * kGridRows + cr.y0]; t < e; t++) {
+      const int idx = A.items[t];
+      const YdKeyPoint kp = A.kps[idx];
+      if (!in_window(kp, mp.proj_x, mp.proj_y, r, L - 1, L)) continue;             // :31
+      const float rx = A.right_x[idx];
+      if (!(rx <= 0.f || fabsf(__fsub_rn(mp.proj_right_x, rx)) <= r)) continue;    // :41
+      f(idx, kp.octave, hamming256(q0, q1, A.desc[2 * idx], A.desc[2 * idx + 1]));
     }
+  }
+}
+
+struct Top2 {
+  int bestDist = 256, bestLevel = -1, secondDist = 256, secondLevel = -1, best_idx = -1;
+  __device__ __forceinline__ void push(int idx, int octave, int d) {  // :43-52
+    if (d < bestDist) {
+      secondDist = bestDist; bestDist = d; secondLevel = bestLevel; bestLevel = octave; best_idx = idx;
+    } else if (d < secondDist) {
+      secondLevel = octave; secondDist = d;
+    }
+  }
+  __device__ __forceinline__ int result(float ratio) const {  // :56
     const bool accept = best_idx >= 0 && bestDist <= 100 &&
-                        (bestLevel != secondLevel || (float)bestDist <= __fmul_rn(A.ratio, (float)secondDist));  // :56
-    if (!accept) best_idx = -1;
+                        (bestLevel != secondLevel || (float)bestDist <= __fmul_rn(ratio, (float)secondDist));
+    return accept ? best_idx : -1;
   }
-  A.best_of[j] = best_idx;
-  if (best_idx >= 0) {
-    atomicAdd(&A.flags[1], 1);
-    atomicMax(&A.last_writer[best_idx], j);
-    if (A.mp_obs[j]) atomicMin(&A.blocker_next[best_idx], j);
+};
+
+// one warp per map point of [j0, j1): walk the window (lanes over the items of a grid column), keep what does not
+// depend on the claims.  Pass 1 counts, lane 0 reserves exactly that much of the pool, pass 2 fills in walk order.
+__global__ void __launch_bounds__(256) k_search_build(SearchArgs A, int j0, int j1) {
+  const int j = j0 + ((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (j >= j1) return;
+  const YdMapPointProj mp = A.mps[j];
+  if (!mp.active) return;  // :27
+  const int L = mp.level;
+  const float r = search_radius(A, mp);
+  CellRange cr;
+  if (!cell_range(A.gp, mp.proj_x, mp.proj_y, r, cr)) return;
+  auto passes = [&](int idx, int* octave) {
+    const YdKeyPoint kp = A.kps[idx];
+    *octave = kp.octave;
+    if (!in_window(kp, mp.proj_x, mp.proj_y, r, L - 1, L)) return false;             // :31
+    if (A.occupied && A.occupied[idx]) return false;                                 // :40, slot held before the call
+    const float rx = A.right_x[idx];
+    return rx <= 0.f || fabsf(__fsub_rn(mp.proj_right_x, rx)) <= r;                  // :41
+  };
+  // cells (ix, y0..y1) are adjacent in the CSR table: one item range per grid column.  Lanes take the columns'
+  // ranges (32 columns at a time), then the items of all those columns as one flat index space.
+  struct Group { int b, incl, total, ncol; };
+  auto load_group = [&](int cg) {
+    Group g;
+    g.ncol = min(32, cr.x1 - cg + 1);
+    int len = 0;
+    g.b = 0;
+    if (lane < g.ncol) {
+      g.b = A.cell_start[(cg + lane) * kGridRows + cr.y0];
+      len = A.cell_start[(cg + lane) * kGridRows + cr.y1 + 1] - g.b;
+    }
+    g.incl = len;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, g.incl, o);
+      if (lane >= o) g.incl += v;
+    }
+    g.total = __shfl_sync(0xffffffffu, g.incl, 31);
+    return g;
+  };
+  auto locate = [&](const Group& g, int fi) {  // flat index -> CSR slot (all lanes call)
+    int t = -1, prev = 0;
+    for (int c = 0; c < g.ncol; c++) {
+      const int inc = __shfl_sync(0xffffffffu, g.incl, c), bc = __shfl_sync(0xffffffffu, g.b, c);
+      if (fi >= prev && fi < inc) t = bc + fi - prev;
+      prev = inc;
+    }
+    return t;
+  };
+  const bool one_group = cr.x1 - cr.x0 < 32;
+  int cnt = 0, first_idx = 0, first_oct = 0, first_total = 0;
+  bool first_ok = false;
+  for (int cg = cr.x0; cg <= cr.x1; cg += 32) {
+    const Group g = load_group(cg);
+    if (cg == cr.x0) first_total = g.total;
+    for (int base = 0; base < g.total; base += 32) {
+      const int t = locate(g, base + lane);
+      int octave = 0, idx = 0;
+      bool ok = false;
+      if (t >= 0) { idx = A.items[t]; ok = passes(idx, &octave); }
+      if (cg == cr.x0 && base == 0) { first_ok = ok; first_idx = idx; first_oct = octave; }
+      cnt += __popc(__ballot_sync(0xffffffffu, ok));
+    }
+  }
+  if (cnt == 0) return;
+  int start = 0;
+  if (lane == 0) {
+    start = atomicAdd(&A.ctr[1], cnt);
+    const int slot = atomicAdd(&A.ctr[0], 1);
+    const bool fits = start >= 0 && start + cnt <= A.pool_cap;
+    A.live[slot] = fits ? make_int3(j, start, cnt) : make_int3(j, 0, -1);
+    A.best_prev[slot] = -2;
+    if (!fits) start = -1;
+  }
+  start = __shfl_sync(0xffffffffu, start, 0);
+  if (start < 0) return;
+  const uint4 q0 = A.mp_desc[2 * j], q1 = A.mp_desc[2 * j + 1];
+  auto emit = [&](bool ok, int idx, int octave, int pos) {
+    const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+    if (ok) {
+      const int d = hamming256(q0, q1, A.desc[2 * idx], A.desc[2 * idx + 1]);
+      A.pool[pos + __popc(bal & ((1u << lane) - 1u))] = ((uint32_t)idx << 13) | ((uint32_t)octave << 9) | (uint32_t)d;
+    }
+    return pos + __popc(bal);
+  };
+  if (one_group && first_total <= 32) {  // the usual case: what pass 1 looked at is still in registers
+    emit(first_ok, first_idx, first_oct, start);
+    return;
+  }
+  int pos = start;
+  for (int cg = cr.x0; cg <= cr.x1; cg += 32) {
+    const Group g = load_group(cg);
+    for (int base = 0; base < g.total; base += 32) {
+      const int t = locate(g, base + lane);
+      int octave = 0, idx = 0;
+      bool ok = false;
+      if (t >= 0) { idx = A.items[t]; ok = passes(idx, &octave); }
+      pos = emit(ok, idx, octave, pos);
+    }
   }
 }
 
-__global__ void k_blocker_diff(const int* __restrict__ a, const int* __restrict__ b, int n, int* __restrict__ flags) {
+__global__ void k_search_init(SearchArgs A) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n && a[i] != b[i]) flags[0] = 1;
-}
-
-__global__ void k_blocker_init(const uint8_t* __restrict__ occupied, int n, int* __restrict__ b) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) b[i] = (occupied && occupied[i]) ? -1 : kNoBlocker;
-}
-
-__global__ void k_round_init(const int* __restrict__ b0, int n, int* __restrict__ bnext, int* __restrict__ last, int* __restrict__ flags) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) {
-    bnext[i] = (b0[i] == -1) ? -1 : kNoBlocker;  // pre-occupied slots stay blocked
-    last[i] = -1;
+  if (i < A.n) {
+    const int v = (A.occupied && A.occupied[i]) ? -1 : kNoBlocker;
+    A.blockers[i] = v;
+    A.blockers[A.n + i] = v;
+    A.last_writer[i] = -1;
   }
-  if (i == 0) { flags[0] = 0; flags[1] = 0; }
+  if (i < 4 + 16) A.ctr[i] = 0;
+}
+
+// claim round r: every live map point re-decides against the claims of round r-1.  Rounds are launched ahead of the
+// host; once a round changes nothing the rest return at once.
+__global__ void __launch_bounds__(256) k_search_round(SearchArgs A, int r) {
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
+  if (tid == 0) A.ctr[kCtrChanged + ((r + 1) & 15)] = 0;
+  if (r > 0 && A.ctr[kCtrChanged + ((r - 1) & 15)] == 0) return;
+  const int* cur = A.blockers + (size_t)(r % 3) * A.n;
+  int* nxt = A.blockers + (size_t)((r + 1) % 3) * A.n;
+  int* clr = A.blockers + (size_t)((r + 2) % 3) * A.n;
+  for (int i = tid; i < A.n; i += nthreads) clr[i] = (A.occupied && A.occupied[i]) ? -1 : kNoBlocker;
+  const int nlive = A.ctr[0];
+  bool changed = false;
+  for (int e = tid; e < nlive; e += nthreads) {
+    const int3 lv = A.live[e];
+    const int j = lv.x;
+    Top2 t2;
+    if (lv.z >= 0) {
+      for (int i = 0; i < lv.z; i++) {
+        const uint32_t c = A.pool[lv.y + i];
+        const int idx = (int)(c >> 13);
+        if (cur[idx] < j) continue;  // :40 claimed by an earlier map point with observations > 0
+        t2.push(idx, (int)((c >> 9) & 15u), (int)(c & 511u));
+      }
+    } else {
+      search_walk(A, j, A.mps[j], [&](int idx, int octave, int d) {
+        if (cur[idx] < j) return;
+        t2.push(idx, octave, d);
+      });
+    }
+    const int best = t2.result(A.ratio);
+    if (best >= 0 && A.mp_obs[j]) atomicMin(&nxt[best], j);
+    if (best != A.best_prev[e]) { A.best_prev[e] = best; changed = true; }
+  }
+  if (changed) A.ctr[kCtrChanged + (r & 15)] = 1;
+}
+
+// after `rounds` rounds: if the last one changed nothing the claims are final (:57-60)
+__global__ void __launch_bounds__(256) k_search_final(SearchArgs A, int rounds) {
+  if (A.ctr[kCtrChanged + ((rounds - 1) & 15)] != 0) return;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
+  if (tid == 0) A.ctr[3] = 1;
+  const int nlive = A.ctr[0];
+  for (int e = tid; e < nlive; e += nthreads) {
+    const int best = A.best_prev[e];
+    if (best >= 0) {
+      atomicAdd(&A.ctr[2], 1);
+      atomicMax(&A.last_writer[best], A.live[e].x);
+    }
+  }
 }
 
 }  // namespace ydorb
@@ -264,31 +416,41 @@ int ydorb_frame_keypoints_in_area(YdFrame* f, float x, float y, float r, int min
   return YDORB_OK;
 }
 
-int ydorb_search_by_projection(YdFrame* f, const YdMapPointProj* map_points, const uint8_t* mp_descriptors,
-                               const uint8_t* mp_obs_positive, int n_map_points, const uint8_t* kp_occupied, float th,
-                               float ratio, int32_t* match_out, int32_t* n_matches) {
-  YD_REQUIRE(f && match_out && n_matches && n_map_points >= 0, "bad argument");
-  YD_REQUIRE(n_map_points == 0 || (map_points && mp_descriptors && mp_obs_positive), "null map point arrays");
+// shared body of the host and device entry points; device == true: every pointer is a device pointer
+static int search_by_projection_impl(YdFrame* f, const YdMapPointProj* map_points, const uint8_t* mp_descriptors,
+                                     const uint8_t* mp_obs_positive, int nmp, const uint8_t* kp_occupied, float th,
+                                     float ratio, int32_t* match_out, int32_t* n_matches, bool device) {
   YdMatcher* m = f->m;
-  YD_CUDA(cudaSetDevice(m->device));
   cudaStream_t s = m->stream;
-  const int n = f->n, nmp = n_map_points;
-  for (int i = 0; i < n; i++) match_out[i] = -1;
-  *n_matches = 0;
-  if (n == 0 || nmp == 0) return YDORB_OK;
-  // staging: map points | descriptors | obs | occupied | best_of
-  const size_t o_mp = 0, o_desc = (sizeof(YdMapPointProj) * (size_t)nmp + 255) / 256 * 256,
-               o_obs = o_desc + (size_t)32 * nmp, o_occ = o_obs + ((size_t)nmp + 255) / 256 * 256,
-               o_best = o_occ + ((size_t)n + 255) / 256 * 256, total = o_best + sizeof(int) * (size_t)nmp;
-  int rc = matcher_reserve_io(m, total);
+  const int n = f->n;
+  auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+  // staging (host entry only): map points | descriptors | obs | occupied
+  const size_t o_mp = 0, o_desc = al(sizeof(YdMapPointProj) * (size_t)nmp), o_obs = o_desc + (size_t)32 * nmp,
+               o_occ = o_obs + al((size_t)nmp), total = o_occ + al((size_t)n);
+  uint8_t* io = nullptr;
+  if (!device) {
+    const int rc = matcher_reserve_io(m, total);
+    if (rc != YDORB_OK) return rc;
+    io = reinterpret_cast<uint8_t*>(m->d_io);
+  }
+  // work: candidate pool | live list | previous best | three blocker tables | counters
+  const int pool_cap = n <= (1 << 19) ? (int)std::min<size_t>((size_t)32 * nmp + 65536, (size_t)1 << 30) : 0;
+  const size_t w_pool = 0, w_live = w_pool + al(sizeof(uint32_t) * (size_t)std::max(pool_cap, 1)),
+               w_prev = w_live + al(sizeof(int3) * (size_t)nmp), w_blk = w_prev + al(sizeof(int) * (size_t)nmp),
+               w_ctr = w_blk + al(sizeof(int) * 3 * (size_t)n), w_total = w_ctr + 256;
+  const int rc = matcher_reserve(m, w_total);
   if (rc != YDORB_OK) return rc;
-  uint8_t* io = reinterpret_cast<uint8_t*>(m->d_io);
-  YD_CUDA(cudaMemcpyAsync(io + o_mp, map_points, sizeof(YdMapPointProj) * (size_t)nmp, cudaMemcpyHostToDevice, s));
-  YD_CUDA(cudaMemcpyAsync(io + o_desc, mp_descriptors, (size_t)32 * nmp, cudaMemcpyHostToDevice, s));
-  YD_CUDA(cudaMemcpyAsync(io + o_obs, mp_obs_positive, (size_t)nmp, cudaMemcpyHostToDevice, s));
-  if (kp_occupied) YD_CUDA(cudaMemcpyAsync(io + o_occ, kp_occupied, (size_t)n, cudaMemcpyHostToDevice, s));
-  const int gb = (n + 255) / 256;
-  k_blocker_init<<<gb, 256, 0, s>>>(kp_occupied ? io + o_occ : nullptr, n, f->d_blocker);
+  uint8_t* wk = reinterpret_cast<uint8_t*>(m->d_scratch);
+  static const bool trace = getenv("YDORB_SEARCH_TRACE") != nullptr;  // diagnostic: per-phase wall times on stderr
+  auto now = [] { return std::chrono::steady_clock::now(); };
+  auto t_prev = now();
+  auto lap = [&](const char* what, int v) {
+    if (!trace) return;
+    cudaStreamSynchronize(s);
+    const auto t = now();
+    fprintf(stderr, "[ydorb search] %s %d: %.1f us\n", what, v, std::chrono::duration<double, std::micro>(t - t_prev).count());
+    t_prev = t;
+  };
   SearchArgs A;
   A.gp = f->gp;
   A.kps = f->d_kps;
@@ -296,37 +458,93 @@ int ydorb_search_by_projection(YdFrame* f, const YdMapPointProj* map_points, con
   A.right_x = f->d_right_x;
   A.cell_start = f->d_cell_start;
   A.items = f->d_cell_items;
-  A.mps = reinterpret_cast<const YdMapPointProj*>(io + o_mp);
-  A.mp_desc = reinterpret_cast<const uint4*>(io + o_desc);
-  A.mp_obs = io + o_obs;
+  A.mps = device ? map_points : reinterpret_cast<const YdMapPointProj*>(io + o_mp);
+  A.mp_desc = reinterpret_cast<const uint4*>(device ? mp_descriptors : io + o_desc);
+  A.mp_obs = device ? mp_obs_positive : io + o_obs;
   A.nmp = nmp;
   A.th = th;
   A.ratio = ratio;
-  A.last_writer = f->d_last;
-  A.best_of = reinterpret_cast<int*>(io + o_best);
-  A.flags = f->d_flags;
-  int* cur = f->d_blocker;
-  int* nxt = f->d_blocker2;
-  int flags[2] = {1, 0};
-  // fixed-point iteration: round t makes at least the first t claimants final, in practice 2-5 rounds
-  for (int round = 0; round <= nmp + 1 && flags[0]; round++) {
-    k_round_init<<<gb, 256, 0, s>>>(f->d_blocker, n, nxt, f->d_last, f->d_flags);
-    A.blocker = cur;
-    A.blocker_next = nxt;
-    k_search_projection<<<(nmp + 127) / 128, 128, 0, s>>>(A);
-    k_blocker_diff<<<gb, 256, 0, s>>>(cur, nxt, n, f->d_flags);
-    YD_CUDA(cudaGetLastError());
-    YD_CUDA(cudaMemcpyAsync(flags, f->d_flags, sizeof flags, cudaMemcpyDeviceToHost, s));
-    YD_CUDA(cudaStreamSynchronize(s));
-    std::swap(cur, nxt);
-    if (cur == f->d_blocker) {  // keep the pristine "occupied before the call" table in d_blocker
-      // after an even number of swaps cur is d_blocker again: we must not have overwritten its -1 entries;
-      // k_round_init re-derives them from d_blocker, and d_blocker's -1 entries are never changed by atomicMin.
+  A.occupied = !kp_occupied ? nullptr : device ? kp_occupied : io + o_occ;
+  A.pool = reinterpret_cast<uint32_t*>(wk + w_pool);
+  A.pool_cap = pool_cap;
+  A.live = reinterpret_cast<int3*>(wk + w_live);
+  A.best_prev = reinterpret_cast<int*>(wk + w_prev);
+  A.blockers = reinterpret_cast<int*>(wk + w_blk);
+  A.n = n;
+  A.last_writer = device ? match_out : f->d_last;
+  A.ctr = reinterpret_cast<int*>(wk + w_ctr);
+  if (kp_occupied && !device) YD_CUDA(cudaMemcpyAsync(io + o_occ, kp_occupied, (size_t)n, cudaMemcpyHostToDevice, s));
+  k_search_init<<<(std::max(n, 32) + 255) / 256, 256, 0, s>>>(A);
+  count_launches(1);
+  // host entry: the window walk of a slice runs while the next slice is staged from the caller's pageable arrays
+  const int slice = device ? nmp : 32768;
+  for (int j0 = 0; j0 < nmp; j0 += slice) {
+    const int j1 = std::min(nmp, j0 + slice), c = j1 - j0;
+    if (!device) {
+      YD_CUDA(cudaMemcpyAsync(io + o_mp + sizeof(YdMapPointProj) * (size_t)j0, map_points + j0,
+                              sizeof(YdMapPointProj) * (size_t)c, cudaMemcpyHostToDevice, s));
+      YD_CUDA(cudaMemcpyAsync(io + o_desc + (size_t)32 * j0, mp_descriptors + (size_t)32 * j0, (size_t)32 * c,
+                              cudaMemcpyHostToDevice, s));
+      YD_CUDA(cudaMemcpyAsync(io + o_obs + j0, mp_obs_positive + j0, (size_t)c, cudaMemcpyHostToDevice, s));
     }
+    k_search_build<<<(c + 7) / 8, 256, 0, s>>>(A, j0, j1);
+    count_launches(1);
   }
-  *n_matches = flags[1];
-  YD_CUDA(cudaMemcpy(match_out, f->d_last, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost));
+  lap("stage+walk", nmp);
+  // claim rounds, launched ahead in batches: round t makes at least the first t claimants final (in practice < 12
+  // rounds); a round that changes nothing turns the rest of its batch into no-ops
+  int h_ctr[4] = {0, 0, 0, 0};
+  int rounds = 0;
+  const int grid = 148 * 2;
+  while (!h_ctr[3]) {
+    for (int b = 0; b < 12; b++) k_search_round<<<grid, 256, 0, s>>>(A, rounds++);
+    k_search_final<<<grid, 256, 0, s>>>(A, rounds);
+    count_launches(13);
+    YD_CUDA(cudaGetLastError());
+    YD_CUDA(cudaMemcpyAsync(h_ctr, A.ctr, sizeof h_ctr, cudaMemcpyDeviceToHost, s));
+    YD_CUDA(cudaStreamSynchronize(s));
+    lap("rounds", rounds);
+    if (trace) fprintf(stderr, "[ydorb search] live %d pool %d of %d\n", h_ctr[0], h_ctr[1], pool_cap);
+    if (rounds > nmp + 16) { set_error("projection search did not converge"); return YDORB_E_STATE; }
+  }
+  *n_matches = h_ctr[2];
+  if (!device) {
+    YD_CUDA(cudaMemcpyAsync(match_out, f->d_last, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
+    YD_CUDA(cudaStreamSynchronize(s));
+    lap("d2h", n);
+  }
   return YDORB_OK;
+}
+
+int ydorb_search_by_projection(YdFrame* f, const YdMapPointProj* map_points, const uint8_t* mp_descriptors,
+                               const uint8_t* mp_obs_positive, int n_map_points, const uint8_t* kp_occupied, float th,
+                               float ratio, int32_t* match_out, int32_t* n_matches) {
+  YD_REQUIRE(f && match_out && n_matches && n_map_points >= 0, "bad argument");
+  YD_REQUIRE(n_map_points == 0 || (map_points && mp_descriptors && mp_obs_positive), "null map point arrays");
+  YD_CUDA(cudaSetDevice(f->m->device));
+  for (int i = 0; i < f->n; i++) match_out[i] = -1;
+  *n_matches = 0;
+  if (f->n == 0 || n_map_points == 0) return YDORB_OK;
+  return search_by_projection_impl(f, map_points, mp_descriptors, mp_obs_positive, n_map_points, kp_occupied, th, ratio,
+                                   match_out, n_matches, false);
+}
+
+int ydorb_search_by_projection_device(YdFrame* f, const YdMapPointProj* map_points, const uint8_t* mp_descriptors,
+                                      const uint8_t* mp_obs_positive, int n_map_points, const uint8_t* kp_occupied,
+                                      float th, float ratio, int32_t* match_out, int32_t* n_matches) {
+  YD_REQUIRE(f && n_matches && n_map_points >= 0 && (f->n == 0 || match_out), "bad argument");
+  YD_REQUIRE(n_map_points == 0 || (map_points && mp_descriptors && mp_obs_positive), "null map point arrays");
+  YD_REQUIRE((reinterpret_cast<uintptr_t>(mp_descriptors) & 15) == 0, "map point descriptors must be 16-byte aligned");
+  YD_CUDA(cudaSetDevice(f->m->device));
+  *n_matches = 0;
+  if (f->n == 0) return YDORB_OK;
+  if (n_map_points == 0) {
+    YD_CUDA(cudaMemsetAsync(match_out, 0xFF, sizeof(int32_t) * (size_t)f->n, f->m->stream));
+    YD_CUDA(cudaStreamSynchronize(f->m->stream));
+    return YDORB_OK;
+  }
+  return search_by_projection_impl(f, map_points, mp_descriptors, mp_obs_positive, n_map_points, kp_occupied, th, ratio,
+                                   match_out, n_matches, true);
 }
 
 }  // extern "C"

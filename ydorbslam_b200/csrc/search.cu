@@ -62,12 +62,14 @@ struct WindowArgs {
   int* blocker_next;
   int* last_writer;
   int* best_of;
-  int* flags;  // [0] changed, [1] accepted count
+  int* flags;  // see k_window_search
 };
 
+// flags: [0]/[1] "round changed the blocker table" (even / odd rounds), [2] accepted count, [3] fixed point reached.
+// Rounds are launched ahead of the host in batches; once [3] is set the remaining kernels of a batch return at once.
 __global__ void __launch_bounds__(128) k_window_search(WindowArgs A) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= A.nq) return;
+  if (j >= A.nq || A.flags[3]) return;
   const YdWindowQuery q = A.q[j];
   int best_idx = -1;
   if (q.flags & YDORB_Q_ACTIVE) {
@@ -107,7 +109,7 @@ __global__ void __launch_bounds__(128) k_window_search(WindowArgs A) {
   }
   A.best_of[j] = best_idx;
   if (best_idx >= 0) {
-    atomicAdd(&A.flags[1], 1);
+    atomicAdd(&A.flags[2], 1);
     atomicMax(&A.last_writer[best_idx], j);
     if (A.exclusive && (q.flags & YDORB_Q_BLOCKS)) atomicMin(&A.blocker_next[best_idx], j);
   }
@@ -119,18 +121,26 @@ __global__ void k_win_blocker_init(const uint8_t* __restrict__ occupied, int n, 
 }
 
 __global__ void k_win_round_init(const int* __restrict__ b0, int n, int* __restrict__ bnext, int* __restrict__ last,
-                                 int* __restrict__ flags) {
+                                 int* __restrict__ flags, int round) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  // every thread derives the same verdict from values no thread of this kernel changes
+  const bool done = flags[3] || (round > 0 && flags[(round - 1) & 1] == 0);
+  if (i == 0) {
+    if (done) flags[3] = 1;
+    else { flags[round & 1] = 0; flags[2] = 0; }
+  }
+  if (done) return;
   if (i < n) {
     bnext[i] = (b0[i] == -1) ? -1 : kNoBlocker;
     last[i] = -1;
   }
-  if (i == 0) { flags[0] = 0; flags[1] = 0; }
 }
 
-__global__ void k_win_blocker_diff(const int* __restrict__ a, const int* __restrict__ b, int n, int* __restrict__ flags) {
+__global__ void k_win_blocker_diff(const int* __restrict__ a, const int* __restrict__ b, int n, int* __restrict__ flags,
+                                   int round) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n && a[i] != b[i]) flags[0] = 1;
+  if (flags[3]) return;
+  if (i < n && a[i] != b[i]) flags[round & 1] = 1;
 }
 
 // rotation histogram + three maxima + clearing, one CTA (:138-153).  src_angle[j] is the query's source angle;
@@ -163,7 +173,7 @@ k_orientation_cull(const YdWindowQuery* __restrict__ q, const YdKeyPoint* __rest
   }
   if (culled) atomicAdd(&s_culled, culled);
   __syncthreads();
-  if (threadIdx.x == 0) flags[1] -= s_culled;  // :148
+  if (threadIdx.x == 0) flags[2] -= s_culled;  // :148
 }
 
 }  // namespace ydorb
@@ -223,20 +233,29 @@ int ydorb_search_windows(YdFrame* f, const YdWindowQuery* queries, const uint8_t
   A.flags = f->d_flags;
   int* cur = f->d_blocker;
   int* nxt = f->d_blocker2;
-  int flags[2] = {1, 0};
-  for (int round = 0; round <= nq + 1 && flags[0]; round++) {
-    k_win_round_init<<<gb, 256, 0, s>>>(f->d_blocker, n, nxt, f->d_last, f->d_flags);
-    A.blocker = cur;
-    A.blocker_next = nxt;
-    k_window_search<<<(nq + 127) / 128, 128, 0, s>>>(A);
-    count_launches(2);
-    if (!prm->exclusive) { flags[0] = 0; break; }  // no greedy dependence: one pass is the answer
-    k_win_blocker_diff<<<gb, 256, 0, s>>>(cur, nxt, n, f->d_flags);
+  int flags[4] = {0, 0, 0, 0};
+  YD_CUDA(cudaMemsetAsync(f->d_flags, 0, sizeof flags, s));
+  const int batch = prm->exclusive ? 6 : 1;  // no greedy dependence: one pass is the answer
+  for (int round = 0; !flags[3];) {
+    for (int b = 0; b < batch; b++, round++) {
+      k_win_round_init<<<gb, 256, 0, s>>>(f->d_blocker, n, nxt, f->d_last, f->d_flags, round);
+      A.blocker = cur;
+      A.blocker_next = nxt;
+      k_window_search<<<(nq + 127) / 128, 128, 0, s>>>(A);
+      count_launches(2);
+      if (!prm->exclusive) break;
+      k_win_blocker_diff<<<gb, 256, 0, s>>>(cur, nxt, n, f->d_flags, round);
+      count_launches(1);
+      std::swap(cur, nxt);
+    }
+    if (!prm->exclusive) break;
+    // a seventh init only folds the last round's verdict into flags[3]; it resets nothing unless another round is due
+    k_win_round_init<<<gb, 256, 0, s>>>(f->d_blocker, n, nxt, f->d_last, f->d_flags, round);
     count_launches(1);
     YD_CUDA(cudaGetLastError());
     YD_CUDA(cudaMemcpyAsync(flags, f->d_flags, sizeof flags, cudaMemcpyDeviceToHost, s));
     YD_CUDA(cudaStreamSynchronize(s));
-    std::swap(cur, nxt);
+    if (round > nq + 8) { set_error("window search did not converge"); return YDORB_E_STATE; }
   }
   if (prm->check_orientation) {
     k_orientation_cull<<<1, 1024, 0, s>>>(A.q, f->d_kps, A.best_of, nq, f->d_last, f->d_flags);
@@ -247,7 +266,7 @@ int ydorb_search_windows(YdFrame* f, const YdWindowQuery* queries, const uint8_t
   if (best_of) YD_CUDA(cudaMemcpyAsync(best_of, A.best_of, sizeof(int) * (size_t)nq, cudaMemcpyDeviceToHost, s));
   if (match_out) YD_CUDA(cudaMemcpyAsync(match_out, f->d_last, sizeof(int) * (size_t)n, cudaMemcpyDeviceToHost, s));
   YD_CUDA(cudaStreamSynchronize(s));
-  *n_matches = flags[1];
+  *n_matches = flags[2];
   return YDORB_OK;
 }
 

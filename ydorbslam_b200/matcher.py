@@ -147,6 +147,15 @@ class OrbMatcher:
                                                C.c_float(self.ratio), ptr(out), C.byref(n)))
         return n.value, out[: frame.n]
 
+    def searchByProjectionInFrameAndMapPoint_device(self, frame, d_map_points, d_mp_descriptors, d_mp_obs_positive, n_map_points,
+                                                    d_match_out, thd=3.0, d_kp_occupied=None):
+        """Raw device addresses (ints); d_match_out int32[n_kp] on the device.  Returns the match count."""
+        n = C.c_int32()
+        check(lib().ydorb_search_by_projection_device(frame._h, ptr(d_map_points), ptr(d_mp_descriptors), ptr(d_mp_obs_positive),
+                                                      n_map_points, ptr(d_kp_occupied), C.c_float(thd), C.c_float(self.ratio),
+                                                      ptr(d_match_out), C.byref(n)))
+        return n.value
+
     # ---- M2/M3/M4: everything after the projection (include/ydorb.h ydorb_search_windows)
     def searchWindows(self, frame, queries, q_descriptors, params, kp_occupied=None):
         """Returns (n_matches, best_of[nq], match_of_keypoint[n_kp]); match codes: >=0 query, -1 untouched, -2 cleared."""
