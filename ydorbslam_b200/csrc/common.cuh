@@ -22,6 +22,34 @@ void set_error(const std::string& msg);
 void count_launches(int n);  // bookkeeping for ydorb_kernel_launches()
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
 
+// Programmatic dependent launch: the kernels of one extract call form a chain in one stream.  Launched with the
+// stream-serialization attribute, the next kernel's CTAs are placed while the previous kernel drains and block in
+// pdl_wait() until it has completed and flushed, which takes the launch latency off a single frame's critical path.
+// Every kernel launched through launch_chain MUST call pdl_wait() before anything else (also before an early return:
+// a kernel that finishes without waiting would release its successor early).
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  // the successor may be placed as soon as every CTA of this grid is resident; it blocks in its own pdl_wait()
+  asm volatile("griddepcontrol.launch_dependents;");
+}
+#endif
+bool pdl_enabled();  // YDORB_PDL=0 switches the attribute off
+template <class... P, class... A>
+inline cudaError_t launch_chain(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, A&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, P(std::forward<A>(args))...);
+}
+
 #define YD_CUDA(expr)                                                         \
   do {                                                                        \
     cudaError_t _e = (expr);                                                  \

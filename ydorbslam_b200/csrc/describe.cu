@@ -10,6 +10,7 @@
 //     done once for the 43 x 37 window, the vertical pass only at the 512 sampled positions, rounded once
 //     ((v + 32768) >> 16) -- bit-identical to blurring the whole level, without writing a blurred level to HBM;
 //   * rBRIEF: lane j produces byte j (8 comparisons), coordinates rotated in fp32 without contraction.
+#include <cstdlib>
 #include "kernels.cuh"
 
 namespace ydorb {
@@ -50,7 +51,6 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
   return a;
 }
 
-constexpr int kKpPerWarp = 8;                               // consecutive keypoint slots a warp works through
 constexpr int kDescPf = (kPatchRows * kPatchWords + 31) / 32;  // 32-bit words per lane of one staged neighbourhood
 
 struct DescLevel {      // per-level facts of this frame, built once per CTA
@@ -114,10 +114,13 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
                              uint16_t* __restrict__ hb, const uint32_t* __restrict__ s_pat, YdKeyPoint* __restrict__ kps,
                              uint8_t* __restrict__ desc, int capacity);
 
+// KPW = consecutive keypoint slots a warp works through (8 for batches that fill the GPU; fewer spreads a small batch)
+template <int KPW>
 __global__ void __launch_bounds__(kDescWarps * 32, 5)
 k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, const int4* __restrict__ sel,
            const int* __restrict__ sel_n, YdKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc, int capacity,
            int32_t* __restrict__ n_out, int* __restrict__ status) {
+  pdl_wait();
   __shared__ __align__(16) uint8_t s_patch[kDescWarps][2][kPatchRows * kPatchStride];  // double buffered
   __shared__ __align__(16) uint16_t s_hb[kDescWarps][kHbCols * kHbColStride];
   __shared__ uint32_t s_pat[256];  // [bit b][lane]: the two pattern points (x0,y0,x1,y1 as s8) of bit b of byte `lane`
@@ -149,7 +152,7 @@ k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, 
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int slot0 = (blockIdx.x * kDescWarps + warp) * kKpPerWarp;
+  const int slot0 = (blockIdx.x * kDescWarps + warp) * KPW;
   const int4* sel_frame = sel + (size_t)frame * n_quota;
   const uint8_t* pyr_frame = pyr + (size_t)frame * g->pyr_bytes;
   uint16_t* hb = s_hb[warp];
@@ -157,12 +160,12 @@ k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, 
   // the other patch buffer while this one computes
   DescKp cur = desc_setup(s_lvl, n_levels, n_quota, slot0, sel_frame, pyr_frame, capacity);
   if (cur.valid) desc_prefetch(cur, lane, s_patch[warp][0]);
-  for (int k = 0; k < kKpPerWarp; k++) {
+  for (int k = 0; k < KPW; k++) {
     desc_wait_patch();
     __syncwarp();
     DescKp nxt;
     nxt.valid = 0;
-    if (k + 1 < kKpPerWarp) {
+    if (k + 1 < KPW) {
       nxt = desc_setup(s_lvl, n_levels, n_quota, slot0 + k + 1, sel_frame, pyr_frame, capacity);
       if (nxt.valid) desc_prefetch(nxt, lane, s_patch[warp][(k + 1) & 1]);
     }
@@ -276,10 +279,20 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
 
 int launch_describe(const YdExtractor* ex, int batch, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity,
                     int32_t* d_nout, cudaStream_t s) {
-  const int per_cta = kDescWarps * kKpPerWarp;
-  dim3 grid((ex->geom.n_quota + per_cta - 1) / per_cta, batch);
-  k_describe<<<grid, kDescWarps * 32, 0, s>>>(ex->d_geom, ex->d_pyr, ex->d_sel, ex->d_sel_n, d_kps, d_desc, capacity,
-                                              d_nout, ex->d_status);
+  // warps at 8 slots each; a launch with few of them is latency-bound: spread the slots over more warps instead
+  const long long warps8 = (long long)((ex->geom.n_quota + 7) / 8) * batch;
+  static const int force = getenv("YDORB_DESC_KPW") ? atoi(getenv("YDORB_DESC_KPW")) : 0;  // tuning knob
+  const int kpw = force ? force : warps8 >= 148 * 32 ? 8 : 1;  // measured: bench.py --batch 16/64/256, tools/latency_probe.py
+  auto launch = [&](auto kernel, int k) -> int {
+    const int per_cta = kDescWarps * k;
+    dim3 grid((ex->geom.n_quota + per_cta - 1) / per_cta, batch);
+    YD_CUDA(launch_chain(kernel, grid, dim3(kDescWarps * 32), 0, s, ex->d_geom, ex->d_pyr, ex->d_sel, ex->d_sel_n, d_kps, d_desc,
+                         capacity, d_nout, ex->d_status));
+    return YDORB_OK;
+  };
+  const int rc = kpw >= 8 ? launch(k_describe<8>, 8) : kpw >= 4 ? launch(k_describe<4>, 4) : kpw >= 2 ? launch(k_describe<2>, 2)
+                                                                                                      : launch(k_describe<1>, 1);
+  if (rc != YDORB_OK) return rc;
   count_launches(1);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;

@@ -17,6 +17,11 @@ static std::atomic<long long> g_launches{0};
 
 void count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
+bool pdl_enabled() {
+  static const bool on = !(getenv("YDORB_PDL") && atoi(getenv("YDORB_PDL")) == 0);
+  return on;
+}
+
 void set_error(const std::string& msg) { g_last_error = msg; }
 
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
@@ -580,16 +585,16 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
                     dcap, ex->d_nout);
   if (rc != YDORB_OK) return rc;
   YD_CUDA(cudaMemcpyAsync(n_out, ex->d_nout, sizeof(int32_t) * batch, cudaMemcpyDeviceToHost, s));
+  if (capacity == dcap) {  // same layout on both sides: two bulk copies instead of two per frame, one wait for everything
+    YD_CUDA(cudaMemcpyAsync(keypoints, ex->d_kps, sizeof(YdKeyPoint) * (size_t)batch * dcap, cudaMemcpyDeviceToHost, s));
+    YD_CUDA(cudaMemcpyAsync(descriptors, ex->d_desc, (size_t)32 * batch * dcap, cudaMemcpyDeviceToHost, s));
+    YD_CUDA(cudaStreamSynchronize(s));
+    return check_status(ex);
+  }
   YD_CUDA(cudaStreamSynchronize(s));
   rc = check_status(ex);
   if (rc != YDORB_OK) return rc;
   int ret = YDORB_OK;
-  if (capacity == dcap) {  // same layout on both sides: two bulk copies instead of two per frame
-    YD_CUDA(cudaMemcpyAsync(keypoints, ex->d_kps, sizeof(YdKeyPoint) * (size_t)batch * dcap, cudaMemcpyDeviceToHost, s));
-    YD_CUDA(cudaMemcpyAsync(descriptors, ex->d_desc, (size_t)32 * batch * dcap, cudaMemcpyDeviceToHost, s));
-    YD_CUDA(cudaStreamSynchronize(s));
-    return ret;
-  }
   for (int b = 0; b < batch; b++) {
     int n = n_out[b];
     if (n > capacity) { n = capacity; ret = YDORB_E_CAPACITY; set_error("keypoint capacity too small"); }

@@ -18,6 +18,7 @@
 //           min3(min3) over a circular array (16+16 ops), the max over arcs 8 ops.  Stored value: max(m - t_low, 0);
 //   nms     packed: the 8-neighbour maximum of a pair is 4 funnel shifts + 4 VIMNMX; keep <=> centre > neighbours.
 // This is integer-pipe work, not HBM-bound: the level is read from HBM once.
+#include <cstdlib>
 #include "kernels.cuh"
 
 namespace ydorb {
@@ -121,7 +122,6 @@ __host__ __device__ inline FastSmemLayout fast_layout(int max_tw, int max_th) {
   return L;
 }
 
-constexpr int kCellsPerWarp = 4;  // consecutive cells a warp works through
 constexpr int kFastPf = 14;       // 32-bit words per lane prefetched for the next cell (covers 36 x 36 px cells)
 
 struct FastCell {
@@ -365,10 +365,14 @@ __device__ void fast_cell_compute(const FastCell& fc, int frame, int lane, int i
   if (lane == 0) { *out_count = count; *out_start = start; }
 }
 
+// CPW = consecutive cells a warp works through (the next cell's pixels prefetched into registers while this one
+// computes); 1 spreads a single frame's ~1000 cells over all SMs and is what launch_fast uses
+template <int CPW>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells, const uint8_t* __restrict__ pyr,
              int ini_th, int min_th, int max_tw, int max_th, uint32_t* __restrict__ raw, int* __restrict__ raw_counter,
              int* __restrict__ cell_count, int* __restrict__ cell_start, int* __restrict__ status) {
+  pdl_wait();
   extern __shared__ __align__(16) uint8_t smem_raw[];
   const FastSmemLayout L = fast_layout(max_tw, max_th);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -380,15 +384,15 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
   uint16_t* queue = nz + L.nz_cap;
   const FastOut O{g, raw, raw_counter, cell_count, cell_start, status};
   // software pipeline over the warp's cells: the next cell's pixels travel HBM -> registers while this one computes
-  const int cell0 = (blockIdx.x * kWarpsPerCta + warp) * kCellsPerWarp;
+  const int cell0 = (blockIdx.x * kWarpsPerCta + warp) * CPW;
   uint32_t v[kFastPf];
   FastCell cur = fast_cell_setup(g, cells, pyr, cell0, frame, lane, cell_count, cell_start);
   if (cur.valid) fast_prefetch(cur, lane, v);
-  for (int k = 0; k < kCellsPerWarp; k++) {
+  for (int k = 0; k < CPW; k++) {
     if (cur.valid) fast_stage(cur, lane, v, tile, L.wpr);
     FastCell nxt;
     nxt.valid = 0;
-    if (k + 1 < kCellsPerWarp) {
+    if (k + 1 < CPW) {
       nxt = fast_cell_setup(g, cells, pyr, cell0 + k + 1, frame, lane, cell_count, cell_start);
       if (nxt.valid) fast_prefetch(nxt, lane, v);
     }
@@ -404,12 +408,21 @@ int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s) {
   const int mn = ex->params.reference_min_th_quirk ? ini : ex->params.min_th_fast;
   const FastSmemLayout L = fast_layout(ex->max_cell_w, ex->max_cell_h);
   const size_t smem = (size_t)L.warp_bytes * kWarpsPerCta;
-  if (smem > 48 * 1024) YD_CUDA(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int per_cta = kWarpsPerCta * kCellsPerWarp;
-  dim3 grid((ex->geom.n_cells + per_cta - 1) / per_cta, batch);
-  k_fast_cells<<<grid, kWarpsPerCta * 32, smem, s>>>(ex->d_geom, ex->d_cells, ex->d_pyr, ini, mn, ex->max_cell_w,
-                                                     ex->max_cell_h, ex->d_raw, ex->d_raw_counter, ex->d_cell_count,
-                                                     ex->d_cell_start, ex->d_status);
+  // measured on a B200 (bench.py --batch 16/64/256, tools/latency_probe.py): one cell per warp is fastest at every
+  // batch size (0.747 vs 0.764 ms per 256 frames, 22 vs 50 us for a single frame); 2 and 4 stay as a tuning knob
+  static const int force_cpw = getenv("YDORB_FAST_CPW") ? atoi(getenv("YDORB_FAST_CPW")) : 0;
+  const int cpw = force_cpw ? force_cpw : 1;
+  auto launch = [&](auto kernel, int c) -> int {
+    if (smem > 48 * 1024) YD_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int per_cta = kWarpsPerCta * c;
+    dim3 grid((ex->geom.n_cells + per_cta - 1) / per_cta, batch);
+    YD_CUDA(launch_chain(kernel, grid, dim3(kWarpsPerCta * 32), smem, s, ex->d_geom, ex->d_cells, ex->d_pyr, ini, mn,
+                         ex->max_cell_w, ex->max_cell_h, ex->d_raw, ex->d_raw_counter, ex->d_cell_count, ex->d_cell_start,
+                         ex->d_status));
+    return YDORB_OK;
+  };
+  const int rc = cpw == 4 ? launch(k_fast_cells<4>, 4) : cpw == 2 ? launch(k_fast_cells<2>, 2) : launch(k_fast_cells<1>, 1);
+  if (rc != YDORB_OK) return rc;
   count_launches(1);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;

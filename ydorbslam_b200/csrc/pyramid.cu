@@ -38,6 +38,7 @@ constexpr int kPy0Rows = 8;
 __global__ void __launch_bounds__(256) k_pyr_level0(const uint8_t* __restrict__ images, int in_stride, size_t frame_stride,
                                                     int aligned4, int w, int h, int dstride, long long doff,
                                                     long long pyr_bytes, uint8_t* __restrict__ pyr) {
+  pdl_wait();
   const int frame = blockIdx.z;
   const int pw = w + 2 * kPad, ph = h + 2 * kPad;
   const uint8_t* src = images + (size_t)frame * frame_stride;
@@ -130,6 +131,7 @@ struct PyrArgs {
 template <int SS>  // SS: row stride (bytes) of the staged source copies
 __global__ void __launch_bounds__(256) k_pyr_resize(const PyrArgs a, const int* __restrict__ tab_ofs,
                                                     const short2* __restrict__ tab_a, uint8_t* __restrict__ pyr) {
+  pdl_wait();
   extern __shared__ __align__(16) uint8_t smem[];
   int* s_h = reinterpret_cast<int*>(smem);                                   // [nsr_cap][kPyHS]
   int4* s_row = reinterpret_cast<int4*>(s_h + a.nsr_cap * kPyHS);            // [kPyMaxTH] {r0*kPyHS, r1*kPyHS, b0, b1}
@@ -306,8 +308,8 @@ int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, s
     if (l == 0) {
       const int n_int = std::max(aligned4 ? (lv.w + 3) / 16 - 1 : 0, 0);  // interior 16-byte groups per row
       dim3 grid((n_int + 63) / 64 + 1, (lv.h + 2 * kPad + 4 * kPy0Rows - 1) / (4 * kPy0Rows), batch);
-      k_pyr_level0<<<grid, 256, 0, s>>>(d_images, stride, frame_stride, aligned4, lv.w, lv.h, lv.stride, lv.offset,
-                                        g.pyr_bytes, ex->d_pyr);
+      YD_CUDA(launch_chain(k_pyr_level0, grid, dim3(256), 0, s, d_images, stride, frame_stride, aligned4, lv.w, lv.h, lv.stride,
+                           lv.offset, g.pyr_bytes, ex->d_pyr));
     } else {
       const LevelGeom& sv = g.lv[l - 1];
       ResizePlan p;
@@ -324,9 +326,9 @@ int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, s
       if (p.smem > 48 * 1024)  // only reached with scale factors well above the reference's 1.2
         YD_CUDA(cudaFuncSetAttribute(k_pyr_resize<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
       if (p.ss == 192)
-        k_pyr_resize<192><<<grid, 256, p.smem, s>>>(a, ex->d_tab_ofs, ta, ex->d_pyr);
+        YD_CUDA(launch_chain(k_pyr_resize<192>, grid, dim3(256), p.smem, s, a, ex->d_tab_ofs, ta, ex->d_pyr));
       else
-        k_pyr_resize<512><<<grid, 256, p.smem, s>>>(a, ex->d_tab_ofs, ta, ex->d_pyr);
+        YD_CUDA(launch_chain(k_pyr_resize<512>, grid, dim3(256), p.smem, s, a, ex->d_tab_ofs, ta, ex->d_pyr));
     }
   }
   count_launches(g.n_levels);

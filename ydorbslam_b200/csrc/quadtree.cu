@@ -345,6 +345,7 @@ struct StdSortEmu {
 // ---- per-frame exclusive scan of the per-cell candidate counts (candidate order = cell-major)
 __global__ void __launch_bounds__(256) k_cell_scan(const FrameGeomDev* __restrict__ g, const int* __restrict__ cell_count,
                                                    int* __restrict__ cell_rank) {
+  pdl_wait();
   __shared__ int s_warp[8];
   __shared__ int s_carry;
   const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -435,6 +436,7 @@ __device__ void qt_fill(const QtArgs& A, const LevelGeom& lv, int frame, int lev
 // CTA that owns a (level, frame) segment.  The rare deeper case recomputes full codes inside k_quadtree (qt_fill).
 constexpr int kCodeWarps = 8;
 __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
+  pdl_wait();
   const FrameGeomDev* g = A.g;
   const int frame = blockIdx.y, lane = threadIdx.x & 31;
   const int c = blockIdx.x * kCodeWarps + (threadIdx.x >> 5);  // cell index within the frame
@@ -473,6 +475,7 @@ __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
 enum { kMetaN = 0, kMetaD = 1, kMetaM = 2, kMetaDeep = 3, kMetaBase = 4 };
 
 __global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
+  pdl_wait();
   __shared__ uint32_t s_map[kQtMapWords];
   __shared__ uint32_t s_fold[kQtMapWords];
   __shared__ int s_cnt[kQtMapDig + 1];
@@ -643,6 +646,7 @@ __device__ __forceinline__ bool qt_locate(const QtArgs& A, int frame, int pos, Q
 // the lanes of a warp that hit the same node combine their contribution (MATCH.ANY + REDUX) and one of them issues the
 // atomics, instead of up to 32 same-address atomics serialising in L2.
 __global__ void __launch_bounds__(256) k_qt_pass1(QtArgs A) {
+  pdl_wait();
   const int frame = blockIdx.y, lane = threadIdx.x & 31;
   const int total = A.cell_rank[(size_t)frame * (A.g->n_cells + 1) + A.g->n_cells];
   for (int base = blockIdx.x * 256 + (threadIdx.x & ~31); base < total; base += gridDim.x * 256) {  // warp-uniform
@@ -666,6 +670,7 @@ __global__ void __launch_bounds__(256) k_qt_pass1(QtArgs A) {
 }
 
 __global__ void __launch_bounds__(256) k_qt_pass2(QtArgs A) {
+  pdl_wait();
   const int frame = blockIdx.y, lane = threadIdx.x & 31;
   const FrameGeomDev* g = A.g;
   const int total = A.cell_rank[(size_t)frame * (g->n_cells + 1) + g->n_cells];
@@ -718,6 +723,7 @@ struct QtFinSmem {
 };
 
 __global__ void __launch_bounds__(kQtThreads) k_qt_finish(QtArgs A) {
+  pdl_wait();
   __shared__ QtFinSmem fs;
   QtSmem& sm = fs.q;
   const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
@@ -914,6 +920,7 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_finish(QtArgs A) {
 }
 
 __global__ void __launch_bounds__(kQtThreads, 3) k_quadtree(QtArgs A) {
+  pdl_wait();
   __shared__ QtSmem sm;
   const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
   const FrameGeomDev* g = A.g;
@@ -1151,7 +1158,7 @@ __global__ void __launch_bounds__(kQtThreads, 3) k_quadtree(QtArgs A) {
 }
 
 int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
-  k_cell_scan<<<batch, 256, 0, s>>>(ex->d_geom, ex->d_cell_count, ex->d_cell_rank);
+  YD_CUDA(launch_chain(k_cell_scan, dim3(batch), dim3(256), 0, s, ex->d_geom, ex->d_cell_count, ex->d_cell_rank));
   QtArgs A;
   A.g = ex->d_geom;
   A.cells = ex->d_cells;
@@ -1168,16 +1175,16 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
   A.level_ncand = ex->d_level_ncand;
   A.status = ex->d_status;
   if (ex->geom.n_cells > 0)
-    k_qt_codes<<<dim3((ex->geom.n_cells + kCodeWarps - 1) / kCodeWarps, batch), kCodeWarps * 32, 0, s>>>(A);
+    YD_CUDA(launch_chain(k_qt_codes, dim3((ex->geom.n_cells + kCodeWarps - 1) / kCodeWarps, batch), dim3(kCodeWarps * 32), 0, s, A));
   // candidate passes: grid-stride over the frame's candidates (their number is only known on the device); enough CTAs per
   // frame to fill the GPU when the batch is small, few when it is large
   const int per_frame = std::max(1, std::min((ex->geom.raw_cap + 255) / 256, (148 * 8 + batch - 1) / batch));
   dim3 grid(ex->geom.n_levels, batch), cgrid(per_frame, batch);
-  k_qt_depth<<<grid, kQtThreads, 0, s>>>(A);
-  k_qt_pass1<<<cgrid, 256, 0, s>>>(A);
-  k_qt_pass2<<<cgrid, 256, 0, s>>>(A);
-  k_qt_finish<<<grid, kQtThreads, 0, s>>>(A);
-  k_quadtree<<<grid, kQtThreads, 0, s>>>(A);  // segments deeper than kQtMapDig only
+  YD_CUDA(launch_chain(k_qt_depth, grid, dim3(kQtThreads), 0, s, A));
+  YD_CUDA(launch_chain(k_qt_pass1, cgrid, dim3(256), 0, s, A));
+  YD_CUDA(launch_chain(k_qt_pass2, cgrid, dim3(256), 0, s, A));
+  YD_CUDA(launch_chain(k_qt_finish, grid, dim3(kQtThreads), 0, s, A));
+  YD_CUDA(launch_chain(k_quadtree, grid, dim3(kQtThreads), 0, s, A));  // segments deeper than kQtMapDig only
   count_launches(7);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
