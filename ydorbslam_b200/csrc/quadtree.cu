@@ -472,7 +472,7 @@ __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
 //   k_qt_finish  (CTA/segment) node records, std::sort emulation for the nodes that need it (members gathered in
 //                             candidate order through the FAST cell grid), list-order sort, truncate, emit
 // Segments that need more than kQtMapDig passes (tightly clustered points) keep the sort-based k_quadtree below.
-enum { kMetaN = 0, kMetaD = 1, kMetaM = 2, kMetaDeep = 3, kMetaBase = 4 };
+enum { kMetaN = 0, kMetaD = 1, kMetaM = 2, kMetaDeep = 3, kMetaBase = 4, kMetaFlagged = 5, kMetaBig = 6 };
 
 __global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
   pdl_wait();
@@ -722,20 +722,17 @@ struct QtFinSmem {
   uint32_t prefix[kQtMapWords]; // exclusive popcount prefix per word
 };
 
-__global__ void __launch_bounds__(kQtThreads) k_qt_finish(QtArgs A) {
+__global__ void __launch_bounds__(kQtThreads) k_qt_records(QtArgs A) {
   pdl_wait();
   __shared__ QtFinSmem fs;
   QtSmem& sm = fs.q;
   const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
   const FrameGeomDev* g = A.g;
-  const int* meta = A.meta + ((size_t)frame * kMaxLevels + level) * 8;
+  int* meta = A.meta + ((size_t)frame * kMaxLevels + level) * 8;
   const int n = meta[kMetaN];
   if (n == 0 || meta[kMetaDeep]) return;
-  const LevelGeom lv = g->lv[level];
-  const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase], want = lv.quota;
-  const int sh = kQtBits - 2 * D;
+  const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase];
   const size_t seg = (size_t)frame * g->raw_cap + level_base;
-  const uint32_t* CK = A.keys[0] + seg;   // path codes, candidate order
   const uint32_t* CV = A.vals[0] + seg;   // packed candidates, candidate order
   uint32_t* best = A.keys[1] + seg;       // node winners (NV) once the records are written
   uint32_t* cnt = A.vals[1] + seg;
@@ -784,18 +781,45 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_finish(QtArgs A) {
     NV[m] = CV[first_max];
   }
   __syncthreads();
-  // nodes whose winner std::sort decides: one warp per node.  Its members, in candidate order, are the candidates with
-  // the node's prefix found by walking the FAST cells (candidate order = cell-major) that overlap the node's rectangle.
-  {
-    const int nflag = sm.misc[4];
-    const int lane = tid & 31, warp = tid >> 5;
-    uint32_t* big_buf = ties;  // node tables are dead from here on: scratch for nodes with more than 128 members
-    uint32_t* big_pos = cnt;
-    if (tid == 0) sm.misc[5] = 0;
-    __syncthreads();
+  if (tid == 0) { meta[kMetaFlagged] = sm.misc[4]; meta[kMetaBig] = 0; }
+}
+
+// nodes whose winner std::sort decides (tied maxima among more than 16 members): one warp per node, the
+// flagged nodes of all levels of a frame spread over the frame's CTAs (a 4K frame has hundreds of them on level 0).
+// The members, in candidate order, are the candidates with the node's prefix found by walking the FAST cells
+// (candidate order = cell-major) that overlap the node's rectangle.
+constexpr int kTieWarps = 8;
+__global__ void __launch_bounds__(kTieWarps * 32) k_qt_ties(QtArgs A) {
+  pdl_wait();
+  __shared__ alignas(8) uint32_t s_buf[kTieWarps][256];
+  const int frame = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const FrameGeomDev* g = A.g;
+  int* fmeta = A.meta + (size_t)frame * kMaxLevels * 8;
+  const int n_levels = g->n_levels;
+  int total = 0;
+  for (int l = 0; l < n_levels; l++)
+    if (fmeta[l * 8 + kMetaN] != 0 && !fmeta[l * 8 + kMetaDeep]) total += fmeta[l * 8 + kMetaFlagged];
+  const int nwarps = gridDim.x * kTieWarps;
+  for (int item = blockIdx.x * kTieWarps + warp; item < total; item += nwarps) {
+    int level = 0, f = item;
+    for (; level < n_levels; level++) {
+      const int c = (fmeta[level * 8 + kMetaN] != 0 && !fmeta[level * 8 + kMetaDeep]) ? fmeta[level * 8 + kMetaFlagged] : 0;
+      if (f < c) break;
+      f -= c;
+    }
+    int* meta = fmeta + level * 8;
+    const LevelGeom lv = g->lv[level];
+    const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase];
+    const int sh = kQtBits - 2 * D;
+    const size_t seg = (size_t)frame * g->raw_cap + level_base;
+    const uint32_t* CK = A.keys[0] + seg;
+    const uint32_t* CV = A.vals[0] + seg;
+    uint32_t* NV = A.keys[1] + seg;
+    const uint32_t* flagged = A.vals[2] + seg + M;
+    uint32_t* big_buf = A.keys[2] + seg;  // node tables are dead by now: scratch for nodes with more than 128 members
+    uint32_t* big_pos = A.vals[1] + seg;
     const size_t cbase = (size_t)frame * g->n_cells + lv.cell_base;
     const int* rank = A.cell_rank + (size_t)frame * (g->n_cells + 1) + lv.cell_base;
-    for (int f = warp; f < nflag; f += kQtWarps) {
       const int m = (int)flagged[3 * f], len = (int)flagged[3 * f + 2];
       const uint32_t pre = flagged[3 * f + 1];
       // rectangle of the node: replay divideNode on the prefix digits, tracking the true bounds of the members
@@ -817,11 +841,11 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_finish(QtArgs A) {
       const int i0 = max(0, (max(ylo, 3) - 3) / lv.cell_h), i1 = min(lv.cell_rows - 1, (max(yhi - 1, 3) - 3) / lv.cell_h);
       uint32_t *buf, *pos;
       if (len <= 128) {
-        buf = reinterpret_cast<uint32_t*>(sm.warp_cnt[warp]);
+        buf = s_buf[warp];
         pos = buf + 128;
       } else {
         int o = 0;
-        if (lane == 0) o = atomicAdd(&sm.misc[5], len);
+        if (lane == 0) o = atomicAdd(&meta[kMetaBig], len);
         o = __shfl_sync(0xffffffffu, o, 0);
         buf = big_buf + o;
         pos = big_pos + o;
@@ -878,11 +902,25 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_finish(QtArgs A) {
         NV[m] = CV[pos[bst & 0xFFFFFFu]];
       }
       __syncwarp();
-    }
   }
-  __syncthreads();
+}
 
-  // list order, then the first min(M, want) winners (:541-543), coordinates back in level space (:597-598)
+// list order, then the first min(M, want) winners (:541-543), coordinates back in level space (:597-598)
+__global__ void __launch_bounds__(kQtThreads) k_qt_emit(QtArgs A) {
+  pdl_wait();
+  __shared__ QtSmem sm;
+  const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
+  const FrameGeomDev* g = A.g;
+  const int* meta = A.meta + ((size_t)frame * kMaxLevels + level) * 8;
+  const int n = meta[kMetaN];
+  if (n == 0 || meta[kMetaDeep]) return;
+  const LevelGeom lv = g->lv[level];
+  const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase], want = lv.quota;
+  const size_t seg = (size_t)frame * g->raw_cap + level_base;
+  uint32_t* NV = A.keys[1] + seg;
+  uint32_t* cnt = A.vals[1] + seg;
+  uint32_t* ties = A.keys[2] + seg;
+  uint32_t* NK = A.vals[2] + seg;
   const int m_out = min(M, want);
   int4* sel = A.sel + (size_t)frame * g->n_quota + lv.quota_base;
   constexpr int kSmemSort = kQtWarps * 256 / 2;  // 64-bit (order key, winner) pairs that fit the radix counters' space
@@ -1183,9 +1221,11 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
   YD_CUDA(launch_chain(k_qt_depth, grid, dim3(kQtThreads), 0, s, A));
   YD_CUDA(launch_chain(k_qt_pass1, cgrid, dim3(256), 0, s, A));
   YD_CUDA(launch_chain(k_qt_pass2, cgrid, dim3(256), 0, s, A));
-  YD_CUDA(launch_chain(k_qt_finish, grid, dim3(kQtThreads), 0, s, A));
+  YD_CUDA(launch_chain(k_qt_records, grid, dim3(kQtThreads), 0, s, A));
+  YD_CUDA(launch_chain(k_qt_ties, cgrid, dim3(kTieWarps * 32), 0, s, A));
+  YD_CUDA(launch_chain(k_qt_emit, grid, dim3(kQtThreads), 0, s, A));
   YD_CUDA(launch_chain(k_quadtree, grid, dim3(kQtThreads), 0, s, A));  // segments deeper than kQtMapDig only
-  count_launches(7);
+  count_launches(9);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
 }
