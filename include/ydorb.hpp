@@ -44,6 +44,22 @@ inline void check(int rc) {
   if (rc != YDORB_OK) throw Error(rc, std::string("libydorb: ") + ydorb_last_error());
 }
 
+// Page-locked host memory (ydorb_host_alloc).  Frames and outputs kept in it are moved by DMA without the driver's
+// staging copy; a cv::Mat header can wrap data(): cv::Mat(rows, cols, CV_8UC1, buf.data(), step).
+class PinnedBuffer {
+ public:
+  explicit PinnedBuffer(size_t bytes) : m_p(nullptr), m_n(bytes) { check(ydorb_host_alloc(bytes, &m_p)); }
+  ~PinnedBuffer() { ydorb_host_free(m_p); }
+  PinnedBuffer(const PinnedBuffer&) = delete;
+  PinnedBuffer& operator=(const PinnedBuffer&) = delete;
+  uint8_t* data() const { return static_cast<uint8_t*>(m_p); }
+  size_t size() const { return m_n; }
+
+ private:
+  void* m_p;
+  size_t m_n;
+};
+
 // ---------------------------------------------------------------------------------------------- OrbExtractor
 class OrbExtractor {
  public:

@@ -132,3 +132,19 @@ def test_clustered_corners_deep_quadtree(patch, nf):
     ok, od, _ = orc.extract(orc.make_params(nf, 1.2, 8, 20), img)
     assert len(kps) == len(ok) and len(kps) > 20
     assert np.array_equal(kps, ok) and np.array_equal(desc, od)
+
+
+@pytest.mark.gpu
+def test_pinned_host_buffers_same_result():
+    """ydorb_host_alloc buffers (include/ydorb.h) through the host entry point give what pageable arrays give."""
+    from ydorbslam_b200 import PinnedArray
+
+    imgs = np.stack([synth.synth_frame(640, 480, 90 + i) for i in range(8)])
+    ex = OrbExtractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480, max_batch=8)
+    kps, desc, n = ex.extract_batch(imgs)
+    pin = PinnedArray(imgs.shape)
+    pin.array[...] = imgs
+    kps2, desc2, n2 = ex.extract_batch(pin.array)
+    assert np.array_equal(n, n2) and np.array_equal(kps, kps2) and np.array_equal(desc, desc2)
+    pin.close()
+    ex.close()

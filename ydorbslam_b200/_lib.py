@@ -93,8 +93,9 @@ def lib():
         _lib.ydorb_matcher_stream.restype = C.c_void_p
         _lib.ydorb_kernel_launches.restype = C.c_longlong
         for name in ("ydorb_extractor_destroy", "ydorb_matcher_destroy", "ydorb_frame_destroy", "ydorb_three_maxima",
-                     "ydorb_vocabulary_destroy"):
+                     "ydorb_vocabulary_destroy", "ydorb_host_free"):
             getattr(_lib, name).restype = None
+        _lib.ydorb_host_free.argtypes = [C.c_void_p]
     return _lib
 
 
@@ -109,3 +110,27 @@ def ptr(a):
     if isinstance(a, np.ndarray):
         return a.ctypes.data_as(C.c_void_p)
     return C.c_void_p(int(a))  # raw device pointer
+
+
+class PinnedArray:
+    """numpy view of page-locked host memory from ydorb_host_alloc (include/ydorb.h); frees it on close()/GC."""
+
+    def __init__(self, shape, dtype=np.uint8):
+        self._p = C.c_void_p()
+        dtype = np.dtype(dtype)
+        nbytes = int(np.prod(shape)) * dtype.itemsize
+        check(lib().ydorb_host_alloc(C.c_size_t(nbytes), C.byref(self._p)))
+        buf = (C.c_uint8 * max(nbytes, 1)).from_address(self._p.value)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def close(self):
+        if self._p is not None and self._p.value:
+            self.array = None
+            lib().ydorb_host_free(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -289,6 +289,17 @@ int ydorb_device_count(void) {
   return n;
 }
 
+int ydorb_host_alloc(size_t bytes, void** out) {
+  YD_REQUIRE(out, "null argument");
+  *out = nullptr;
+  YD_CUDA(cudaHostAlloc(out, std::max<size_t>(bytes, 1), cudaHostAllocPortable));
+  return YDORB_OK;
+}
+
+void ydorb_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
 int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int max_height, int max_batch, int device,
                            YdExtractor** out) {
   YD_REQUIRE(params && out, "null argument");
