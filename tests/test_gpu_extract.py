@@ -148,3 +148,39 @@ def test_pinned_host_buffers_same_result():
     assert np.array_equal(n, n2) and np.array_equal(kps, kps2) and np.array_equal(desc, desc2)
     pin.close()
     ex.close()
+
+
+_KNOB_SCRIPT = r"""
+import hashlib, sys
+import numpy as np
+from ydorbslam_b200 import OrbExtractor, OrbMatcher, synth
+left, right = synth.synth_stereo_pair(1241, 376, 64)
+ex = OrbExtractor(2000, 1.2, 8, 20, 7, max_width=1241, max_height=376, max_batch=2)
+kps, desc, n = ex.extract_batch(np.stack([left, right]))
+m = OrbMatcher()
+rx, dp = m.computeStereoMatches(ex, 0, ex, 1, kps[0, :n[0]], desc[0, :n[0]], kps[1, :n[1]], desc[1, :n[1]], 386.1448, np.inf, 0)
+h = hashlib.sha256()
+for a in (n, kps[0, :n[0]], kps[1, :n[1]], desc[0, :n[0]], desc[1, :n[1]], rx, dp):
+    h.update(np.ascontiguousarray(a).tobytes())
+print("HASH", h.hexdigest())
+"""
+
+
+def test_tuning_knobs_same_result():
+    """The launch-shape knobs (cells / key points per warp, programmatic dependent launch, general stereo chain) change
+    how the work is spread, never the result."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+    def run(env):
+        e = dict(os.environ, PYTHONPATH=root, **env)
+        out = subprocess.run([sys.executable, "-c", _KNOB_SCRIPT], env=e, cwd=root, capture_output=True, text=True, timeout=600)
+        assert out.returncode == 0, out.stderr[-2000:]
+        return [l for l in out.stdout.splitlines() if l.startswith("HASH")][0]
+
+    base = run({})
+    assert run({"YDORB_PDL": "0", "YDORB_FAST_CPW": "4", "YDORB_DESC_KPW": "8", "YDORB_STEREO_CHAIN": "1"}) == base
+    assert run({"YDORB_FAST_CPW": "2", "YDORB_DESC_KPW": "2", "YDORB_DEVICE_SPLIT": "1"}) == base
