@@ -30,7 +30,7 @@ constexpr int kQtMapDig = 8;                 // depth covered by the occupancy b
 static_assert(kQtMapWords == (1 << (2 * kQtMapDig)) / 32, "kQtMapWords (common.cuh) must cover 4^kQtMapDig bits");
 
 struct QtSmem {
-  uint32_t bitmap[kQtMapWords];  // bit p set <=> some candidate's path starts with the 8-digit prefix p
+  alignas(16) uint32_t bitmap[kQtMapWords];  // bit p set <=> some candidate's path starts with the 8-digit prefix p
   int cnt[kQtMapDig + 1];        // number of distinct d-digit prefixes, d = 0..8
   uint32_t ballots[kQtThreads / 32];
   int hist[256];
@@ -476,8 +476,8 @@ enum { kMetaN = 0, kMetaD = 1, kMetaM = 2, kMetaDeep = 3, kMetaBase = 4, kMetaFl
 
 __global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
   pdl_wait();
-  __shared__ uint32_t s_map[kQtMapWords];
-  __shared__ uint32_t s_fold[kQtMapWords];
+  __shared__ alignas(16) uint32_t s_map[kQtMapWords];
+  __shared__ alignas(16) uint32_t s_fold[kQtMapWords];
   __shared__ int s_cnt[kQtMapDig + 1];
   __shared__ uint32_t s_ballots[kQtThreads / 32];
   __shared__ int s_scan[kQtWarps];
@@ -505,10 +505,14 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
       for (int i = tid; i < kQtMapWords; i += kQtThreads) gmap[i] = 0;
     return;
   }
-  for (int i = tid; i < kQtMapWords; i += kQtThreads) {
-    s_map[i] = gmap[i];
-    gmap[i] = 0;  // zero between calls
-    s_fold[i] = 0;
+  {
+    // one 16-byte load per thread (the whole bitmap in a single round trip), then zero it for the next call
+    static_assert(kQtMapWords == 4 * kQtThreads, "one uint4 per thread");
+    uint4* gm4 = reinterpret_cast<uint4*>(gmap);
+    const uint4 v = gm4[tid];
+    gm4[tid] = make_uint4(0u, 0u, 0u, 0u);
+    reinterpret_cast<uint4*>(s_map)[tid] = v;
+    reinterpret_cast<uint4*>(s_fold)[tid] = make_uint4(0u, 0u, 0u, 0u);
   }
   if (tid <= kQtMapDig) s_cnt[tid] = 0;
   __syncthreads();
@@ -719,7 +723,7 @@ __device__ __forceinline__ int qt_next_prefix(const uint32_t* fold, int nwords, 
 
 struct QtFinSmem {
   QtSmem q;                     // radix-sort workspace (q.bitmap holds the D-digit occupancy here)
-  uint32_t prefix[kQtMapWords]; // exclusive popcount prefix per word
+  alignas(16) uint32_t prefix[kQtMapWords]; // exclusive popcount prefix per word
 };
 
 __global__ void __launch_bounds__(kQtThreads) k_qt_records(QtArgs A) {
@@ -742,9 +746,11 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_records(QtArgs A) {
   uint32_t* flagged = NK + M;             // M + 3 * #(nodes with > 16 members) <= n
   const uint32_t* gfold = A.fold + ((size_t)frame * kMaxLevels + level) * 2 * kQtMapWords;
   const int nbits = 1 << (2 * D), nwords = (nbits + 31) >> 5;
-  for (int w = tid; w < nwords; w += kQtThreads) {
-    sm.bitmap[w] = gfold[w];
-    fs.prefix[w] = gfold[kQtMapWords + w];
+  if (4 * tid < nwords) {  // both tables are full kQtMapWords arrays: one 16-byte load each per thread, one round trip
+    const uint4* gf4 = reinterpret_cast<const uint4*>(gfold);
+    const uint4 bm = gf4[tid], pf = gf4[kQtMapWords / 4 + tid];
+    reinterpret_cast<uint4*>(sm.bitmap)[tid] = bm;
+    reinterpret_cast<uint4*>(fs.prefix)[tid] = pf;
   }
   if (tid == 0) sm.misc[4] = 0;
   __syncthreads();
