@@ -935,7 +935,22 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_emit(QtArgs A) {
     unsigned long long* sk = reinterpret_cast<unsigned long long*>(&sm.warp_cnt[0][0]);
     int P = 2;
     while (P < M) P <<= 1;
-    for (int i = tid; i < P; i += kQtThreads) sk[i] = i < M ? ((unsigned long long)NK[i] << 32) | NV[i] : ~0ull;
+    {
+      // all of a thread's loads first (P <= 4 * kQtThreads): one round trip instead of one per element
+      constexpr int kPer = kSmemSort / kQtThreads;
+      uint32_t k4[kPer], v4[kPer];
+#pragma unroll
+      for (int k = 0; k < kPer; k++) {
+        const int i = tid + k * kQtThreads;
+        k4[k] = 0xFFFFFFFFu; v4[k] = 0xFFFFFFFFu;
+        if (i < M) { k4[k] = NK[i]; v4[k] = NV[i]; }
+      }
+#pragma unroll
+      for (int k = 0; k < kPer; k++) {
+        const int i = tid + k * kQtThreads;
+        if (i < P) sk[i] = ((unsigned long long)k4[k] << 32) | v4[k];
+      }
+    }
     __syncthreads();
     for (int k = 2; k <= P; k <<= 1)
       for (int j = k >> 1; j > 0; j >>= 1) {
