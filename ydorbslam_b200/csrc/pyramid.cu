@@ -128,6 +128,9 @@ struct PyrArgs {
   int tile_base;         // index (in the int table array) of this level's tile descriptors, see pyramid_tile_tables
 };
 
+#ifndef YD_PYR_STAGE_ILP
+#define YD_PYR_STAGE_ILP 3
+#endif
 template <int SS>  // SS: row stride (bytes) of the staged source copies
 __global__ void __launch_bounds__(256) k_pyr_resize(const PyrArgs a, const int* __restrict__ tab_ofs,
                                                     const short2* __restrict__ tab_a, uint8_t* __restrict__ pyr) {
@@ -162,15 +165,30 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const PyrArgs a, const int* 
   }
   if (tid < nsr) s_h[tid * kPyHS + kPyHS - 1] = 0;
   // ---- stage
+  constexpr int kStageIlp = YD_PYR_STAGE_ILP;  // rows whose loads are in flight together per thread
   for (int c = tid & 15; c < nchunk; c += 16) {
-    for (int r = tid >> 4; r < nsr; r += 16) {
-      const uint8_t* gp = src0 + (long long)(sy_lo + r) * a.sstride + sxa + 16 * c;
-      const uint4 v = *reinterpret_cast<const uint4*>(gp);
-      const uint32_t nx = (c + 1 < nchunk) ? *reinterpret_cast<const uint32_t*>(gp + 16) : 0u;
-      *reinterpret_cast<uint4*>(s_a + r * SS + 16 * c) = v;
-      *reinterpret_cast<uint4*>(s_b + r * SS + 16 * c) =
-          make_uint4(__funnelshift_r(v.x, v.y, 8), __funnelshift_r(v.y, v.z, 8), __funnelshift_r(v.z, v.w, 8),
-                     __funnelshift_r(v.w, nx, 8));
+    for (int r0 = tid >> 4; r0 < nsr; r0 += 16 * kStageIlp) {
+      uint4 v[kStageIlp];
+      uint32_t nx[kStageIlp];
+#pragma unroll
+      for (int k = 0; k < kStageIlp; k++) {
+        const int r = r0 + 16 * k;
+        if (r < nsr) {
+          const uint8_t* gp = src0 + (long long)(sy_lo + r) * a.sstride + sxa + 16 * c;
+          v[k] = *reinterpret_cast<const uint4*>(gp);
+          nx[k] = (c + 1 < nchunk) ? *reinterpret_cast<const uint32_t*>(gp + 16) : 0u;
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < kStageIlp; k++) {
+        const int r = r0 + 16 * k;
+        if (r < nsr) {
+          *reinterpret_cast<uint4*>(s_a + r * SS + 16 * c) = v[k];
+          *reinterpret_cast<uint4*>(s_b + r * SS + 16 * c) =
+              make_uint4(__funnelshift_r(v[k].x, v[k].y, 8), __funnelshift_r(v[k].y, v[k].z, 8),
+                         __funnelshift_r(v[k].z, v[k].w, 8), __funnelshift_r(v[k].w, nx[k], 8));
+        }
+      }
     }
   }
   __syncthreads();
