@@ -802,17 +802,25 @@ __global__ void __launch_bounds__(kTieWarps * 32) k_qt_ties(QtArgs A) {
   const FrameGeomDev* g = A.g;
   int* fmeta = A.meta + (size_t)frame * kMaxLevels * 8;
   const int n_levels = g->n_levels;
-  int total = 0;
-  for (int l = 0; l < n_levels; l++)
-    if (fmeta[l * 8 + kMetaN] != 0 && !fmeta[l * 8 + kMetaDeep]) total += fmeta[l * 8 + kMetaFlagged];
+  // lane l holds level l's flagged count and the inclusive prefix over the levels (most warps find nothing to do:
+  // keep that path to one round trip)
+  static_assert(kMaxLevels <= 32, "one lane per level");
+  int lc = 0;
+  if (lane < n_levels) {
+    const int* mm = fmeta + lane * 8;
+    lc = (mm[kMetaN] != 0 && !mm[kMetaDeep]) ? mm[kMetaFlagged] : 0;
+  }
+  int lincl = lc;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, lincl, o);
+    if (lane >= o) lincl += t;
+  }
+  const int total = __shfl_sync(0xffffffffu, lincl, 31);
   const int nwarps = gridDim.x * kTieWarps;
   for (int item = blockIdx.x * kTieWarps + warp; item < total; item += nwarps) {
-    int level = 0, f = item;
-    for (; level < n_levels; level++) {
-      const int c = (fmeta[level * 8 + kMetaN] != 0 && !fmeta[level * 8 + kMetaDeep]) ? fmeta[level * 8 + kMetaFlagged] : 0;
-      if (f < c) break;
-      f -= c;
-    }
+    const int level = __popc(__ballot_sync(0xffffffffu, lincl <= item));  // lanes past n_levels hold `total` > item
+    const int f = item - (__shfl_sync(0xffffffffu, lincl, level) - __shfl_sync(0xffffffffu, lc, level));
     int* meta = fmeta + level * 8;
     const LevelGeom lv = g->lv[level];
     const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase];
