@@ -469,8 +469,10 @@ __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
 //   k_qt_depth   (CTA/segment) depth D from the bitmap, D-digit occupancy + popcount prefix = node index of a prefix
 //   k_qt_pass1/2 (GPU-wide)   per node: member count, first maximum in candidate order (atomicMax on
 //                             response << 24 | ~position), number of members that tie with it
-//   k_qt_finish  (CTA/segment) node records, std::sort emulation for the nodes that need it (members gathered in
-//                             candidate order through the FAST cell grid), list-order sort, truncate, emit
+//   k_qt_records (CTA/segment) node records (order key + winner); nodes whose winner std::sort decides are queued
+//   k_qt_ties    (GPU-wide)   warp per queued node: members gathered in candidate order through the FAST cell grid,
+//                             libstdc++ std::sort emulation
+//   k_qt_emit    (CTA/segment) list-order sort, truncate, emit
 // Segments that need more than kQtMapDig passes (tightly clustered points) keep the sort-based k_quadtree below.
 enum { kMetaN = 0, kMetaD = 1, kMetaM = 2, kMetaDeep = 3, kMetaBase = 4, kMetaFlagged = 5, kMetaBig = 6 };
 
