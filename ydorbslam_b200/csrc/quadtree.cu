@@ -435,11 +435,16 @@ __device__ void qt_fill(const QtArgs& A, const LevelGeom& lv, int frame, int lev
 // common case needs (depth <= 8) -- so this instruction-heavy step runs across the whole GPU instead of inside the one
 // CTA that owns a (level, frame) segment.  The rare deeper case recomputes full codes inside k_quadtree (qt_fill).
 constexpr int kCodeWarps = 8;
+// kCodeLanes = lanes that share one FAST cell: 8 for launches that fill the GPU anyway, 32 spreads a small launch
+template <int kCodeLanes>
 __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
+  constexpr int kCodeCells = kCodeWarps * 32 / kCodeLanes;  // cells per CTA
   pdl_wait();
   const FrameGeomDev* g = A.g;
-  const int frame = blockIdx.y, lane = threadIdx.x & 31;
-  const int c = blockIdx.x * kCodeWarps + (threadIdx.x >> 5);  // cell index within the frame
+  // a cell holds a handful of candidates (~6 on a 640x480 frame): kCodeLanes lanes per cell, several cells per warp
+  // (no warp-level collectives below, the groups of a warp simply diverge)
+  const int frame = blockIdx.y, lane = threadIdx.x & (kCodeLanes - 1);
+  const int c = blockIdx.x * kCodeCells + threadIdx.x / kCodeLanes;  // cell index within the frame
   if (c >= g->n_cells) return;
   const int cnt = A.cell_count[(size_t)frame * g->n_cells + c];
   if (cnt == 0) return;
@@ -450,7 +455,7 @@ __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
   const size_t pos0 = (size_t)frame * g->raw_cap + A.cell_rank[(size_t)frame * (g->n_cells + 1) + c];
   const uint32_t* raw = A.raw + (size_t)frame * g->raw_cap;
   uint32_t* bitmap = A.bitmap + ((size_t)frame * kMaxLevels + level) * kQtMapWords;
-  for (int e = lane; e < cnt; e += 32) {
+  for (int e = lane; e < cnt; e += kCodeLanes) {
     const uint32_t r = raw[start + e];  // y:12 | x:12 | response:8, border-relative coordinates
     const uint32_t code = qt_code<kQtMapDig>((int)((r >> 8) & 4095u), (int)(r >> 20), root_w, root_h);
     A.keys[0][pos0 + e] = code;
@@ -1244,7 +1249,14 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
   A.level_ncand = ex->d_level_ncand;
   A.status = ex->d_status;
   if (ex->geom.n_cells > 0)
-    YD_CUDA(launch_chain(k_qt_codes, dim3((ex->geom.n_cells + kCodeWarps - 1) / kCodeWarps, batch), dim3(kCodeWarps * 32), 0, s, A));
+  {
+    if ((long long)ex->geom.n_cells * batch >= 148 * 8 * 32) {  // measured: 0.276 -> 0.266 ms per 256 frames; a single frame prefers 32
+      constexpr int cells = kCodeWarps * 32 / 8;
+      YD_CUDA(launch_chain(k_qt_codes<8>, dim3((ex->geom.n_cells + cells - 1) / cells, batch), dim3(kCodeWarps * 32), 0, s, A));
+    } else {
+      YD_CUDA(launch_chain(k_qt_codes<32>, dim3((ex->geom.n_cells + kCodeWarps - 1) / kCodeWarps, batch), dim3(kCodeWarps * 32), 0, s, A));
+    }
+  }
   // candidate passes: grid-stride over the frame's candidates (their number is only known on the device); enough CTAs per
   // frame to fill the GPU when the batch is small, few when it is large
   const int per_frame = std::max(1, std::min((ex->geom.raw_cap + 255) / 256, (148 * 8 + batch - 1) / batch));
