@@ -68,6 +68,10 @@ void ydorb_host_free(void* p);
  * out[0] POPC, [1] LOP3, [2] VIMNMX3.S16x2 (DPX), [3] IMAD, [4] LOP3+IMAD alternating.  Denominators of the integer
  * roofline bench.py reports for the FAST and Hamming kernels. */
 int ydorb_diag_int_peaks(int device, double* ops_per_s, int n);
+/* Diagnostics: the device's sinf/cosf of computeDescriptors (src/orbExtractor.cpp:426 resolves to libm sincosf) for the
+ * `count` consecutive floats whose bit patterns start at first_bits; out[2*i] = sin, out[2*i+1] = cos.  Lets a test
+ * compare the kernel's trigonometry with the host libm over the whole input domain. */
+int ydorb_diag_sincosf(int device, uint32_t first_bits, uint32_t count, float* out_sin_cos);
 
 /* ---- OrbExtractor -------------------------------------------------------------------------------------- */
 /* OrbExtractor::OrbExtractor (src/orbExtractor.cpp:315-354).  max_* size the device buffers. */

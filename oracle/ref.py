@@ -1,0 +1,140 @@
+"""ctypes binding for oracle/_ref/libydorb_ref.so: the REFERENCE's own translation units, compiled unmodified
+(oracle/refshim/Makefile) against the OpenCV stand-in headers.  TEST INFRASTRUCTURE -- the top of the parity chain:
+
+    _ref (reference code)  ==  oracle (restatement)  ==  tests/golden fixtures;   CUDA == oracle == _ref
+
+Only tests/, __graft_entry__ and bench.py's cpu_baseline / --impl reference legs may import this.  The library is built
+in the container that has /root/reference; the GPU box receives the prebuilt .so with the snapshot (never the sources).
+"""
+import ctypes as C
+import os
+import pathlib
+import subprocess
+
+import numpy as np
+
+from . import orc
+
+_HERE = pathlib.Path(__file__).resolve().parent
+_SO = _HERE / "_ref" / "libydorb_ref.so"
+REFERENCE = pathlib.Path(os.environ.get("YDORB_REFERENCE", "/root/reference"))
+
+KP_DTYPE = orc.KP_DTYPE
+CAND_DTYPE = orc.CAND_DTYPE
+PAD = orc.PAD
+
+
+def can_build():
+    return (REFERENCE / "src" / "orbExtractor.cpp").exists()
+
+
+def build():
+    """Build (or refresh) oracle/_ref when the reference checkout is present; otherwise use the prebuilt library."""
+    orc.build()
+    if can_build():
+        subprocess.check_call(["make", "-C", str(_HERE / "refshim"), f"REF={REFERENCE}"], stdout=subprocess.DEVNULL)
+    return _SO
+
+
+def available():
+    return _SO.exists() or can_build()
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        if not _SO.exists():
+            raise ImportError(f"{_SO} is missing and {REFERENCE} is not present to build it from")
+        _lib = C.CDLL(str(_SO))
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def ctor_tables(n_features=1000, scale=1.2, n_levels=8, ini_th=20, min_th=7):
+    """Tables of OrbExtractor::OrbExtractor (src/orbExtractor.cpp:315-354) as the compiled reference produces them."""
+    sf, isf, sf2, isf2 = (np.zeros(n_levels, np.float32) for _ in range(4))
+    quota = np.zeros(n_levels, np.int32)
+    umax = np.zeros(64, np.int32)
+    th = np.zeros(2, np.int32)
+    n = lib().ref_ctor_tables(
+        n_features, C.c_float(scale), n_levels, ini_th, min_th, _p(sf), _p(isf), _p(sf2), _p(isf2), _p(quota), _p(umax), 64, _p(th)
+    )
+    return dict(sf=sf, inv_sf=isf, sf2=sf2, inv_sf2=isf2, quota=quota, umax=umax[:n], ini_th=int(th[0]), min_th=int(th[1]))
+
+
+def extract(img, n_features=1000, scale=1.2, n_levels=8, ini_th=20, min_th=7, cap=None, want_pyramid=False,
+            want_candidates=False):
+    """extractAndCompute on a fresh reference OrbExtractor.  Returns (kps, desc, per_level_n[, pyramid][, candidates])."""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w = img.shape
+    cap = cap or (n_features + 64)
+    kps = np.zeros(cap, KP_DTYPE)
+    desc = np.zeros((cap, 32), np.uint8)
+    per = np.zeros(n_levels, np.int32)
+    pyr = off = None
+    pyr_cap = 0
+    if want_pyramid:
+        pyr_cap = int(sum((int(w * scale ** -l) + 40) * (int(h * scale ** -l) + 40) for l in range(n_levels)))
+        pyr = np.zeros(pyr_cap, np.uint8)
+        off = np.zeros(n_levels, np.int64)
+    cand = start = None
+    cand_cap = 0
+    if want_candidates:
+        cand_cap = w * h // 4 + 1024
+        cand = np.zeros(cand_cap, CAND_DTYPE)
+        start = np.zeros(n_levels + 1, np.int32)
+    n = lib().ref_extract(
+        n_features, C.c_float(scale), n_levels, ini_th, min_th, _p(img), w, h, w, _p(kps), _p(desc), cap, _p(per), _p(pyr),
+        _p(off), C.c_int64(pyr_cap), _p(cand), cand_cap, _p(start),
+    )
+    assert 0 <= n <= cap, n
+    out = [kps[:n], desc[:n], per]
+    if want_pyramid:
+        levels = []
+        for l in range(n_levels):
+            end = off[l + 1] if l + 1 < n_levels else None
+            nxt = int(end) if end is not None else None
+            levels.append((int(off[l]), nxt))
+        out.append((pyr, levels))
+    if want_candidates:
+        assert start[-1] <= cand_cap
+        out.append([cand[start[l] : start[l + 1]] for l in range(n_levels)])
+    return tuple(out)
+
+
+def pyramid_levels(pyr_and_levels, level_sizes):
+    """Split the flat pyramid buffer returned by extract(want_pyramid=True) into padded (lh+38, lw+38) arrays."""
+    pyr, levels = pyr_and_levels
+    out = []
+    for (o, _), (lw, lh) in zip(levels, level_sizes):
+        out.append(pyr[o : o + (lw + 2 * PAD) * (lh + 2 * PAD)].reshape(lh + 2 * PAD, lw + 2 * PAD))
+    return out
+
+
+def quadtree(cand, rootw, rooth, want):
+    """distributeQuadTree (src/orbExtractor.cpp:455-544) of the compiled reference; returns indices into cand."""
+    cand = np.ascontiguousarray(cand, dtype=CAND_DTYPE)
+    sel = np.zeros(max(2 * want + 8, len(cand) + 8), np.int32)
+    m = lib().ref_quadtree(_p(cand), len(cand), rootw, rooth, want, _p(sel))
+    return sel[:m]
+
+
+def extract_batch(imgs, threads, n_features=1000, scale=1.2, n_levels=8, ini_th=20, min_th=7, cap=None):
+    imgs = np.ascontiguousarray(imgs, dtype=np.uint8)
+    b, h, w = imgs.shape
+    cap = cap or (n_features + 64)
+    kps = np.zeros((b, cap), KP_DTYPE)
+    desc = np.zeros((b, cap, 32), np.uint8)
+    n = np.zeros(b, np.int32)
+    lib().ref_extract_batch(
+        n_features, C.c_float(scale), n_levels, ini_th, min_th, _p(imgs), w, h, w, C.c_int64(h * w), b, _p(kps), _p(desc), cap,
+        _p(n), threads,
+    )
+    return kps, desc, n

@@ -550,11 +550,102 @@ float orc_ic_angle(const OrcParams* p, const uint8_t* lvl, int stride, int x, in
   return orc_fast_atan2((float)m01, (float)m10);  // :419
 }
 
+/* glibc 2.39 sincosf, x86-64 FMA variant (sysdeps/ieee754/flt-32/s_sincosf.c + sysdeps/x86_64/fpu/sincosf_poly.h,
+ * selected by ifunc on every CPU with FMA+AVX2), restated for the device kernel to follow: the published algorithm of
+ * the ARM optimized-routines sincosf -- argument reduction and two short polynomials evaluated in double, every
+ * `a + b*c` a fused multiply-add, result rounded once to float.  Only the branches an angle in [0, 120) can take.
+ * tests/test_oracle_ref.py checks this model against libm's sincosf over the whole input domain of
+ * src/orbExtractor.cpp:425 (every float in [0, 2*pi]).  Constants: __sincosf_table of the same glibc. */
+__attribute__((target("fma"))) void orc_sincosf_model(float y, float* sinp, float* cosp) {
+  static const double kHpiInv = 0x1.45F306DC9C883p+23, kHpi = 0x1.921FB54442D18p0;
+  static const double C0 = 0x1p0, C1 = -0x1.ffffffd0c621cp-2, C2 = 0x1.55553e1068f19p-5, C3 = -0x1.6c087e89a359dp-10,
+                      C4 = 0x1.99343027bf8c3p-16;
+  static const double S1 = -0x1.555545995a603p-3, S2 = 0x1.1107605230bc4p-7, S3 = -0x1.994eb3774cf24p-13;
+  uint32_t bits;
+  memcpy(&bits, &y, 4);
+  const uint32_t top12 = (bits >> 20) & 0x7ff;
+  double x = (double)y, xs = x, neg = 1.0;
+  int n = 0;
+  if (top12 < 0x3f4) {       // |y| < 0.75 (abstop12(y) < abstop12(pi/4))
+    if (top12 < 0x398) {     // |y| < 2^-12
+      *sinp = y;
+      *cosp = 1.0f;
+      return;
+    }
+  } else {                   // reduce_fast, valid below 120.0f
+    const double r = x * kHpiInv;
+    n = ((int32_t)r + 0x800000) >> 24;
+    x = __builtin_fma(-(double)n, kHpi, x);
+    xs = x * ((n + 1) & 2 ? -1.0 : 1.0);  // sign[n & 3] = {1, -1, -1, 1}
+    if (n & 2) neg = -1.0;                 // __sincosf_table[1]: cosine coefficients negated
+  }
+  const double x2 = x * x;
+  const double x3 = x2 * xs, x4 = x2 * x2;
+  const double s1 = __builtin_fma(x2, S3, S2), c2 = __builtin_fma(x2, neg * C4, neg * C3);
+  const double c1 = __builtin_fma(x2, neg * C1, neg * C0);
+  const double x5 = x2 * x3, x6 = x2 * x4;
+  const double s = __builtin_fma(x3, S1, xs), c = __builtin_fma(x4, neg * C2, c1);
+  const float sv = (float)__builtin_fma(s1, x5, s), cv = (float)__builtin_fma(c2, x6, c);
+  if (n & 1) {
+    *sinp = cv;
+    *cosp = sv;
+  } else {
+    *sinp = sv;
+    *cosp = cv;
+  }
+}
+
+/* count of floats in [lo_bits, hi_bits] (step `stride`) where orc_sincosf_model differs from libm sincosf */
+int64_t orc_sincosf_model_mismatches(uint32_t lo_bits, uint32_t hi_bits, uint32_t stride, int threads) {
+  if (threads < 1) threads = 1;
+  std::vector<int64_t> bad((size_t)threads, 0);
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; t++) {
+    pool.emplace_back([&, t]() {
+      for (uint64_t u = (uint64_t)lo_bits + (uint64_t)t * stride; u <= hi_bits; u += (uint64_t)stride * threads) {
+        const uint32_t b = (uint32_t)u;
+        float y, s0, c0, s1, c1;
+        memcpy(&y, &b, 4);
+        sincosf(y, &s0, &c0);
+        orc_sincosf_model(y, &s1, &c1);
+        if (memcmp(&s0, &s1, 4) || memcmp(&c0, &c1, 4)) bad[t]++;
+      }
+    });
+  }
+  for (auto& th : pool) th.join();
+  int64_t n = 0;
+  for (int64_t b : bad) n += b;
+  return n;
+}
+
+/* libm sincosf (what src/orbExtractor.cpp:426 calls) for `count` consecutive float bit patterns; out[2i] = sin, [2i+1] = cos */
+void orc_sincosf_range(uint32_t first_bits, uint32_t count, float* out, int threads) {
+  if (threads < 1) threads = 1;
+  std::vector<std::thread> pool;
+  for (int t = 0; t < threads; t++) {
+    pool.emplace_back([=]() {
+      const uint64_t lo = (uint64_t)count * t / threads, hi = (uint64_t)count * (t + 1) / threads;
+      for (uint64_t i = lo; i < hi; i++) {
+        const uint32_t b = first_bits + (uint32_t)i;
+        float y;
+        memcpy(&y, &b, 4);
+        sincosf(y, &out[2 * i], &out[2 * i + 1]);
+      }
+    });
+  }
+  for (auto& th : pool) th.join();
+}
+
 /* E7  computeDescriptors  src/orbExtractor.cpp:422-454 */
 void orc_descriptor(const uint8_t* img, int stride, int x, int y, float angle_deg, uint8_t* desc32) {
   const float deg2rad = (float)(M_PI / 180.0);  // src/orbExtractor.hpp:57
   volatile float angle = angle_deg * deg2rad;   // :425
-  const float cosA = (float)cos((double)angle), sinB = (float)sin((double)angle);  // :426
+  // :426  `(float)cos(angle), (float)sin(angle)` with a float argument: <math.h>/<cmath> of libstdc++ put the float
+  // overloads into the global namespace, so the reference calls cosf/sinf (g++ -O3 fuses the pair into one sincosf
+  // call -- checked with nm on the compiled reference object, oracle/_ref/orbExtractor.o).  NOT double cos/sin: those
+  // differ from cosf/sinf by one float ulp on 0.04 % / 0.09 % of the floats in [0, 2*pi].
+  float cosA, sinB;
+  sincosf(angle, &sinB, &cosA);
   auto get = [&](int idx) -> int {  // GET_VALUE :427-429
     const int px = kPattern[2 * idx], py = kPattern[2 * idx + 1];
     volatile float a = px * sinB, b = py * cosA, r = a + b;

@@ -1,0 +1,66 @@
+"""GPU parity against the REFERENCE's own code: CUDA (through the C ABI) == oracle/_ref (orbExtractor.cpp compiled
+unmodified, see tests/test_oracle_ref.py) on the BASELINE config shapes, and the device trigonometry == host libm sincosf
+over the whole input domain.  /root/reference is not needed at run time: the prebuilt oracle/_ref travels with the repo."""
+import ctypes as C
+import os
+import struct
+
+import numpy as np
+import pytest
+
+from oracle import orc, ref
+from ydorbslam_b200 import OrbExtractor, synth
+from ydorbslam_b200._lib import check, lib
+
+pytestmark = pytest.mark.gpu
+
+
+def _same(kps, desc, rk, rd):
+    assert len(kps) == len(rk)
+    for f in orc.KP_DTYPE.names:
+        assert np.array_equal(kps[f].view(np.uint32), rk[f].view(np.uint32)), f
+    assert np.array_equal(desc, rd)
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+@pytest.mark.parametrize("shape,nf,seed", [((480, 640), 1000, 31), ((376, 1241), 2000, 32), ((1080, 1920), 4000, 33),
+                                           ((2160, 3840), 8000, 34), ((97, 97), 1000, 4)])
+def test_cuda_matches_compiled_reference(shape, nf, seed):
+    """Key points, order, octaves, angles and descriptors bit-exact against the reference build (configs 1, 2, 3, 5)."""
+    h, w = shape
+    img = synth.synth_frame(w, h, seed)
+    rk, rd, _ = ref.extract(img, nf, cap=nf + 64)
+    ex = OrbExtractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=1)
+    kps, desc = ex.extractAndCompute(img)
+    _same(kps, desc, rk, rd)
+    ex.close()
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+def test_cuda_batch_matches_compiled_reference():
+    imgs = synth.synth_batch(640, 480, 6, seed0=300)
+    imgs[4] = synth.synth_sparse_frame(640, 480, 12)
+    ex = OrbExtractor(1000, 1.2, 8, 20, 7, max_width=640, max_height=480, max_batch=6)
+    kps, desc, n = ex.extract_batch(imgs)
+    for b in range(6):
+        rk, rd, _ = ref.extract(imgs[b], 1000)
+        _same(kps[b, : n[b]], desc[b, : n[b]], rk, rd)
+    ex.close()
+
+
+def test_device_sincosf_equals_libm_everywhere():
+    """src/orbExtractor.cpp:426 is libm sincosf on the host.  glibc_sincosf (csrc/common.cuh) must return the same bits
+    for every float an angle in radians can be: all of [0, 2*pi], 1.09e9 values."""
+    hi = struct.unpack("<I", struct.pack("<f", 6.2831855))[0]
+    chunk = 1 << 25
+    l = orc.lib()
+    l.orc_sincosf_range.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p, C.c_int]
+    dev = np.empty(2 * chunk, np.float32)
+    host = np.empty(2 * chunk, np.float32)
+    bad = 0
+    for first in range(0, hi + 1, chunk):
+        cnt = min(chunk, hi + 1 - first)
+        check(lib().ydorb_diag_sincosf(0, C.c_uint32(first), C.c_uint32(cnt), dev.ctypes.data_as(C.c_void_p)))
+        l.orc_sincosf_range(first, cnt, host.ctypes.data_as(C.c_void_p), os.cpu_count() or 8)
+        bad += int((dev[: 2 * cnt].view(np.uint32) != host[: 2 * cnt].view(np.uint32)).sum())
+    assert bad == 0, f"{bad} of {2 * (hi + 1)} sin/cos values differ from libm"

@@ -34,6 +34,42 @@ __device__ __forceinline__ void pdl_wait() {
   asm volatile("griddepcontrol.launch_dependents;");
 }
 #endif
+#ifdef __CUDACC__
+// sinf/cosf exactly as the reference's host libm computes them (src/orbExtractor.cpp:426: `cos(angle)` / `sin(angle)`
+// on a float resolve to the float overloads, fused by g++ -O3 into one sincosf call -- NOT double cos/sin).  This is
+// glibc 2.39's sincosf in its x86-64 FMA variant (ARM optimized-routines algorithm): reduction by pi/2 and two short
+// polynomials in double, every a + b*c fused, one final rounding to float.  Branches for |y| < 120 only (angles are
+// degrees in [0, 360) times pi/180).  Model + exhaustive check against libm: oracle/ydorb_oracle.cpp orc_sincosf_model;
+// the device function itself is checked over the same domain by tests/test_gpu_extract.py through ydorb_diag_sincosf.
+__device__ __forceinline__ void glibc_sincosf(float y, float& sn, float& cs) {
+  const uint32_t top12 = (__float_as_uint(y) >> 20) & 0x7ffu;
+  double x = (double)y, xs = x, neg = 1.0;
+  int n = 0;
+  if (top12 < 0x3f4u) {      // |y| < 0.75
+    if (top12 < 0x398u) {    // |y| < 2^-12
+      sn = y;
+      cs = 1.0f;
+      return;
+    }
+  } else {
+    const double r = __dmul_rn(x, 0x1.45F306DC9C883p+23);
+    n = (__double2int_rz(r) + 0x800000) >> 24;
+    x = __fma_rn(-(double)n, 0x1.921FB54442D18p0, x);
+    xs = ((n + 1) & 2) ? -x : x;     // sign[n & 3] = {1, -1, -1, 1}
+    if (n & 2) neg = -1.0;           // second table: cosine coefficients negated
+  }
+  const double x2 = __dmul_rn(x, x);
+  const double x3 = __dmul_rn(x2, xs), x4 = __dmul_rn(x2, x2);
+  const double s1 = __fma_rn(x2, -0x1.994eb3774cf24p-13, 0x1.1107605230bc4p-7);
+  const double c2 = __fma_rn(x2, neg * 0x1.99343027bf8c3p-16, neg * -0x1.6c087e89a359dp-10);
+  const double c1 = __fma_rn(x2, neg * -0x1.ffffffd0c621cp-2, neg);
+  const double x5 = __dmul_rn(x2, x3), x6 = __dmul_rn(x2, x4);
+  const double s = __fma_rn(x3, -0x1.555545995a603p-3, xs), c = __fma_rn(x4, neg * 0x1.55553e1068f19p-5, c1);
+  const float sv = __double2float_rn(__fma_rn(s1, x5, s)), cv = __double2float_rn(__fma_rn(c2, x6, c));
+  sn = (n & 1) ? cv : sv;
+  cs = (n & 1) ? sv : cv;
+}
+#endif
 bool pdl_enabled();  // YDORB_PDL=0 switches the attribute off
 template <class... P, class... A>
 inline cudaError_t launch_chain(void (*kernel)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, A&&... args) {

@@ -227,7 +227,8 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
   __syncwarp();
   // ---- E7 rBRIEF
   const float a_rad = __fmul_rn(angle, (float)(3.14159265358979323846 / 180.0));  // :425
-  const float cosA = (float)cos((double)a_rad), sinB = (float)sin((double)a_rad);    // :426
+  float cosA, sinB;
+  glibc_sincosf(a_rad, sinB, cosA);                                                  // :426 (float overloads: sincosf)
   // 32-bit view of hb; a sample at (rr, cc) reads rows 18+rr .. 24+rr of column 19+a+cc: four consecutive words,
   // realigned by a funnel shift when the first row is odd, then 4 x DP2A with the tap pairs (18,34)(48,56)(48,34)(18,0)
   const uint32_t* hw32 = reinterpret_cast<const uint32_t*>(hb) + (26 + a - kHbCol0) * (kHbColStride / 2);

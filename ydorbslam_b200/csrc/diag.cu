@@ -69,9 +69,34 @@ static int run_rate(int sm_count, int iters, uint32_t* d_sink, double* ops_per_s
   return YDORB_OK;
 }
 
+// glibc_sincosf over consecutive float bit patterns: out[2*i] = sin, out[2*i+1] = cos of the float with bits first+i
+__global__ void __launch_bounds__(256) k_diag_sincosf(uint32_t first_bits, uint32_t count, float* __restrict__ out) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+    float s, c;
+    glibc_sincosf(__uint_as_float(first_bits + i), s, c);
+    reinterpret_cast<float2*>(out)[i] = make_float2(s, c);
+  }
+}
+
 }  // namespace ydorb
 
 using namespace ydorb;
+
+extern "C" int ydorb_diag_sincosf(int device, uint32_t first_bits, uint32_t count, float* out_sin_cos) {
+  YD_REQUIRE(out_sin_cos && count > 0, "need an output buffer of 2*count floats");
+  int ndev = 0;
+  YD_CUDA(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) { set_error("no such CUDA device"); return YDORB_E_CUDA; }
+  YD_CUDA(cudaSetDevice(device));
+  float* d = nullptr;
+  YD_CUDA(cudaMalloc(&d, (size_t)count * 8));
+  k_diag_sincosf<<<148 * 8, 256>>>(first_bits, count, d);
+  count_launches(1);
+  cudaError_t e = cudaMemcpy(out_sin_cos, d, (size_t)count * 8, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  YD_CUDA(e);
+  return YDORB_OK;
+}
 
 extern "C" int ydorb_diag_int_peaks(int device, double* ops_per_s, int n) {
   YD_REQUIRE(ops_per_s && n >= kOpCount, "need room for 5 rates: popc, lop3, vimnmx3.s16x2, imad, lop3+imad mix");
