@@ -329,33 +329,51 @@ def run_gpu(args):
     h2d = B * W * H + 2 * 4 * B
     d2h = B * cap * (28 + 32) + 4 * B + B * cap * (16 + 1)
 
-    # ---- secondary metric: Hamming top-2, 2000 queries x 1M database rows sharded over the ranks
+    # ---- secondary metric: Hamming top-2, 2000 queries x 1M database rows sharded over the ranks, through the
+    # library's own multi-GPU path (csrc/shard.cu: ydorb_comm_create + ydorb_hamming_top2_sharded_device): ONE kernel per
+    # GPU and call -- shard scan, peer-memory push of the 16 B/query records over NVLink, merge + ratio test
     ham = None
     if not args.skip_hamming:
+        from ydorbslam_b200 import sharding
+
         rows = HAMMING_NDB // world
         base = rank * rows
-        db_np = synth.synth_descriptors(rows, 1000 + rank)
-        q_np = synth.synth_descriptors(HAMMING_NQ, 7)
-        d_db = torch.from_numpy(db_np).to(dev)
+        shards_np = [synth.synth_descriptors(rows, 1000 + r) for r in range(world)]
+        q_np, _ = synth.synth_query_descriptors(np.concatenate(shards_np), HAMMING_NQ, 7)
+        d_db = torch.from_numpy(shards_np[rank]).to(dev)
         d_q = torch.from_numpy(q_np).to(dev)
-        d_part = torch.zeros(HAMMING_NQ, 4, dtype=torch.int32, device=dev)
-        d_all = torch.zeros(world, HAMMING_NQ, 4, dtype=torch.int32, device=dev)
         d_out = torch.zeros(HAMMING_NQ, 4, dtype=torch.int32, device=dev)
         d_ok = torch.zeros(HAMMING_NQ, dtype=torch.uint8, device=dev)
         m.set_stream(stream.cuda_stream)
+        uid = [sharding.comm_unique_id() if (rank == 0 and world > 1) else None]
+        if world > 1:
+            dist.broadcast_object_list(uid, src=0)  # host-side plumbing only: ships the 128-byte ncclUniqueId
+        comm = sharding.Communicator(m, rank, world, HAMMING_NQ, uid[0])
 
         def ham_step():
-            m.top2_device(d_q.data_ptr(), HAMMING_NQ, d_db.data_ptr(), rows, base, d_part.data_ptr())
-            if world > 1:
-                dist.all_gather_into_tensor(d_all, d_part)  # NCCL: 32 KB per rank
-                m.top2_merge_device(d_all.data_ptr(), world, HAMMING_NQ, d_out.data_ptr())
-                src = d_out
-            else:
-                src = d_part
-            m.ratio_accept_device(src.data_ptr(), HAMMING_NQ, d_ok.data_ptr(), RATIO, TH_LOW)
+            sharding.sharded_top2_device(comm, d_q.data_ptr(), HAMMING_NQ, d_db.data_ptr(), rows, base, RATIO, TH_LOW,
+                                         d_out.data_ptr(), d_ok.data_ptr())
+
+        # correctness before timing, on EVERY rank: the merged result must equal one scan of the whole database on this
+        # GPU (ydorb_hamming_top2_device over all shards + ratio test), field by field
+        with torch.cuda.stream(stream):
+            ham_step()
+            ham_step()  # second call: the other parity of the double-buffered exchange
+        comm.check()
+        d_full = torch.from_numpy(np.concatenate(shards_np)).to(dev)
+        d_ref = torch.zeros(HAMMING_NQ, 4, dtype=torch.int32, device=dev)
+        d_ref_ok = torch.zeros(HAMMING_NQ, dtype=torch.uint8, device=dev)
+        m.top2_device(d_q.data_ptr(), HAMMING_NQ, d_full.data_ptr(), rows * world, 0, d_ref.data_ptr())
+        m.ratio_accept_device(d_ref.data_ptr(), HAMMING_NQ, d_ref_ok.data_ptr(), RATIO, TH_LOW)
+        m.sync()
+        got, want = d_out.cpu().numpy(), d_ref.cpu().numpy()
+        assert np.array_equal(got[:, :3], want[:, :3]), f"rank {rank}: sharded top-2 differs from the single scan"
+        assert np.array_equal(d_ok.cpu().numpy(), d_ref_ok.cpu().numpy()), f"rank {rank}: ratio-test flags differ"
+        del d_full
+        ham_true = int((got[: HAMMING_NQ // 2, 0] >= 0).sum())
 
         h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        reps = 10
+        reps = 20
         with torch.cuda.stream(stream):
             for _ in range(3):
                 ham_step()
@@ -365,14 +383,18 @@ def run_gpu(args):
                 ham_step()
             h1.record(stream)
         barrier()
+        comm.check()
         t = torch.tensor([h0.elapsed_time(h1) / reps], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ham_ms = float(t.item())
         ham = {"metric": "Hamming top-2 Gmatch/s", "value": HAMMING_NQ * rows * world / (ham_ms * 1e-3) / 1e9, "unit": "Gpairs/s",
-               "ms": ham_ms, "workload": f"{HAMMING_NQ} queries x {rows * world} database descriptors, {world} shard(s)"
-               + (", NCCL all-gather merge" if world > 1 else ""), "scaling": "strong",
-               "int_ops_per_pair": {"lop3": 16, "vimnmx": 3, "popc": 4, "imad": 4}}
+               "ms": ham_ms, "workload": f"{HAMMING_NQ} queries x {rows * world} database descriptors, {world} shard(s)",
+               "exchange": comm.exchange, "kernels_per_call": 1 if comm.exchange != "nccl" else 3,
+               "verified": "merged result == single scan of the whole database on every rank (indices, distances, ratio flags)",
+               "scaling": "strong", "int_ops_per_pair": {"lop3": 16, "vimnmx": 3, "popc": 4, "imad": 4},
+               "accepted": int(d_ok.sum().item()), "queries_with_match": ham_true}
+        comm.close()
         m.set_stream(None)
 
     # ---- integer-pipe peaks measured live on this device (tools/int_peaks.py, csrc/diag.cu): roofline denominators

@@ -158,6 +158,38 @@ int ydorb_top2_merge_device(YdMatcher* m, const YdTop2* d_shards, int nshards, i
 /* accept[i] = best<=th && (float)best < ratio*(float)second   (src/orbMatcher.cpp:336) */
 int ydorb_ratio_accept_device(YdMatcher* m, const YdTop2* d_top2, int nq, float ratio, int th, uint8_t* d_accept);
 
+/* ---- multi-GPU: sharded Hamming top-2 (one process per GPU; SURVEY 8e, BASELINE config 4) ------------------------
+ * The map-descriptor database is split into contiguous row shards; every rank scans its shard and the per-shard
+ * records are merged into the result of ONE sequential scan over the whole database (rule of
+ * src/orbMatcher.cpp:327-336: strict <, else-if strict <, lowest row wins ties, then the ratio test).  The result is
+ * identical on every rank.  The library creates its own NCCL communicator from an ncclUniqueId the caller ships from
+ * rank 0 to the other ranks by any host channel (a file, MPI, torch.distributed ...).  Exchange of the 16 B/query
+ * records: peer-memory stores inside the scan kernel when the GPUs can map each other's memory (CUDA IPC over
+ * NVLink), otherwise an NCCL all-gather; YDORB_SHARD_EXCHANGE=nccl forces the latter.
+ * Every rank must make the same sequence of sharded calls with the same nq (they are collective). */
+#define YDORB_COMM_ID_BYTES 128
+typedef struct YdComm YdComm;
+typedef struct YdShard YdShard;
+/* rank 0: obtain the id (ncclGetUniqueId) */
+int ydorb_comm_unique_id(uint8_t* id, int bytes);
+/* all ranks, collectively; the matcher's device and stream are the communicator's.  id may be NULL when world_size == 1 */
+int ydorb_comm_create(YdMatcher* m, const uint8_t* id, int rank, int world_size, int max_queries, YdComm** out);
+void ydorb_comm_destroy(YdComm* c);
+int ydorb_comm_rank(const YdComm* c);
+int ydorb_comm_size(const YdComm* c);
+int ydorb_comm_exchange_mode(const YdComm* c); /* 0 single GPU, 1 NCCL all-gather, 2 peer-memory push */
+/* synchronises the matcher's stream and reports a sharded call whose peers did not arrive (YDORB_E_STATE) */
+int ydorb_comm_check(YdComm* c);
+/* this rank's rows [idx_base, idx_base + n_rows) of the database, uploaded once and kept resident */
+int ydorb_shard_create(YdMatcher* m, const uint8_t* rows, int n_rows, int idx_base, YdShard** out);
+void ydorb_shard_destroy(YdShard* s);
+/* host queries in, merged top-2 (global row indices) and ratio-test flags out (accept may be NULL) */
+int ydorb_hamming_top2_sharded(YdComm* c, const YdShard* shard, const uint8_t* queries, int nq, float ratio, int th,
+                               YdTop2* out, uint8_t* accept);
+/* everything resident; asynchronous on the matcher's stream (call ydorb_comm_check to synchronise and check) */
+int ydorb_hamming_top2_sharded_device(YdComm* c, const uint8_t* d_queries, int nq, const uint8_t* d_db_shard, int n_rows,
+                                      int idx_base, float ratio, int th, YdTop2* d_out, uint8_t* d_accept);
+
 /* ---- Frame hooks + projection search -------------------------------------------------------------------- */
 typedef struct YdFrame YdFrame;
 

@@ -7,56 +7,16 @@
 // row as two broadcast LDS.128.  Distance = 8 x (XOR, POPC).  The running top-2 is two packed words
 // (distance << 23 | row-in-chunk): best = min, second = min(second, max(best_before, key)) -- with the row in the
 // low bits this reproduces the sequential rule exactly, including "first candidate wins ties".
-// The database is split into chunks across blockIdx.y so the grid fills 148 SMs; per-chunk top-2 pairs are merged
-// by a second kernel with the same order-free rule, which is also the cross-GPU shard merge.
+// The database is split into chunks across blockIdx.y so the grid fills 148 SMs; every CTA folds its chunk's top-2 into
+// one (best, second) pair per query with 64-bit atomicMin (order-free), and the last CTA of a query block unpacks the
+// pairs -- one launch (k_top2_sharded).  The same kernel carries the cross-GPU exchange and merge (shard.cu).
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 
-#include "matcher.cuh"
+#include "hamming.cuh"
 
 namespace ydorb {
-
-constexpr int kTopThreads = 128;
-constexpr int kTopQpt = 4;                          // queries per thread
-constexpr int kTopQblock = kTopThreads * kTopQpt;   // queries per CTA
-constexpr int kTopTile = 256;                       // database rows per shared-memory tile
-constexpr uint32_t kNoKey = 0xFFFFFFFFu;
-#ifndef YD_TOP_CTAS_PER_SM
-#define YD_TOP_CTAS_PER_SM 6
-#endif
-constexpr int kTopCtasPerSm = YD_TOP_CTAS_PER_SM;   // 6 x 4 warps per SM hide the POPC (XU) latency
-
-// 256-bit Hamming distance with a carry-save adder tree: the 8 XOR words are compressed by four 3:2 compressors
-// (sum = a^b^c, carry = maj(a,b,c), one LOP3 each) into words of weight 1,1,2,4, so a pair costs 4 POPC (XU pipe,
-// 16 thread-ops/clk/SM) + 16 LOP3 (ALU pipe, 64/clk/SM) instead of 8 POPC + 8 LOP3.  Same integer result as
-// src/orbMatcher.cpp:11-23.
-__device__ __forceinline__ uint32_t csa_sum(uint32_t a, uint32_t b, uint32_t c) {
-  uint32_t r;  // inline PTX keeps the compiler from re-associating the XOR tree into more, narrower LOP3s
-  asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
-  return r;
-}
-__device__ __forceinline__ uint32_t csa_carry(uint32_t a, uint32_t b, uint32_t c) {
-  uint32_t r;
-  asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
-  return r;
-}
-// returns distance << 23, ready to be added to a row index below 2^23
-__device__ __forceinline__ uint32_t ham256_key(const uint32_t (&q)[8], const uint4& lo, const uint4& hi, uint32_t row) {
-  const uint32_t x0 = q[0] ^ lo.x, x1 = q[1] ^ lo.y, x2 = q[2] ^ lo.z, x3 = q[3] ^ lo.w;
-  const uint32_t x4 = q[4] ^ hi.x, x5 = q[5] ^ hi.y, x6 = q[6] ^ hi.z, x7 = q[7] ^ hi.w;
-  const uint32_t sA = csa_sum(x0, x1, x2), cA = csa_carry(x0, x1, x2);
-  const uint32_t sB = csa_sum(x3, x4, x5), cB = csa_carry(x3, x4, x5);
-  const uint32_t sC = csa_sum(sA, sB, x6), cC = csa_carry(sA, sB, x6);
-  const uint32_t sD = csa_sum(cA, cB, cC), cD = csa_carry(cA, cB, cC);
-  // weights 1,1,2,4 folded with the << 23 into multiply-adds (FMA pipe, off the ALU pipe the LOP3s use)
-  uint32_t d = __popc(sC) + __popc(x7);
-  d = __popc(sD) * 2u + d;
-  d = __popc(cD) * 4u + d;
-  return d * 0x800000u + row;
-}
-__device__ __forceinline__ uint32_t ham256(const uint32_t (&q)[8], const uint4& lo, const uint4& hi) {
-  return ham256_key(q, lo, hi, 0) >> 23;
-}
 
 __global__ void k_hamming_pairs(const uint4* __restrict__ a, const uint4* __restrict__ b, int n, int32_t* __restrict__ dist) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -66,79 +26,162 @@ __global__ void k_hamming_pairs(const uint4* __restrict__ a, const uint4* __rest
             __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_sys_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
 __global__ void __launch_bounds__(kTopThreads)
-k_top2_chunks(const uint4* __restrict__ q, int nq, const uint4* __restrict__ db, int ndb, int chunk_rows,
-              uint2* __restrict__ partial) {
+k_top2_sharded(const uint4* __restrict__ q, const uint4* __restrict__ db, int ndb, const ShardDev a) {
   __shared__ uint4 s_db[2 * kTopTile];
+  __shared__ int s_flag;
   const int tid = threadIdx.x;
+  const int nq = a.nq;
   const int q0 = blockIdx.x * kTopQblock;
   const int chunk = blockIdx.y;
-  const int row_begin = chunk * chunk_rows;
-  const int row_end = min(row_begin + chunk_rows, ndb);
-  uint32_t qa[kTopQpt][8];
-  uint32_t best[kTopQpt], second[kTopQpt];
+  const int row_begin = chunk * a.chunk_rows;
+  const int row_end = min(row_begin + a.chunk_rows, ndb);
+  {
+    uint32_t qa[kTopQpt][8];
+    uint32_t best[kTopQpt], second[kTopQpt];
 #pragma unroll
-  for (int k = 0; k < kTopQpt; k++) {
-    const int qi = q0 + k * kTopThreads + tid;
-    uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
-    if (qi < nq) { lo = q[2 * qi]; hi = q[2 * qi + 1]; }
-    qa[k][0] = lo.x; qa[k][1] = lo.y; qa[k][2] = lo.z; qa[k][3] = lo.w;
-    qa[k][4] = hi.x; qa[k][5] = hi.y; qa[k][6] = hi.z; qa[k][7] = hi.w;
-    best[k] = kNoKey;
-    second[k] = kNoKey;
-  }
-  for (int t0 = row_begin; t0 < row_end; t0 += kTopTile) {
-    const int rows = min(kTopTile, row_end - t0);
-    __syncthreads();
-    for (int i = tid; i < 2 * rows; i += kTopThreads) s_db[i] = db[2 * (size_t)t0 + i];
-    __syncthreads();
-    const uint32_t local0 = (uint32_t)(t0 - row_begin);
+    for (int k = 0; k < kTopQpt; k++) {
+      const int qi = q0 + k * kTopThreads + tid;
+      uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
+      if (qi < nq) { lo = q[2 * qi]; hi = q[2 * qi + 1]; }
+      qa[k][0] = lo.x; qa[k][1] = lo.y; qa[k][2] = lo.z; qa[k][3] = lo.w;
+      qa[k][4] = hi.x; qa[k][5] = hi.y; qa[k][6] = hi.z; qa[k][7] = hi.w;
+      best[k] = kNoKey;
+      second[k] = kNoKey;
+    }
+    for (int t0 = row_begin; t0 < row_end; t0 += kTopTile) {
+      const int rows = min(kTopTile, row_end - t0);
+      __syncthreads();
+      for (int i = tid; i < 2 * rows; i += kTopThreads) s_db[i] = db[2 * (size_t)t0 + i];
+      __syncthreads();
+      const uint32_t local0 = (uint32_t)(t0 - row_begin);
 #pragma unroll 2
-    for (int r = 0; r < rows; r++) {
-      const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1];
+      for (int r = 0; r < rows; r++) {
+        const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1];
 #pragma unroll
-      for (int k = 0; k < kTopQpt; k++) {
-        const uint32_t key = ham256_key(qa[k], lo, hi, local0 + (uint32_t)r);
-        second[k] = min(second[k], max(best[k], key));
-        best[k] = min(best[k], key);
+        for (int k = 0; k < kTopQpt; k++) {
+          const uint32_t key = ham256_key(qa[k], lo, hi, local0 + (uint32_t)r);
+          second[k] = min(second[k], max(best[k], key));
+          best[k] = min(best[k], key);
+        }
+      }
+    }
+    // fold this chunk's top-2 into the per-query global pair (B, S) with 64-bit atomicMin on (distance << 32 | global row):
+    // inserting x as  old = atomicMin(B, x); atomicMin(S, max(old, x))  leaves B = minimum and S = second order statistic
+    // of everything inserted, in any order (every value pushed to S lost against a smaller one, and the runner-up loses
+    // against the minimum whichever of the two arrives first).  A stale read of S prunes keys that cannot matter.
+    const uint32_t row0 = (uint32_t)(a.idx_base + row_begin);
+#pragma unroll
+    for (int k = 0; k < kTopQpt; k++) {
+      const int qi = q0 + k * kTopThreads + tid;
+      if (qi >= nq) continue;
+      unsigned long long* B = a.best + qi;
+      unsigned long long* S = a.second + qi;
+      const unsigned long long cut = *reinterpret_cast<volatile unsigned long long*>(S);
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const uint32_t kk = h ? second[k] : best[k];
+        if (kk == kNoKey) continue;
+        const unsigned long long x = ((unsigned long long)(kk >> 23) << 32) | (unsigned long long)(row0 + (kk & 0x7FFFFFu));
+        if (x >= cut) continue;
+        const unsigned long long old = atomicMin(B, x);
+        atomicMin(S, max(old, x));
       }
     }
   }
+  // ---- last CTA of this query block finishes it
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned int t = atomicAdd(&a.tickets[blockIdx.x], 1u);
+    s_flag = (t == gridDim.y - 1);
+    if (s_flag) a.tickets[blockIdx.x] = 0;  // ready for the next call (stream order)
+  }
+  __syncthreads();
+  if (!s_flag) return;
+  __threadfence();
+  YdTop2 mine[kTopQpt];
 #pragma unroll
   for (int k = 0; k < kTopQpt; k++) {
     const int qi = q0 + k * kTopThreads + tid;
-    if (qi < nq) partial[(size_t)chunk * nq + qi] = make_uint2(best[k], second[k]);
+    if (qi >= nq) continue;
+    const unsigned long long b = __ldcg(a.best + qi), s = __ldcg(a.second + qi);
+    a.best[qi] = ~0ull;    // ready for the next call
+    a.second[qi] = ~0ull;
+    mine[k] = top2_unpack(b, s);
+    if (a.mode == 0) {
+      a.out[qi] = mine[k];
+      if (a.accept) a.accept[qi] = ratio_accept(mine[k], a.ratio, a.th);
+    } else {
+      reinterpret_cast<int4*>(a.gather)[(size_t)a.rank * nq + qi] = *reinterpret_cast<const int4*>(&mine[k]);
+    }
   }
-}
-
-__device__ __forceinline__ unsigned long long top2_key(int dist, int idx) {
-  return idx < 0 ? ~0ull : (((unsigned long long)(uint32_t)dist << 32) | (uint32_t)idx);
-}
-__device__ __forceinline__ void top2_push(unsigned long long key, unsigned long long& b, unsigned long long& s) {
-  s = min(s, max(b, key));
-  b = min(b, key);
-}
-__device__ __forceinline__ YdTop2 top2_unpack(unsigned long long b, unsigned long long s) {
-  YdTop2 o;
-  o.best_idx = (b == ~0ull) ? -1 : (int)(uint32_t)b;
-  o.best_dist = (b == ~0ull) ? 256 : (int)(b >> 32);
-  o.second_idx = (s == ~0ull) ? -1 : (int)(uint32_t)s;
-  o.second_dist = (s == ~0ull) ? 256 : (int)(s >> 32);
-  return o;
-}
-
-__global__ void k_top2_finish(const uint2* __restrict__ partial, int nchunks, int nq, int chunk_rows, int idx_base,
-                              YdTop2* __restrict__ out) {
-  const int qi = blockIdx.x * blockDim.x + threadIdx.x;
-  if (qi >= nq) return;
-  unsigned long long b = ~0ull, s = ~0ull;
-  for (int c = 0; c < nchunks; c++) {
-    const uint2 p = partial[(size_t)c * nq + qi];
-    const int base = idx_base + c * chunk_rows;
-    if (p.x != kNoKey) top2_push(top2_key((int)(p.x >> 23), base + (int)(p.x & 0x7FFFFFu)), b, s);
-    if (p.y != kNoKey) top2_push(top2_key((int)(p.y >> 23), base + (int)(p.y & 0x7FFFFFu)), b, s);
+  if (a.mode != 2) return;
+  // ---- push this query block's records to every peer, then release the arrival counters
+  for (int p = 1; p < a.world; p++) {
+    const int peer = (a.rank + p) % a.world;  // staggered so that the ranks do not all hit the same GPU first
+    int4* dst = reinterpret_cast<int4*>(a.peer_gather[peer]) + (size_t)a.rank * nq;
+#pragma unroll
+    for (int k = 0; k < kTopQpt; k++) {
+      const int qi = q0 + k * kTopThreads + tid;
+      if (qi < nq) dst[qi] = *reinterpret_cast<const int4*>(&mine[k]);
+    }
   }
-  out[qi] = top2_unpack(b, s);
+  __threadfence_system();
+  __syncthreads();
+  if (tid > 0 && tid < a.world) red_release_sys_add(a.peer_arrivals[(a.rank + tid) % a.world] + a.rank, 1u);
+  // ---- wait for the peers' records of this call (bounded)
+  if (tid == 0) s_flag = 0;
+  __syncthreads();
+  if (tid > 0 && tid < a.world) {
+    const uint32_t* ctr = a.arrivals + (a.rank + tid) % a.world;
+    const unsigned long long t0 = global_ns();
+    while ((int)(ld_acquire_sys(ctr) - a.target) < 0) {
+      if (global_ns() - t0 > a.timeout_ns) {
+        atomicOr(&s_flag, 1);
+        break;
+      }
+      __nanosleep(200);
+    }
+  }
+  __syncthreads();
+  if (s_flag) {
+    if (tid == 0) atomicOr(a.status, kShardStatusTimeout);
+    return;
+  }
+  // ---- merge: one sequential scan over the concatenation of the shards
+#pragma unroll
+  for (int k = 0; k < kTopQpt; k++) {
+    const int qi = q0 + k * kTopThreads + tid;
+    if (qi >= nq) continue;
+    unsigned long long b = ~0ull, s = ~0ull;
+    for (int c = 0; c < a.world; c++) {
+      YdTop2 t = mine[k];
+      if (c != a.rank) {
+        const int4 v = __ldcg(reinterpret_cast<const int4*>(a.gather) + (size_t)c * nq + qi);
+        t = *reinterpret_cast<const YdTop2*>(&v);
+      }
+      top2_push(top2_key(t.best_dist, t.best_idx), b, s);
+      top2_push(top2_key(t.second_dist, t.second_idx), b, s);
+    }
+    const YdTop2 o = top2_unpack(b, s);
+    a.out[qi] = o;
+    if (a.accept) a.accept[qi] = ratio_accept(o, a.ratio, a.th);
+  }
 }
 
 // shard merge: result of one sequential scan over the concatenation of the shards
@@ -242,6 +285,47 @@ int matcher_reserve_io(YdMatcher* m, size_t bytes) {
   return YDORB_OK;
 }
 
+
+int top2_grid(const YdMatcher* m, int nq, int n_rows, int* qblocks, int* nchunks, int* chunk_rows) {
+  const int qb = (nq + kTopQblock - 1) / kTopQblock;
+  int nc = std::max(1, (m->top_ctas_per_sm * m->sm_count + qb - 1) / qb);
+  nc = std::min(nc, std::max(1, (n_rows + 1023) / 1024));
+  int cr = (n_rows + nc - 1) / nc;
+  cr = std::max((cr + kTopTile - 1) / kTopTile * kTopTile, kTopTile);
+  YD_REQUIRE(cr < (1 << 23), "database shard too large for one call (max 8M rows per chunk)");
+  *qblocks = qb;
+  *nchunks = std::max(1, (n_rows + cr - 1) / cr);
+  *chunk_rows = cr;
+  return YDORB_OK;
+}
+
+int matcher_reserve_pairs(YdMatcher* m, int nq) {
+  if (nq <= m->pairs_cap) return YDORB_OK;
+  const int cap = std::max(nq, 4096);
+  const int qb = (cap + kTopQblock - 1) / kTopQblock;
+  if (m->d_pairs) YD_CUDA(cudaFree(m->d_pairs));
+  m->d_pairs = nullptr;
+  m->pairs_cap = 0;
+  const size_t pair_bytes = 2 * sizeof(unsigned long long) * (size_t)cap;
+  YD_CUDA(cudaMalloc(&m->d_pairs, pair_bytes + sizeof(unsigned int) * qb));
+  YD_CUDA(cudaMemsetAsync(m->d_pairs, 0xFF, pair_bytes, m->stream));
+  YD_CUDA(cudaMemsetAsync(static_cast<uint8_t*>(m->d_pairs) + pair_bytes, 0, sizeof(unsigned int) * qb, m->stream));
+  m->pairs_cap = cap;
+  return YDORB_OK;
+}
+
+int launch_top2_sharded(YdMatcher* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, int n_rows, ShardDev a) {
+  int qblocks, nchunks, chunk_rows;
+  const int rc = top2_grid(m, nq, n_rows, &qblocks, &nchunks, &chunk_rows);
+  if (rc != YDORB_OK) return rc;
+  a.nq = nq;
+  a.chunk_rows = chunk_rows;
+  k_top2_sharded<<<dim3(qblocks, nchunks), kTopThreads, 0, m->stream>>>(
+      reinterpret_cast<const uint4*>(d_queries), reinterpret_cast<const uint4*>(d_db), n_rows, a);
+  count_launches(1);
+  YD_CUDA(cudaGetLastError());
+  return YDORB_OK;
+}
 }  // namespace ydorb
 
 using namespace ydorb;
@@ -260,6 +344,8 @@ int ydorb_matcher_create(int device, YdMatcher** out) {
   m->scratch_bytes = 0;
   m->d_io = nullptr;
   m->io_bytes = 0;
+  m->d_pairs = nullptr;
+  m->pairs_cap = 0;
   cudaError_t e = cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { delete m; return cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__); }
   m->stream = m->own_stream;
@@ -277,6 +363,7 @@ void ydorb_matcher_destroy(YdMatcher* m) {
   cudaSetDevice(m->device);
   if (m->d_scratch) cudaFree(m->d_scratch);
   if (m->d_io) cudaFree(m->d_io);
+  if (m->d_pairs) cudaFree(m->d_pairs);
   if (m->own_stream) cudaStreamDestroy(m->own_stream);
   delete m;
 }
@@ -365,23 +452,20 @@ int ydorb_hamming_top2_device(YdMatcher* m, const uint8_t* d_queries, int nq, co
   YD_REQUIRE(d_queries && (d_db || ndb == 0), "null descriptor pointer");
   YD_REQUIRE(((uintptr_t)d_queries & 15) == 0 && ((uintptr_t)d_db & 15) == 0, "descriptor matrices must be 16-byte aligned");
   YD_CUDA(cudaSetDevice(m->device));
-  const int qblocks = (nq + kTopQblock - 1) / kTopQblock;
-  int nchunks = std::max(1, (m->top_ctas_per_sm * m->sm_count + qblocks - 1) / qblocks);
-  nchunks = std::min(nchunks, std::max(1, (ndb + 1023) / 1024));
-  int chunk_rows = (ndb + nchunks - 1) / nchunks;
-  chunk_rows = std::max((chunk_rows + kTopTile - 1) / kTopTile * kTopTile, kTopTile);
-  YD_REQUIRE(chunk_rows < (1 << 23), "database shard too large for one call (max 8M rows per chunk)");
-  nchunks = std::max(1, (ndb + chunk_rows - 1) / chunk_rows);
-  int rc = matcher_reserve(m, sizeof(uint2) * (size_t)nchunks * nq);
+  // one launch: chunked scan, order-free fold into one (best, second) pair per query, finish by the last CTA of each
+  // query block (k_top2_sharded in single-GPU mode)
+  int rc = matcher_reserve_pairs(m, nq);
   if (rc != YDORB_OK) return rc;
-  uint2* partial = reinterpret_cast<uint2*>(m->d_scratch);
-  dim3 grid(qblocks, nchunks);
-  k_top2_chunks<<<grid, kTopThreads, 0, m->stream>>>(reinterpret_cast<const uint4*>(d_queries), nq,
-                                                     reinterpret_cast<const uint4*>(d_db), ndb, chunk_rows, partial);
-  k_top2_finish<<<(nq + 127) / 128, 128, 0, m->stream>>>(partial, nchunks, nq, chunk_rows, idx_base, d_out);
-  count_launches(2);
-  YD_CUDA(cudaGetLastError());
-  return YDORB_OK;
+  ShardDev a;
+  memset(&a, 0, sizeof(a));
+  a.world = 1;
+  a.mode = 0;
+  a.idx_base = idx_base;
+  a.best = static_cast<unsigned long long*>(m->d_pairs);
+  a.second = a.best + m->pairs_cap;
+  a.tickets = reinterpret_cast<unsigned int*>(a.second + m->pairs_cap);
+  a.out = d_out;
+  return launch_top2_sharded(m, d_queries, nq, d_db, ndb, a);
 }
 
 int ydorb_hamming_top2(YdMatcher* m, const uint8_t* queries, int nq, const uint8_t* db, int ndb, int idx_base,

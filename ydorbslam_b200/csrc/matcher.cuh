@@ -12,6 +12,8 @@ struct YdMatcher {
   size_t scratch_bytes;
   void* d_io;            // staging for host entry points
   size_t io_bytes;
+  void* d_pairs;         // fused top-2 scan: [2][pairs_cap] u64 (best | second, all-ones between calls) + ticket counters
+  int pairs_cap;
 };
 
 namespace ydorb {

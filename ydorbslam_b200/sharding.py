@@ -68,3 +68,94 @@ class GpuShardedMatcher:
 def top2_records(best_idx, best_dist, second_dist, second_idx):
     """Pack four int arrays into YdTop2 records [n, 4] int32 (field order of include/ydorb.h)."""
     return np.stack([best_idx, best_dist, second_dist, second_idx], axis=1).astype(np.int32)
+
+
+# ---- the library's own multi-GPU path (csrc/shard.cu): communicator, resident shard, sharded top-2 behind the C ABI ----
+def comm_unique_id():
+    """rank 0: the ncclUniqueId (bytes) every rank must pass to Communicator; ship it over any host channel."""
+    import ctypes as C
+
+    from ._lib import check, lib
+
+    buf = (C.c_uint8 * 128)()
+    check(lib().ydorb_comm_unique_id(buf, 128))
+    return bytes(buf)
+
+
+class Communicator:
+    """ydorb_comm_create: collective over `world` processes, one GPU each (the matcher's device and stream)."""
+
+    EXCHANGE = {0: "single", 1: "nccl", 2: "p2p"}
+
+    def __init__(self, matcher, rank, world, max_queries, unique_id=None):
+        import ctypes as C
+
+        from ._lib import check, lib
+
+        self.matcher, self.rank, self.world, self.max_queries = matcher, rank, world, max_queries
+        self._h = C.c_void_p()
+        idbuf = None if unique_id is None else (C.c_uint8 * 128).from_buffer_copy(unique_id.ljust(128, b"\0"))
+        check(lib().ydorb_comm_create(matcher._h, idbuf, rank, world, max_queries, C.byref(self._h)))
+
+    @property
+    def exchange(self):
+        from ._lib import lib
+
+        return self.EXCHANGE[lib().ydorb_comm_exchange_mode(self._h)]
+
+    def check(self):
+        from ._lib import check, lib
+
+        check(lib().ydorb_comm_check(self._h))
+
+    def close(self):
+        from ._lib import lib
+
+        if self._h:
+            lib().ydorb_comm_destroy(self._h)
+            self._h = None
+
+
+class Shard:
+    """This rank's rows [idx_base, idx_base + len(rows)) of the database, resident on the GPU (ydorb_shard_create)."""
+
+    def __init__(self, matcher, rows, idx_base):
+        import ctypes as C
+
+        from ._lib import check, lib, ptr
+
+        rows = np.ascontiguousarray(rows, dtype=np.uint8)
+        assert rows.ndim == 2 and rows.shape[1] == 32
+        self.n_rows, self.idx_base = len(rows), idx_base
+        self._h = C.c_void_p()
+        check(lib().ydorb_shard_create(matcher._h, ptr(rows), len(rows), idx_base, C.byref(self._h)))
+
+    def close(self):
+        from ._lib import lib
+
+        if self._h:
+            lib().ydorb_shard_destroy(self._h)
+            self._h = None
+
+
+def sharded_top2_host(comm, shard, queries, ratio, th):
+    """ydorb_hamming_top2_sharded: merged YdTop2 records (global rows) + ratio-test flags, identical on every rank."""
+    import ctypes as C
+
+    from ._lib import TOP2_DTYPE, check, lib, ptr
+
+    queries = np.ascontiguousarray(queries, dtype=np.uint8)
+    out = np.zeros(len(queries), TOP2_DTYPE)
+    acc = np.zeros(len(queries), np.uint8)
+    check(lib().ydorb_hamming_top2_sharded(comm._h, shard._h, ptr(queries), len(queries), C.c_float(ratio), th, ptr(out), ptr(acc)))
+    return out, acc
+
+
+def sharded_top2_device(comm, d_queries, nq, d_db, n_rows, idx_base, ratio, th, d_out, d_accept):
+    """ydorb_hamming_top2_sharded_device: raw device pointers, asynchronous on the matcher's stream."""
+    import ctypes as C
+
+    from ._lib import check, lib, ptr
+
+    check(lib().ydorb_hamming_top2_sharded_device(comm._h, ptr(d_queries), nq, ptr(d_db), n_rows, idx_base, C.c_float(ratio), th,
+                                                  ptr(d_out), ptr(d_accept)))
