@@ -11,6 +11,14 @@ pytestmark = pytest.mark.gpu
 CASES = ["image0", "synth640", "sparse640", "synth1241", "tiny97"]
 
 
+@pytest.fixture(autouse=True, params=["cells", "blocks"])
+def fast_kernel(request, monkeypatch):
+    """Every test of this module runs under both FAST kernels: warp-per-cell (fast.cu, what small launches take) and
+    CTA-per-cell-block with TMA staging (fast2.cu, what batches take).  libydorb reads the variable on every call."""
+    monkeypatch.setenv("YDORB_FAST_KERNEL", request.param)
+    return request.param
+
+
 def _check_against(ex, img, kps, desc, gk, gd):
     assert len(kps) == len(gk)
     for f in ("x", "y", "size", "response", "octave", "class_id"):

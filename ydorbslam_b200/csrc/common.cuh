@@ -1,5 +1,6 @@
 // Internal definitions shared by the libydorb.so translation units (sm_100a only).
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -125,6 +126,14 @@ struct FrameGeomDev {
   LevelGeom lv[kMaxLevels];
 };
 
+// fast2.cu: a block of up to 4 x 2 FAST cells handled by one CTA
+struct FastBlock {
+  int level;
+  int x0, y0, w, h;          // union of the valid cells' ROIs (level coordinates); w = h = 0: no valid cell
+  int cell0, ncx, ncy, cols; // first grid cell (index in the frame's cell table), cells covered, the level's cell_cols
+  int pad[3];
+};
+
 // device pointer to the padded level origin (pixel (0,0) of the level, pad readable around it)
 __host__ __device__ inline int64_t level_origin(const LevelGeom& g) {
   return g.offset + (int64_t)kPad * g.stride + kPad;
@@ -162,6 +171,10 @@ struct YdExtractor {
   uint8_t* d_pyr;        // [max_batch][cap_pyr_bytes]
   int* d_tab_ofs;        // resize source offsets
   short* d_tab_a;        // resize weights (a0,a1 interleaved)
+  ydorb::FastBlock* d_fast_blocks;  // [cap_cells] cell blocks of the current geometry (fast2.cu)
+  int n_fast_blocks, fb_max_w, fb_max_h;
+  uint8_t* pyr_base;     // d_pyr of the handle itself (frame_view() shifts d_pyr; TMA coordinates count from here)
+  CUtensorMap tmap_level[ydorb::kMaxLevels];  // u8 [frame][row][byte] per pyramid level, box = FAST block tile
   int4* d_cells;         // per-cell ROI {x0,y0,x1,y1} (level coords), [cap_cells]
   int* d_cell_count;     // [max_batch][cap_cells]
   int* d_cell_start;     // [max_batch][cap_cells]

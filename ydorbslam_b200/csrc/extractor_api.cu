@@ -9,6 +9,7 @@
 #include <cstring>
 
 #include "kernels.cuh"
+#include "tma.cuh"
 
 namespace ydorb {
 
@@ -189,6 +190,24 @@ static int set_size(YdExtractor* ex, int w, int h) {
   }
   if (!hg.cells.empty())
     YD_CUDA(cudaMemcpyAsync(ex->d_cells, hg.cells.data(), hg.cells.size() * sizeof(int4), cudaMemcpyHostToDevice, ex->stream));
+  // fast2.cu: cell blocks and one tensor map per level whose box is the largest block's tile
+  std::vector<FastBlock> blocks;
+  rc = fast2_build_blocks(hg.g, hg.cells, &blocks, &ex->fb_max_w, &ex->fb_max_h);
+  if (rc != YDORB_OK) return rc;
+  ex->n_fast_blocks = (int)blocks.size();
+  if (!blocks.empty())
+    YD_CUDA(cudaMemcpyAsync(ex->d_fast_blocks, blocks.data(), blocks.size() * sizeof(FastBlock), cudaMemcpyHostToDevice, ex->stream));
+  {
+    int box_w = 0, box_h = 0;
+    fast2_box(ex->fb_max_w, ex->fb_max_h, &box_w, &box_h);
+    for (int l = 0; l < hg.g.n_levels; l++) {
+      const LevelGeom& lv = hg.g.lv[l];
+      rc = tma_encode_u8_3d(&ex->tmap_level[l], ex->pyr_base + lv.offset, (uint64_t)lv.stride, (uint64_t)(lv.h + 2 * kPad),
+                            (uint64_t)ex->max_batch, (uint64_t)lv.stride, (uint64_t)hg.g.pyr_bytes, (uint32_t)box_w,
+                            (uint32_t)box_h);
+      if (rc != YDORB_OK) return rc;
+    }
+  }
   YD_CUDA(cudaStreamSynchronize(ex->stream));  // host vectors go out of scope
   ex->cur_w = w;
   ex->cur_h = h;
@@ -349,6 +368,7 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
   alloc((void**)&ex->d_tab_ofs, sizeof(int) * ex->cap_tab);
   alloc((void**)&ex->d_tab_a, sizeof(short) * 2 * ex->cap_tab);
   alloc((void**)&ex->d_cells, sizeof(int4) * ex->cap_cells);
+  alloc((void**)&ex->d_fast_blocks, sizeof(FastBlock) * ex->cap_cells);
   alloc((void**)&ex->d_cell_count, sizeof(int) * B * ex->cap_cells);
   alloc((void**)&ex->d_cell_start, sizeof(int) * B * ex->cap_cells);
   alloc((void**)&ex->d_cell_rank, sizeof(int) * B * (ex->cap_cells + 1));
@@ -371,6 +391,9 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
   alloc((void**)&ex->d_desc, 32 * B * nq);
   alloc((void**)&ex->d_nout, sizeof(int32_t) * B);
   if (e == cudaSuccess) e = cudaMemset(ex->d_status, 0, sizeof(int));
+  // the memsets above ran on the legacy stream; every stream of the handle is non-blocking, so order them here
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  ex->pyr_base = ex->d_pyr;
   if (e != cudaSuccess) {
     int r = cuda_fail(e, "extractor allocation", __FILE__, __LINE__);
     ydorb_extractor_destroy(ex);
@@ -384,7 +407,7 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
 void ydorb_extractor_destroy(YdExtractor* ex) {
   if (!ex) return;
   cudaSetDevice(ex->device);
-  void* ptrs[] = {ex->d_geom, ex->d_pyr, ex->d_tab_ofs, ex->d_tab_a, ex->d_cells, ex->d_cell_count, ex->d_cell_start,
+  void* ptrs[] = {ex->d_geom, ex->d_pyr, ex->d_tab_ofs, ex->d_tab_a, ex->d_cells, ex->d_fast_blocks, ex->d_cell_count, ex->d_cell_start,
                   ex->d_cell_rank, ex->d_raw, ex->d_raw_counter, ex->d_qt_keys[0], ex->d_qt_keys[1], ex->d_qt_keys[2],
                   ex->d_qt_vals[0], ex->d_qt_vals[1], ex->d_qt_vals[2], ex->d_qt_bitmap, ex->d_qt_fold, ex->d_qt_meta, ex->d_level_ncand, ex->d_sel, ex->d_sel_n,
                   ex->d_status, ex->d_images, ex->d_kps, ex->d_desc, ex->d_nout};

@@ -19,91 +19,12 @@
 //   nms     packed: the 8-neighbour maximum of a pair is 4 funnel shifts + 4 VIMNMX; keep <=> centre > neighbours.
 // This is integer-pipe work, not HBM-bound: the level is read from HBM once.
 #include <cstdlib>
-#include "kernels.cuh"
+#include "fast_common.cuh"
 
 namespace ydorb {
 
 constexpr int kWarpsPerCta = 4;
 constexpr int kFastQueue = 64;  // compaction queue entries per warp
-
-// circular 9-arc extremum: r[k] = op3 over D[k..k+8]
-#define YD_ARC_TREE(OP3, D, OUT)                                                   \
-  {                                                                                \
-    uint32_t w3[16];                                                               \
-    _Pragma("unroll") for (int k = 0; k < 16; k++) w3[k] = OP3(D[k], D[(k + 1) & 15], D[(k + 2) & 15]); \
-    _Pragma("unroll") for (int k = 0; k < 16; k++) OUT[k] = OP3(w3[k], w3[(k + 3) & 15], w3[(k + 6) & 15]); \
-  }
-
-__device__ __forceinline__ uint32_t max16_s16x2(const uint32_t (&v)[16]) {
-  uint32_t a = __vimax3_s16x2(v[0], v[1], v[2]), b = __vimax3_s16x2(v[3], v[4], v[5]);
-  uint32_t c = __vimax3_s16x2(v[6], v[7], v[8]), d = __vimax3_s16x2(v[9], v[10], v[11]);
-  uint32_t e = __vimax3_s16x2(v[12], v[13], v[14]);
-  a = __vimax3_s16x2(a, b, c);
-  d = __vimax3_s16x2(d, e, v[15]);
-  return __vmaxs2(a, d);
-}
-__device__ __forceinline__ uint32_t min16_s16x2(const uint32_t (&v)[16]) {
-  uint32_t a = __vimin3_s16x2(v[0], v[1], v[2]), b = __vimin3_s16x2(v[3], v[4], v[5]);
-  uint32_t c = __vimin3_s16x2(v[6], v[7], v[8]), d = __vimin3_s16x2(v[9], v[10], v[11]);
-  uint32_t e = __vimin3_s16x2(v[12], v[13], v[14]);
-  a = __vimin3_s16x2(a, b, c);
-  d = __vimin3_s16x2(d, e, v[15]);
-  return __vmins2(a, d);
-}
-
-__device__ __forceinline__ uint32_t fsr16(uint32_t lo, uint32_t hi) { return __funnelshift_r(lo, hi, 16); }
-
-// Word j of a tile row holds tile columns (2j, 2j+1).  For the pixel pair at `row` (= &tile[r][j]): an even dx reads
-// word j + dx/2, an odd dx the funnel shift of words j+(dx-1)/2 and j+(dx+1)/2.
-
-// Cheap necessary condition for "one of the two pixels is a corner at threshold t" (see header).
-// k1 = (0x7FFF - (t+256)) * 0x10001,  k2 = (0x8000 + 255 - t) * 0x10001.
-__device__ __forceinline__ bool fast_quick_pair(const uint32_t* __restrict__ row, int wpr, uint32_t k1, uint32_t k2) {
-  const uint32_t cb = row[0] + 0x01000100u;  // centre + 256 in both halves
-  const uint32_t d0 = cb - row[3 * wpr], d8 = cb - row[-3 * wpr];                      // (0,3) (0,-3)
-  const uint32_t d4 = cb - fsr16(row[1], row[2]), d12 = cb - fsr16(row[-2], row[-1]);  // (3,0) (-3,0)
-  const uint32_t d2 = cb - row[2 * wpr + 1], d10 = cb - row[-2 * wpr - 1];             // (2,2) (-2,-2)
-  const uint32_t d6 = cb - row[-2 * wpr + 1], d14 = cb - row[2 * wpr - 1];             // (2,-2) (-2,2)
-  const uint32_t a = __vimin3_s16x2(__vmaxs2(d0, d8), __vmaxs2(d4, d12), __vmins2(__vmaxs2(d2, d10), __vmaxs2(d6, d14)));
-  const uint32_t b = __vimax3_s16x2(__vmins2(d0, d8), __vmins2(d4, d12), __vmaxs2(__vmins2(d2, d10), __vmins2(d6, d14)));
-  // half of a > t+256  <=> bit 15 of (a + k1);  half of b < 256-t  <=> bit 15 of (k2 - b); no carries between halves
-  return (((a + k1) | (k2 - b)) & 0x80008000u) != 0u;
-}
-
-// Exact FAST-9/16 score of both pixels of the pair, returned biased: each half = m + 256, m in [-255, 255].
-__device__ __forceinline__ uint32_t fast_score_pair(const uint32_t* __restrict__ row, int wpr) {
-  uint32_t P[16];
-  {
-    const uint32_t* r = row + 3 * wpr;  // dy = +3: k0 (0,3) k1 (1,3) k15 (-1,3)
-    const uint32_t a = r[-1], b = r[0], c = r[1];
-    P[0] = b; P[1] = fsr16(b, c); P[15] = fsr16(a, b);
-  }
-  {
-    const uint32_t* r = row - 3 * wpr;  // dy = -3: k8 (0,-3) k7 (1,-3) k9 (-1,-3)
-    const uint32_t a = r[-1], b = r[0], c = r[1];
-    P[8] = b; P[7] = fsr16(b, c); P[9] = fsr16(a, b);
-  }
-  P[2] = row[2 * wpr + 1];    // (2,2)
-  P[14] = row[2 * wpr - 1];   // (-2,2)
-  P[6] = row[-2 * wpr + 1];   // (2,-2)
-  P[10] = row[-2 * wpr - 1];  // (-2,-2)
-  P[3] = fsr16(row[wpr + 1], row[wpr + 2]);      // (3,1)
-  P[13] = fsr16(row[wpr - 2], row[wpr - 1]);     // (-3,1)
-  P[5] = fsr16(row[-wpr + 1], row[-wpr + 2]);    // (3,-1)
-  P[11] = fsr16(row[-wpr - 2], row[-wpr - 1]);   // (-3,-1)
-  P[4] = fsr16(row[1], row[2]);                  // (3,0)
-  P[12] = fsr16(row[-2], row[-1]);               // (-3,0)
-  const uint32_t cb = row[0] + 0x01000100u;      // centre + 256 in both halves
-  uint32_t D[16];
-#pragma unroll
-  for (int k = 0; k < 16; k++) D[k] = cb - P[k];  // halves in [1, 511]: no borrow between halves
-  uint32_t lo9[16], hi9[16];
-  YD_ARC_TREE(__vimin3_s16x2, D, lo9)
-  YD_ARC_TREE(__vimax3_s16x2, D, hi9)
-  const uint32_t dark = max16_s16x2(lo9);    // max over arcs of min d (+256)
-  const uint32_t bright = min16_s16x2(hi9);  // min over arcs of max d (+256)
-  return __vmaxs2(dark, 0x02000200u - bright);  // halves of (512 - bright) in [1, 511]: no borrow
-}
 
 struct FastSmemLayout {
   int wpr;          // pair words per tile row (even)
@@ -243,7 +164,6 @@ __device__ void fast_cell_compute(const FastCell& fc, int frame, int lane, int i
   {
     // ---- reject + exact score
     const uint32_t k1 = (uint32_t)(0x7FFF - (low_th + 256)) * 0x10001u;
-    const uint32_t k2 = (uint32_t)(0x8000 + 255 - low_th) * 0x10001u;
     const uint32_t kc = (uint32_t)(256 + low_th) * 0x10001u;
     auto score_batch = [&](int nvalid) {
       uint32_t s = 0;
@@ -266,7 +186,7 @@ __device__ void fast_cell_compute(const FastCell& fc, int frame, int lane, int i
     int r = r_first, jj = j_first;
     for (int base = 0; base < npairs; base += 32) {
       bool pass = false;
-      if (base + lane < npairs) pass = fast_quick_pair(tile + r * wpr + j0 + jj, wpr, k1, k2);
+      if (base + lane < npairs) pass = fast_quick_pair(tile + r * wpr + j0 + jj, wpr, k1);
       const uint32_t bal = __ballot_sync(0xffffffffu, pass);
       if (pass) queue[qn + __popc(bal & lt_mask)] = (uint16_t)((r << 8) | (j0 + jj));
       qn += __popc(bal);
@@ -404,6 +324,17 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
 
 int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s) {
   YD_CUDA(cudaMemsetAsync(ex->d_raw_counter, 0, sizeof(int) * batch, s));
+  // launches that fill the GPU with 8-warp CTAs take the CTA-per-cell-block kernel (fast2.cu); a single frame's ~100
+  // blocks would leave SMs idle, the warp-per-cell kernel below spreads its ~800 cells over all of them.
+  // YDORB_FAST_KERNEL=cells|blocks forces one of them (tests run both and compare).
+  {
+    const char* force = getenv("YDORB_FAST_KERNEL");  // read per call: tests flip it in-process
+    static const int min_ctas = getenv("YDORB_FAST_BLOCKS_MIN_CTAS") ? atoi(getenv("YDORB_FAST_BLOCKS_MIN_CTAS")) : 592;
+    bool blocks = (long long)ex->n_fast_blocks * batch >= min_ctas;
+    if (force && force[0] == 'c') blocks = false;
+    if (force && force[0] == 'b') blocks = true;
+    if (blocks && ex->n_fast_blocks > 0) return launch_fast_blocks(ex, batch, s);
+  }
   const int ini = ex->params.ini_th_fast;
   const int mn = ex->params.reference_min_th_quirk ? ini : ex->params.min_th_fast;
   const FastSmemLayout L = fast_layout(ex->max_cell_w, ex->max_cell_h);

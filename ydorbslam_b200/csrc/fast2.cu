@@ -1,0 +1,420 @@
+// E3  per-cell cv::FAST(TYPE_9_16, nonmax=true) with the iniThFAST -> minThFAST fallback, CTA-per-block-of-cells form
+//     (OrbExtractor::computeKeyPointsPyramid, src/orbExtractor.cpp:562-593; OpenCV model: SURVEY Appendix A3).
+//
+// The reference's cells overlap by 6 px only in what they READ; the pixels they TEST tile the level exactly
+// (cell j tests [iniX_j + 3, iniX_j + wCell + 3)).  The FAST score of a pixel does not depend on the cell it is tested
+// in -- only non-max suppression (a cv::Mat ROI is a standalone image: neighbours outside the cell count as 0), the
+// empty-cell threshold fallback and the order of the candidate list are per cell.  So a CTA owns a block of up to
+// 4 x 2 cells and works in dense phases over the whole block:
+//   stage    one TMA box load (cp.async.bulk.tensor.3d) of the block's ROI (the box starts on a 16-byte boundary left
+//            of the ROI: TMA needs that); bytes -> s16x2 pixel-pair plane, shifted so that word j of a row holds ROI
+//            columns (2j - 1, 2j): the first tested column (3) is then the low half of word 2 and a row of up to
+//            128 tested pixels is exactly 64 fully tested pairs;
+//   reject   a warp per row, a thread per two adjacent pairs (one LDS.64 feeds both): antipodal necessary condition
+//            (fast_common.cuh); survivors go to one CTA-wide queue with a warp-aggregated shared-memory atomic;
+//   score    exact branch-free score of the queued pairs on full warps -> score plane, max(m - low_th, 0) per half;
+//   nms      queued pairs with a non-zero score: 8-neighbour maximum with the neighbours across a cell seam masked
+//            to 0 (per-column / per-row seam masks); survivors set their bit in a per-row keep bitmap;
+//   cells    warp per cell, lane per row: popcount of the row's keep bits inside the cell, warp scan -> row offsets;
+//            an empty cell re-runs NMS at minThFAST (:582-585); the cell reserves a slice of the frame's candidate
+//            buffer and every lane walks its row's bits, which is the reference's row-major order.
+// Results are bit-identical to fast.cu's warp-per-cell kernel (tests run both); that kernel remains the choice for
+// launches too small to fill the GPU with 8-warp CTAs (single frames).
+#include <algorithm>
+#include <cstdlib>
+
+#include "fast_common.cuh"
+#include "tma.cuh"
+
+namespace ydorb {
+
+constexpr int kF2Threads = 256;
+constexpr int kF2Warps = kF2Threads / 32;
+constexpr int kF2MaxW = 134, kF2MaxH = 70;  // largest block ROI: 4 cells of 32 + 6, 2 cells of 32 + 6
+constexpr int kF2BoxW = 160, kF2BoxH = 70;  // TMA box: up to 15 + 1 bytes left of the ROI, one word of look-ahead
+constexpr int kF2Wpr = 68;                  // pair words per plane row: word j = ROI columns (2j - 1, 2j), j <= 67
+constexpr int kF2KeepWords = 5;             // keep bitmap words per row (tile columns 0..159)
+constexpr int kF2QueueCap = 64 * 64;        // tested pairs of the largest block
+constexpr int kF2MaxCells = 8;
+
+// shared memory map (bytes)
+constexpr int kF2OffTab = 128;                                         // cmL[68] cmR[68] rmU[70] rmD[70]
+constexpr int kF2OffKeep = kF2OffTab + 4 * (2 * kF2Wpr + 2 * kF2MaxH); // keep bitmap [70][5]
+constexpr int kF2OffRowBase = (kF2OffKeep + 4 * kF2MaxH * kF2KeepWords + 15) & ~15;  // u16 [8][64]
+constexpr int kF2OffQueue = kF2OffRowBase + 2 * kF2MaxCells * 64;      // u16 [4096]
+constexpr int kF2OffPair = (kF2OffQueue + 2 * kF2QueueCap + 127) & ~127;
+constexpr int kF2PlaneBytes = 4 * kF2Wpr * kF2MaxH;
+constexpr int kF2OffScore = (kF2OffPair + kF2PlaneBytes + 127) & ~127;  // the TMA byte tile lands here first
+constexpr int kF2SmemBytes = kF2OffScore + kF2PlaneBytes;
+static_assert(kF2BoxW * kF2BoxH <= kF2PlaneBytes, "the byte tile aliases the score plane");
+
+struct Fast2Maps {
+  CUtensorMap lv[kMaxLevels];
+};
+
+// reject test of the two adjacent pairs at words j (even) and j + 1 of row `row` (= &pair[r][j])
+__device__ __forceinline__ void fast2_quick2(const uint32_t* __restrict__ row, uint32_t k1, bool& passA, bool& passB) {
+  constexpr int S = kF2Wpr;
+  const uint2 u3 = *reinterpret_cast<const uint2*>(row + 3 * S), d3 = *reinterpret_cast<const uint2*>(row - 3 * S);
+  const uint2 u2 = *reinterpret_cast<const uint2*>(row + 2 * S), d2 = *reinterpret_cast<const uint2*>(row - 2 * S);
+  const uint32_t u2l = row[2 * S - 1], u2r = row[2 * S + 2], d2l = row[-2 * S - 1], d2r = row[-2 * S + 2];
+  const uint2 c0 = *reinterpret_cast<const uint2*>(row - 2), c1 = *reinterpret_cast<const uint2*>(row),
+              c2 = *reinterpret_cast<const uint2*>(row + 2);
+  {
+    // pair A at word j: (0,3) (0,-3) | (3,0) (-3,0) | (2,2) (-2,-2) | (2,-2) (-2,2)
+    const uint32_t cb = c1.x + 0x01000100u;
+    const uint32_t p0 = u3.x, p8 = d3.x, p4 = fsr16(c1.y, c2.x), p12 = fsr16(c0.x, c0.y);
+    const uint32_t p2 = u2.y, p10 = d2l, p6 = d2.y, p14 = u2l;
+    const uint32_t hi = __vimax3_s16x2(__vmins2(p0, p8), __vmins2(p4, p12), __vmaxs2(__vmins2(p2, p10), __vmins2(p6, p14)));
+    const uint32_t lo = __vimin3_s16x2(__vmaxs2(p0, p8), __vmaxs2(p4, p12), __vmins2(__vmaxs2(p2, p10), __vmaxs2(p6, p14)));
+    passA = ((((cb - hi) + k1) | ((lo + 0x02000200u - cb) + k1)) & 0x80008000u) != 0u;
+  }
+  {
+    // pair B at word j + 1
+    const uint32_t cb = c1.y + 0x01000100u;
+    const uint32_t p0 = u3.y, p8 = d3.y, p4 = fsr16(c2.x, c2.y), p12 = fsr16(c0.y, c1.x);
+    const uint32_t p2 = u2r, p10 = d2.x, p6 = d2r, p14 = u2.x;
+    const uint32_t hi = __vimax3_s16x2(__vmins2(p0, p8), __vmins2(p4, p12), __vmaxs2(__vmins2(p2, p10), __vmins2(p6, p14)));
+    const uint32_t lo = __vimin3_s16x2(__vmaxs2(p0, p8), __vmaxs2(p4, p12), __vmins2(__vmaxs2(p2, p10), __vmaxs2(p6, p14)));
+    passB = ((((cb - hi) + k1) | ((lo + 0x02000200u - cb) + k1)) & 0x80008000u) != 0u;
+  }
+}
+
+// 8-neighbour maximum of the pair at p inside its cell, thresholded, and the keep flags (bit 15: low half survives,
+// bit 31: high half).  c = the pair's own thresholded score (non-zero).
+__device__ __forceinline__ uint32_t fast2_nms_flags(const uint32_t* __restrict__ p, uint32_t c, uint32_t kd, uint32_t mL,
+                                                    uint32_t mR, uint32_t mU, uint32_t mD) {
+  constexpr int S = kF2Wpr;
+  const uint32_t cl = p[-1], c0 = p[0], cr = p[1];
+  const uint32_t ul = p[-S - 1], um = p[-S], ur = p[-S + 1];
+  const uint32_t dl = p[S - 1], dm = p[S], dr = p[S + 1];
+  // left-shifted words hold columns (x-1, x) of the pair (x, x+1), right-shifted (x+1, x+2): the left / right
+  // neighbours of both halves
+  const uint32_t L = __vimax3_s16x2(fsr16(ul, um) & mU, fsr16(cl, c0), fsr16(dl, dm) & mD) & mL;
+  const uint32_t R = __vimax3_s16x2(fsr16(um, ur) & mU, fsr16(c0, cr), fsr16(dm, dr) & mD) & mR;
+  uint32_t n = __vimax3_s16x2(L, R, __vmaxs2(um & mU, dm & mD));
+  n = __vmaxs2(n, kd) - kd;
+  uint32_t flags = (c + 0x7FFF7FFFu - n) & 0x80008000u;  // half of c > half of n (all values in [0, 255])
+  if ((c & 0xFFFFu) == 0u) flags &= 0x80000000u;         // a zero half is not a corner at this threshold
+  if ((c >> 16) == 0u) flags &= 0x00008000u;
+  return flags;
+}
+
+// bits [xa, xb) of a keep-bitmap row
+__device__ __forceinline__ int fast2_row_count(const uint32_t* __restrict__ krow, int xa, int xb) {
+  int n = 0;
+  for (int k = xa >> 5; k <= (xb - 1) >> 5; k++) {
+    uint32_t m = krow[k];
+    if (k == (xa >> 5)) m &= 0xFFFFFFFFu << (xa & 31);
+    if (k == ((xb - 1) >> 5) && (xb & 31)) m &= (1u << (xb & 31)) - 1u;
+    n += __popc(m);
+  }
+  return n;
+}
+
+__global__ void __launch_bounds__(kF2Threads, 4)
+k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
+              const FastBlock* __restrict__ blocks, int frame0, int ini_th, int min_th, uint32_t* __restrict__ raw,
+              int* __restrict__ raw_counter, int* __restrict__ cell_count, int* __restrict__ cell_start,
+              int* __restrict__ status) {
+  pdl_wait();
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
+  int* s_qn = reinterpret_cast<int*>(smem + 8);
+  uint32_t* cmL = reinterpret_cast<uint32_t*>(smem + kF2OffTab);  // [68] seam masks of the left / right neighbours
+  uint32_t* cmR = cmL + kF2Wpr;
+  uint32_t* rmU = cmR + kF2Wpr;                                   // [70] row above / below in the same cell
+  uint32_t* rmD = rmU + kF2MaxH;
+  uint32_t* keep = reinterpret_cast<uint32_t*>(smem + kF2OffKeep);       // [70][5] bit x of row r: pixel survives NMS
+  uint16_t* rowbase = reinterpret_cast<uint16_t*>(smem + kF2OffRowBase);  // [8][64] survivors of the cell above row
+  uint16_t* queue = reinterpret_cast<uint16_t*>(smem + kF2OffQueue);
+  uint32_t* pair = reinterpret_cast<uint32_t*>(smem + kF2OffPair);        // [70][68]
+  uint32_t* score = reinterpret_cast<uint32_t*>(smem + kF2OffScore);      // [70][68]
+  const uint32_t* tile8 = reinterpret_cast<const uint32_t*>(smem + kF2OffScore);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const int frame = blockIdx.y;
+  const FastBlock b = blocks[blockIdx.x];
+  constexpr int S = kF2Wpr;
+  const int low_th = min(max(min(ini_th, min_th), 0), 255);
+  const int W = b.w, H = b.h;
+
+  if (W > 0) {
+    // the box starts on the 16-byte boundary at or left of ROI column -1 (plane word j = columns 2j - 1, 2j)
+    const int bx = kPad + b.x0 - 1, box_x = bx & ~15, a = bx & 15;
+    if (tid == 0) {
+      mbar_init(bar, 1);
+      *s_qn = 0;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      mbar_expect_tx(bar, (uint32_t)(kF2BoxW * kF2BoxH));
+      tma_load_3d(smem + kF2OffScore, &maps.lv[b.level], bar, box_x, kPad + b.y0, frame0 + frame);
+    }
+    // ---- while the box is in flight: keep bitmap := 0, seam masks
+    {
+      for (int i = tid; i < kF2MaxH * kF2KeepWords; i += kF2Threads) keep[i] = 0u;
+      const int cw = g->lv[b.level].cell_w, ch = g->lv[b.level].cell_h;
+      // first(x): tile column x is the first tested column of a cell (cells test [k * cw + 3, (k + 1) * cw + 3))
+      auto first = [](int x, int pitch) { return x >= 3 && (x - 3) % pitch == 0; };
+      if (tid < S) {
+        const int x = 2 * tid;  // word tid = columns (x - 1, x)
+        const bool fl = first(x - 1, cw), fh = first(x, cw), fn = first(x + 1, cw);
+        cmL[tid] = (fl ? 0u : 0x0000FFFFu) | (fh ? 0u : 0xFFFF0000u);
+        cmR[tid] = (fh ? 0u : 0x0000FFFFu) | (fn ? 0u : 0xFFFF0000u);
+      } else if (tid >= 128 && tid < 128 + kF2MaxH) {
+        const int r = tid - 128;
+        rmU[r] = first(r, ch) ? 0u : 0xFFFFFFFFu;
+        rmD[r] = first(r + 1, ch) ? 0u : 0xFFFFFFFFu;
+      }
+    }
+    mbar_wait(bar, 0);
+    // ---- bytes -> pixel pairs: tile bytes a + 4w .. a + 4w + 3 of row r = columns 4w - 1 .. 4w + 2 -> words 2w, 2w + 1
+    // words needed: 0 .. j1 + 2 (the reject / score of the last tested pair reads two words to its right)
+    const int c_hi = W - 4;                // last tested column
+    const int j1 = (c_hi + 1) >> 1;        // its word
+    {
+      const int k0 = a >> 2, ash = 8 * (a & 3);
+      const int tw4 = kF2BoxW / 4, nw4 = ((j1 + 2) >> 1) + 1, total = nw4 * H;
+      const int sr = kF2Threads / nw4, sw = kF2Threads - sr * nw4;
+      int r = tid / nw4, w = tid - r * nw4;
+      for (int i = tid; i < total; i += kF2Threads) {
+        const uint32_t* t = tile8 + r * tw4 + k0 + w;
+        const uint32_t v = __funnelshift_r(t[0], t[1], ash);
+        *reinterpret_cast<uint2*>(pair + r * S + 2 * w) = make_uint2(__byte_perm(v, 0, 0x4140), __byte_perm(v, 0, 0x4342));
+        r += sr;
+        w += sw;
+        if (w >= nw4) { w -= nw4; r++; }
+      }
+    }
+    __syncthreads();  // pair plane complete; the byte tile is dead, its memory becomes the score plane
+    {
+      uint4* z = reinterpret_cast<uint4*>(score);
+      for (int i = tid; i < kF2PlaneBytes / 16; i += kF2Threads) z[i] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    // tested pixels: columns [3, W - 4] = words [2, j1], rows [3, H - 4]
+    const int ipw = j1 - 1, ih = H - 6;
+    // ---- reject: a thread per two adjacent pairs, tpr threads per row
+    {
+      const uint32_t k1 = (uint32_t)(0x7FFF - (low_th + 256)) * 0x10001u;
+      const int ipw2 = (ipw + 1) >> 1;
+      const int sh = ipw2 <= 8 ? 3 : ipw2 <= 16 ? 4 : 5;  // log2(threads per row)
+      const int q = tid & ((1 << sh) - 1), rstep = kF2Threads >> sh;
+      const int j = 2 + 2 * q;
+      const bool colA = j <= j1, colB = j + 1 <= j1;
+      for (int rb = 3; rb < 3 + ih; rb += rstep) {  // same trip count for every thread: the ballots need full warps
+        const int r = rb + (tid >> sh);
+        bool pa = false, pb = false;
+        if (colA && r < 3 + ih) {
+          fast2_quick2(pair + r * S + j, k1, pa, pb);
+          pb = pb && colB;
+        }
+        const uint32_t ba = __ballot_sync(0xffffffffu, pa), bb = __ballot_sync(0xffffffffu, pb);
+        if ((ba | bb) != 0u) {
+          int at = 0;
+          const int na = __popc(ba);
+          if (lane == 0) at = atomicAdd(s_qn, na + __popc(bb));
+          at = __shfl_sync(0xffffffffu, at, 0);
+          const uint32_t e = (uint32_t)((r << 7) | j);
+          if (pa) queue[at + __popc(ba & lt_mask)] = (uint16_t)e;
+          if (pb) queue[at + na + __popc(bb & lt_mask)] = (uint16_t)(e + 1u);
+        }
+      }
+    }
+    __syncthreads();
+    const int qn = *s_qn;
+    // ---- exact score of the survivors
+    {
+      const uint32_t kc = (uint32_t)(256 + low_th) * 0x10001u;
+      for (int i = tid; i < qn; i += kF2Threads) {
+        const uint32_t e = queue[i];
+        const int r = (int)(e >> 7), j = (int)(e & 127u);
+        const uint32_t mm = fast_score_pair(pair + r * S + j, S);  // m + 256
+        uint32_t s = __vmaxs2(mm, kc) - kc;                        // max(m - low_th, 0), no borrow
+        if (2 * j > c_hi) s &= 0x0000FFFFu;                        // column W - 3 is not tested
+        if (s != 0u) score[r * S + j] = s;
+      }
+    }
+    __syncthreads();
+    // ---- non-max suppression at iniThFAST over the survivors -> keep bitmap
+    {
+      const uint32_t kd = (uint32_t)(min(max(ini_th, 0), 255) - low_th) * 0x10001u;
+      for (int i = tid; i < qn; i += kF2Threads) {
+        const uint32_t e = queue[i];
+        const int r = (int)(e >> 7), j = (int)(e & 127u);
+        const uint32_t* p = score + r * S + j;
+        const uint32_t c = __vmaxs2(p[0], kd) - kd;
+        if (c != 0u) {
+          const uint32_t fl = fast2_nms_flags(p, c, kd, cmL[j], cmR[j], rmU[r], rmD[r]);
+          if (fl & 0x8000u) atomicOr(&keep[r * kF2KeepWords + ((2 * j - 1) >> 5)], 1u << ((2 * j - 1) & 31));
+          if (fl & 0x80000000u) atomicOr(&keep[r * kF2KeepWords + ((2 * j) >> 5)], 1u << ((2 * j) & 31));
+        }
+      }
+    }
+    __syncthreads();
+  }
+
+  // ---- cells: warp per cell, lane per row
+  const int n_cells = g->n_cells;
+  for (int ci = warp; ci < b.ncx * b.ncy; ci += kF2Warps) {
+    const int cyi = ci / b.ncx, cxi = ci - cyi * b.ncx;
+    const int cell = b.cell0 + cyi * b.cols + cxi;
+    int* out_count = cell_count + (size_t)frame * n_cells + cell;
+    int* out_start = cell_start + (size_t)frame * n_cells + cell;
+    const int4 roi = cells[cell];
+    if (roi.z - roi.x < 7 || roi.w - roi.y < 7) {  // skipped cell (:565, :574) or nothing testable
+      if (lane == 0) { *out_count = 0; *out_start = 0; }
+      continue;
+    }
+    // tested columns [xa, xb), rows [ya, yb) in tile coordinates
+    const int xa = roi.x - b.x0 + 3, xb = roi.z - b.x0 - 3, ya = roi.y - b.y0 + 3, yb = roi.w - b.y0 - 3;
+    const int nrows = yb - ya;
+    uint16_t* rbase = rowbase + ci * 64;
+    auto count_rows = [&]() -> int {
+      int total = 0;
+      for (int r0 = 0; r0 < nrows; r0 += 32) {
+        const int rr = r0 + lane;
+        const int n = rr < nrows ? fast2_row_count(keep + (ya + rr) * kF2KeepWords, xa, xb) : 0;
+        int inc = n;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int t = __shfl_up_sync(0xffffffffu, inc, d);
+          if (lane >= d) inc += t;
+        }
+        if (rr < nrows) rbase[rr] = (uint16_t)(total + inc - n);
+        total += __shfl_sync(0xffffffffu, inc, 31);
+      }
+      return total;
+    };
+    int count = count_rows();
+    if (count == 0 && min_th != ini_th) {
+      // keyPointsInCell.empty() is judged after NMS (src/orbExtractor.cpp:582): second FAST call at minThFAST.  Rare:
+      // dense pass over the cell's words; the other half of a word on a seam belongs to the neighbouring cell's warp
+      const uint32_t kd = (uint32_t)(min(max(min_th, 0), 255) - low_th) * 0x10001u;
+      const int jA = (xa + 1) >> 1, jB = xb >> 1;
+      for (int r = ya; r < yb; r++)
+        for (int j = jA + lane; j <= jB; j += 32) {
+          const uint32_t* p = score + r * S + j;
+          uint32_t c0 = p[0];
+          if (2 * j - 1 < xa) c0 &= 0xFFFF0000u;
+          if (2 * j >= xb) c0 &= 0x0000FFFFu;
+          const uint32_t c = __vmaxs2(c0, kd) - kd;
+          if (c != 0u) {
+            const uint32_t fl = fast2_nms_flags(p, c, kd, cmL[j], cmR[j], rmU[r], rmD[r]);
+            if (fl & 0x8000u) atomicOr(&keep[r * kF2KeepWords + ((2 * j - 1) >> 5)], 1u << ((2 * j - 1) & 31));
+            if (fl & 0x80000000u) atomicOr(&keep[r * kF2KeepWords + ((2 * j) >> 5)], 1u << ((2 * j) & 31));
+          }
+        }
+      __syncwarp();
+      count = count_rows();
+    }
+    if (count == 0) {
+      if (lane == 0) { *out_count = 0; *out_start = 0; }
+      continue;
+    }
+    int start = 0;
+    if (lane == 0) start = atomicAdd(raw_counter + frame, count);
+    start = __shfl_sync(0xffffffffu, start, 0);
+    if (start + count > g->raw_cap) {  // candidate buffer exhausted: report, drop the cell
+      if (lane == 0) { atomicOr(status, kStatusRawOverflow); *out_count = 0; *out_start = 0; }
+      continue;
+    }
+    // ---- emit: lane = row, walking the row's keep bits gives the reference's row-major order.
+    // y:12 | x:12 | response:8, coordinates relative to the 16 px border as distributeQuadTree sees them (:586-590);
+    // response = m - 1 = stored + low_th - 1
+    {
+      const uint32_t pos_base = ((uint32_t)(b.y0 - kBorder) << 20) + ((uint32_t)(b.x0 - kBorder) << 8) + (uint32_t)(low_th - 1);
+      uint32_t* dst = raw + (size_t)frame * g->raw_cap + start;
+      for (int rr = lane; rr < nrows; rr += 32) {
+        const int r = ya + rr;
+        uint32_t* o = dst + rbase[rr];
+        const uint32_t* krow = keep + r * kF2KeepWords;
+        for (int k = xa >> 5; k <= (xb - 1) >> 5; k++) {
+          uint32_t m = krow[k];
+          if (k == (xa >> 5)) m &= 0xFFFFFFFFu << (xa & 31);
+          if (k == ((xb - 1) >> 5) && (xb & 31)) m &= (1u << (xb & 31)) - 1u;
+          while (m) {
+            const int x = 32 * k + __ffs(m) - 1;
+            m &= m - 1u;
+            const uint32_t v = score[r * S + ((x + 1) >> 1)];  // column x: low half of word (x + 1) / 2 if x is odd
+            *o++ = pos_base + ((uint32_t)r << 20) + ((uint32_t)x << 8) + ((x & 1) ? (v & 0xFFu) : ((v >> 16) & 0xFFu));
+          }
+        }
+      }
+    }
+    if (lane == 0) { *out_count = count; *out_start = start; }
+  }
+}
+
+// Host: partition every level's cell grid into blocks whose ROI fits the shared-memory tile.
+int fast2_build_blocks(const FrameGeomDev& g, const std::vector<int4>& cells, std::vector<FastBlock>* out, int* max_w,
+                       int* max_h) {
+  constexpr int kMaxW = kF2MaxW, kMaxH = kF2MaxH;
+  *max_w = 16;
+  *max_h = 8;
+  for (int l = 0; l < g.n_levels; l++) {
+    const LevelGeom& lv = g.lv[l];
+    if (lv.cell_cols <= 0 || lv.cell_rows <= 0) continue;
+    const int bx = std::max(1, std::min(4, (kMaxW - 6) / lv.cell_w)), by = std::max(1, std::min(2, (kMaxH - 6) / lv.cell_h));
+    for (int cy = 0; cy < lv.cell_rows; cy += by)
+      for (int cx = 0; cx < lv.cell_cols; cx += bx) {
+        FastBlock b = {};
+        b.level = l;
+        b.cell0 = lv.cell_base + cy * lv.cell_cols + cx;
+        b.ncx = std::min(bx, lv.cell_cols - cx);
+        b.ncy = std::min(by, lv.cell_rows - cy);
+        b.cols = lv.cell_cols;
+        int x0 = 1 << 30, y0 = 1 << 30, x1 = -1, y1 = -1;
+        for (int i = 0; i < b.ncy; i++)
+          for (int j = 0; j < b.ncx; j++) {
+            const int4 c = cells[b.cell0 + i * lv.cell_cols + j];
+            if (c.z - c.x < 7 || c.w - c.y < 7) continue;
+            x0 = std::min(x0, c.x); y0 = std::min(y0, c.y);
+            x1 = std::max(x1, c.z); y1 = std::max(y1, c.w);
+          }
+        if (x1 > x0) {
+          b.x0 = x0; b.y0 = y0; b.w = x1 - x0; b.h = y1 - y0;
+          // the block's first cell must be the one at its ROI origin (seam masks count cells from column / row 3)
+          const int4 c0 = cells[b.cell0];
+          if (c0.x != x0 || c0.y != y0 || c0.z - c0.x < 7 || c0.w - c0.y < 7) {
+            set_error("internal: FAST block does not start at a valid cell");
+            return YDORB_E_INVALID;
+          }
+          if (b.w > kF2MaxW || b.h > kF2MaxH || b.w < 7 || b.h < 7) {
+            set_error("internal: FAST block larger than the shared-memory tile");
+            return YDORB_E_INVALID;
+          }
+          *max_w = std::max(*max_w, b.w);
+          *max_h = std::max(*max_h, b.h);
+        }
+        out->push_back(b);
+      }
+  }
+  return YDORB_OK;
+}
+
+size_t fast2_smem_bytes(int, int) { return (size_t)kF2SmemBytes; }
+
+void fast2_box(int, int, int* box_w, int* box_h) {
+  *box_w = kF2BoxW;
+  *box_h = kF2BoxH;
+}
+
+int launch_fast_blocks(const YdExtractor* ex, int batch, cudaStream_t s) {
+  const int ini = ex->params.ini_th_fast;
+  const int mn = ex->params.reference_min_th_quirk ? ini : ex->params.min_th_fast;
+  const size_t smem = fast2_smem_bytes(ex->fb_max_w, ex->fb_max_h);
+  if (smem > 48 * 1024) YD_CUDA(cudaFuncSetAttribute(k_fast_blocks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  Fast2Maps maps;
+  for (int l = 0; l < kMaxLevels; l++) maps.lv[l] = ex->tmap_level[l];
+  const int frame0 = (int)((ex->d_pyr - ex->pyr_base) / ex->geom.pyr_bytes);
+  dim3 grid(ex->n_fast_blocks, batch);
+  YD_CUDA(launch_chain(k_fast_blocks, grid, dim3(kF2Threads), smem, s, maps, ex->d_geom, ex->d_cells, ex->d_fast_blocks, frame0,
+                       ini, mn, ex->d_raw, ex->d_raw_counter, ex->d_cell_count, ex->d_cell_start,
+                       ex->d_status));
+  count_launches(1);
+  YD_CUDA(cudaGetLastError());
+  return YDORB_OK;
+}
+
+}  // namespace ydorb

@@ -11,6 +11,12 @@ int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, s
 int pyramid_tile_tables(FrameGeomDev* g, std::vector<int>* tab);
 // E3 per-cell FAST with threshold fallback (src/orbExtractor.cpp:562-593)
 int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s);
+// CTA-per-cell-block form (fast2.cu) and its host-side set-up
+int launch_fast_blocks(const YdExtractor* ex, int batch, cudaStream_t s);
+int fast2_build_blocks(const FrameGeomDev& g, const std::vector<int4>& cells, std::vector<FastBlock>* out, int* max_w,
+                       int* max_h);
+size_t fast2_smem_bytes(int max_w, int max_h);
+void fast2_box(int max_w, int max_h, int* box_w, int* box_h);
 // E4 distributeQuadTree (src/orbExtractor.cpp:455-544)
 int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s);
 // E5+E6+E7 orientation, blur, descriptors, output assembly (src/orbExtractor.cpp:379-454)
