@@ -131,7 +131,8 @@ struct FastBlock {
   int level;
   int x0, y0, w, h;          // union of the valid cells' ROIs (level coordinates); w = h = 0: no valid cell
   int cell0, ncx, ncy, cols; // first grid cell (index in the frame's cell table), cells covered, the level's cell_cols
-  int pad[3];
+  int conv_n, conv_magic;    // bytes -> pairs conversion: 16-byte groups per row, 65536 / conv_n + 1 (i / conv_n = i * magic >> 16)
+  int pad;
 };
 
 // device pointer to the padded level origin (pixel (0,0) of the level, pad readable around it)
@@ -172,6 +173,7 @@ struct YdExtractor {
   int* d_tab_ofs;        // resize source offsets
   short* d_tab_a;        // resize weights (a0,a1 interleaved)
   ydorb::FastBlock* d_fast_blocks;  // [cap_cells] cell blocks of the current geometry (fast2.cu)
+  uint32_t* d_fast_seams;           // [kMaxLevels][276] per-level cell-seam masks of the NMS (fast2.cu)
   int n_fast_blocks, fb_max_w, fb_max_h;
   uint8_t* pyr_base;     // d_pyr of the handle itself (frame_view() shifts d_pyr; TMA coordinates count from here)
   CUtensorMap tmap_level[ydorb::kMaxLevels];  // u8 [frame][row][byte] per pyramid level, box = FAST block tile

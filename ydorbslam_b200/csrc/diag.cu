@@ -10,7 +10,8 @@ namespace ydorb {
 constexpr int kChains = 8;
 constexpr int kUnroll = 8;
 
-enum DiagOp { kOpPopc = 0, kOpLop3 = 1, kOpVimnmx3 = 2, kOpImad = 3, kOpMix = 4, kOpCount = 5 };
+enum DiagOp { kOpPopc = 0, kOpLop3 = 1, kOpVimnmx3 = 2, kOpImad = 3, kOpMix = 4, kOpCount = 5,
+              kOpHmnmx2 = 5, kOpMixHmnmxVimnmx = 6, kOpCountAll = 7 };  // 5, 6: only when the caller has room for 7
 
 template <int OP>
 __global__ void __launch_bounds__(256) k_diag_rate(int iters, uint32_t seed, uint32_t* __restrict__ sink) {
@@ -31,6 +32,12 @@ __global__ void __launch_bounds__(256) k_diag_rate(int iters, uint32_t seed, uin
           a[i] = (u & 1) ? __vimax3_s16x2(a[i], b, a[(i + 1) % kChains]) : __vimin3_s16x2(a[i], c, a[(i + 1) % kChains]);
         } else if (OP == kOpImad) {
           asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
+        } else if (OP == kOpHmnmx2) {  // packed half min / max: which pipe, what rate?
+          if (u & 1) asm volatile("max.f16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+          else asm volatile("min.f16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(c));
+        } else if (OP == kOpMixHmnmxVimnmx) {  // does packed half min / max co-issue with the integer one?
+          if (i & 1) asm volatile("max.f16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+          else a[i] = __vimax3_s16x2(a[i], b, c);
         } else {  // alternate the alu and fma pipes: is the limit the pipe or the issue slot?
           if (i & 1) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b), "r"(c));
           else asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
@@ -114,6 +121,10 @@ extern "C" int ydorb_diag_int_peaks(int device, double* ops_per_s, int n) {
   if (rc == YDORB_OK) rc = run_rate<kOpVimnmx3>(prop.multiProcessorCount, iters, d_sink, &ops_per_s[kOpVimnmx3]);
   if (rc == YDORB_OK) rc = run_rate<kOpImad>(prop.multiProcessorCount, iters, d_sink, &ops_per_s[kOpImad]);
   if (rc == YDORB_OK) rc = run_rate<kOpMix>(prop.multiProcessorCount, iters, d_sink, &ops_per_s[kOpMix]);
+  if (n >= kOpCountAll) {
+    if (rc == YDORB_OK) rc = run_rate<kOpHmnmx2>(prop.multiProcessorCount, iters, d_sink, &ops_per_s[kOpHmnmx2]);
+    if (rc == YDORB_OK) rc = run_rate<kOpMixHmnmxVimnmx>(prop.multiProcessorCount, iters, d_sink, &ops_per_s[kOpMixHmnmxVimnmx]);
+  }
   cudaFree(d_sink);
   return rc;
 }

@@ -192,8 +192,10 @@ static int set_size(YdExtractor* ex, int w, int h) {
     YD_CUDA(cudaMemcpyAsync(ex->d_cells, hg.cells.data(), hg.cells.size() * sizeof(int4), cudaMemcpyHostToDevice, ex->stream));
   // fast2.cu: cell blocks and one tensor map per level whose box is the largest block's tile
   std::vector<FastBlock> blocks;
-  rc = fast2_build_blocks(hg.g, hg.cells, &blocks, &ex->fb_max_w, &ex->fb_max_h);
+  std::vector<uint32_t> seams;
+  rc = fast2_build_blocks(hg.g, hg.cells, &blocks, &seams, &ex->fb_max_w, &ex->fb_max_h);
   if (rc != YDORB_OK) return rc;
+  YD_CUDA(cudaMemcpyAsync(ex->d_fast_seams, seams.data(), seams.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ex->stream));
   ex->n_fast_blocks = (int)blocks.size();
   if (!blocks.empty())
     YD_CUDA(cudaMemcpyAsync(ex->d_fast_blocks, blocks.data(), blocks.size() * sizeof(FastBlock), cudaMemcpyHostToDevice, ex->stream));
@@ -369,6 +371,7 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
   alloc((void**)&ex->d_tab_a, sizeof(short) * 2 * ex->cap_tab);
   alloc((void**)&ex->d_cells, sizeof(int4) * ex->cap_cells);
   alloc((void**)&ex->d_fast_blocks, sizeof(FastBlock) * ex->cap_cells);
+  alloc((void**)&ex->d_fast_seams, sizeof(uint32_t) * kMaxLevels * 512);
   alloc((void**)&ex->d_cell_count, sizeof(int) * B * ex->cap_cells);
   alloc((void**)&ex->d_cell_start, sizeof(int) * B * ex->cap_cells);
   alloc((void**)&ex->d_cell_rank, sizeof(int) * B * (ex->cap_cells + 1));
@@ -407,7 +410,7 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
 void ydorb_extractor_destroy(YdExtractor* ex) {
   if (!ex) return;
   cudaSetDevice(ex->device);
-  void* ptrs[] = {ex->d_geom, ex->d_pyr, ex->d_tab_ofs, ex->d_tab_a, ex->d_cells, ex->d_fast_blocks, ex->d_cell_count, ex->d_cell_start,
+  void* ptrs[] = {ex->d_geom, ex->d_pyr, ex->d_tab_ofs, ex->d_tab_a, ex->d_cells, ex->d_fast_blocks, ex->d_fast_seams, ex->d_cell_count, ex->d_cell_start,
                   ex->d_cell_rank, ex->d_raw, ex->d_raw_counter, ex->d_qt_keys[0], ex->d_qt_keys[1], ex->d_qt_keys[2],
                   ex->d_qt_vals[0], ex->d_qt_vals[1], ex->d_qt_vals[2], ex->d_qt_bitmap, ex->d_qt_fold, ex->d_qt_meta, ex->d_level_ncand, ex->d_sel, ex->d_sel_n,
                   ex->d_status, ex->d_images, ex->d_kps, ex->d_desc, ex->d_nout};

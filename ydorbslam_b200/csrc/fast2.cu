@@ -36,6 +36,7 @@ constexpr int kF2Wpr = 68;                  // pair words per plane row: word j 
 constexpr int kF2KeepWords = 5;             // keep bitmap words per row (tile columns 0..159)
 constexpr int kF2QueueCap = 64 * 64;        // tested pairs of the largest block
 constexpr int kF2MaxCells = 8;
+constexpr int kF2SeamWords = 2 * kF2Wpr + 2 * kF2MaxH;  // cmL[68] cmR[68] rmU[70] rmD[70] of one level
 
 // shared memory map (bytes)
 constexpr int kF2OffTab = 128;                                         // cmL[68] cmR[68] rmU[70] rmD[70]
@@ -114,7 +115,7 @@ __device__ __forceinline__ int fast2_row_count(const uint32_t* __restrict__ krow
 
 __global__ void __launch_bounds__(kF2Threads, 4)
 k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
-              const FastBlock* __restrict__ blocks, int frame0, int ini_th, int min_th, uint32_t* __restrict__ raw,
+              const FastBlock* __restrict__ blocks, const uint32_t* __restrict__ seams, int frame0, int ini_th, int min_th, uint32_t* __restrict__ raw,
               int* __restrict__ raw_counter, int* __restrict__ cell_count, int* __restrict__ cell_start,
               int* __restrict__ status) {
   pdl_wait();
@@ -151,40 +152,32 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
       mbar_expect_tx(bar, (uint32_t)(kF2BoxW * kF2BoxH));
       tma_load_3d(smem + kF2OffScore, &maps.lv[b.level], bar, box_x, kPad + b.y0, frame0 + frame);
     }
-    // ---- while the box is in flight: keep bitmap := 0, seam masks
+    // ---- while the box is in flight: keep bitmap := 0, this level's seam masks (host-built, fast2_build_blocks)
     {
       for (int i = tid; i < kF2MaxH * kF2KeepWords; i += kF2Threads) keep[i] = 0u;
-      const int cw = g->lv[b.level].cell_w, ch = g->lv[b.level].cell_h;
-      // first(x): tile column x is the first tested column of a cell (cells test [k * cw + 3, (k + 1) * cw + 3))
-      auto first = [](int x, int pitch) { return x >= 3 && (x - 3) % pitch == 0; };
-      if (tid < S) {
-        const int x = 2 * tid;  // word tid = columns (x - 1, x)
-        const bool fl = first(x - 1, cw), fh = first(x, cw), fn = first(x + 1, cw);
-        cmL[tid] = (fl ? 0u : 0x0000FFFFu) | (fh ? 0u : 0xFFFF0000u);
-        cmR[tid] = (fh ? 0u : 0x0000FFFFu) | (fn ? 0u : 0xFFFF0000u);
-      } else if (tid >= 128 && tid < 128 + kF2MaxH) {
-        const int r = tid - 128;
-        rmU[r] = first(r, ch) ? 0u : 0xFFFFFFFFu;
-        rmD[r] = first(r + 1, ch) ? 0u : 0xFFFFFFFFu;
-      }
+      const uint32_t* src = seams + b.level * kF2SeamWords;
+      for (int i = tid; i < kF2SeamWords; i += kF2Threads) cmL[i] = src[i];
     }
     mbar_wait(bar, 0);
     // ---- bytes -> pixel pairs: tile bytes a + 4w .. a + 4w + 3 of row r = columns 4w - 1 .. 4w + 2 -> words 2w, 2w + 1
     // words needed: 0 .. j1 + 2 (the reject / score of the last tested pair reads two words to its right)
     const int c_hi = W - 4;                // last tested column
     const int j1 = (c_hi + 1) >> 1;        // its word
+    // a thread converts 16 bytes: five tile words -> four shifted words -> eight plane words (row = i / conv_n by a
+    // host-made reciprocal)
     {
       const int k0 = a >> 2, ash = 8 * (a & 3);
-      const int tw4 = kF2BoxW / 4, nw4 = ((j1 + 2) >> 1) + 1, total = nw4 * H;
-      const int sr = kF2Threads / nw4, sw = kF2Threads - sr * nw4;
-      int r = tid / nw4, w = tid - r * nw4;
+      const int ng = b.conv_n, total = ng * H;
       for (int i = tid; i < total; i += kF2Threads) {
-        const uint32_t* t = tile8 + r * tw4 + k0 + w;
-        const uint32_t v = __funnelshift_r(t[0], t[1], ash);
-        *reinterpret_cast<uint2*>(pair + r * S + 2 * w) = make_uint2(__byte_perm(v, 0, 0x4140), __byte_perm(v, 0, 0x4342));
-        r += sr;
-        w += sw;
-        if (w >= nw4) { w -= nw4; r++; }
+        const int r = (int)(((uint32_t)i * (uint32_t)b.conv_magic) >> 16), gq = i - r * ng;
+        const uint32_t* t = tile8 + r * (kF2BoxW / 4) + k0 + 4 * gq;
+        const uint32_t t0 = t[0], t1 = t[1], t2 = t[2], t3 = t[3], t4 = t[4];
+        const uint32_t v0 = __funnelshift_r(t0, t1, ash), v1 = __funnelshift_r(t1, t2, ash),
+                       v2 = __funnelshift_r(t2, t3, ash), v3 = __funnelshift_r(t3, t4, ash);
+        uint4* o = reinterpret_cast<uint4*>(pair + r * S + 8 * gq);
+        o[0] = make_uint4(__byte_perm(v0, 0, 0x4140), __byte_perm(v0, 0, 0x4342), __byte_perm(v1, 0, 0x4140), __byte_perm(v1, 0, 0x4342));
+        if (8 * gq + 4 < S)
+          o[1] = make_uint4(__byte_perm(v2, 0, 0x4140), __byte_perm(v2, 0, 0x4342), __byte_perm(v3, 0, 0x4140), __byte_perm(v3, 0, 0x4342));
       }
     }
     __syncthreads();  // pair plane complete; the byte tile is dead, its memory becomes the score plane
@@ -257,7 +250,7 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
   // ---- cells: warp per cell, lane per row
   const int n_cells = g->n_cells;
   for (int ci = warp; ci < b.ncx * b.ncy; ci += kF2Warps) {
-    const int cyi = ci / b.ncx, cxi = ci - cyi * b.ncx;
+    const int cyi = ci >= b.ncx ? 1 : 0, cxi = ci - cyi * b.ncx;  // at most two rows of cells
     const int cell = b.cell0 + cyi * b.cols + cxi;
     int* out_count = cell_count + (size_t)frame * n_cells + cell;
     int* out_start = cell_start + (size_t)frame * n_cells + cell;
@@ -347,14 +340,31 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
 }
 
 // Host: partition every level's cell grid into blocks whose ROI fits the shared-memory tile.
-int fast2_build_blocks(const FrameGeomDev& g, const std::vector<int4>& cells, std::vector<FastBlock>* out, int* max_w,
-                       int* max_h) {
+int fast2_build_blocks(const FrameGeomDev& g, const std::vector<int4>& cells, std::vector<FastBlock>* out,
+                       std::vector<uint32_t>* seams, int* max_w, int* max_h) {
   constexpr int kMaxW = kF2MaxW, kMaxH = kF2MaxH;
   *max_w = 16;
   *max_h = 8;
+  seams->assign((size_t)kMaxLevels * kF2SeamWords, 0xFFFFFFFFu);
   for (int l = 0; l < g.n_levels; l++) {
     const LevelGeom& lv = g.lv[l];
     if (lv.cell_cols <= 0 || lv.cell_rows <= 0) continue;
+    {
+      // seam masks.  first(x): tile column (row) x is the first tested column of a cell -- cells test
+      // [k * pitch + 3, (k + 1) * pitch + 3) and every block starts at a cell's origin.  Plane word j holds columns
+      // (2j - 1, 2j): cmL masks the left neighbours of its two halves, cmR the right ones; rmU / rmD the rows.
+      auto first = [](int x, int pitch) { return x >= 3 && (x - 3) % pitch == 0; };
+      uint32_t* t = seams->data() + (size_t)l * kF2SeamWords;
+      for (int j = 0; j < kF2Wpr; j++) {
+        const bool fl = first(2 * j - 1, lv.cell_w), fh = first(2 * j, lv.cell_w), fn = first(2 * j + 1, lv.cell_w);
+        t[j] = (fl ? 0u : 0x0000FFFFu) | (fh ? 0u : 0xFFFF0000u);
+        t[kF2Wpr + j] = (fh ? 0u : 0x0000FFFFu) | (fn ? 0u : 0xFFFF0000u);
+      }
+      for (int r = 0; r < kF2MaxH; r++) {
+        t[2 * kF2Wpr + r] = first(r, lv.cell_h) ? 0u : 0xFFFFFFFFu;
+        t[2 * kF2Wpr + kF2MaxH + r] = first(r + 1, lv.cell_h) ? 0u : 0xFFFFFFFFu;
+      }
+    }
     const int bx = std::max(1, std::min(4, (kMaxW - 6) / lv.cell_w)), by = std::max(1, std::min(2, (kMaxH - 6) / lv.cell_h));
     for (int cy = 0; cy < lv.cell_rows; cy += by)
       for (int cx = 0; cx < lv.cell_cols; cx += bx) {
@@ -384,6 +394,17 @@ int fast2_build_blocks(const FrameGeomDev& g, const std::vector<int4>& cells, st
             set_error("internal: FAST block larger than the shared-memory tile");
             return YDORB_E_INVALID;
           }
+          {
+            // conversion plan: plane words 0 .. j1 + 2 are needed, 8 per thread
+            const int j1 = (b.w - 3) >> 1, nw4 = ((j1 + 2) >> 1) + 1;
+            b.conv_n = (nw4 + 3) / 4;
+            b.conv_magic = 65536 / b.conv_n + 1;
+            for (int i = 0; i < b.conv_n * kF2MaxH; i++)
+              if ((int)(((uint32_t)i * (uint32_t)b.conv_magic) >> 16) != i / b.conv_n) {
+                set_error("internal: FAST block reciprocal");
+                return YDORB_E_INVALID;
+              }
+          }
           *max_w = std::max(*max_w, b.w);
           *max_h = std::max(*max_h, b.h);
         }
@@ -409,7 +430,7 @@ int launch_fast_blocks(const YdExtractor* ex, int batch, cudaStream_t s) {
   for (int l = 0; l < kMaxLevels; l++) maps.lv[l] = ex->tmap_level[l];
   const int frame0 = (int)((ex->d_pyr - ex->pyr_base) / ex->geom.pyr_bytes);
   dim3 grid(ex->n_fast_blocks, batch);
-  YD_CUDA(launch_chain(k_fast_blocks, grid, dim3(kF2Threads), smem, s, maps, ex->d_geom, ex->d_cells, ex->d_fast_blocks, frame0,
+  YD_CUDA(launch_chain(k_fast_blocks, grid, dim3(kF2Threads), smem, s, maps, ex->d_geom, ex->d_cells, ex->d_fast_blocks, ex->d_fast_seams, frame0,
                        ini, mn, ex->d_raw, ex->d_raw_counter, ex->d_cell_count, ex->d_cell_start,
                        ex->d_status));
   count_launches(1);

@@ -13,8 +13,8 @@ int pyramid_tile_tables(FrameGeomDev* g, std::vector<int>* tab);
 int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s);
 // CTA-per-cell-block form (fast2.cu) and its host-side set-up
 int launch_fast_blocks(const YdExtractor* ex, int batch, cudaStream_t s);
-int fast2_build_blocks(const FrameGeomDev& g, const std::vector<int4>& cells, std::vector<FastBlock>* out, int* max_w,
-                       int* max_h);
+int fast2_build_blocks(const FrameGeomDev& g, const std::vector<int4>& cells, std::vector<FastBlock>* out,
+                       std::vector<uint32_t>* seams, int* max_w, int* max_h);
 size_t fast2_smem_bytes(int max_w, int max_h);
 void fast2_box(int max_w, int max_h, int* box_w, int* box_h);
 // E4 distributeQuadTree (src/orbExtractor.cpp:455-544)
