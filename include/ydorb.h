@@ -264,6 +264,21 @@ int ydorb_search_windows(YdFrame* f, const YdWindowQuery* queries, const uint8_t
                          const YdWindowParams* prm, const uint8_t* kp_occupied, int32_t* best_of, int32_t* match_out,
                          int32_t* n_matches);
 
+/* ---- EXTRA: searchForInitialization ------------------------------------------------------------------------
+ * `north_star` names it; the reference has no such function (absent from src/orbMatcher.hpp:24-66).  This is
+ * ORB-SLAM2's published ORBmatcher::SearchForInitialization on this reference's own pieces: getKeyPointsInArea
+ * (src/frame.cpp:337-361), the descriptor distance (src/orbMatcher.cpp:11-23), the rotation histogram of :120-131 and
+ * computeThreeMaxima (:827-854).  NO reference parity claim; parity is against the sequential restatement in oracle/.
+ *   f2            frame searched (its grid and descriptors are resident)
+ *   kps1 / desc1  keypoints and 32-byte descriptors of the first frame (host); only octave-0 keypoints are matched
+ *   prev_matched  [n1][2] floats, in: window centres (vbPrevMatched), out: position of the match where one was made
+ *   window_size   radius handed to getKeyPointsInArea; nn_ratio / th_low: best < nn_ratio * second, best <= th_low
+ *   area_mode     0: the reference's window predicate; 1: ORB-SLAM2's |dx| < r && |dy| < r, octave == 0
+ *   matches12     [n1] matched keypoint of f2 or -1; *n_matches = the function's return value */
+int ydorb_match_windowed_top2(YdFrame* f2, const YdKeyPoint* kps1, const uint8_t* desc1, int n1, float* prev_matched,
+                              int window_size, float nn_ratio, int th_low, int check_orientation, int area_mode,
+                              int32_t* matches12, int32_t* n_matches);
+
 /* ---- BoW matchers ---------------------------------------------------------------------------------------
  * DBoW3::FeatureVector (std::map<NodeId, std::vector<unsigned>>, thirdParty/DBow3/src/FeatureVector.h:19-21) in CSR
  * form: node_ids ascending (= std::map order), node_start[n_nodes+1], items in push_back order.  Every feature index

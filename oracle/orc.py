@@ -322,6 +322,22 @@ def search_windows(g, kps, desc, right_x, kp_occupied, queries, q_desc, prm):
     return n, best[: len(q)], match[: len(kps)]
 
 
+def search_for_initialization(g2, kps1, desc1, kps2, desc2, prev_matched, window_size, nn_ratio, th_low, check_orientation,
+                              area_mode=0):
+    """EXTRA (not in the reference): ORB-SLAM2's SearchForInitialization, sequential restatement."""
+    k1 = np.ascontiguousarray(kps1, dtype=KP_DTYPE)
+    k2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+    d1 = np.ascontiguousarray(desc1, dtype=np.uint8)
+    d2 = np.ascontiguousarray(desc2, dtype=np.uint8)
+    prev = np.array(prev_matched, dtype=np.float32).reshape(len(k1), 2).copy()
+    m12 = np.full(max(len(k1), 1), -1, np.int32)
+    lib().orc_search_for_initialization.restype = C.c_int
+    n = lib().orc_search_for_initialization(C.byref(g2), _p(k1), _p(d1), len(k1), _p(k2), _p(d2), len(k2), _p(prev),
+                                            int(window_size), C.c_float(nn_ratio), int(th_low), int(bool(check_orientation)),
+                                            int(area_mode), _p(m12))
+    return n, m12[: len(k1)], prev
+
+
 def three_maxima(sizes):
     sz = np.ascontiguousarray(sizes, dtype=np.int32)
     a, b, c = C.c_int32(), C.c_int32(), C.c_int32()

@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <cassert>
 #include <cfloat>
+#include <climits>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -1111,6 +1112,86 @@ int orc_search_windows(const OrcFrameGeom* g, const OrcKeyPoint* kps, const uint
   for (int i = 0; i < nkp; i++) match_out[i] = slot[i] >= 0 ? slot[i] : (slot[i] == -3 ? -2 : -1);
   delete grid;
   return matches;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * EXTRA  searchForInitialization.  `north_star` names it, the reference does not have it (absent from
+ * src/orbMatcher.hpp:24-66).  This restates the published algorithm the reference descends from -- ORB-SLAM2,
+ * ORBmatcher::SearchForInitialization (Mur-Artal & Tardos, ORB_SLAM2 src/ORBmatcher.cc) -- on this reference's own
+ * pieces: Frame::getKeyPointsInArea (G2, area_mode 0: the reference's predicate; area_mode 1: ORB-SLAM2's
+ * |dx| < r && |dy| < r with minLevel <= octave <= maxLevel), computeDescriptorsDistance (M0), the rotation histogram
+ * convention of src/orbMatcher.cpp:120-131 and computeThreeMaxima (M7).  NO reference parity claim: it pins the CUDA
+ * path to this sequential statement only.
+ *   for every level-0 keypoint i1 of frame 1, in index order: window around prev_matched[i1] in frame 2 (levels 0..0);
+ *   best / second distance over candidates whose recorded match distance is still larger than this one
+ *   (vMatchedDistance[i2] <= dist -> skip); accept if best <= th_low and best < nn_ratio * second; a keypoint of
+ *   frame 2 taken again un-matches its previous owner; orientation cull over every push (un-matched owners included);
+ *   prev_matched[i1] := position of the match.
+ * ---------------------------------------------------------------------------------------------- */
+int orc_search_for_initialization(const OrcFrameGeom* g2, const OrcKeyPoint* kps1, const uint8_t* desc1, int n1,
+                                  const OrcKeyPoint* kps2, const uint8_t* desc2, int n2, float* prev_matched,
+                                  int window_size, float nn_ratio, int th_low, int check_orientation, int area_mode,
+                                  int32_t* matches12) {
+  Grid* grid = new Grid();
+  build_grid(g2, kps2, n2, *grid);
+  for (int i = 0; i < n1; i++) matches12[i] = -1;
+  std::vector<int> matched_distance(n2, INT_MAX), matches21(n2, -1);
+  std::vector<std::vector<int>> hist(kHistLen);
+  int nmatches = 0;
+  std::vector<int> cands;
+  for (int i1 = 0; i1 < n1; i1++) {
+    const int level1 = kps1[i1].octave;
+    if (level1 > 0) continue;
+    const float x = prev_matched[2 * i1], y = prev_matched[2 * i1 + 1], r = (float)window_size;
+    if (area_mode == 0) {
+      keypoints_in_area(g2, *grid, kps2, x, y, r, level1, level1, cands);
+    } else {
+      cands.clear();
+      const int minCellX = std::max(0, (int)floor((double)((x - g2->min_x - r) * grid->inv_w)));
+      const int maxCellX = std::min(kGridCols - 1, (int)ceil((double)((x - g2->min_x + r) * grid->inv_w)));
+      const int minCellY = std::max(0, (int)floor((double)((y - g2->min_y - r) * grid->inv_h)));
+      const int maxCellY = std::min(kGridRows - 1, (int)ceil((double)((y - g2->min_y + r) * grid->inv_h)));
+      if (minCellX < kGridCols && maxCellX >= 0 && minCellY < kGridRows && maxCellY >= 0)
+        for (int ix = minCellX; ix <= maxCellX; ix++)
+          for (int iy = minCellY; iy <= maxCellY; iy++)
+            for (int idx : grid->cell[ix][iy]) {
+              if (kps2[idx].octave < level1 || kps2[idx].octave > level1) continue;
+              if (fabsf(kps2[idx].x - x) < r && fabsf(kps2[idx].y - y) < r) cands.push_back(idx);
+            }
+    }
+    if (cands.empty()) continue;
+    int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+    for (int i2 : cands) {
+      const int dist = orc_hamming(desc1 + (size_t)i1 * 32, desc2 + (size_t)i2 * 32);
+      if (matched_distance[i2] <= dist) continue;
+      if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+      else if (dist < bestDist2) bestDist2 = dist;
+    }
+    if (bestDist <= th_low && (float)bestDist < (float)bestDist2 * nn_ratio) {
+      if (matches21[bestIdx2] >= 0) { matches12[matches21[bestIdx2]] = -1; nmatches--; }
+      matches12[i1] = bestIdx2;
+      matches21[bestIdx2] = i1;
+      matched_distance[bestIdx2] = bestDist;
+      nmatches++;
+      if (check_orientation) hist[rotation_bin(kps1[i1].angle, kps2[bestIdx2].angle, false)].push_back(i1);
+    }
+  }
+  if (check_orientation) {
+    int32_t sizes[kHistLen], a, b, c;
+    for (int k = 0; k < kHistLen; k++) sizes[k] = (int32_t)hist[k].size();
+    orc_three_maxima(sizes, kHistLen, &a, &b, &c);
+    for (int k = 0; k < kHistLen; k++)
+      if (k != a && k != b && k != c)
+        for (int i1 : hist[k])
+          if (matches12[i1] >= 0) { matches12[i1] = -1; nmatches--; }
+  }
+  for (int i1 = 0; i1 < n1; i1++)
+    if (matches12[i1] >= 0) {
+      prev_matched[2 * i1] = kps2[matches12[i1]].x;
+      prev_matched[2 * i1 + 1] = kps2[matches12[i1]].y;
+    }
+  delete grid;
+  return nmatches;
 }
 
 /* ------------------------------------------------------------------------------------------------

@@ -118,3 +118,48 @@ def fundamental(seed):
     # scaled so that num^2 / den^2 of :814 straddles 3.841 * sf2 (the reference squares the denominator)
     F = np.array([[0.2, -0.4, 80.0], [0.4, 0.2, -140.0], [60.0, 100.0, 4000.0]], np.float32) * (1 + 0.2 * rng.rand(3, 3).astype(np.float32))
     return F.astype(np.float32), (np.float32(300.0 + 50 * rng.rand()), np.float32(200.0 + 50 * rng.rand()))
+
+
+def init_scene(n_clusters, n_noise, seed, area_mode, window=30, w=W, h=H):
+    """Two frames for the searchForInitialization extra.  Frame 1 has clusters of 1-4 nearby key points whose
+    descriptors are noisy copies of one base descriptor; frame 2 has one key point per cluster carrying the base
+    descriptor, placed where the window predicate of `area_mode` keeps it for every member (mode 0 = the reference's
+    getKeyPointsInArea: |dx| > r and |dy| < r; mode 1 = ORB-SLAM2's |dx| < r and |dy| < r), so members
+    compete for it: later members with a smaller distance steal it, others are blocked by the recorded distance.
+    Unrelated level-0 key points in frame 2 supply second-best distances; ~30 % of frame 1 sits above level 0."""
+    rng = np.random.RandomState(seed)
+    base = synth.synth_descriptors(n_clusters, seed + 1)
+    k1, d1, k2, d2 = [], [], [], []
+    for c in range(n_clusters):
+        cx, cy = rng.uniform(60, w - 60), rng.uniform(60, h - 60)
+        ang = rng.uniform(0, 360)
+        members = rng.randint(1, 5)
+        for _ in range(members):
+            octv = 0 if rng.rand() < 0.7 else rng.randint(1, 8)
+            k1.append((np.floor(cx + rng.uniform(-1.5, 1.5)), np.floor(cy + rng.uniform(-1.5, 1.5)), octv,
+                       (ang + rng.uniform(-3, 3)) % 360.0))
+            d1.append(synth.flip_bits(base[c : c + 1], rng.choice([0.02, 0.05, 0.08, 0.12]), seed * 1000 + len(k1))[0])
+        if area_mode == 0:
+            dx = rng.choice([-1.0, 1.0]) * (window + 2.0 + rng.uniform(0, 6))
+        else:
+            dx = rng.uniform(-10, 10)
+        rot = 0.0 if rng.rand() < 0.8 else rng.uniform(0, 360)  # most pairs share one rotation, some are outliers
+        k2.append((np.floor(cx + dx), np.floor(cy + rng.uniform(-10, 10)), 0, (ang + 20.0 + rot) % 360.0))
+        d2.append(base[c])
+    noise = synth.synth_descriptors(max(n_noise, 1), seed + 2)
+    for i in range(n_noise):
+        k2.append((np.floor(rng.uniform(20, w - 20)), np.floor(rng.uniform(20, h - 20)), 0 if rng.rand() < 0.8 else 1, rng.uniform(0, 360)))
+        d2.append(noise[i])
+
+    def pack(ks):
+        out = np.zeros(len(ks), KP_DTYPE)
+        for i, (x, y, o, a) in enumerate(ks):
+            out[i]["x"], out[i]["y"], out[i]["octave"], out[i]["angle"] = x, y, o, a
+        out["size"] = 31
+        out["response"] = 40
+        out["class_id"] = -1
+        return out
+
+    kps1, kps2 = pack(k1), pack(k2)
+    perm = rng.permutation(len(kps2))  # frame 2 in arbitrary order
+    return kps1, np.ascontiguousarray(np.array(d1, np.uint8)), kps2[perm], np.ascontiguousarray(np.array(d2, np.uint8)[perm])

@@ -169,3 +169,25 @@ def test_triangulation_gates_both_ways():
                                              zeros, s["fv2"], F * 1e4, ep, mc.SF, mc.SF2, False, False)
     assert 0 < n < n_free
     m.close()
+
+
+@pytest.mark.parametrize("area_mode", [0, 1])
+@pytest.mark.parametrize("clusters,noise,seed,check_ori", [(150, 200, 7, True), (600, 800, 9, True), (600, 100, 10, False),
+                                                         (40, 0, 11, True), (0, 50, 12, True)])
+def test_search_for_initialization(area_mode, clusters, noise, seed, check_ori):
+    """EXTRA `ydorb_match_windowed_top2` (the reference has no searchForInitialization): CUDA fixed-point
+    rounds == the sequential restatement in the oracle -- matches, count and updated window centres."""
+    kps1, d1, kps2, d2 = mc.init_scene(clusters, noise, seed, area_mode)
+    g = _geom()
+    prev = np.stack([kps1["x"], kps1["y"]], 1).astype(np.float32) if len(kps1) else np.zeros((0, 2), np.float32)
+    rn, rm12, rprev = orc.search_for_initialization(g, kps1, d1.reshape(-1, 32), kps2, d2, prev, 30, 0.9, 50, check_ori, area_mode)
+    m = OrbMatcher(0.9, check_ori)
+    fr = m.make_frame(kps2, d2, None, bounds=(0, 0, mc.W, mc.H), scale_factors=mc.SF)
+    n, m12, pout = m.searchForInitialization(fr, kps1, d1.reshape(-1, 32), prev, window_size=30, area_mode=area_mode)
+    assert n == rn
+    assert np.array_equal(m12, rm12)
+    assert np.array_equal(pout, rprev)
+    if clusters >= 150:
+        assert n > clusters // 3
+    fr.close()
+    m.close()

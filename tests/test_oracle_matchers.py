@@ -198,3 +198,73 @@ def test_triangulation_oracle_properties():
     n_all, _ = orc.search_for_triangulation(s["k1"], s["d1"], s["rx1"], has1, s["fv1"], s["k2"], s["d2"], s["rx2"], has2,
                                             s["fv2"], F, ep, mc.SF, mc.SF2, False, False)
     assert n_all > 10
+
+
+def _search_for_initialization_py(g2, kps1, desc1, kps2, desc2, prev, window, ratio, th_low, check_ori):
+    """Plain-Python reading of ORB-SLAM2's ORBmatcher::SearchForInitialization on the reference's getKeyPointsInArea."""
+    n1, n2 = len(kps1), len(kps2)
+    m12 = np.full(n1, -1, np.int32)
+    m21 = np.full(n2, -1, np.int64)
+    mdist = np.full(n2, 2 ** 31 - 1, np.int64)
+    hist = [[] for _ in range(30)]
+    prev = prev.copy()
+    nm = 0
+    for i1 in range(n1):
+        if kps1["octave"][i1] > 0:
+            continue
+        cands = orc.keypoints_in_area(g2, kps2, prev[i1, 0], prev[i1, 1], float(window), 0, 0)
+        if len(cands) == 0:
+            continue
+        best, best2, bi = 2 ** 31 - 1, 2 ** 31 - 1, -1
+        for i2 in cands:
+            d = _popcount(desc1[i1], desc2[i2])
+            if mdist[i2] <= d:
+                continue
+            if d < best:
+                best2, best, bi = best, d, i2
+            elif d < best2:
+                best2 = d
+        if best <= th_low and np.float32(best) < np.float32(np.float32(best2) * np.float32(ratio)):
+            if m21[bi] >= 0:
+                m12[m21[bi]] = -1
+                nm -= 1
+            m12[i1] = bi
+            m21[bi] = i1
+            mdist[bi] = best
+            nm += 1
+            if check_ori:
+                hist[_bin(kps1["angle"][i1], kps2["angle"][bi])].append(i1)
+    if check_ori:
+        keep = _three_maxima_py([len(h) for h in hist])
+        for b in range(30):
+            if b not in keep:
+                for i1 in hist[b]:
+                    if m12[i1] >= 0:
+                        m12[i1] = -1
+                        nm -= 1
+    for i1 in range(n1):
+        if m12[i1] >= 0:
+            prev[i1] = (kps2["x"][m12[i1]], kps2["y"][m12[i1]])
+    return nm, m12, prev
+
+
+@pytest.mark.parametrize("check_ori", [True, False])
+def test_search_for_initialization_oracle_vs_python(check_ori):
+    """EXTRA (no reference parity): the C++ restatement agrees with a plain-Python reading; contention
+    (steals and blocked candidates) does occur in the scene."""
+    p = orc.make_params(1000, 1.2, 8, 20)
+    g = orc.make_geom(p, mc.W, mc.H)
+    kps1, d1, kps2, d2 = mc.init_scene(150, 200, 7, 0)
+    prev = np.stack([kps1["x"], kps1["y"]], 1).astype(np.float32)
+    n, m12, pout = orc.search_for_initialization(g, kps1, d1, kps2, d2, prev, 30, 0.9, 50, check_ori, 0)
+    pn, pm12, pprev = _search_for_initialization_py(g, kps1, d1, kps2, d2, prev, 30, 0.9, 50, check_ori)
+    assert n == pn and np.array_equal(m12, pm12) and np.array_equal(pout, pprev)
+    assert n == int((m12 >= 0).sum()) and n > 60
+    # every match is one-to-one
+    used = m12[m12 >= 0]
+    assert len(np.unique(used)) == len(used)
+    # mode 1 (ORB-SLAM2's own window predicate) runs and matches too
+    kps1, d1, kps2, d2 = mc.init_scene(150, 200, 8, 1)
+    prev = np.stack([kps1["x"], kps1["y"]], 1).astype(np.float32)
+    n1_, m1_, _ = orc.search_for_initialization(g, kps1, d1, kps2, d2, prev, 30, 0.9, 50, check_ori, 1)
+    assert n1_ > 60 and n1_ == int((m1_ >= 0).sum())

@@ -170,6 +170,21 @@ class OrbMatcher:
                                          C.byref(n)))
         return n.value, best[: len(q)], match[: frame.n]
 
+    def searchForInitialization(self, frame2, kps1, desc1, prev_matched, window_size=100, nn_ratio=None, th_low=LOW_THD,
+                                area_mode=0):
+        """EXTRA: `north_star` names searchForInitialization, the reference has none (src/orbMatcher.hpp:24-66, SURVEY
+        F12).  ORB-SLAM2's published algorithm on this reference's Frame hooks (ydorb_match_windowed_top2); no reference
+        parity claim.  Returns (n_matches, matches12, prev_matched updated)."""
+        k1 = np.ascontiguousarray(kps1, dtype=KP_DTYPE)
+        d1 = np.ascontiguousarray(desc1, dtype=np.uint8)
+        prev = np.array(prev_matched, dtype=np.float32).reshape(len(k1), 2).copy()
+        m12 = np.full(max(len(k1), 1), -1, np.int32)
+        n = C.c_int32()
+        check(lib().ydorb_match_windowed_top2(frame2._h, ptr(k1), ptr(d1), len(k1), ptr(prev), int(window_size),
+                                              C.c_float(self.ratio if nn_ratio is None else nn_ratio), int(th_low),
+                                              int(self.check_orientation), int(area_mode), ptr(m12), C.byref(n)))
+        return n.value, m12[: len(k1)], prev
+
     def searchByProjectionInLastAndCurrentFrame(self, cur_frame, proj_x, proj_y, proj_right_x, octave, angle, active,
                                                 obs_positive, q_descriptors, scale_factors, thd, motion="none",
                                                 kp_occupied=None):
