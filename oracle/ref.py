@@ -138,3 +138,73 @@ def extract_batch(imgs, threads, n_features=1000, scale=1.2, n_levels=8, ini_th=
         _p(n), threads,
     )
     return kps, desc, n
+
+
+# ---- Frame / OrbMatcher of the compiled reference (oracle/refshim/ref_frame_driver.cpp) -----------------------------
+
+def descriptor_distance(a, b):
+    """OrbMatcher::computeDescriptorsDistance (src/orbMatcher.cpp:11-23) of the compiled reference."""
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    b = np.ascontiguousarray(b, dtype=np.uint8)
+    assert a.size == 32 and b.size == 32
+    return int(lib().ref_descriptor_distance(_p(a), _p(b)))
+
+
+class RefFrame:
+    """A YDORBSLAM::Frame of the compiled reference: either its stereo constructor (src/frame.cpp:57-110: two
+    extractors on two threads, computeStereoMatches, computeImageBounds, assignKeyPointsToGrid) or a frame holding
+    given key points with the grid built by assignKeyPointsToGrid."""
+
+    def __init__(self, handle):
+        self._h = C.c_void_p(handle)
+        n = np.zeros(2, np.int32)
+        lib().ref_frame_sizes(self._h, _p(n))
+        self.n_left, self.n_right = int(n[0]), int(n[1])
+
+    @classmethod
+    def stereo(cls, left, right, fx, fy, cx, cy, bf, depth_thd=35.0, n_features=2000, scale=1.2, n_levels=8, ini_th=20, min_th=7,
+               baseline_before=0.0):
+        """baseline_before: value of the static Frame::m_flt_baseLine when the constructor runs -- 0 for the first frame
+        of a run (maxD = +inf), bf / fx afterwards (src/frame.cpp:101 vs :108)."""
+        left = np.ascontiguousarray(left, dtype=np.uint8)
+        right = np.ascontiguousarray(right, dtype=np.uint8)
+        h, w = left.shape
+        assert right.shape == left.shape
+        lib().ref_frame_stereo_create.restype = C.c_void_p
+        hdl = lib().ref_frame_stereo_create(n_features, C.c_float(scale), n_levels, ini_th, min_th, _p(left), _p(right), w, h, w,
+                                            C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), C.c_float(bf),
+                                            C.c_float(depth_thd), C.c_float(baseline_before))
+        return cls(hdl)
+
+    @classmethod
+    def from_keypoints(cls, kps, bounds):
+        kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+        lib().ref_frame_from_keypoints.restype = C.c_void_p
+        hdl = lib().ref_frame_from_keypoints(_p(kps), len(kps), *(C.c_float(float(v)) for v in bounds))
+        return cls(hdl)
+
+    def get(self):
+        """(kps_left, desc_left, kps_right, desc_right, right_x, depth, bounds)."""
+        kl, kr = np.zeros(self.n_left, KP_DTYPE), np.zeros(self.n_right, KP_DTYPE)
+        dl, dr = np.zeros((self.n_left, 32), np.uint8), np.zeros((self.n_right, 32), np.uint8)
+        rx, dp = np.zeros(self.n_left, np.float32), np.zeros(self.n_left, np.float32)
+        b = np.zeros(4, np.float32)
+        lib().ref_frame_get(self._h, _p(kl), _p(dl), _p(kr), _p(dr), _p(rx), _p(dp), _p(b))
+        return kl, dl, kr, dr, rx, dp, b
+
+    def keypoints_in_area(self, x, y, r, min_level=-1, max_level=-1):
+        out = np.zeros(max(self.n_left, 1), np.int32)
+        n = lib().ref_frame_keypoints_in_area(self._h, C.c_float(x), C.c_float(y), C.c_float(r), int(min_level), int(max_level),
+                                              _p(out), len(out))
+        return out[:n].copy()
+
+    def close(self):
+        if self._h:
+            lib().ref_frame_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

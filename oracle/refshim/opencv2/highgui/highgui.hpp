@@ -1,0 +1,2 @@
+/* stand-in: see opencv.hpp */
+#include "../opencv.hpp"

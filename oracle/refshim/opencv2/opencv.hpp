@@ -29,10 +29,17 @@
 #include <climits>
 #include <cmath>
 #include <cstddef>
+#include <cstdio>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
+#include <iostream>
+#include <list>
+#include <map>
 #include <memory>
+#include <mutex>
+#include <set>
+#include <stdexcept>
 #include <string>
 #include <utility>
 #include <vector>
@@ -208,6 +215,8 @@ class KeyPoint {
 /* ---- Mat ---------------------------------------------------------------------------------------------------- */
 class Mat;
 class MatExpr;
+class FileStorage;  /* persistence is never used on the hot path: declaration only */
+class FileNode;
 
 static inline size_t cvshim_elem_size1(int depth) {
   static const size_t tab[8] = {1, 1, 2, 2, 4, 4, 8, 2};
@@ -487,13 +496,26 @@ static inline MatCommaInitializer_<T> operator<<(const Mat_<T>& m, U v) {
 /* ---- MatExpr: eager value + the two lazily-assigned forms the reference relies on ------------------------------- */
 class MatExpr {
  public:
-  enum Kind { VALUE = 0, FILL = 1, EYE = 2 };
+  enum Kind { VALUE = 0, FILL = 1, EYE = 2, GEMM = 3 };
   Kind kind;
   Mat value;            // VALUE
+  Mat a, b, c;          // GEMM: alpha * a * b (+ c), kept unfused so that `A * B + C` is ONE gemm as in OpenCV
+  double alpha;
   int rows, cols, type; // FILL / EYE
   double fill;
-  MatExpr() : kind(VALUE), rows(0), cols(0), type(0), fill(0) {}
-  MatExpr(const Mat& m) : kind(VALUE), value(m), rows(m.rows), cols(m.cols), type(m.type()), fill(0) {}
+  MatExpr() : kind(VALUE), alpha(1), rows(0), cols(0), type(0), fill(0) {}
+  MatExpr(const Mat& m) : kind(VALUE), value(m), alpha(1), rows(m.rows), cols(m.cols), type(m.type()), fill(0) {}
+  static MatExpr product(const Mat& x, const Mat& y, double al) {
+    MatExpr e;
+    e.kind = GEMM;
+    e.a = x;
+    e.b = y;
+    e.alpha = al;
+    e.rows = x.rows;
+    e.cols = y.cols;
+    e.type = x.type();
+    return e;
+  }
   static MatExpr filled(Kind k, int r, int c, int t, double v) {
     MatExpr e;
     e.kind = k;
@@ -504,9 +526,14 @@ class MatExpr {
     return e;
   }
   /* MatOp_Initializer::assign: m.create(size, type) [keeps a matching buffer], then fill */
+  inline Mat gemm_value() const;
   void assignTo(Mat& m) const {
     if (kind == VALUE) {
       m = value;
+      return;
+    }
+    if (kind == GEMM) {
+      m = gemm_value();
       return;
     }
     m.create(rows, cols, type);
@@ -662,5 +689,8 @@ static inline float fastAtan2(float y, float x) { return orc_fast_atan2(y, x); }
 }  // namespace cv
 
 #include "cvshim_matops.hpp"
+namespace cv {
+inline Mat MatExpr::gemm_value() const { return cvshim_gemm(a, b, alpha, c, 1.0); }
+}
 
 #endif  // YDORB_REFSHIM_OPENCV_HPP

@@ -1,0 +1,163 @@
+/*
+ * ref_frame_driver.cpp -- extern "C" entry points around the REFERENCE's own Frame and OrbMatcher.  TEST INFRASTRUCTURE.
+ *
+ * Linked with /root/reference/src/{frame,orbMatcher,mapPoint,keyFrame,map,keyFrameDatabase,orbExtractor}.cpp and
+ * thirdParty/DBow3/src/{BowVector,FeatureVector,ScoringObject,QueryResults}.cpp, all compiled UNMODIFIED
+ * (oracle/refshim/Makefile) against the OpenCV stand-in.  Nothing here restates the algorithm:
+ *   M0  OrbMatcher::computeDescriptorsDistance          src/orbMatcher.cpp:11-23
+ *   G1  Frame::assignKeyPointsToGrid                     src/frame.cpp:249-264  (through the stereo constructor)
+ *   G2  Frame::getKeyPointsInArea                        src/frame.cpp:337-361
+ *   S1  Frame::computeStereoMatches                      src/frame.cpp:362-472  (through the stereo constructor, which
+ *       also runs the two extractors on two threads, :84-87)
+ * What could NOT be built from reference sources and is stood in for here:
+ *   src/converter.hpp        needs Eigen + g2o's cmake-generated config.h; its include guard is pre-defined and
+ *                            stubs/converter_stub.hpp declares the one member frame.cpp names (defined below)
+ *   DBoW3 Vocabulary.cpp / Database.cpp   need cv::FileStorage (YAML persistence); the members the linked objects
+ *                            reference are defined below and abort if ever called (Frame::computeBoW is not on this path)
+ */
+#include <stdint.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <memory>
+#include <vector>
+
+#include "frame.hpp"
+#include "orbMatcher.hpp"
+
+namespace YDORBSLAM {
+std::vector<cv::Mat> Converter::descriptors_cvMat_cvMatVector(const cv::Mat& d) {
+  std::vector<cv::Mat> v;
+  v.reserve(d.rows);
+  for (int i = 0; i < d.rows; i++) v.push_back(d.row(i));
+  return v;
+}
+}  // namespace YDORBSLAM
+
+namespace {
+
+struct RefKeyPoint {  // = cv::KeyPoint = OrcKeyPoint = YdKeyPoint (28 B)
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+};
+
+void put(const std::vector<cv::KeyPoint>& in, RefKeyPoint* out) {
+  if (!out) return;
+  for (size_t i = 0; i < in.size(); i++) {
+    out[i].x = in[i].pt.x;
+    out[i].y = in[i].pt.y;
+    out[i].size = in[i].size;
+    out[i].angle = in[i].angle;
+    out[i].response = in[i].response;
+    out[i].octave = in[i].octave;
+    out[i].class_id = in[i].class_id;
+  }
+}
+
+void put(const cv::Mat& d, uint8_t* out) {
+  if (!out) return;
+  for (int i = 0; i < d.rows; i++) memcpy(out + (size_t)32 * i, d.ptr(i), 32);
+}
+
+/* protected members are reachable from a derived class; nothing is overridden */
+struct GridFrame : YDORBSLAM::Frame {
+  void assign() { assignKeyPointsToGrid(); }
+};
+
+}  // namespace
+
+extern "C" {
+
+/* M0 */
+int ref_descriptor_distance(const uint8_t* a, const uint8_t* b) {
+  cv::Mat ma(1, 32, CV_8UC1, const_cast<uint8_t*>(a)), mb(1, 32, CV_8UC1, const_cast<uint8_t*>(b));
+  return YDORBSLAM::OrbMatcher::computeDescriptorsDistance(ma, mb);
+}
+
+/* E1 x 2 + S1 + G1: the reference's stereo Frame constructor (src/frame.cpp:57-110) on a rectified pair, zero distortion.
+ * Fresh extractors per call; Frame::m_b_isComputeInit is re-armed so the image bounds follow THIS image. */
+void* ref_frame_stereo_create(int n_features, float scale_factor, int n_levels, int ini_th, int min_th, const uint8_t* left,
+                              const uint8_t* right, int w, int h, int stride, float fx, float fy, float cx, float cy, float bf,
+                              float depth_thd, float baseline_before) {
+  using namespace YDORBSLAM;
+  cv::Mat L(h, w, CV_8UC1, const_cast<uint8_t*>(left), (size_t)stride), R(h, w, CV_8UC1, const_cast<uint8_t*>(right), (size_t)stride);
+  cv::Mat K = cv::Mat::eye(3, 3, CV_32F);
+  K.at<float>(0, 0) = fx;
+  K.at<float>(1, 1) = fy;
+  K.at<float>(0, 2) = cx;
+  K.at<float>(1, 2) = cy;
+  cv::Mat dist = cv::Mat::zeros(4, 1, CV_32F);
+  std::shared_ptr<OrbExtractor> el = std::make_shared<OrbExtractor>(n_features, scale_factor, n_levels, ini_th, min_th);
+  std::shared_ptr<OrbExtractor> er = std::make_shared<OrbExtractor>(n_features, scale_factor, n_levels, ini_th, min_th);
+  Frame::m_b_isComputeInit = true;
+  /* the static base line is assigned AFTER computeStereoMatches (src/frame.cpp:101 vs :108): the first frame of a run
+   * searches with maxD = bf / 0 = +inf, later frames with bf / (bf / fx).  The caller says which frame this is. */
+  Frame::m_flt_baseLine = baseline_before;
+  return new Frame(L, R, 0.0, K, dist, dist, bf, depth_thd, el, er, std::shared_ptr<DBoW3::Vocabulary>());
+}
+
+/* G1 alone: a Frame holding the caller's key points, grid built by the reference's assignKeyPointsToGrid */
+void* ref_frame_from_keypoints(const RefKeyPoint* kps, int n, float min_x, float min_y, float max_x, float max_y) {
+  using namespace YDORBSLAM;
+  GridFrame* f = new GridFrame();
+  f->m_v_keyPoints.resize(n);
+  for (int i = 0; i < n; i++) {
+    cv::KeyPoint k;
+    k.pt.x = kps[i].x;
+    k.pt.y = kps[i].y;
+    k.size = kps[i].size;
+    k.angle = kps[i].angle;
+    k.response = kps[i].response;
+    k.octave = kps[i].octave;
+    k.class_id = kps[i].class_id;
+    f->m_v_keyPoints[i] = k;
+  }
+  f->m_int_keyPointsNum = n;
+  Frame::m_flt_minX = min_x;
+  Frame::m_flt_minY = min_y;
+  Frame::m_flt_maxX = max_x;
+  Frame::m_flt_maxY = max_y;
+  Frame::m_flt_gridCellWidthInv = static_cast<float>(Frame::m_int_gridColsNum) / (max_x - min_x);   // src/frame.cpp:99
+  Frame::m_flt_gridCellHeightInv = static_cast<float>(Frame::m_int_gridRowsNum) / (max_y - min_y);  // src/frame.cpp:100
+  f->assign();
+  return static_cast<Frame*>(f);
+}
+
+void ref_frame_destroy(void* p) { delete static_cast<YDORBSLAM::Frame*>(p); }
+
+/* sizes: n[0] = left key points, n[1] = right key points */
+void ref_frame_sizes(void* p, int32_t* n) {
+  const YDORBSLAM::Frame* f = static_cast<YDORBSLAM::Frame*>(p);
+  n[0] = (int32_t)f->m_v_keyPoints.size();
+  n[1] = (int32_t)f->m_v_rightKeyPoints.size();
+}
+
+/* bounds[4] = minX, minY, maxX, maxY as computeImageBounds left them */
+void ref_frame_get(void* p, RefKeyPoint* kpl, uint8_t* dl, RefKeyPoint* kpr, uint8_t* dr, float* right_x, float* depth,
+                   float* bounds) {
+  const YDORBSLAM::Frame* f = static_cast<YDORBSLAM::Frame*>(p);
+  put(f->m_v_keyPoints, kpl);
+  put(f->m_v_rightKeyPoints, kpr);
+  put(f->m_cvMat_descriptors, dl);
+  put(f->m_cvMat_rightDescriptors, dr);
+  for (size_t i = 0; i < f->m_v_rightXcords.size(); i++) {
+    if (right_x) right_x[i] = f->m_v_rightXcords[i];
+    if (depth) depth[i] = f->m_v_depth[i];
+  }
+  if (bounds) {
+    bounds[0] = YDORBSLAM::Frame::m_flt_minX;
+    bounds[1] = YDORBSLAM::Frame::m_flt_minY;
+    bounds[2] = YDORBSLAM::Frame::m_flt_maxX;
+    bounds[3] = YDORBSLAM::Frame::m_flt_maxY;
+  }
+}
+
+/* G2 */
+int ref_frame_keypoints_in_area(void* p, float x, float y, float r, int min_level, int max_level, int32_t* out, int cap) {
+  const YDORBSLAM::Frame* f = static_cast<YDORBSLAM::Frame*>(p);
+  const std::vector<int> v = f->getKeyPointsInArea(x, y, r, min_level, max_level);
+  for (size_t i = 0; i < v.size() && (int)i < cap; i++) out[i] = v[i];
+  return (int)v.size();
+}
+
+}  // extern "C"

@@ -64,3 +64,53 @@ def test_device_sincosf_equals_libm_everywhere():
         l.orc_sincosf_range(first, cnt, host.ctypes.data_as(C.c_void_p), os.cpu_count() or 8)
         bad += int((dev[: 2 * cnt].view(np.uint32) != host[: 2 * cnt].view(np.uint32)).sum())
     assert bad == 0, f"{bad} of {2 * (hi + 1)} sin/cos values differ from libm"
+
+
+KITTI = dict(fx=718.856, fy=718.856, cx=607.1928, cy=185.2157, bf=386.1448)
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+@pytest.mark.parametrize("w,h,nf,seed,steady", [(1241, 376, 2000, 64, False), (1241, 376, 2000, 65, True), (640, 480, 1000, 66, False)])
+def test_cuda_stereo_frame_matches_compiled_reference(w, h, nf, seed, steady):
+    """CUDA extract x 2 + computeStereoMatches + frame grid == the reference's own stereo Frame constructor
+    (src/frame.cpp:57-110 compiled unmodified): key points, descriptors, rightX, depth, getKeyPointsInArea."""
+    from ydorbslam_b200 import OrbMatcher
+
+    left, right = synth.synth_stereo_pair(w, h, seed)
+    base = np.float32(np.float32(KITTI["bf"]) / np.float32(KITTI["fx"]))
+    f = ref.RefFrame.stereo(left, right, n_features=nf, baseline_before=float(base) if steady else 0.0, **KITTI)
+    rkl, rdl, rkr, rdr, rrx, rdp, bounds = f.get()
+    ex = OrbExtractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=2)
+    kps, desc, n = ex.extract_batch(np.stack([left, right]))
+    kl, dl, kr, dr = kps[0, : n[0]], desc[0, : n[0]], kps[1, : n[1]], desc[1, : n[1]]
+    _same(kl, dl, rkl, rdl)
+    _same(kr, dr, rkr, rdr)
+    m = OrbMatcher()
+    max_d = np.float32(np.float32(KITTI["bf"]) / base) if steady else np.inf
+    rx, dp = m.computeStereoMatches(ex, 0, ex, 1, kl, dl, kr, dr, KITTI["bf"], max_d, 0)
+    assert np.array_equal(rx.view(np.uint32), rrx.view(np.uint32))
+    assert np.array_equal(dp.view(np.uint32), rdp.view(np.uint32))
+    assert (rx >= 0).sum() > 20
+    sf = np.array([np.float32(pow(np.float32(1.2), l)) for l in range(8)], np.float32)
+    fr = m.make_frame(kl, dl, rx, bounds=tuple(float(v) for v in bounds), scale_factors=sf)
+    rng = np.random.RandomState(seed)
+    for _ in range(200):
+        x, y, r = rng.uniform(-20, w + 20), rng.uniform(-20, h + 20), rng.uniform(1, 90)
+        mn, mx = rng.randint(-1, 8), rng.randint(-1, 8)
+        assert np.array_equal(fr.getKeyPointsInArea(x, y, r, mn, mx), f.keypoints_in_area(x, y, r, mn, mx))
+    fr.close(); m.close(); ex.close(); f.close()
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+def test_cuda_hamming_matches_compiled_reference():
+    """M0: the device distance (through ydorb_hamming_top2 on 1-row databases) == OrbMatcher::computeDescriptorsDistance."""
+    from ydorbslam_b200 import OrbMatcher
+
+    d = synth.synth_descriptors(400, 5)
+    m = OrbMatcher()
+    t = m.top2(d[:200], d[200:])
+    for i in range(200):
+        j = int(t["best_idx"][i])
+        assert int(t["best_dist"][i]) == ref.descriptor_distance(d[i], d[200 + j])
+        assert m.computeDescriptorsDistance(d[i], d[200 + i]) == ref.descriptor_distance(d[i], d[200 + i])
+    m.close()

@@ -1,0 +1,75 @@
+"""The compiled REFERENCE (oracle/_ref: src/frame.cpp, src/orbMatcher.cpp ... unmodified, against the OpenCV stand-in)
+vs the oracle restatement, for the rows the extractor tests do not reach:
+  M0 computeDescriptorsDistance, G1 assignKeyPointsToGrid, G2 getKeyPointsInArea, S1 computeStereoMatches
+(the stereo constructor also runs both extractors on two threads, src/frame.cpp:84-87).  CPU only."""
+import numpy as np
+import pytest
+
+from oracle import orc, ref
+from tests import matcher_cases as mc
+from ydorbslam_b200 import synth
+
+pytestmark = pytest.mark.skipif(not ref.available(), reason="oracle/_ref not built and /root/reference absent")
+
+KITTI = dict(fx=718.856, fy=718.856, cx=607.1928, cy=185.2157, bf=386.1448)
+
+
+def test_descriptor_distance_is_popcount():
+    d = synth.synth_descriptors(300, 3)
+    for i in range(0, 299):
+        assert ref.descriptor_distance(d[i], d[i + 1]) == orc.hamming(d[i], d[i + 1]) == int(np.unpackbits(d[i] ^ d[i + 1]).sum())
+    assert ref.descriptor_distance(d[0], d[0]) == 0
+    assert ref.descriptor_distance(np.zeros(32, np.uint8), np.full(32, 255, np.uint8)) == 256
+
+
+def _stereo_case(w, h, nf, seed, baseline_before):
+    left, right = synth.synth_stereo_pair(w, h, seed)
+    f = ref.RefFrame.stereo(left, right, n_features=nf, baseline_before=baseline_before, **KITTI)
+    kl, dl, kr, dr, rx, dp, bounds = f.get()
+    p = orc.make_params(nf, 1.2, 8, 20)
+    ok, od, _ = orc.extract(p, left, cap=nf + 64)
+    rk, rd, _ = orc.extract(p, right, cap=nf + 64)
+    return f, (kl, dl, kr, dr, rx, dp, bounds), p, (ok, od, rk, rd), left, right
+
+
+@pytest.mark.parametrize("w,h,nf,seed,steady", [(1241, 376, 2000, 64, False), (1241, 376, 2000, 65, True), (640, 480, 1000, 66, False),
+                                                (752, 480, 1200, 67, True)])
+def test_stereo_frame_reference_equals_oracle(w, h, nf, seed, steady):
+    """The reference's stereo Frame constructor == oracle extract x 2 + stereo_match(mode 0) -- rightX and depth bit for
+    bit, the leftIdx lag included.  steady: m_flt_baseLine already set by an earlier frame (finite maxD)."""
+    base = np.float32(np.float32(KITTI["bf"]) / np.float32(KITTI["fx"]))
+    f, (kl, dl, kr, dr, rx, dp, bounds), p, (ok, od, rk, rd), left, right = _stereo_case(w, h, nf, seed, float(base) if steady else 0.0)
+    assert np.array_equal(kl, ok) and np.array_equal(dl, od) and np.array_equal(kr, rk) and np.array_equal(dr, rd)
+    assert bounds.tolist() == [0.0, 0.0, float(w), float(h)]
+    (_, pl), (_, pr) = orc.pyramid(p, left), orc.pyramid(p, right)
+    max_d = np.float32(np.float32(KITTI["bf"]) / base) if steady else np.inf
+    orx, odp = orc.stereo_match(p, w, h, pl, pr, ok, od, rk, rd, KITTI["bf"], max_d, 0)
+    assert np.array_equal(orx.view(np.uint32), rx.view(np.uint32))
+    assert np.array_equal(odp.view(np.uint32), dp.view(np.uint32))
+    assert (rx >= 0).sum() > 20  # matches exist
+    f.close()
+
+
+def test_keypoints_in_area_reference_equals_oracle():
+    """G1 + G2 on the frame the stereo constructor built, and on lattice key points with shifted image bounds."""
+    f, (kl, *_), p, (ok, *_), _, _ = _stereo_case(1241, 376, 2000, 64, 0.0)
+    g = orc.make_geom(p, 1241, 376)
+    rng = np.random.RandomState(1)
+    nonempty = 0
+    for _ in range(400):
+        x, y, r = rng.uniform(-20, 1260), rng.uniform(-20, 400), rng.uniform(1, 90)
+        mn, mx = rng.randint(-1, 8), rng.randint(-1, 8)
+        a, o = f.keypoints_in_area(x, y, r, mn, mx), orc.keypoints_in_area(g, ok, x, y, r, mn, mx)
+        assert np.array_equal(a, o), (x, y, r, mn, mx)
+        nonempty += len(a) > 0
+    assert nonempty > 100
+    f.close()
+    kps, _ = mc.synth_keypoints(1500, 9)
+    bounds = (-12.5, -7.25, 655.0, 490.5)  # undistorted bounds need not start at 0 (src/frame.cpp:238-246)
+    f = ref.RefFrame.from_keypoints(kps, bounds)
+    g.min_x, g.min_y, g.max_x, g.max_y = bounds
+    for _ in range(400):
+        x, y, r = rng.uniform(-30, 680), rng.uniform(-30, 510), rng.uniform(1, 60)
+        mn, mx = rng.randint(-1, 8), rng.randint(-1, 8)
+        assert np.array_equal(f.keypoints_in_area(x, y, r, mn, mx), orc.keypoints_in_area(g, kps, x, y, r, mn, mx))
+    f.close()
