@@ -198,6 +198,26 @@ class RefFrame:
                                               _p(out), len(out))
         return out[:n].copy()
 
+    def set_features(self, desc, right_x, scale_factors):
+        """Descriptors, rightX and scale factors of a frame made by from_keypoints (what M1 reads from the frame)."""
+        desc = np.ascontiguousarray(desc, dtype=np.uint8)
+        rx = None if right_x is None else np.ascontiguousarray(right_x, dtype=np.float32)
+        sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+        assert desc.shape == (self.n_left, 32)
+        lib().ref_frame_set_features(self._h, _p(desc), _p(rx), _p(sf), len(sf))
+
+    def search_by_projection(self, mps, mp_desc, mp_obs_positive, kp_occupied, thd, ratio):
+        """OrbMatcher(ratio).searchByProjectionInFrameAndMapPoint(frame, mapPoints, thd) of the compiled reference
+        (src/orbMatcher.cpp:24-64); the MapPoint objects are built by the reference's own constructor."""
+        mps = np.ascontiguousarray(mps, dtype=orc.MPPROJ_DTYPE)
+        mpd = np.ascontiguousarray(mp_desc, dtype=np.uint8)
+        obs = np.ascontiguousarray(mp_obs_positive, dtype=np.uint8)
+        occ = None if kp_occupied is None else np.ascontiguousarray(kp_occupied, dtype=np.uint8)
+        out = np.full(max(self.n_left, 1), -1, np.int32)
+        n = lib().ref_search_by_projection(self._h, _p(mps), _p(mpd), _p(obs), len(mps), _p(occ), C.c_float(thd), C.c_float(ratio),
+                                           _p(out))
+        return n, out[: self.n_left]
+
     def close(self):
         if self._h:
             lib().ref_frame_destroy(self._h)

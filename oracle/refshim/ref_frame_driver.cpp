@@ -9,6 +9,8 @@
  *   G2  Frame::getKeyPointsInArea                        src/frame.cpp:337-361
  *   S1  Frame::computeStereoMatches                      src/frame.cpp:362-472  (through the stereo constructor, which
  *       also runs the two extractors on two threads, :84-87)
+ *   M1  OrbMatcher::searchByProjectionInFrameAndMapPoint src/orbMatcher.cpp:24-64, on MapPoint objects made by the
+ *       reference's own MapPoint(pos, map, frame, idx) constructor (src/mapPoint.cpp:26-51)
  * What could NOT be built from reference sources and is stood in for here:
  *   src/converter.hpp        needs Eigen + g2o's cmake-generated config.h; its include guard is pre-defined and
  *                            stubs/converter_stub.hpp declares the one member frame.cpp names (defined below)
@@ -23,6 +25,7 @@
 #include <vector>
 
 #include "frame.hpp"
+#include "mapPoint.hpp"
 #include "orbMatcher.hpp"
 
 namespace YDORBSLAM {
@@ -64,9 +67,81 @@ struct GridFrame : YDORBSLAM::Frame {
   void assign() { assignKeyPointsToGrid(); }
 };
 
+/* protected state of a MapPoint is reachable from a derived class; nothing is overridden */
+struct ProbePoint : YDORBSLAM::MapPoint {
+  ProbePoint(const cv::Mat& pos, YDORBSLAM::Frame& f, int idx) : YDORBSLAM::MapPoint(pos, std::shared_ptr<YDORBSLAM::Map>(), f, idx) {}
+  void observations(int n) { m_int_observationsNum = n; }
+};
+
+struct RefMapPointProj {  // = OrcMapPointProj = YdMapPointProj
+  float proj_x, proj_y, proj_right_x, view_cos;
+  int32_t level;
+  int32_t active;
+};
+
+void fill_features(YDORBSLAM::Frame* f, const uint8_t* desc, const float* right_x, const float* sf, int n_levels) {
+  const int n = (int)f->m_v_keyPoints.size();
+  f->m_cvMat_descriptors.create(n, 32, CV_8UC1);
+  for (int i = 0; i < n; i++) memcpy(f->m_cvMat_descriptors.ptr(i), desc + (size_t)32 * i, 32);
+  f->m_v_rightXcords.assign(n, -1.0f);
+  if (right_x) f->m_v_rightXcords.assign(right_x, right_x + n);
+  f->m_v_scaleFactors.assign(sf, sf + n_levels);
+  f->m_int_scaleLevelsNum = n_levels;
+  f->m_v_sptrMapPoints.assign(n, std::shared_ptr<YDORBSLAM::MapPoint>());
+}
+
 }  // namespace
 
 extern "C" {
+
+/* descriptors, rightX and scale factors of a frame made by ref_frame_from_keypoints */
+void ref_frame_set_features(void* p, const uint8_t* desc, const float* right_x, const float* sf, int n_levels) {
+  fill_features(static_cast<YDORBSLAM::Frame*>(p), desc, right_x, sf, n_levels);
+}
+
+/* M1.  kp_occupied[i] != 0: slot i holds a map point with observations > 0 before the call.  match_out[i] = index of the
+ * map point the call assigned to key point i, or -1.  Returns the function's return value. */
+int ref_search_by_projection(void* p, const RefMapPointProj* mps, const uint8_t* mp_desc, const uint8_t* mp_obs_positive,
+                             int nmp, const uint8_t* kp_occupied, float thd, float ratio, int32_t* match_out) {
+  using namespace YDORBSLAM;
+  Frame* f = static_cast<Frame*>(p);
+  const int n = (int)f->m_v_keyPoints.size();
+  /* a source frame at the identity pose whose "key points" carry the map points' descriptors: the reference's own
+   * constructor then builds each MapPoint (descriptor copy, normal, distances) */
+  Frame src;
+  src.m_v_keyPoints.assign(nmp + 1, cv::KeyPoint());
+  src.m_v_scaleFactors = f->m_v_scaleFactors;
+  src.m_cvMat_descriptors.create(nmp + 1, 32, CV_8UC1);
+  for (int i = 0; i < nmp; i++) memcpy(src.m_cvMat_descriptors.ptr(i), mp_desc + (size_t)32 * i, 32);
+  memset(src.m_cvMat_descriptors.ptr(nmp), 0, 32);
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  cv::Mat pos = (cv::Mat_<float>(3, 1) << 0.f, 0.f, 1.f);
+  std::vector<std::shared_ptr<MapPoint>> points(nmp);
+  for (int i = 0; i < nmp; i++) {
+    std::shared_ptr<ProbePoint> mp = std::make_shared<ProbePoint>(pos, src, i);
+    mp->observations(mp_obs_positive && mp_obs_positive[i] ? 1 : 0);
+    mp->m_b_isTrackInView = mps[i].active != 0;
+    mp->m_int_trackScaleLevel = mps[i].level;
+    mp->m_flt_trackProjX = mps[i].proj_x;
+    mp->m_flt_trackProjY = mps[i].proj_y;
+    mp->m_flt_trackProjRightX = mps[i].proj_right_x;
+    mp->m_flt_trackViewCos = mps[i].view_cos;
+    points[i] = mp;
+  }
+  std::shared_ptr<ProbePoint> held = std::make_shared<ProbePoint>(pos, src, nmp);
+  held->observations(1);
+  for (int i = 0; i < n; i++)
+    f->m_v_sptrMapPoints[i] = (kp_occupied && kp_occupied[i]) ? std::static_pointer_cast<MapPoint>(held) : std::shared_ptr<MapPoint>();
+  OrbMatcher matcher(ratio, true);
+  const int ret = matcher.searchByProjectionInFrameAndMapPoint(*f, points, thd);
+  std::map<const MapPoint*, int> index;
+  for (int i = 0; i < nmp; i++) index[points[i].get()] = i;
+  for (int i = 0; i < n; i++) {
+    const MapPoint* q = f->m_v_sptrMapPoints[i].get();
+    match_out[i] = (q && q != held.get()) ? index[q] : -1;
+  }
+  return ret;
+}
 
 /* M0 */
 int ref_descriptor_distance(const uint8_t* a, const uint8_t* b) {

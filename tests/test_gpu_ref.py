@@ -114,3 +114,30 @@ def test_cuda_hamming_matches_compiled_reference():
         assert int(t["best_dist"][i]) == ref.descriptor_distance(d[i], d[200 + j])
         assert m.computeDescriptorsDistance(d[i], d[200 + i]) == ref.descriptor_distance(d[i], d[200 + i])
     m.close()
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+@pytest.mark.parametrize("nkp,nmp,th,occupied,seed", [(900, 3000, 3.0, False, 1), (900, 12000, 1.0, True, 2), (400, 500, 5.0, True, 3)])
+def test_cuda_search_by_projection_matches_compiled_reference(nkp, nmp, th, occupied, seed):
+    """M1: CUDA == the reference's own OrbMatcher::searchByProjectionInFrameAndMapPoint (src/orbMatcher.cpp:24-64,
+    compiled unmodified, MapPoint objects from its own constructor)."""
+    from tests import matcher_cases as mc
+    from ydorbslam_b200 import MPPROJ_DTYPE, OrbMatcher
+
+    kps, desc = mc.synth_keypoints(nkp, seed)
+    mp = mc.window_scene(kps, desc, nmp, 50 + seed, th * 4.0)
+    mps = np.zeros(nmp, MPPROJ_DTYPE)
+    for f in ("proj_x", "proj_y", "proj_right_x", "level", "active"):
+        mps[f] = mp[f]
+    mps["view_cos"] = np.float32(0.9)
+    rng = np.random.RandomState(seed)
+    occ = (rng.rand(nkp) < 0.1).astype(np.uint8) if occupied else np.zeros(nkp, np.uint8)
+    f = ref.RefFrame.from_keypoints(kps, (0, 0, mc.W, mc.H))
+    f.set_features(desc, mp["right_x_kp"], mc.SF)
+    rn, rmatch = f.search_by_projection(mps, mp["desc"], mp["obs_positive"], occ, th, 0.8)
+    m = OrbMatcher(0.8)
+    fr = m.make_frame(kps, desc, mp["right_x_kp"], bounds=(0, 0, mc.W, mc.H), scale_factors=mc.SF)
+    n, match = m.searchByProjectionInFrameAndMapPoint(fr, mps, mp["desc"], mp["obs_positive"], th, kp_occupied=occ if occupied else None)
+    assert n == rn and np.array_equal(match, rmatch)
+    assert n > 30
+    fr.close(); m.close(); f.close()

@@ -73,3 +73,32 @@ def test_keypoints_in_area_reference_equals_oracle():
         mn, mx = rng.randint(-1, 8), rng.randint(-1, 8)
         assert np.array_equal(f.keypoints_in_area(x, y, r, mn, mx), orc.keypoints_in_area(g, kps, x, y, r, mn, mx))
     f.close()
+
+
+@pytest.mark.parametrize("nkp,nmp,th,occupied,seed", [(900, 3000, 3.0, False, 1), (900, 12000, 1.0, True, 2), (400, 500, 5.0, True, 3),
+                                                      (40, 2000, 7.0, False, 4), (900, 0, 3.0, False, 5)])
+def test_search_by_projection_reference_equals_oracle(nkp, nmp, th, occupied, seed):
+    """M1: the reference's own OrbMatcher::searchByProjectionInFrameAndMapPoint (on MapPoint objects built by its own
+    constructor) == the oracle's restatement -- assignments per key point and the return value."""
+    kps, desc = mc.synth_keypoints(nkp, seed)
+    p = orc.make_params(1000, 1.2, 8, 20)
+    g = orc.make_geom(p, mc.W, mc.H)
+    # points projected just outside the radius in x (the reference keeps |dx| > r, SURVEY F9); view_cos 0.9 -> factor 4.0
+    mp = mc.window_scene(kps, desc, max(nmp, 1), 50 + seed, th * 4.0)
+    mps = np.zeros(max(nmp, 1), orc.MPPROJ_DTYPE)
+    for f in ("proj_x", "proj_y", "proj_right_x", "level", "active"):
+        mps[f][: len(mp[f])] = mp[f]
+    mps["view_cos"] = np.float32(0.9)
+    mps, mpd, obs = mps[:nmp], mp["desc"][:nmp], mp["obs_positive"][:nmp]
+    rng = np.random.RandomState(seed)
+    right_x = mp["right_x_kp"]
+    occ = (rng.rand(nkp) < 0.1).astype(np.uint8) if occupied else np.zeros(nkp, np.uint8)
+    f = ref.RefFrame.from_keypoints(kps, (0, 0, mc.W, mc.H))
+    f.set_features(desc, right_x, mc.SF)
+    n, match = f.search_by_projection(mps, mpd, obs, occ, th, 0.8)
+    on, omatch = orc.search_by_projection(g, kps, desc, right_x, occ, mps, mpd, obs, th, 0.8)
+    assert n == on
+    assert np.array_equal(match, omatch)
+    if nmp >= 3000:
+        assert n > 30
+    f.close()
