@@ -120,13 +120,36 @@ def make_frames(batch, rank):
 
 
 # ------------------------------------------------------------------------------------------------ reference arm
-def cpu_extract_match(frames, threads):
-    """The oracle port of the reference CPU path on `frames` with `threads` host threads.  Returns seconds."""
+def cpu_kind():
+    """("reference", note) when oracle/_ref (the reference's own translation units compiled unmodified against the OpenCV
+    stand-in, oracle/refshim/Makefile) is present, else ("port", note)."""
+    try:
+        from oracle import ref
+
+        if ref.available():
+            ref.lib()
+            return "reference", ("oracle/_ref: /root/reference/src/orbExtractor.cpp compiled unmodified (-std=c++11 -O3) against the "
+                                 "OpenCV stand-in (scalar resize / FAST / GaussianBlur models, no SIMD OpenCV in this image); "
+                                 "dense top-2 + ratio test = the rule of src/orbMatcher.cpp:319-336 in oracle/ydorb_oracle.cpp")
+    except Exception:  # noqa: BLE001
+        pass
+    return "port", "oracle/ydorb_oracle.cpp (oracle/_ref not shipped)"
+
+
+def cpu_extract_match(frames, threads, kind="port"):
+    """The reference CPU path on `frames` with `threads` host threads: a fresh OrbExtractor(1000,1.2,8,20,7) per frame
+    (kind "reference": the compiled reference; "port": the oracle restatement), then top-2 + ratio test of every frame
+    against the previous one.  Returns seconds."""
     from oracle import orc
 
-    p = orc.make_params(*EXTRACTOR_ARGS[:4])
     t0 = time.perf_counter()
-    kps, desc, n = orc.extract_batch(p, frames, threads, cap=NFEAT + 64)
+    if kind == "reference":
+        from oracle import ref
+
+        kps, desc, n = ref.extract_batch(frames, threads, *EXTRACTOR_ARGS, cap=NFEAT + 64)
+    else:
+        p = orc.make_params(*EXTRACTOR_ARGS[:4])
+        kps, desc, n = orc.extract_batch(p, frames, threads, cap=NFEAT + 64)
     for b in range(len(frames)):
         a = (b - 1) % len(frames)
         t = orc.top2(desc[b, : n[b]], desc[a, : n[a]], 0, threads)
@@ -134,28 +157,77 @@ def cpu_extract_match(frames, threads):
     return time.perf_counter() - t0
 
 
+def cv2_primitives(frames, threads):
+    """Secondary bracket: only the OpenCV calls the reference makes per frame -- resize x7,
+    copyMakeBorder x8, FAST, GaussianBlur x8 -- through real SIMD OpenCV (cv2), in the reference's call order
+    (oracle/cv2_flow.py).  No quadtree, angles or descriptors, so `frames_per_s` is an UPPER bound on what a build of the
+    reference against real OpenCV reaches per `threads`.  FAST is timed twice: per cell from Python as the reference
+    calls it (~800 calls per frame, dominated by call overhead here) and once per level, scaled by the (36/30)^2 pixels
+    the overlapping cells re-read -- the bound uses the latter.  Returns a dict or None without cv2."""
+    try:
+        import cv2
+
+        from oracle import cv2_flow
+    except Exception:  # noqa: BLE001
+        return None
+    cv2.setNumThreads(threads)
+    inv = cv2_flow.ctor(*EXTRACTOR_ARGS[:3])[1]
+    det = cv2.FastFeatureDetector_create(EXTRACTOR_ARGS[3], True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+    t_pyr = t_cell = t_level = t_blur = 0.0
+    pad = cv2_flow.PAD
+    for img in frames:
+        t0 = time.perf_counter()
+        levels = cv2_flow.pyramid(img, inv, EXTRACTOR_ARGS[2])
+        t1 = time.perf_counter()
+        for pl in levels:
+            cv2_flow.level_candidates(pl[pad:-pad, pad:-pad], EXTRACTOR_ARGS[3], EXTRACTOR_ARGS[3])
+        t2 = time.perf_counter()
+        for pl in levels:
+            det.detect(np.ascontiguousarray(pl[pad - 3:-(pad - 3), pad - 3:-(pad - 3)]))
+        t3 = time.perf_counter()
+        for pl in levels:
+            cv2.GaussianBlur(pl, (7, 7), 2, None, 2, cv2.BORDER_REFLECT_101)
+        t4 = time.perf_counter()
+        t_pyr += t1 - t0
+        t_cell += t2 - t1
+        t_level += t3 - t2
+        t_blur += t4 - t3
+    n = len(frames)
+    per_frame = (t_pyr + 1.44 * t_level + t_blur) / n
+    return {"threads": threads, "frames_per_s": 1.0 / per_frame, "ms_per_frame": {
+        "pyramid": 1e3 * t_pyr / n, "fast_per_cell_calls": 1e3 * t_cell / n, "fast_whole_levels": 1e3 * t_level / n,
+        "gaussian_blur": 1e3 * t_blur / n}}
+
+
 def run_reference(args):
     rank, world, _ = dist_env()
     if rank != 0:
         return 0
     threads = os.cpu_count() or 1
-    sample = max(2 * threads, 8)
-    frames = make_frames(sample, 0)
-    cpu_extract_match(frames[: min(threads, sample)], threads)  # page in / warm up
+    kind, note = cpu_kind()
+    frames = make_frames(args.batch, 0)
+    tp = cpu_extract_match(frames[: min(threads, args.batch)], threads, kind)  # page in / warm up, and a speed probe
+    per_frame = tp / min(threads, args.batch)
+    # the GPU arm's own batch per step when the whole run then stays within a few minutes, else a bounded sample
+    budget = 150.0
+    sample = args.batch if per_frame * args.batch * (args.steps + args.warmup) <= budget else \
+        max(threads, int(budget / ((args.steps + args.warmup) * per_frame)))
+    frames = frames[:sample]
     for _ in range(max(args.warmup - 1, 0)):
-        cpu_extract_match(frames, threads)
-    times = [cpu_extract_match(frames, threads) for _ in range(args.steps)]
+        cpu_extract_match(frames, threads, kind)
+    times = [cpu_extract_match(frames, threads, kind) for _ in range(args.steps)]
     total = sum(times)
     value = sample * args.steps / total
     line = {
         "impl": "reference", "metric": "ORB extract+match frames/s (640x480, 1000 kp)", "value": value, "unit": "frames/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"{sample} synthetic 640x480 frames/step (bounded sample of the GPU arm's workload): "
-                               "extractAndCompute(1000,1.2,8,20,7) + Hamming top-2 ratio match vs previous frame, CPU",
-                   "parallelism": f"{threads} host threads"},
-        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": "port",
-                         "sample": f"{sample} frames x {args.steps} steps, oracle/ydorb_oracle.cpp (reference cannot be built: needs OpenCV C++)"},
+        "config": {"workload": f"{sample} synthetic 640x480 frames/step"
+                               + ("" if sample == args.batch else " (bounded sample of the GPU arm's batch)")
+                               + ": extractAndCompute(1000,1.2,8,20,7) + Hamming top-2 ratio match vs previous frame, CPU",
+                   "parallelism": f"{threads} host threads", "same_batch_as_gpu_arm": sample == args.batch},
+        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": kind,
+                         "sample": f"{sample} frames x {args.steps} steps; {note}"},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -231,6 +303,25 @@ def run_gpu(args):
     ms_total = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
     launches = lib().ydorb_kernel_launches() - launches0
+    # sustained figure: the same step looped for >= 2 s of device time (the 20-step region above lasts ~45 ms, a burst)
+    sustained = None
+    if args.sustain_s > 0:
+        ks = max(K, int(args.sustain_s / max(ms_total / K * 1e-3, 1e-6)) + 1)
+        s_sampler = ClockSampler(local)
+        if rank == 0:
+            s_sampler.start()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(stream):
+            s0.record(stream)
+            for _ in range(ks):
+                step()
+            s1.record(stream)
+        barrier()
+        ts_ms = torch.tensor([s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ts_ms, op=dist.ReduceOp.MAX)
+        sustained = {"value": world * B * ks / (float(ts_ms.item()) * 1e-3), "unit": "frames/s", "steps": ks,
+                     "seconds": float(ts_ms.item()) * 1e-3, "clocks": s_sampler.stop() if rank == 0 else None}
     # per-stage times: the same K steps again with the handle's stage events on (serial stages, one stream); the timed
     # region above runs the production path, which overlaps two sub-batches on two streams
     ex.set_profiling(True)
@@ -407,22 +498,36 @@ def run_gpu(args):
         check(lib().ydorb_diag_int_peaks(local, rates, 5))
         int_peaks = dict(zip(["popc", "lop3", "vimnmx3_s16x2", "imad", "lop3_imad_mix"], [r / 1e9 for r in rates]))
 
-    # ---- CPU baseline beside it (rank 0, N=1 only): oracle port on the host cores, bounded sample of ~12 s
+    # ---- CPU baseline beside it (rank 0, N=1 only): the reference's CPU path on the host cores, bounded sample of ~12 s,
+    # plus the two figures BASELINE.md 3 asks for: reference-faithful threading (ONE thread per extractor,
+    # src/frame.cpp:84-87) and the share real SIMD OpenCV would take (cv2 primitives only)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
+        kind, note = cpu_kind()
         probe = frames[: min(threads, B)]
-        tp = cpu_extract_match(probe, threads)
+        tp = cpu_extract_match(probe, threads, kind)
         per_frame = tp / len(probe)
         want = max(len(probe), int(12.0 / max(per_frame, 1e-6)))
         done, ts = 0, 0.0
         while done < want and ts < 30.0:
             chunk = frames[: min(B, want - done)]
-            ts += cpu_extract_match(chunk, threads)
+            ts += cpu_extract_match(chunk, threads, kind)
             done += len(chunk)
-        cpu = {"value": done / ts, "unit": "frames/s", "cores": threads, "kind": "port",
-               "sample": f"{done} frames (the batch's frames, repeated) extract + match vs previous frame, "
-                         f"oracle/ydorb_oracle.cpp with {threads} threads, {ts:.1f} s"}
+        n1 = max(4, min(B, int(3.0 / max(per_frame * threads, 1e-6))))
+        t1 = cpu_extract_match(frames[:n1], 1, kind)
+        cv_one = cv2_primitives(frames[:16], 1)
+        cv_all = cv2_primitives(frames[:32], threads)
+        cpu = {"value": done / ts, "unit": "frames/s", "cores": threads, "kind": kind,
+               "sample": f"{done} frames (the batch's frames, repeated) extract + match vs previous frame, {threads} threads, "
+                         f"{ts:.1f} s; {note}",
+               "one_thread_per_extractor": {"value": n1 / t1, "unit": "frames/s", "cores": 1,
+                                            "sample": f"{n1} frames, one extractor on one thread (the reference's own threading, "
+                                                      "src/frame.cpp:84-87)"},
+               "cv2_primitives_only": None if cv_one is None else {
+                   "one_thread": cv_one, "all_threads": cv_all,
+                   "what": "UPPER bound for a real-OpenCV build: only cv2 4.13 resize / copyMakeBorder / FAST / GaussianBlur in "
+                           "the reference's call order (oracle/cv2_flow.py), no quadtree / angle / descriptor"}}
 
     if rank == 0:
         peak, peak_kind = measured_peak()
@@ -474,11 +579,49 @@ def run_gpu(args):
         if int_peaks:
             pairs = float(n_kp.astype(np.float64).dot(np.roll(n_kp, 1).astype(np.float64)))  # frame b vs frame b-1
             line["int_roofline"] = dict(kernel="k_top2_frames", **ham_roofline(pairs / (match_ms * 1e-3) / 1e9, 1))
+        line["sustained"] = sustained
+        # every stage against the measured HBM peak (algorithmic bytes of SURVEY 8d), and the fused lower bound SURVEY 8d
+        # also names: input + outputs only, 367 200 B/frame
+        tr = {}
         traffic_path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if os.path.exists(traffic_path):
+            tr = json.load(open(traffic_path))
+        sr = {}
+        for i, nm in enumerate(names):
+            gbs = ab[nm] * B / (stage_ms[i] * 1e-3) / 1e9 if stage_ms[i] > 0 else 0.0
+            sr[nm] = {"ms": stage_ms[i], "algorithmic_bytes_per_frame": ab[nm], "achieved_gbs": gbs, "frac_hbm": gbs / peak,
+                      "dram_bytes_per_frame_ncu": tr.get("bytes_per_frame", {}).get(nm)}
+        mbytes = 2 * 32 * NFEAT + 17 * NFEAT  # both descriptor sets read once, top-2 record + flag written
+        sr["match"] = {"ms": match_ms, "algorithmic_bytes_per_frame": mbytes,
+                       "achieved_gbs": mbytes * B / (match_ms * 1e-3) / 1e9, "frac_hbm": mbytes * B / (match_ms * 1e-3) / 1e9 / peak}
+        line["stage_roofline"] = sr
+        fused = W * H + NFEAT * (28 + 32)
+        line["roofline_step"]["fused_lower_bound_bytes_per_frame"] = fused
+        line["roofline_step"]["fused_lower_bound_ms_per_step"] = fused * B / (peak * 1e9) * 1e3
+        line["roofline_step"]["frac_of_fused_bound"] = (fused * B / (peak * 1e9) * 1e3) / (ms_total / K)
+        # FAST is integer-issue bound, not HBM bound: warp instructions per frame from the committed ncu capture of the
+        # same launch shape x frames/s of the stage, against the issue rate (4 schedulers x 1 warp-instruction per clock
+        # per SM) at the SM clock sampled during the timed region; the ALU-pipe utilisation (the binding pipe: VIMNMX / LOP3 /
+        # IADD3 issue at half rate) is the figure ncu measured for the same launch
+        wi = tr.get("warp_inst_per_frame", {}).get("fast")
+        if wi and clocks and clocks.get("sm_mhz"):
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            f_hz = clocks["sm_mhz"] * 1e6
+            rate = wi * B / (stage_ms[1] * 1e-3)
+            alu = tr.get("alu_pipe_pct_ncu", {}).get("fast")
+            px = sum(a * b for a, b in level_sizes(W, H))
+            line["fast_int_roofline"] = {
+                "kernel": "k_fast_blocks", "bound": "instruction issue / ALU pipe", "warp_inst_per_frame": wi,
+                "thread_inst_per_level_pixel": wi * 32 / px, "issue_rate_gwarp_inst_s": rate / 1e9,
+                "issue_peak_gwarp_inst_s": sms * 4 * f_hz / 1e9, "frac_issue": rate / (sms * 4 * f_hz),
+                "frac_alu_pipe_ncu": None if not alu else alu / 100.0,
+                "algorithmic_ops": "per tested pixel pair: reject 21 packed ALU ops (8 min/max antipodal, 4 combine, 9 compare) on "
+                                   "every pair; exact score 106 (two 9-arc trees 2 x 32, two 16-way reductions 2 x 8, 10 shifts, "
+                                   "16 compare / select) on the pairs that pass (DESIGN.md 4)",
+                "source": tr.get("source")}
         if os.path.exists(traffic_path):
             # dram__bytes_read.sum + dram__bytes_write.sum per frame of each stage kernel, from the committed
             # `ncu --set full` capture (profiles/): scaled to this launch's batch
-            tr = json.load(open(traffic_path))
             if names[dom] in tr.get("bytes_per_frame", {}):
                 line["roofline"]["traffic"] = tr["bytes_per_frame"][names[dom]] * B
                 line["roofline"]["traffic_source"] = tr.get("source")
@@ -498,6 +641,7 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--skip-hamming", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sustain-s", type=float, default=2.0, help="also loop the step for this many seconds (0 = off)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

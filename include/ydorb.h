@@ -150,7 +150,8 @@ int ydorb_hamming_top2_frames_device(YdMatcher* m, const uint8_t* d_desc, const 
                                      const int32_t* d_q_frame, const int32_t* d_db_frame, int npairs, YdTop2* d_out,
                                      uint8_t* d_accept, float ratio, int th);
 /* same on the descriptors left on the device by the last ydorb_extract_batch (host API) of `ex`; host in/out.
- * out[p*capacity + i] with capacity = sum of the per-level quotas of `ex` (ydorb_extractor_quotas). */
+ * out[p*capacity + i] with capacity = sum of the per-level quotas of `ex` (ydorb_extractor_quotas).  Only the first
+ * n_out[q_frame[p]] rows of a pair are results; the rows after them come back as {-1, -1, -1, -1} with accept = 0. */
 int ydorb_match_frames(YdMatcher* m, const YdExtractor* ex, const int32_t* q_frame, const int32_t* db_frame, int npairs,
                        float ratio, int th, YdTop2* out, uint8_t* accept);
 /* merge per-shard results (shards[s*nq + i]) into the result of one scan over the whole database */

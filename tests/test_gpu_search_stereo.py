@@ -166,3 +166,49 @@ def test_stereo_lag_window(keep_rows, expect_big_lag):
         assert np.array_equal(rx.view(np.uint32), orx.view(np.uint32))
         assert np.array_equal(dp.view(np.uint32), odp.view(np.uint32))
     exl.close(); exr.close()
+
+
+@pytest.mark.parametrize("pool_cap", ["0", "7", "200"])
+def test_search_by_projection_pool_fallbacks(frame640, pool_cap, monkeypatch):
+    """M1 with the candidate pool forced small (lists that do not fit are walked again every round) or absent (the path
+    of a frame with more than 2^19 key points), and with windows wide enough to span more than 32 grid columns and
+    hold more than 32 candidates: same assignments as the oracle."""
+    img, kps, desc, sf = frame640
+    monkeypatch.setenv("YDORB_SEARCH_POOL_CAP", pool_cap)
+    p = orc.make_params(1000, 1.2, 8, 20)
+    g = orc.make_geom(p, 640, 480)
+    mp = synth.synth_map_points(kps, desc, 4000, 640, 480, 8, seed=77)
+    mps = _mps_array(mp)
+    mps["level"] = np.minimum(mps["level"], 2)  # low levels keep most octaves (SURVEY F9), so windows are well filled
+    rng = np.random.RandomState(2)
+    right_x = np.where(rng.rand(len(kps)) < 0.5, kps["x"] - rng.uniform(0, 30, len(kps)), -1.0).astype(np.float32)
+    occ = (rng.rand(len(kps)) < 0.1).astype(np.uint8)
+    m = OrbMatcher(0.8)
+    fr = m.make_frame(kps, desc, right_x, bounds=(0, 0, 640, 480), scale_factors=sf)
+    for th in (3.0, 40.0):  # th 40: radius 100..230 px -> 10..23 grid columns either side, hundreds of candidates
+        n, match = m.searchByProjectionInFrameAndMapPoint(fr, mps, mp["desc"], mp["obs_positive"], th, kp_occupied=occ)
+        rn, rmatch = orc.search_by_projection(g, kps, desc, right_x, occ, mps, mp["desc"], mp["obs_positive"], th, 0.8)
+        assert n == rn and np.array_equal(match, rmatch), (pool_cap, th)
+    fr.close(); m.close()
+
+
+def test_octaves_outside_the_pyramid_are_rejected(frame640):
+    """Caller-supplied octaves / levels index per-level tables on the device: the host entry points refuse bad ones."""
+    from ydorbslam_b200._lib import YdorbError
+
+    img, kps, desc, sf = frame640
+    m = OrbMatcher(0.8)
+    bad = kps.copy()
+    bad["octave"][3] = 8
+    with pytest.raises(YdorbError):
+        m.make_frame(bad, desc, None, bounds=(0, 0, 640, 480), scale_factors=sf)
+    bad["octave"][3] = -1
+    with pytest.raises(YdorbError):
+        m.make_frame(bad, desc, None, bounds=(0, 0, 640, 480), scale_factors=sf)
+    fr = m.make_frame(kps, desc, None, bounds=(0, 0, 640, 480), scale_factors=sf)
+    mp = synth.synth_map_points(kps, desc, 10, 640, 480, 8, seed=5)
+    mps = _mps_array(mp)
+    mps["level"][4] = 9
+    with pytest.raises(YdorbError):
+        m.searchByProjectionInFrameAndMapPoint(fr, mps, mp["desc"], mp["obs_positive"], 3.0)
+    fr.close(); m.close()

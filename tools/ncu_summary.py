@@ -1,48 +1,71 @@
 """Summarise an `ncu --set full` report of the headline step into profiles/:
-    ncu -i gpurun_out/prof_vN.ncu-rep --page raw --csv > /tmp/raw.csv; python tools/ncu_summary.py /tmp/raw.csv vN "<commit note>"
-writes profiles/r1_ncu_full_vN_summary.txt (per-launch counters) and profiles/ncu_traffic.json (DRAM bytes per frame and
-stage, which bench.py reports as roofline.traffic)."""
+    ncu -i gpurun_out/<rep>.ncu-rep --page raw --csv > /tmp/raw.csv
+    python tools/ncu_summary.py /tmp/raw.csv <tag> <frames_per_launch> "<capture command / commit note>"
+writes profiles/<tag>_ncu_full_summary.txt (per-launch counters of every distinct kernel/grid) and
+profiles/ncu_traffic.json (per frame and stage: DRAM bytes, warp instructions, ALU-pipe warp instructions), which bench.py
+reads for roofline.traffic and the instruction-issue roofline of FAST."""
 import csv
 import json
 import sys
 
-raw, ver, note = sys.argv[1], sys.argv[2], sys.argv[3] if len(sys.argv) > 3 else ""
+raw, tag, fpl = sys.argv[1], sys.argv[2], int(sys.argv[3])
+note = sys.argv[4] if len(sys.argv) > 4 else ""
 rows = list(csv.reader(open(raw)))
 hdr, units = rows[0], rows[1]
 keys = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
         "sm__throughput.avg.pct_of_peak_sustained_elapsed", "smsp__issue_active.avg.pct_of_peak_sustained_active",
         "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
         "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__occupancy_limit_shared_mem",
-        "launch__occupancy_limit_registers", "smsp__inst_executed.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
-        "lts__t_sector_hit_rate.pct"] + [f"smsp__average_warps_issue_stalled_{s}_per_issue_active.ratio" for s in
-                                         ("long_scoreboard", "short_scoreboard", "barrier", "mio_throttle", "math_pipe_throttle", "wait", "not_selected")]
+        "launch__occupancy_limit_registers", "smsp__inst_executed.sum", "sm__inst_executed_pipe_alu.sum",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "lts__t_sector_hit_rate.pct", "sm__cycles_active.avg"] + [
+    f"smsp__average_warps_issue_stalled_{s}_per_issue_active.ratio" for s in
+    ("long_scoreboard", "short_scoreboard", "barrier", "mio_throttle", "math_pipe_throttle", "wait", "not_selected")]
 idx = {h: i for i, h in enumerate(hdr)}
-out = ["# ncu --set full --clock-control none --import-source on, bench.py --steps 1 --warmup 3 --batch 64 --skip-hamming --no-cpu-baseline "
-       "(64 frames 640x480 per step; the device entry splits a batch into two 32-frame sub-batches on two streams)",
-       f"# source report: gpurun_out/prof_{ver}.ncu-rep (round 1, {note}); per-launch values; cold-cache, serialised: compare shares, not absolutes"]
+out = [f"# ncu --set full --clock-control none --import-source on; {note}",
+       f"# {fpl} frames per launch; per-launch values of every distinct (kernel, grid); cold-cache, serialised: compare shares, not absolutes"]
 scale = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+
+def num(r, m):
+    return float(r[idx[m]].replace(",", "")) if m in idx and r[idx[m]] not in ("", "n/a") else 0.0
+
+
 agg, seen = {}, set()
 for r in rows[2:]:
     name = r[idx["Kernel Name"]]
+    key = (name[:40], r[idx["launch__grid_size"]])
+    if key in seen:
+        continue
+    seen.add(key)
     out.append(f"kernel: {name} grid {r[idx['launch__grid_size']]} block {r[idx['launch__block_size']]}")
     for k in keys:
         if k in idx:
             out.append(f"  {k:<78}{r[idx[k]]} {units[idx[k]]}")
     stage = ("pyramid" if "k_pyr" in name else "fast" if "k_fast" in name else
              "quadtree" if ("k_quadtree" in name or "k_cell_scan" in name or "k_qt_" in name) else
-             "describe" if "k_describe" in name else "match" if "k_top2" in name else None)
-    b = sum(float(r[idx[m]]) * scale[units[idx[m]]] for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
-    key = (name[:30], r[idx["launch__grid_size"]])
-    if key in seen:
-        continue
-    seen.add(key)
-    agg.setdefault(stage, [0, []])
-    agg[stage][0] += b
-    agg[stage][1].append((name[:18], r[idx["launch__grid_size"]], round(b / 1e6, 2), r[idx["gpu__time_duration.sum"]]))
-open(f"profiles/r1_ncu_full_{ver}_summary.txt", "w").write("\n".join(out) + "\n")
+             "describe" if "k_describe" in name else "match" if "k_top2" in name else "other")
+    b = sum(num(r, m) * scale.get(units[idx[m]], 1) for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+    a = agg.setdefault(stage, {"bytes": 0.0, "inst": 0.0, "alu": 0.0, "us": 0.0, "kernels": []})
+    a["bytes"] += b
+    a["inst"] += num(r, "smsp__inst_executed.sum")
+    us0 = num(r, "gpu__time_duration.sum")
+    a["alu"] += num(r, "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active") * us0
+    a["issue"] = a.get("issue", 0.0) + num(r, "smsp__issue_active.avg.pct_of_peak_sustained_active") * us0
+    a["w"] = a.get("w", 0.0) + us0
+    us = num(r, "gpu__time_duration.sum") * {"us": 1, "ms": 1e3, "ns": 1e-3, "s": 1e6}.get(units[idx["gpu__time_duration.sum"]], 1)
+    a["us"] += us
+    a["kernels"].append((name.split("(")[0][-28:], r[idx["launch__grid_size"]], round(b / 1e6, 2), round(us, 1)))
+open(f"profiles/{tag}_ncu_full_summary.txt", "w").write("\n".join(out) + "\n")
 for k, v in agg.items():
-    print(k, round(v[0] / 1e6, 2), v[1])
-d = {"source": f"profiles/r1_ncu_full_{ver}_summary.txt (ncu --set full, 32-frame launches; dram__bytes_read.sum + dram__bytes_write.sum; "
-               "writes of a 32-frame launch largely stay in the 126 MB L2 during the kernel)",
-     "frames_per_launch": 32, "bytes_per_frame": {k: v[0] / 32 for k, v in agg.items() if k in ("pyramid", "fast", "quadtree", "describe")}}
+    print(k, f"{v['bytes'] / 1e6:.1f} MB, {v['inst'] / 1e6:.1f} M warp-inst, {v['us']:.0f} us", v["kernels"])
+stages = ("pyramid", "fast", "quadtree", "describe", "match")
+d = {"source": f"profiles/{tag}_ncu_full_summary.txt (ncu --set full, {fpl}-frame launches as in the timed bench; "
+               "dram__bytes_read.sum + dram__bytes_write.sum, smsp__inst_executed.sum; pipe / issue percentages are time-weighted over the stage's kernels)",
+     "frames_per_launch": fpl,
+     "bytes_per_frame": {k: agg[k]["bytes"] / fpl for k in stages if k in agg},
+     "warp_inst_per_frame": {k: agg[k]["inst"] / fpl for k in stages if k in agg},
+     "alu_pipe_pct_ncu": {k: agg[k]["alu"] / agg[k]["w"] for k in stages if k in agg},
+     "issue_active_pct_ncu": {k: agg[k]["issue"] / agg[k]["w"] for k in stages if k in agg},
+     "ncu_us_per_launch": {k: agg[k]["us"] for k in stages if k in agg}}
 json.dump(d, open("profiles/ncu_traffic.json", "w"), indent=1)

@@ -303,6 +303,7 @@ int ydorb_search_for_triangulation(YdMatcher* m, const YdKeyPoint* kps1, const u
   YD_REQUIRE(n_levels >= 1 && n_levels <= kMaxLevels, "n_levels out of range");
   YD_REQUIRE(n1 == 0 || (kps1 && desc1 && right_x1 && has_mp1), "null first-side arrays");
   YD_REQUIRE(n2 == 0 || (kps2 && desc2 && right_x2 && has_mp2), "null second-side arrays");
+  YD_REQUIRE(octaves_in_range(kps1, n1, n_levels) && octaves_in_range(kps2, n2, n_levels), "keypoint octave outside [0, n_levels)");
   BowArgs A;
   memset(&A, 0, sizeof A);
   A.mode = 2;

@@ -22,6 +22,9 @@ constexpr int kQtMapWords = 2048;  // 4^8 bits: occupancy bitmap of the 8 leadin
 void set_error(const std::string& msg);
 void count_launches(int n);  // bookkeeping for ydorb_kernel_launches()
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+// wait for everything enqueued on `s`; sleep = block in the driver on `blocking_event` (created with
+// cudaEventBlockingSync) instead of spinning: batch calls issued from many host threads leave the cores to each other
+int wait_stream(cudaStream_t s, cudaEvent_t blocking_event, bool sleep);
 
 // Programmatic dependent launch: the kernels of one extract call form a chain in one stream.  Launched with the
 // stream-serialization attribute, the next kernel's CTAs are placed while the previous kernel drains and block in
@@ -151,6 +154,7 @@ struct YdExtractor {
   cudaStream_t own_stream;
   cudaStream_t aux_stream;  // second stream of the host entry points: chunk i+1's H2D overlaps chunk i's kernels
   cudaEvent_t ev_fork, ev_join;
+  cudaEvent_t ev_block;     // blocking-sync event of the batched host entry point
   cudaStream_t in_stream, out_stream;   // H2D and D2H copy streams of the chunked host entry point
   cudaEvent_t ev_in[16], ev_done[16];   // per chunk: input resident / results ready
   int profiling;            // record per-stage events

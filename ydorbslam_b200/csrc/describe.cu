@@ -1,8 +1,10 @@
 // E5 computeOrientation (src/orbExtractor.cpp:400-421), E6 GaussianBlur 7x7 sigma 2 (:385-386),
 // E7 computeDescriptors (:422-454) and the output assembly of extractAndCompute (:372-398).
 //
-// One warp per selected keypoint.  The warp stages the 43 x 53 px neighbourhood of the keypoint from the padded,
-// UNBLURRED level (rows y-21..y+21, columns x-26..x+26) in shared memory and derives everything from it:
+// One warp per selected keypoint.  The 43 x 53 px neighbourhood of the keypoint in the padded, UNBLURRED level (rows
+// y-21..y+21, columns x-26..x+26) is fetched by ONE TMA box load (cp.async.bulk.tensor.3d, 80 bytes x 43 rows starting
+// on the 16-byte boundary at or left of column x-26; an mbarrier per buffer, double buffered so that the next
+// keypoint's box is in flight while this one computes) and everything is derived from it:
 //   * IC angle: integer moments over the reference's footprint (half-width table of SURVEY F4: rows +-1..+-10 only
 //     their centre column, rows +-11..+-15 are 53/51/45/39/31 px wide), lane-parallel + shuffle reduction, then
 //     cv::fastAtan2's polynomial with individually rounded fp32 operations;
@@ -12,14 +14,16 @@
 //   * rBRIEF: lane j produces byte j (8 comparisons), coordinates rotated in fp32 without contraction.
 #include <cstdlib>
 #include "kernels.cuh"
+#include "tma.cuh"
 
 namespace ydorb {
 
 constexpr int kDescWarps = 4;
 constexpr int kPatchRows = 43;    // y-21 .. y+21  (18 px pattern reach + 3 px blur reach)
-constexpr int kPatchStride = 68;  // bytes per staged row (15 aligned words cover x-26-a .. x+26, IC-angle reach 26);
-                                  // 17 words: lanes walking down a column hit 32 different banks
-constexpr int kPatchWords = 15;
+constexpr int kPatchStride = 80;  // bytes per staged row = TMA box width: 53 columns + up to 15 bytes of alignment (a box
+                                  // starts on a 16-byte boundary).  20 words: 8 consecutive rows x 4 consecutive words hit
+                                  // 32 different banks, which is how the horizontal blur walks it
+constexpr int kPatchBytes = (kPatchRows * kPatchStride + 127) / 128 * 128;  // TMA destinations are 128-byte aligned
 constexpr int kHbGroups = 11;     // horizontal-blur outputs per row in groups of 4: patch columns 7 .. 50
 constexpr int kHbCols = 4 * kHbGroups;    // horizontal-blur columns kept
 constexpr int kHbColStride = 44;          // u16 per COLUMN: the buffer is stored transposed, hb[col][row], rows 0..42 (+1 pad)
@@ -51,7 +55,9 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
   return a;
 }
 
-constexpr int kDescPf = (kPatchRows * kPatchWords + 31) / 32;  // 32-bit words per lane of one staged neighbourhood
+struct DescMaps {
+  CUtensorMap lv[kMaxLevels];  // u8 [frame][row][byte] per level, box = kPatchStride x kPatchRows
+};
 
 struct DescLevel {      // per-level facts of this frame, built once per CTA
   int quota_base, cnt, out_base, stride;
@@ -62,13 +68,11 @@ struct DescLevel {      // per-level facts of this frame, built once per CTA
 struct DescKp {
   int valid, level, oi, a;
   int4 kp;              // x, y (level coords), response, level
-  const uint32_t* src_al;
-  int stride_w;
+  int bx, by;           // TMA box origin in the padded level (byte column on a 16-byte boundary, row)
 };
 
 __device__ __forceinline__ DescKp desc_setup(const DescLevel* __restrict__ lvl, int n_levels, int n_quota, int slot,
-                                             const int4* __restrict__ sel_frame, const uint8_t* __restrict__ pyr_frame,
-                                             int capacity) {
+                                             const int4* __restrict__ sel_frame, int capacity) {
   DescKp d;
   d.valid = 0;
   if (slot >= n_quota) return d;
@@ -82,33 +86,24 @@ __device__ __forceinline__ DescKp desc_setup(const DescLevel* __restrict__ lvl, 
   if (d.oi >= capacity) return d;
   d.level = level;
   d.kp = sel_frame[slot];
-  // the 19 px reflect-101 pad makes every read legal: keypoints are >= 19 px from the edge, rows are padded to 16 B
-  const uint8_t* src = pyr_frame + L.origin + (ptrdiff_t)(d.kp.y - 21) * L.stride + (d.kp.x - 26);
-  d.a = (int)(reinterpret_cast<uintptr_t>(src) & 3u);
-  d.src_al = reinterpret_cast<const uint32_t*>(src - d.a);
-  d.stride_w = L.stride >> 2;
+  // the 19 px reflect-101 pad makes every byte the kernel reads a pixel of the level: keypoints are >= 16 px from the
+  // edge; the box may reach past the row / buffer end, TMA zero-fills there and nothing reads it
+  const int px = kPad + d.kp.x - 26;  // >= 9
+  d.a = px & 15;
+  d.bx = px - d.a;
+  d.by = kPad + d.kp.y - 21;
   d.valid = 1;
   return d;
 }
 
-// Asynchronous copy HBM -> shared of one 43 x 15-word neighbourhood (cp.async, 4 bytes per request because the source
-// is only word aligned); lane i owns words i, i+32, ... in row-major order.  No registers are held across the copy.
-__device__ __forceinline__ void desc_prefetch(const DescKp& d, int lane, uint8_t* __restrict__ patch) {
-  int r = lane / kPatchWords, w = lane - r * kPatchWords;
-  const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(patch);
-#pragma unroll
-  for (int i = 0; i < kDescPf; i++) {
-    if (r < kPatchRows)
-      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sbase + (uint32_t)(r * kPatchStride + 4 * w)),
-                   "l"(d.src_al + (ptrdiff_t)r * d.stride_w + w)
-                   : "memory");
-    r += 2;
-    w += 2;
-    if (w >= kPatchWords) { w -= kPatchWords; r++; }
+// One elected lane arms the buffer's mbarrier with the box size and issues the TMA load; everybody waits on the barrier.
+__device__ __forceinline__ void desc_prefetch(const DescKp& d, int lane, uint8_t* __restrict__ patch, uint64_t* bar,
+                                              const CUtensorMap* map, int frame) {
+  if (lane == 0) {
+    mbar_expect_tx(bar, (uint32_t)(kPatchRows * kPatchStride));
+    tma_load_3d(patch, map, bar, d.bx, d.by, frame);
   }
-  asm volatile("cp.async.commit_group;" ::: "memory");
 }
-__device__ __forceinline__ void desc_wait_patch() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, int lane, uint8_t* __restrict__ patch,
                              uint16_t* __restrict__ hb, const uint32_t* __restrict__ s_pat, YdKeyPoint* __restrict__ kps,
@@ -117,11 +112,12 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
 // KPW = consecutive keypoint slots a warp works through (8 for batches that fill the GPU; fewer spreads a small batch)
 template <int KPW>
 __global__ void __launch_bounds__(kDescWarps * 32, 5)
-k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, const int4* __restrict__ sel,
-           const int* __restrict__ sel_n, YdKeyPoint* __restrict__ kps, uint8_t* __restrict__ desc, int capacity,
-           int32_t* __restrict__ n_out, int* __restrict__ status) {
+k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict__ g, int frame0,
+           const int4* __restrict__ sel, const int* __restrict__ sel_n, YdKeyPoint* __restrict__ kps,
+           uint8_t* __restrict__ desc, int capacity, int32_t* __restrict__ n_out, int* __restrict__ status) {
   pdl_wait();
-  __shared__ __align__(16) uint8_t s_patch[kDescWarps][2][kPatchRows * kPatchStride];  // double buffered
+  __shared__ __align__(128) uint8_t s_patch[kDescWarps][2][kPatchBytes];  // double buffered TMA destinations
+  __shared__ __align__(8) uint64_t s_bar[kDescWarps][2];
   __shared__ __align__(16) uint16_t s_hb[kDescWarps][kHbCols * kHbColStride];
   __shared__ uint32_t s_pat[256];  // [bit b][lane]: the two pattern points (x0,y0,x1,y1 as s8) of bit b of byte `lane`
   __shared__ DescLevel s_lvl[kMaxLevels];
@@ -130,6 +126,10 @@ k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, 
   for (int i = threadIdx.x; i < 256; i += blockDim.x) {
     const int b = i >> 5, l = i & 31;
     s_pat[i] = reinterpret_cast<const uint32_t*>(c_pattern)[l * 8 + b];
+  }
+  if ((threadIdx.x & 31) == 0) {
+    mbar_init(&s_bar[threadIdx.x >> 5][0], 1);
+    mbar_init(&s_bar[threadIdx.x >> 5][1], 1);
   }
   if (threadIdx.x < n_levels) {
     const int l = threadIdx.x;
@@ -154,22 +154,23 @@ k_describe(const FrameGeomDev* __restrict__ g, const uint8_t* __restrict__ pyr, 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int slot0 = (blockIdx.x * kDescWarps + warp) * KPW;
   const int4* sel_frame = sel + (size_t)frame * n_quota;
-  const uint8_t* pyr_frame = pyr + (size_t)frame * g->pyr_bytes;
   uint16_t* hb = s_hb[warp];
-  // software pipeline over the warp's keypoints: the next neighbourhood is copied HBM -> shared asynchronously into
-  // the other patch buffer while this one computes
-  DescKp cur = desc_setup(s_lvl, n_levels, n_quota, slot0, sel_frame, pyr_frame, capacity);
-  if (cur.valid) desc_prefetch(cur, lane, s_patch[warp][0]);
+  // software pipeline over the warp's keypoints: the next neighbourhood's box is in flight (TMA into the other patch
+  // buffer) while this one computes; buffer b is used by keypoints b, b + 2, ...: its mbarrier phase is (k >> 1) & 1
+  DescKp cur = desc_setup(s_lvl, n_levels, n_quota, slot0, sel_frame, capacity);
+  if (cur.valid) desc_prefetch(cur, lane, s_patch[warp][0], &s_bar[warp][0], &maps.lv[cur.level], frame0 + frame);
   for (int k = 0; k < KPW; k++) {
-    desc_wait_patch();
-    __syncwarp();
     DescKp nxt;
     nxt.valid = 0;
     if (k + 1 < KPW) {
-      nxt = desc_setup(s_lvl, n_levels, n_quota, slot0 + k + 1, sel_frame, pyr_frame, capacity);
-      if (nxt.valid) desc_prefetch(nxt, lane, s_patch[warp][(k + 1) & 1]);
+      nxt = desc_setup(s_lvl, n_levels, n_quota, slot0 + k + 1, sel_frame, capacity);
+      // the other buffer was last read by keypoint k - 1, whose compute ended with a __syncwarp
+      if (nxt.valid) desc_prefetch(nxt, lane, s_patch[warp][(k + 1) & 1], &s_bar[warp][(k + 1) & 1], &maps.lv[nxt.level], frame0 + frame);
     }
-    if (cur.valid) desc_compute(cur, s_lvl[cur.level], frame, lane, s_patch[warp][k & 1], hb, s_pat, kps, desc, capacity);
+    if (cur.valid) {
+      mbar_wait(&s_bar[warp][k & 1], (uint32_t)((k >> 1) & 1));
+      desc_compute(cur, s_lvl[cur.level], frame, lane, s_patch[warp][k & 1], hb, s_pat, kps, desc, capacity);
+    }
     __syncwarp();
     cur = nxt;
   }

@@ -356,6 +356,7 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->aux_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ex->ev_fork, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ex->ev_join, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ex->ev_block, cudaEventDisableTiming | cudaEventBlockingSync);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->in_stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ex->out_stream, cudaStreamNonBlocking);
   for (int i = 0; i < 16 && e == cudaSuccess; i++) {
@@ -420,6 +421,7 @@ void ydorb_extractor_destroy(YdExtractor* ex) {
     if (ex->ev_ring[i / 5][i % 5]) cudaEventDestroy(ex->ev_ring[i / 5][i % 5]);
   if (ex->ev_fork) cudaEventDestroy(ex->ev_fork);
   if (ex->ev_join) cudaEventDestroy(ex->ev_join);
+  if (ex->ev_block) cudaEventDestroy(ex->ev_block);
   if (ex->aux_stream) cudaStreamDestroy(ex->aux_stream);
   if (ex->in_stream) cudaStreamDestroy(ex->in_stream);
   if (ex->out_stream) cudaStreamDestroy(ex->out_stream);
@@ -585,16 +587,17 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
     YD_CUDA(cudaStreamWaitEvent(ex->in_stream, ex->ev_fork, 0));
     YD_CUDA(cudaStreamWaitEvent(ex->out_stream, ex->ev_fork, 0));
     int k = 0;
-    for (int f0 = 0; f0 < batch; k++) {
-      int n = std::min(plan[std::min(k, nplan - 1)], batch - f0);
-      if (k == 15) n = batch - f0;  // event slots: at most 16 sub-batches
+    // an error inside the loop stops the enqueueing but still joins the four streams below: D2H copies already queued
+    // must not write into the caller's buffers after this call has returned
+    auto enqueue = [&](int f0, int n) -> int {
       cudaStream_t st = (k & 1) ? ex->aux_stream : s;
-      if ((rc = upload(f0, n, ex->in_stream)) != YDORB_OK) return rc;
+      int r = upload(f0, n, ex->in_stream);
+      if (r != YDORB_OK) return r;
       YD_CUDA(cudaEventRecord(ex->ev_in[k], ex->in_stream));
       YD_CUDA(cudaStreamWaitEvent(st, ex->ev_in[k], 0));
-      rc = run_stages(ex, f0, n, st, ex->d_images + (size_t)f0 * width * height, width, (size_t)width * height,
-                      ex->d_kps + (size_t)f0 * dcap, ex->d_desc + (size_t)f0 * dcap * 32, dcap, ex->d_nout + f0);
-      if (rc != YDORB_OK) return rc;
+      r = run_stages(ex, f0, n, st, ex->d_images + (size_t)f0 * width * height, width, (size_t)width * height,
+                     ex->d_kps + (size_t)f0 * dcap, ex->d_desc + (size_t)f0 * dcap * 32, dcap, ex->d_nout + f0);
+      if (r != YDORB_OK) return r;
       YD_CUDA(cudaEventRecord(ex->ev_done[k], st));
       YD_CUDA(cudaStreamWaitEvent(ex->out_stream, ex->ev_done[k], 0));
       YD_CUDA(cudaMemcpyAsync(n_out + f0, ex->d_nout + f0, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, ex->out_stream));
@@ -602,13 +605,31 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
                               cudaMemcpyDeviceToHost, ex->out_stream));
       YD_CUDA(cudaMemcpyAsync(descriptors + (size_t)f0 * dcap * 32, ex->d_desc + (size_t)f0 * dcap * 32, (size_t)32 * n * dcap,
                               cudaMemcpyDeviceToHost, ex->out_stream));
+      return YDORB_OK;
+    };
+    int err = YDORB_OK;
+    for (int f0 = 0; f0 < batch && err == YDORB_OK; k++) {
+      int n = std::min(plan[std::min(k, nplan - 1)], batch - f0);
+      if (k == 15) n = batch - f0;  // event slots: at most 16 sub-batches
+      err = enqueue(f0, n);
       f0 += n;
     }
-    // the copy-out stream has waited for every sub-batch of both compute streams: joining it joins everything
-    YD_CUDA(cudaEventRecord(ex->ev_join, ex->out_stream));
-    YD_CUDA(cudaStreamWaitEvent(s, ex->ev_join, 0));
+    // join: the copy-out stream waits for the copy-in stream and both compute streams, the handle's stream for it
+    cudaEventRecord(ex->ev_join, ex->in_stream);
+    cudaStreamWaitEvent(ex->out_stream, ex->ev_join, 0);
+    cudaEventRecord(ex->ev_join, ex->aux_stream);
+    cudaStreamWaitEvent(ex->out_stream, ex->ev_join, 0);
+    cudaEventRecord(ex->ev_join, ex->out_stream);
+    cudaStreamWaitEvent(s, ex->ev_join, 0);
     const auto t_issued = std::chrono::steady_clock::now();
-    YD_CUDA(cudaStreamSynchronize(s));
+    const int wrc = wait_stream(s, ex->ev_block, true);
+    if (err != YDORB_OK) {
+      // a quadtree launch that failed half-way may have left the occupancy bitmap dirty for the next call
+      cudaMemsetAsync(ex->d_qt_bitmap, 0, sizeof(uint32_t) * (size_t)ex->max_batch * kMaxLevels * kQtMapWords, s);
+      cudaStreamSynchronize(s);
+      return err;
+    }
+    if (wrc != YDORB_OK) return wrc;
     if (trace) {
       const auto t_end = std::chrono::steady_clock::now();
       fprintf(stderr, "[ydorb] extract_batch: %d sub-batches, issue %.3f ms, total %.3f ms\n", k,

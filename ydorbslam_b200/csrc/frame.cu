@@ -338,11 +338,13 @@ int ydorb_frame_create(YdMatcher* m, const YdFrameGeom* geom, const YdKeyPoint* 
   YD_REQUIRE(n == 0 || (keypoints && descriptors), "null keypoints/descriptors");
   YD_REQUIRE(geom->n_levels >= 1 && geom->n_levels <= kMaxLevels, "n_levels out of range");
   YD_REQUIRE(geom->max_x > geom->min_x && geom->max_y > geom->min_y, "empty image bounds");
+  YD_REQUIRE(octaves_in_range(keypoints, n, geom->n_levels), "keypoint octave outside [0, n_levels)");
   YD_CUDA(cudaSetDevice(m->device));
   YdFrame* f = new YdFrame();
   memset(f, 0, sizeof *f);
   f->m = m;
   f->n = n;
+  f->n_levels = geom->n_levels;
   f->gp.min_x = geom->min_x;
   f->gp.min_y = geom->min_y;
   f->gp.inv_w = (float)kGridCols / (geom->max_x - geom->min_x);  // src/frame.cpp:99
@@ -362,28 +364,35 @@ int ydorb_frame_create(YdMatcher* m, const YdFrameGeom* geom, const YdKeyPoint* 
   alloc((void**)&f->d_last, sizeof(int) * nn);
   alloc((void**)&f->d_flags, sizeof(int) * 4);
   if (e != cudaSuccess) { ydorb_frame_destroy(f); return cuda_fail(e, "frame allocation", __FILE__, __LINE__); }
-  cudaStream_t s = m->stream;
-  int* cursor = f->d_cell_start + (kGridCells + 1);
-  YD_CUDA(cudaMemsetAsync(f->d_cell_start, 0, sizeof(int) * (kGridCells + 1) * 2, s));
-  if (n > 0) {
-    YD_CUDA(cudaMemcpyAsync(f->d_kps, keypoints, sizeof(YdKeyPoint) * n, cudaMemcpyHostToDevice, s));
-    YD_CUDA(cudaMemcpyAsync(f->d_desc, descriptors, (size_t)32 * n, cudaMemcpyHostToDevice, s));
-    if (right_x) {
-      YD_CUDA(cudaMemcpyAsync(f->d_right_x, right_x, sizeof(float) * n, cudaMemcpyHostToDevice, s));
-    } else {
-      std::vector<float> neg((size_t)n, -1.0f);
-      YD_CUDA(cudaMemcpyAsync(f->d_right_x, neg.data(), sizeof(float) * n, cudaMemcpyHostToDevice, s));
-      YD_CUDA(cudaStreamSynchronize(s));
+  const int rc = [&]() -> int {
+    cudaStream_t s = m->stream;
+    int* cursor = f->d_cell_start + (kGridCells + 1);
+    YD_CUDA(cudaMemsetAsync(f->d_cell_start, 0, sizeof(int) * (kGridCells + 1) * 2, s));
+    if (n > 0) {
+      YD_CUDA(cudaMemcpyAsync(f->d_kps, keypoints, sizeof(YdKeyPoint) * n, cudaMemcpyHostToDevice, s));
+      YD_CUDA(cudaMemcpyAsync(f->d_desc, descriptors, (size_t)32 * n, cudaMemcpyHostToDevice, s));
+      if (right_x) {
+        YD_CUDA(cudaMemcpyAsync(f->d_right_x, right_x, sizeof(float) * n, cudaMemcpyHostToDevice, s));
+      } else {
+        std::vector<float> neg((size_t)n, -1.0f);
+        YD_CUDA(cudaMemcpyAsync(f->d_right_x, neg.data(), sizeof(float) * n, cudaMemcpyHostToDevice, s));
+        YD_CUDA(cudaStreamSynchronize(s));
+      }
+      k_grid_assign<<<(n + 255) / 256, 256, 0, s>>>(f->gp, f->d_kps, n, f->d_cell_of, f->d_cell_start);
     }
-    k_grid_assign<<<(n + 255) / 256, 256, 0, s>>>(f->gp, f->d_kps, n, f->d_cell_of, f->d_cell_start);
+    k_grid_scan<<<1, 1024, 0, s>>>(f->d_cell_start);
+    if (n > 0) {
+      k_grid_fill<<<(n + 255) / 256, 256, 0, s>>>(f->d_cell_of, n, f->d_cell_start, f->d_cell_items, cursor);
+      k_grid_sort<<<(kGridCells + 127) / 128, 128, 0, s>>>(f->d_cell_start, f->d_cell_items);
+    }
+    YD_CUDA(cudaGetLastError());
+    YD_CUDA(cudaStreamSynchronize(s));
+  return YDORB_OK;
+  }();
+  if (rc != YDORB_OK) {  // no leak on a failed copy / launch
+    ydorb_frame_destroy(f);
+    return rc;
   }
-  k_grid_scan<<<1, 1024, 0, s>>>(f->d_cell_start);
-  if (n > 0) {
-    k_grid_fill<<<(n + 255) / 256, 256, 0, s>>>(f->d_cell_of, n, f->d_cell_start, f->d_cell_items, cursor);
-    k_grid_sort<<<(kGridCells + 127) / 128, 128, 0, s>>>(f->d_cell_start, f->d_cell_items);
-  }
-  YD_CUDA(cudaGetLastError());
-  YD_CUDA(cudaStreamSynchronize(s));
   *out = f;
   return YDORB_OK;
 }
@@ -434,7 +443,11 @@ static int search_by_projection_impl(YdFrame* f, const YdMapPointProj* map_point
     io = reinterpret_cast<uint8_t*>(m->d_io);
   }
   // work: candidate pool | live list | previous best | three blocker tables | counters
-  const int pool_cap = n <= (1 << 19) ? (int)std::min<size_t>((size_t)32 * nmp + 65536, (size_t)1 << 30) : 0;
+  // YDORB_SEARCH_POOL_CAP (debug knob, read per call): a tiny pool forces the candidate lists that do not fit onto the
+  // walk-again-every-round path, 0 forces all of them (what a frame with more than 2^19 key points takes) -- the parity
+  // tests run both so that those paths are pinned against the oracle too
+  int pool_cap = n <= (1 << 19) ? (int)std::min<size_t>((size_t)32 * nmp + 65536, (size_t)1 << 30) : 0;
+  if (const char* e = getenv("YDORB_SEARCH_POOL_CAP")) pool_cap = std::max(0, std::min(pool_cap, atoi(e)));
   const size_t w_pool = 0, w_live = w_pool + al(sizeof(uint32_t) * (size_t)std::max(pool_cap, 1)),
                w_prev = w_live + al(sizeof(int3) * (size_t)nmp), w_blk = w_prev + al(sizeof(int) * (size_t)nmp),
                w_ctr = w_blk + al(sizeof(int) * 3 * (size_t)n), w_total = w_ctr + 256;
@@ -521,6 +534,8 @@ int ydorb_search_by_projection(YdFrame* f, const YdMapPointProj* map_points, con
                                float ratio, int32_t* match_out, int32_t* n_matches) {
   YD_REQUIRE(f && match_out && n_matches && n_map_points >= 0, "bad argument");
   YD_REQUIRE(n_map_points == 0 || (map_points && mp_descriptors && mp_obs_positive), "null map point arrays");
+  for (int i = 0; i < n_map_points; i++)
+    YD_REQUIRE(map_points[i].level >= 0 && map_points[i].level < f->n_levels, "map point level outside [0, n_levels)");
   YD_CUDA(cudaSetDevice(f->m->device));
   for (int i = 0; i < f->n; i++) match_out[i] = -1;
   *n_matches = 0;

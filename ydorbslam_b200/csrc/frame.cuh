@@ -19,6 +19,7 @@ struct GridParams {
 struct YdFrame {
   YdMatcher* m;
   int n;
+  int n_levels;
   ydorb::GridParams gp;
   YdKeyPoint* d_kps;
   uint4* d_desc;

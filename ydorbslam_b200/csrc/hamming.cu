@@ -265,23 +265,32 @@ k_top2_frames(const uint4* __restrict__ desc, const int32_t* __restrict__ n_of, 
   }
 }
 
-int matcher_reserve(YdMatcher* m, size_t bytes) {
-  if (bytes <= m->scratch_bytes) return YDORB_OK;
-  if (m->d_scratch) YD_CUDA(cudaFree(m->d_scratch));
-  m->d_scratch = nullptr;
-  m->scratch_bytes = 0;
-  YD_CUDA(cudaMalloc(&m->d_scratch, bytes));
-  m->scratch_bytes = bytes;
+// Scratch is allocated when the handle is created (kInitScratch / kInitIo cover the headline batch) and only ever
+// grows, geometrically: steady-state calls never reach cudaMalloc / cudaFree.
+constexpr size_t kInitScratch = 8u << 20, kInitIo = 32u << 20;
+
+static int grow(void** p, size_t* have, size_t bytes) {
+  if (bytes <= *have) return YDORB_OK;
+  const size_t want = std::max(bytes, 2 * *have);
+  if (*p) YD_CUDA(cudaFree(*p));  // (synchronises the device: happens only while a workload is still growing)
+  *p = nullptr;
+  *have = 0;
+  YD_CUDA(cudaMalloc(p, want));
+  *have = want;
   return YDORB_OK;
 }
 
-int matcher_reserve_io(YdMatcher* m, size_t bytes) {
-  if (bytes <= m->io_bytes) return YDORB_OK;
-  if (m->d_io) YD_CUDA(cudaFree(m->d_io));
-  m->d_io = nullptr;
-  m->io_bytes = 0;
-  YD_CUDA(cudaMalloc(&m->d_io, bytes));
-  m->io_bytes = bytes;
+int matcher_reserve(YdMatcher* m, size_t bytes) { return grow(&m->d_scratch, &m->scratch_bytes, bytes); }
+int matcher_reserve_io(YdMatcher* m, size_t bytes) { return grow(&m->d_io, &m->io_bytes, bytes); }
+
+int wait_stream(cudaStream_t s, cudaEvent_t blocking_event, bool sleep) {
+  static const bool spin = getenv("YDORB_SPIN_WAIT") && atoi(getenv("YDORB_SPIN_WAIT")) != 0;
+  if (!sleep || spin || !blocking_event) {
+    YD_CUDA(cudaStreamSynchronize(s));
+    return YDORB_OK;
+  }
+  YD_CUDA(cudaEventRecord(blocking_event, s));
+  YD_CUDA(cudaEventSynchronize(blocking_event));
   return YDORB_OK;
 }
 
@@ -349,6 +358,18 @@ int ydorb_matcher_create(int device, YdMatcher** out) {
   cudaError_t e = cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking);
   if (e != cudaSuccess) { delete m; return cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__); }
   m->stream = m->own_stream;
+  m->ev_dep = m->ev_block = nullptr;
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_dep, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev_block, cudaEventDisableTiming | cudaEventBlockingSync);
+  if (e == cudaSuccess) e = cudaMalloc(&m->d_scratch, kInitScratch);
+  if (e == cudaSuccess) m->scratch_bytes = kInitScratch;
+  if (e == cudaSuccess) e = cudaMalloc(&m->d_io, kInitIo);
+  if (e == cudaSuccess) m->io_bytes = kInitIo;
+  if (e != cudaSuccess) {
+    const int rc = cuda_fail(e, "matcher allocation", __FILE__, __LINE__);
+    ydorb_matcher_destroy(m);
+    return rc;
+  }
   cudaDeviceProp prop;
   cudaGetDeviceProperties(&prop, device);
   m->sm_count = prop.multiProcessorCount;
@@ -361,6 +382,8 @@ int ydorb_matcher_create(int device, YdMatcher** out) {
 void ydorb_matcher_destroy(YdMatcher* m) {
   if (!m) return;
   cudaSetDevice(m->device);
+  if (m->ev_dep) cudaEventDestroy(m->ev_dep);
+  if (m->ev_block) cudaEventDestroy(m->ev_block);
   if (m->d_scratch) cudaFree(m->d_scratch);
   if (m->d_io) cudaFree(m->d_io);
   if (m->d_pairs) cudaFree(m->d_pairs);
@@ -430,18 +453,20 @@ int ydorb_match_frames(YdMatcher* m, const YdExtractor* ex, const int32_t* q_fra
   int rc = matcher_reserve_io(m, total);
   if (rc != YDORB_OK) return rc;
   uint8_t* io = reinterpret_cast<uint8_t*>(m->d_io);
-  YD_CUDA(cudaStreamSynchronize(ex->stream));  // descriptors were produced on the extractor's stream
+  // descriptors were produced on the extractor's stream: order the two streams on the device, no host wait
+  YD_CUDA(cudaEventRecord(m->ev_dep, ex->stream));
+  YD_CUDA(cudaStreamWaitEvent(m->stream, m->ev_dep, 0));
   YD_CUDA(cudaMemcpyAsync(io + o_q, q_frame, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, m->stream));
   YD_CUDA(cudaMemcpyAsync(io + o_db, db_frame, sizeof(int32_t) * npairs, cudaMemcpyHostToDevice, m->stream));
-  YD_CUDA(cudaMemsetAsync(io + o_out, 0xFF, sizeof(YdTop2) * nres, m->stream));  // unused rows read as idx -1
+  YD_CUDA(cudaMemsetAsync(io + o_out, 0xFF, sizeof(YdTop2) * nres, m->stream));  // rows >= n_out[q_frame]: all fields -1
+  if (accept) YD_CUDA(cudaMemsetAsync(io + o_acc, 0, nres, m->stream));           // ... and never accepted
   rc = ydorb_hamming_top2_frames_device(m, ex->d_desc, ex->d_nout, cap, reinterpret_cast<int32_t*>(io + o_q),
                                         reinterpret_cast<int32_t*>(io + o_db), npairs, reinterpret_cast<YdTop2*>(io + o_out),
                                         accept ? io + o_acc : nullptr, ratio, th);
   if (rc != YDORB_OK) return rc;
   YD_CUDA(cudaMemcpyAsync(out, io + o_out, sizeof(YdTop2) * nres, cudaMemcpyDeviceToHost, m->stream));
   if (accept) YD_CUDA(cudaMemcpyAsync(accept, io + o_acc, nres, cudaMemcpyDeviceToHost, m->stream));
-  YD_CUDA(cudaStreamSynchronize(m->stream));
-  return YDORB_OK;
+  return wait_stream(m->stream, m->ev_block, npairs >= 8);
 }
 
 int ydorb_hamming_top2_device(YdMatcher* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, int ndb, int idx_base,

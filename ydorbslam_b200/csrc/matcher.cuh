@@ -14,9 +14,17 @@ struct YdMatcher {
   size_t io_bytes;
   void* d_pairs;         // fused top-2 scan: [2][pairs_cap] u64 (best | second, all-ones between calls) + ticket counters
   int pairs_cap;
+  cudaEvent_t ev_dep;     // orders the matcher's stream after the extractor's (no host wait in between)
+  cudaEvent_t ev_block;   // blocking-sync event: batch calls sleep on it instead of spinning in cudaStreamSynchronize
 };
 
 namespace ydorb {
 int matcher_reserve(YdMatcher* m, size_t bytes);
 int matcher_reserve_io(YdMatcher* m, size_t bytes);
+// caller-supplied octaves / levels index fixed per-level tables on the device: reject anything outside [0, n_levels)
+inline bool octaves_in_range(const YdKeyPoint* k, int n, int n_levels) {
+  for (int i = 0; i < n; i++)
+    if (k[i].octave < 0 || k[i].octave >= n_levels) return false;
+  return true;
+}
 }  // namespace ydorb

@@ -349,6 +349,8 @@ extern "C" int ydorb_stereo_match(YdMatcher* m, const YdExtractor* left, int lef
   for (int i = 0; i < n_left; i++) { right_x[i] = -1.0f; depth[i] = -1.0f; }
   if (n_left == 0) return YDORB_OK;
   YD_REQUIRE(kp_left && desc_left && (n_right == 0 || (kp_right && desc_right)), "null keypoints/descriptors");
+  YD_REQUIRE(octaves_in_range(kp_left, n_left, left->geom.n_levels) && octaves_in_range(kp_right, n_right, left->geom.n_levels),
+             "keypoint octave outside [0, n_levels)");
   YD_CUDA(cudaSetDevice(m->device));
   // the pyramids were produced on the extractors' streams
   YD_CUDA(cudaStreamSynchronize(left->stream));
