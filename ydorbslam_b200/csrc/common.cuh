@@ -22,8 +22,10 @@ constexpr int kQtMapWords = 2048;  // 4^8 bits: occupancy bitmap of the 8 leadin
 void set_error(const std::string& msg);
 void count_launches(int n);  // bookkeeping for ydorb_kernel_launches()
 int cuda_fail(cudaError_t e, const char* what, const char* file, int line);
-// wait for everything enqueued on `s`; sleep = block in the driver on `blocking_event` (created with
-// cudaEventBlockingSync) instead of spinning: batch calls issued from many host threads leave the cores to each other
+// wait for everything enqueued on `s`.  sleep: first block in the driver on `blocking_event` (created with
+// cudaEventBlockingSync and already recorded by the caller where the last kernel ends), then spin through the rest --
+// batch calls issued from many host threads leave the cores to each other (policy and measurements: hamming.cu)
+bool wait_sleeps();
 int wait_stream(cudaStream_t s, cudaEvent_t blocking_event, bool sleep);
 
 // Programmatic dependent launch: the kernels of one extract call form a chain in one stream.  Launched with the
@@ -181,6 +183,7 @@ struct YdExtractor {
   int n_fast_blocks, fb_max_w, fb_max_h;
   uint8_t* pyr_base;     // d_pyr of the handle itself (frame_view() shifts d_pyr; TMA coordinates count from here)
   CUtensorMap tmap_level[ydorb::kMaxLevels];  // u8 [frame][row][byte] per pyramid level, box = FAST block tile
+  CUtensorMap tmap_desc[ydorb::kMaxLevels];   // same tensors, box = the keypoint neighbourhood of k_describe
   int4* d_cells;         // per-cell ROI {x0,y0,x1,y1} (level coords), [cap_cells]
   int* d_cell_count;     // [max_batch][cap_cells]
   int* d_cell_start;     // [max_batch][cap_cells]

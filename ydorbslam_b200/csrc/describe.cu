@@ -176,7 +176,7 @@ k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict
   }
 }
 
-// pixel (dx, dy) of the keypoint's neighbourhood sits at patch[(dy+21)*64 + dx+26+a]
+// pixel (dx, dy) of the keypoint's neighbourhood sits at patch[(dy+21)*kPatchStride + dx+26+a], a = 0..15
 __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, int lane, uint8_t* __restrict__ patch,
                              uint16_t* __restrict__ hb, const uint32_t* __restrict__ s_pat, YdKeyPoint* __restrict__ kps,
                              uint8_t* __restrict__ desc, int capacity) {
@@ -210,20 +210,33 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
     m01 += __shfl_xor_sync(0xffffffffu, m01, o);
   }
   const float angle = fast_atan2_deg((float)m01, (float)m10);               // :419
-  // ---- E6 horizontal blur pass over rows y-21..y+21 (exact, <= 65280).  A task = 4 adjacent outputs at patch
-  // columns c0..c0+3 with c0 = 7 + 4*grp, i.e. c0-3 word aligned: taps [18 34 48 56 | 48 34 18 0] as two DP4A.
-  // Tasks run down the rows first (conflict-free loads thanks to the 17-word patch stride) and the results are stored
-  // TRANSPOSED, hb[col][row], so that the 7 vertical taps of a sample are 7 consecutive u16.
-  for (int t = lane; t < kPatchRows * kHbGroups; t += 32) {
-    const int grp = t / kPatchRows, r = t - grp * kPatchRows;
-    const uint32_t* pw = reinterpret_cast<const uint32_t*>(patch) + r * (kPatchStride / 4) + 1 + grp;
-    const uint32_t A = pw[0], B = pw[1], C = pw[2];
-    const uint32_t k_lo = 0x38302212u, k_hi = 0x00122230u;  // (18,34,48,56), (48,34,18,0) little endian
-    uint16_t* o = hb + (4 * grp) * kHbColStride + r;
-    o[0] = (uint16_t)__dp4a(A, k_lo, __dp4a(B, k_hi, 0u));
-    o[kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 8), k_lo, __dp4a(__funnelshift_r(B, C, 8), k_hi, 0u));
-    o[2 * kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 16), k_lo, __dp4a(__funnelshift_r(B, C, 16), k_hi, 0u));
-    o[3 * kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 24), k_lo, __dp4a(__funnelshift_r(B, C, 24), k_hi, 0u));
+  // ---- E6 horizontal blur pass over rows y-21..y+21 (exact, <= 65280).  The whole words of the alignment offset
+  // (a >> 2) move the window, the rest (a & 3) is applied when the samples are read.  A task = 4 adjacent outputs at
+  // window columns c0..c0+3 with c0 = 7 + 4*grp, i.e. c0-3 word aligned: taps [18 34 48 56 | 48 34 18 0] as two DP4A.
+  // A warp step covers 8 rows x 4 groups: with the 20-word row stride of the TMA box those 32 loads hit 32 different
+  // banks, and so do the stores of the results, which go TRANSPOSED, hb[col][row], so that the 7 vertical taps of a
+  // sample are 7 consecutive u16.
+  {
+    const uint32_t* pbase = reinterpret_cast<const uint32_t*>(patch) + 1 + (a >> 2);
+    const int r8 = lane & 7, g4 = lane >> 3;
+#pragma unroll 1
+    for (int gb = 0; gb < kHbGroups; gb += 4) {
+      const int grp = gb + g4;
+#pragma unroll 2
+      for (int rb = 0; rb < kPatchRows; rb += 8) {
+        const int r = rb + r8;
+        if (grp < kHbGroups && r < kPatchRows) {
+          const uint32_t* pw = pbase + r * (kPatchStride / 4) + grp;
+          const uint32_t A = pw[0], B = pw[1], C = pw[2];
+          const uint32_t k_lo = 0x38302212u, k_hi = 0x00122230u;  // (18,34,48,56), (48,34,18,0) little endian
+          uint16_t* o = hb + (4 * grp) * kHbColStride + r;
+          o[0] = (uint16_t)__dp4a(A, k_lo, __dp4a(B, k_hi, 0u));
+          o[kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 8), k_lo, __dp4a(__funnelshift_r(B, C, 8), k_hi, 0u));
+          o[2 * kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 16), k_lo, __dp4a(__funnelshift_r(B, C, 16), k_hi, 0u));
+          o[3 * kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 24), k_lo, __dp4a(__funnelshift_r(B, C, 24), k_hi, 0u));
+        }
+      }
+    }
   }
   __syncwarp();
   // ---- E7 rBRIEF
@@ -232,7 +245,7 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
   glibc_sincosf(a_rad, sinB, cosA);                                                  // :426 (float overloads: sincosf)
   // 32-bit view of hb; a sample at (rr, cc) reads rows 18+rr .. 24+rr of column 19+a+cc: four consecutive words,
   // realigned by a funnel shift when the first row is odd, then 4 x DP2A with the tap pairs (18,34)(48,56)(48,34)(18,0)
-  const uint32_t* hw32 = reinterpret_cast<const uint32_t*>(hb) + (26 + a - kHbCol0) * (kHbColStride / 2);
+  const uint32_t* hw32 = reinterpret_cast<const uint32_t*>(hb) + (26 + (a & 3) - kHbCol0) * (kHbColStride / 2);
   uint32_t byte = 0;
 #pragma unroll
   for (int b = 0; b < 8; b++) {
@@ -285,10 +298,13 @@ int launch_describe(const YdExtractor* ex, int batch, YdKeyPoint* d_kps, uint8_t
   const long long warps8 = (long long)((ex->geom.n_quota + 7) / 8) * batch;
   static const int force = getenv("YDORB_DESC_KPW") ? atoi(getenv("YDORB_DESC_KPW")) : 0;  // tuning knob
   const int kpw = force ? force : warps8 >= 148 * 32 ? 8 : 1;  // measured: bench.py --batch 16/64/256, tools/latency_probe.py
+  DescMaps maps;
+  for (int l = 0; l < kMaxLevels; l++) maps.lv[l] = ex->tmap_desc[l];
+  const int frame0 = (int)((ex->d_pyr - ex->pyr_base) / ex->geom.pyr_bytes);
   auto launch = [&](auto kernel, int k) -> int {
     const int per_cta = kDescWarps * k;
     dim3 grid((ex->geom.n_quota + per_cta - 1) / per_cta, batch);
-    YD_CUDA(launch_chain(kernel, grid, dim3(kDescWarps * 32), 0, s, ex->d_geom, ex->d_pyr, ex->d_sel, ex->d_sel_n, d_kps, d_desc,
+    YD_CUDA(launch_chain(kernel, grid, dim3(kDescWarps * 32), 0, s, maps, ex->d_geom, frame0, ex->d_sel, ex->d_sel_n, d_kps, d_desc,
                          capacity, d_nout, ex->d_status));
     return YDORB_OK;
   };
@@ -298,6 +314,11 @@ int launch_describe(const YdExtractor* ex, int batch, YdKeyPoint* d_kps, uint8_t
   count_launches(1);
   YD_CUDA(cudaGetLastError());
   return YDORB_OK;
+}
+
+void describe_box(int* box_w, int* box_h) {
+  *box_w = kPatchStride;
+  *box_h = kPatchRows;
 }
 
 }  // namespace ydorb

@@ -209,6 +209,14 @@ static int set_size(YdExtractor* ex, int w, int h) {
                             (uint32_t)box_h);
       if (rc != YDORB_OK) return rc;
     }
+    describe_box(&box_w, &box_h);
+    for (int l = 0; l < hg.g.n_levels; l++) {
+      const LevelGeom& lv = hg.g.lv[l];
+      rc = tma_encode_u8_3d(&ex->tmap_desc[l], ex->pyr_base + lv.offset, (uint64_t)lv.stride, (uint64_t)(lv.h + 2 * kPad),
+                            (uint64_t)ex->max_batch, (uint64_t)lv.stride, (uint64_t)hg.g.pyr_bytes, (uint32_t)box_w,
+                            (uint32_t)box_h);
+      if (rc != YDORB_OK) return rc;
+    }
   }
   YD_CUDA(cudaStreamSynchronize(ex->stream));  // host vectors go out of scope
   ex->cur_w = w;
@@ -598,6 +606,7 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
       r = run_stages(ex, f0, n, st, ex->d_images + (size_t)f0 * width * height, width, (size_t)width * height,
                      ex->d_kps + (size_t)f0 * dcap, ex->d_desc + (size_t)f0 * dcap * 32, dcap, ex->d_nout + f0);
       if (r != YDORB_OK) return r;
+      if (f0 + n >= batch && wait_sleeps()) YD_CUDA(cudaEventRecord(ex->ev_block, st));  // last sub-batch's kernels end here
       YD_CUDA(cudaEventRecord(ex->ev_done[k], st));
       YD_CUDA(cudaStreamWaitEvent(ex->out_stream, ex->ev_done[k], 0));
       YD_CUDA(cudaMemcpyAsync(n_out + f0, ex->d_nout + f0, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, ex->out_stream));
@@ -622,7 +631,7 @@ int ydorb_extract_batch(YdExtractor* ex, const uint8_t* images, int width, int h
     cudaEventRecord(ex->ev_join, ex->out_stream);
     cudaStreamWaitEvent(s, ex->ev_join, 0);
     const auto t_issued = std::chrono::steady_clock::now();
-    const int wrc = wait_stream(s, ex->ev_block, true);
+    const int wrc = wait_stream(s, ex->ev_block, err == YDORB_OK);
     if (err != YDORB_OK) {
       // a quadtree launch that failed half-way may have left the occupancy bitmap dirty for the next call
       cudaMemsetAsync(ex->d_qt_bitmap, 0, sizeof(uint32_t) * (size_t)ex->max_batch * kMaxLevels * kQtMapWords, s);

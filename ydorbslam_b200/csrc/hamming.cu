@@ -10,6 +10,8 @@
 // The database is split into chunks across blockIdx.y so the grid fills 148 SMs; every CTA folds its chunk's top-2 into
 // one (best, second) pair per query with 64-bit atomicMin (order-free), and the last CTA of a query block unpacks the
 // pairs -- one launch (k_top2_sharded).  The same kernel carries the cross-GPU exchange and merge (shard.cu).
+#include <time.h>
+
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -283,14 +285,25 @@ static int grow(void** p, size_t* have, size_t bytes) {
 int matcher_reserve(YdMatcher* m, size_t bytes) { return grow(&m->d_scratch, &m->scratch_bytes, bytes); }
 int matcher_reserve_io(YdMatcher* m, size_t bytes) { return grow(&m->d_io, &m->io_bytes, bytes); }
 
-int wait_stream(cudaStream_t s, cudaEvent_t blocking_event, bool sleep) {
+// Waiting policy of the batched host entry points.  Measured on a B200, 256 frames per call, one calling thread:
+// spinning in cudaStreamSynchronize 91.1 k frames/s; cudaEventSynchronize on a cudaEventBlockingSync event 73.8 k (the
+// interrupt-driven wake-up is ~0.3 ms late, twice per step), also when only the kernels are slept through (74.7 k).
+// But spinning keeps one core per calling thread busy for the whole 2-3 ms call, which starves 8 ranks x 4 threads on a
+// 32-core host.  So: POLL the event recorded where the last kernel ends with short timed sleeps (the core is free in
+// between), then SPIN through the remaining device-to-host copy, which hides the last sleep.
+// YDORB_SPIN_WAIT=1 spins all the way, YDORB_SPIN_WAIT=0 (default) is the hybrid.
+bool wait_sleeps() {
   static const bool spin = getenv("YDORB_SPIN_WAIT") && atoi(getenv("YDORB_SPIN_WAIT")) != 0;
-  if (!sleep || spin || !blocking_event) {
-    YD_CUDA(cudaStreamSynchronize(s));
-    return YDORB_OK;
+  return !spin;
+}
+int wait_stream(cudaStream_t s, cudaEvent_t blocking_event, bool sleep) {
+  if (sleep && wait_sleeps() && blocking_event) {  // recorded by the caller
+    const timespec nap = {0, 30 * 1000};
+    cudaError_t e;
+    while ((e = cudaEventQuery(blocking_event)) == cudaErrorNotReady) nanosleep(&nap, nullptr);
+    YD_CUDA(e);
   }
-  YD_CUDA(cudaEventRecord(blocking_event, s));
-  YD_CUDA(cudaEventSynchronize(blocking_event));
+  YD_CUDA(cudaStreamSynchronize(s));
   return YDORB_OK;
 }
 
@@ -464,9 +477,11 @@ int ydorb_match_frames(YdMatcher* m, const YdExtractor* ex, const int32_t* q_fra
                                         reinterpret_cast<int32_t*>(io + o_db), npairs, reinterpret_cast<YdTop2*>(io + o_out),
                                         accept ? io + o_acc : nullptr, ratio, th);
   if (rc != YDORB_OK) return rc;
+  const bool sleep = npairs >= 8 && wait_sleeps();
+  if (sleep) YD_CUDA(cudaEventRecord(m->ev_block, m->stream));  // where the kernel ends: sleep until here, spin through the copies
   YD_CUDA(cudaMemcpyAsync(out, io + o_out, sizeof(YdTop2) * nres, cudaMemcpyDeviceToHost, m->stream));
   if (accept) YD_CUDA(cudaMemcpyAsync(accept, io + o_acc, nres, cudaMemcpyDeviceToHost, m->stream));
-  return wait_stream(m->stream, m->ev_block, npairs >= 8);
+  return wait_stream(m->stream, m->ev_block, sleep);
 }
 
 int ydorb_hamming_top2_device(YdMatcher* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, int ndb, int idx_base,

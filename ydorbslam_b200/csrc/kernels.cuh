@@ -23,6 +23,8 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s);
 int launch_describe(const YdExtractor* ex, int batch, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity,
                     int32_t* d_nout, cudaStream_t s);
 
+void describe_box(int* box_w, int* box_h);  // TMA box of k_describe's patch loads
+
 // status bits written by kernels into YdExtractor::d_status
 constexpr int kStatusRawOverflow = 1;   // candidate buffer too small
 constexpr int kStatusSortDepth = 2;     // std::sort emulation hit an internal limit
