@@ -311,9 +311,12 @@ int wait_stream(cudaStream_t s, cudaEvent_t blocking_event, bool sleep) {
 int top2_grid(const YdMatcher* m, int nq, int n_rows, int* qblocks, int* nchunks, int* chunk_rows) {
   const int qb = (nq + kTopQblock - 1) / kTopQblock;
   int nc = std::max(1, (m->top_ctas_per_sm * m->sm_count + qb - 1) / qb);
-  nc = std::min(nc, std::max(1, (n_rows + 1023) / 1024));
+  nc = std::min(nc, std::max(1, (n_rows + 255) / 256));  // at least one shared-memory tile of rows per chunk
+  // rows per chunk in steps of 32, not of whole shared-memory tiles (the tile loop takes partial tiles): with 256-row
+  // steps a 125 k-row shard got 768-row chunks where 563 fill the GPU evenly, and the busiest SM carried 14 % more
+  // rows than the average -- 2000 x 125 k took 0.416 ms instead of the 0.33 ms an eighth of 1 M rows should take
   int cr = (n_rows + nc - 1) / nc;
-  cr = std::max((cr + kTopTile - 1) / kTopTile * kTopTile, kTopTile);
+  cr = std::max((cr + 31) / 32 * 32, 32);
   YD_REQUIRE(cr < (1 << 23), "database shard too large for one call (max 8M rows per chunk)");
   *qblocks = qb;
   *nchunks = std::max(1, (n_rows + cr - 1) / cr);
