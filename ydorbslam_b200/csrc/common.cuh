@@ -183,6 +183,7 @@ struct YdExtractor {
   int n_fast_blocks, fb_max_w, fb_max_h;
   uint8_t* pyr_base;     // d_pyr of the handle itself (frame_view() shifts d_pyr; TMA coordinates count from here)
   CUtensorMap tmap_level[ydorb::kMaxLevels];  // u8 [frame][row][byte] per pyramid level, box = FAST block tile
+  CUtensorMap tmap_pyr[ydorb::kMaxLevels];    // [l]: level l-1 with the box of k_pyr_resize's source rows (l >= 1)
   CUtensorMap tmap_desc[ydorb::kMaxLevels];   // same tensors, box = the keypoint neighbourhood of k_describe
   int4* d_cells;         // per-cell ROI {x0,y0,x1,y1} (level coords), [cap_cells]
   int* d_cell_count;     // [max_batch][cap_cells]

@@ -209,6 +209,15 @@ static int set_size(YdExtractor* ex, int w, int h) {
                             (uint32_t)box_h);
       if (rc != YDORB_OK) return rc;
     }
+    for (int l = 1; l < hg.g.n_levels; l++) {
+      const LevelGeom& sv = hg.g.lv[l - 1];
+      pyramid_box(hg.g, l, &box_w, &box_h);
+      if (box_w == 0) continue;
+      rc = tma_encode_u8_3d(&ex->tmap_pyr[l], ex->pyr_base + sv.offset, (uint64_t)sv.stride, (uint64_t)(sv.h + 2 * kPad),
+                            (uint64_t)ex->max_batch, (uint64_t)sv.stride, (uint64_t)hg.g.pyr_bytes, (uint32_t)box_w,
+                            (uint32_t)box_h);
+      if (rc != YDORB_OK) return rc;
+    }
     describe_box(&box_w, &box_h);
     for (int l = 0; l < hg.g.n_levels; l++) {
       const LevelGeom& lv = hg.g.lv[l];

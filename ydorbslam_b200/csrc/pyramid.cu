@@ -11,6 +11,7 @@
 #include <algorithm>
 
 #include "kernels.cuh"
+#include "tma.cuh"
 
 namespace ydorb {
 
@@ -131,15 +132,21 @@ struct PyrArgs {
 #ifndef YD_PYR_STAGE_ILP
 #define YD_PYR_STAGE_ILP 3
 #endif
-template <int SS>  // SS: row stride (bytes) of the staged source copies
-__global__ void __launch_bounds__(256) k_pyr_resize(const PyrArgs a, const int* __restrict__ tab_ofs,
-                                                    const short2* __restrict__ tab_a, uint8_t* __restrict__ pyr) {
+struct PyrMap {
+  CUtensorMap m;  // source level as u8 [frame][row][byte], box = 192 bytes x nsr_cap rows
+};
+
+template <int SS>  // SS: row stride (bytes) of the staged source copies; 192 (the reference's scale factors): staged by TMA
+__global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrMap map, int frame0, const PyrArgs a,
+                                                    const int* __restrict__ tab_ofs, const short2* __restrict__ tab_a,
+                                                    uint8_t* __restrict__ pyr) {
   pdl_wait();
-  extern __shared__ __align__(16) uint8_t smem[];
-  int* s_h = reinterpret_cast<int*>(smem);                                   // [nsr_cap][kPyHS]
-  int4* s_row = reinterpret_cast<int4*>(s_h + a.nsr_cap * kPyHS);            // [kPyMaxTH] {r0*kPyHS, r1*kPyHS, b0, b1}
-  uint8_t* s_a = reinterpret_cast<uint8_t*>(s_row + kPyMaxTH);               // [nsr_cap][SS]
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* s_a = smem;                                                       // [nsr_cap][SS]  (TMA destination)
   uint8_t* s_b = s_a + a.nsr_cap * SS;                                       // [nsr_cap][SS], s_b[j] = s_a[j+1]
+  int* s_h = reinterpret_cast<int*>(s_b + a.nsr_cap * SS);                   // [nsr_cap][kPyHS]
+  int4* s_row = reinterpret_cast<int4*>(s_h + a.nsr_cap * kPyHS);            // [kPyMaxTH] {r0*kPyHS, r1*kPyHS, b0, b1}
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_row + kPyMaxTH);
   const int tid = threadIdx.x;
   const int px0 = blockIdx.x * kPyTW, py0 = blockIdx.y * a.th;
   const int pw = a.dw + 2 * kPad, ph = a.dh + 2 * kPad;
@@ -149,7 +156,7 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const PyrArgs a, const int* 
   // tile geometry precomputed on the host (pyramid_tile_tables): nothing below depends on the thread
   const int4* td = reinterpret_cast<const int4*>(tab_ofs + a.tile_base);
   const int4 X0 = __ldg(td + 2 * blockIdx.x), X1 = __ldg(td + 2 * blockIdx.x + 1), Y = __ldg(td + 2 * gridDim.x + blockIdx.y);
-  const int lo = X0.x, hi = X0.y, org = X0.z, sxa = X0.w, nchunk = X1.x;
+  const int sxa = X0.w, nchunk = X1.x;
   const int sy_lo = Y.x, nsr = Y.y;
 
   if (tid < a.th) {
@@ -163,87 +170,87 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const PyrArgs a, const int* 
     }
     s_row[tid] = r;
   }
-  if (tid < nsr) s_h[tid * kPyHS + kPyHS - 1] = 0;
   // ---- stage
-  constexpr int kStageIlp = YD_PYR_STAGE_ILP;  // rows whose loads are in flight together per thread
-  for (int c = tid & 15; c < nchunk; c += 16) {
-    for (int r0 = tid >> 4; r0 < nsr; r0 += 16 * kStageIlp) {
-      uint4 v[kStageIlp];
-      uint32_t nx[kStageIlp];
-#pragma unroll
-      for (int k = 0; k < kStageIlp; k++) {
-        const int r = r0 + 16 * k;
-        if (r < nsr) {
-          const uint8_t* gp = src0 + (long long)(sy_lo + r) * a.sstride + sxa + 16 * c;
-          v[k] = *reinterpret_cast<const uint4*>(gp);
-          nx[k] = (c + 1 < nchunk) ? *reinterpret_cast<const uint32_t*>(gp + 16) : 0u;
-        }
+  if (SS == 192) {
+    // one TMA box load of the source rows (192 bytes x nsr_cap rows from the 16-byte aligned column the host chose);
+    // copy B, shifted by one byte, is then derived from shared memory
+    if (tid == 0) mbar_init(bar, 1);
+    __syncthreads();
+    if (tid == 0) {
+      mbar_expect_tx(bar, (uint32_t)(SS * a.nsr_cap));
+      tma_load_3d(s_a, &map.m, bar, kPad + sxa, kPad + sy_lo, frame0 + (int)blockIdx.z);
+    }
+    mbar_wait(bar, 0);
+    for (int c = tid & 15; c < nchunk; c += 16)
+      for (int r = tid >> 4; r < nsr; r += 16) {
+        const uint4 v = *reinterpret_cast<const uint4*>(s_a + r * SS + 16 * c);
+        const uint32_t nx = (c + 1 < nchunk) ? *reinterpret_cast<const uint32_t*>(s_a + r * SS + 16 * c + 16) : 0u;
+        *reinterpret_cast<uint4*>(s_b + r * SS + 16 * c) =
+            make_uint4(__funnelshift_r(v.x, v.y, 8), __funnelshift_r(v.y, v.z, 8), __funnelshift_r(v.z, v.w, 8),
+                       __funnelshift_r(v.w, nx, 8));
       }
+  } else {
+    constexpr int kStageIlp = YD_PYR_STAGE_ILP;  // rows whose loads are in flight together per thread
+    for (int c = tid & 15; c < nchunk; c += 16) {
+      for (int r0 = tid >> 4; r0 < nsr; r0 += 16 * kStageIlp) {
+        uint4 v[kStageIlp];
+        uint32_t nx[kStageIlp];
 #pragma unroll
-      for (int k = 0; k < kStageIlp; k++) {
-        const int r = r0 + 16 * k;
-        if (r < nsr) {
-          *reinterpret_cast<uint4*>(s_a + r * SS + 16 * c) = v[k];
-          *reinterpret_cast<uint4*>(s_b + r * SS + 16 * c) =
-              make_uint4(__funnelshift_r(v[k].x, v[k].y, 8), __funnelshift_r(v[k].y, v[k].z, 8),
-                         __funnelshift_r(v[k].z, v[k].w, 8), __funnelshift_r(v[k].w, nx[k], 8));
+        for (int k = 0; k < kStageIlp; k++) {
+          const int r = r0 + 16 * k;
+          if (r < nsr) {
+            const uint8_t* gp = src0 + (long long)(sy_lo + r) * a.sstride + sxa + 16 * c;
+            v[k] = *reinterpret_cast<const uint4*>(gp);
+            nx[k] = (c + 1 < nchunk) ? *reinterpret_cast<const uint32_t*>(gp + 16) : 0u;
+          }
+        }
+#pragma unroll
+        for (int k = 0; k < kStageIlp; k++) {
+          const int r = r0 + 16 * k;
+          if (r < nsr) {
+            *reinterpret_cast<uint4*>(s_a + r * SS + 16 * c) = v[k];
+            *reinterpret_cast<uint4*>(s_b + r * SS + 16 * c) =
+                make_uint4(__funnelshift_r(v[k].x, v[k].y, 8), __funnelshift_r(v[k].y, v[k].z, 8),
+                           __funnelshift_r(v[k].z, v[k].w, 8), __funnelshift_r(v[k].w, nx[k], 8));
+          }
         }
       }
     }
   }
   __syncthreads();
-  // ---- phase A
+  // ---- phase A: H column c = PADDED destination column px0 + c, evaluated at its reflected interior coordinate
+  // (REFLECT_101 of the resized level == the resize evaluated at the reflected coordinate), 0 beyond the padded width
   {
     const int c = tid & (kPyTW - 1);
-    const int dx = org + c;
-    if (dx >= lo && dx <= hi) {
+    const int px = px0 + c;
+    int* hp = s_h + (tid >> 7) * kPyHS + c;
+    const int n = (nsr - (tid >> 7) + 1) >> 1;  // rows tid>>7, +2, +4, ...
+    if (px < pw) {
+      const int dx = reflect101(px - kPad, a.dw);
       const int o0 = tab_ofs[a.xb + dx] - sxa;
       const short2 wa = tab_a[a.xb + dx];
       const uint32_t wpk = ((uint32_t)(uint16_t)wa.y << 16) | (uint16_t)wa.x;
       const uint8_t* sp = ((o0 & 1) ? s_b : s_a) + (o0 & ~1) + (tid >> 7) * SS;
-      int* hp = s_h + (tid >> 7) * kPyHS + c;
-      const int n = (nsr - (tid >> 7) + 1) >> 1;  // rows tid>>7, +2, +4, ...
 #pragma unroll 4
       for (int i = 0; i < n; i++)
         hp[i * 2 * kPyHS] = (int)(__dp2a_lo(wpk, (uint32_t) * reinterpret_cast<const uint16_t*>(sp + i * 2 * SS), 0u) >> 4);
-    }
-    const int c2 = kPyTW + (tid >> 5), dx2 = org + c2;  // the up to 3 columns the alignment shift adds: warps 0..2
-    if (tid < 96 && dx2 <= hi) {
-      const int o0 = tab_ofs[a.xb + dx2] - sxa;
-      const short2 wa = tab_a[a.xb + dx2];
-      const uint32_t wpk = ((uint32_t)(uint16_t)wa.y << 16) | (uint16_t)wa.x;
-      const uint8_t* sp = ((o0 & 1) ? s_b : s_a) + (o0 & ~1);
-#pragma unroll 1
-      for (int sr = tid & 31; sr < nsr; sr += 32)
-        s_h[sr * kPyHS + c2] = (int)(__dp2a_lo(wpk, (uint32_t) * reinterpret_cast<const uint16_t*>(sp + sr * SS), 0u) >> 4);
+    } else {
+      for (int i = 0; i < n; i++) hp[i * 2 * kPyHS] = 0;
     }
   }
   __syncthreads();
-  // ---- phase B
-  const int px4 = px0 + 4 * (tid & 31);
+  // ---- phase B: 4 adjacent padded bytes per thread and row, two aligned LDS.128 of H each
+  const int c0 = 4 * (tid & 31);
+  const int px4 = px0 + c0;
   if (px4 >= a.dstride) return;
-  const bool straight = px4 - kPad >= 0 && px4 + 3 - kPad <= a.dw - 1;
-  int c[4];
-#pragma unroll
-  for (int k = 0; k < 4; k++) c[k] = (px4 + k < pw) ? reflect101(px4 + k - kPad, a.dw) - org : kPyHS - 1;
   uint8_t* dcol = fbase + a.doff + px4;
   for (int i = tid >> 5; i < a.th; i += 8) {
     const int py = py0 + i;
     if (py >= ph) break;
     const int4 r = s_row[i];
-    int h0[4], h1[4];
-    if (straight) {
-      const int4 u = *reinterpret_cast<const int4*>(&s_h[r.x + c[0]]);
-      const int4 v = *reinterpret_cast<const int4*>(&s_h[r.y + c[0]]);
-      h0[0] = u.x; h0[1] = u.y; h0[2] = u.z; h0[3] = u.w;
-      h1[0] = v.x; h1[1] = v.y; h1[2] = v.z; h1[3] = v.w;
-    } else {
-#pragma unroll
-      for (int k = 0; k < 4; k++) {
-        h0[k] = s_h[r.x + c[k]];
-        h1[k] = s_h[r.y + c[k]];
-      }
-    }
+    const int4 u = *reinterpret_cast<const int4*>(&s_h[r.x + c0]);
+    const int4 w = *reinterpret_cast<const int4*>(&s_h[r.y + c0]);
+    const int h0[4] = {u.x, u.y, u.z, u.w}, h1[4] = {w.x, w.y, w.z, w.w};
     uint32_t v[4];
 #pragma unroll
     for (int k = 0; k < 4; k++)  // the "+2" rides on the first product as 2 << 16
@@ -267,7 +274,7 @@ static bool plan_resize(const LevelGeom& sv, const LevelGeom& lv, ResizePlan* p)
   // bytes staged per row: <= 15 (alignment) + floor(127*sx) + 3 source columns, in whole 16-byte chunks
   const int need = ((int)((kPyTW - 1) * sx) + 19 + 15) / 16 * 16;
   p->ss = need <= 192 ? 192 : 512;
-  p->smem = (size_t)p->nsr_cap * kPyHS * 4 + sizeof(int4) * kPyMaxTH + 2 * (size_t)p->nsr_cap * p->ss;
+  p->smem = (size_t)p->nsr_cap * kPyHS * 4 + sizeof(int4) * kPyMaxTH + 2 * (size_t)p->nsr_cap * p->ss + 16;
   return need <= 512;
 }
 
@@ -297,7 +304,7 @@ int pyramid_tile_tables(FrameGeomDev* g, std::vector<int>* tab) {
       const int sx_lo = xo[lo], sx_hi = xo[hi] + 1;
       const int sxa = sx_lo - ((sx_lo + mis) & 15);
       const int nchunk = (sx_hi - sxa) / 16 + 1;
-      YD_REQUIRE(nchunk * 16 <= p.ss && hi - org < kPyHS - 1, "internal: resize tile exceeds its shared buffers");
+      YD_REQUIRE(nchunk * 16 <= p.ss, "internal: resize tile exceeds its shared buffers");
       const int v[8] = {lo, hi, org, sxa, nchunk, 0, 0, 0};
       d.insert(d.end(), v, v + 8);
     }
@@ -314,6 +321,15 @@ int pyramid_tile_tables(FrameGeomDev* g, std::vector<int>* tab) {
     tab->insert(tab->end(), d.begin(), d.end());  // (xo is dead from here: the vector may have moved)
   }
   return YDORB_OK;
+}
+
+// box of the TMA map that stages the SOURCE level of destination level l (0 x 0: that launch does not use TMA)
+void pyramid_box(const FrameGeomDev& g, int l, int* box_w, int* box_h) {
+  ResizePlan p;
+  *box_w = *box_h = 0;
+  if (l < 1 || !plan_resize(g.lv[l - 1], g.lv[l], &p) || p.ss != 192) return;
+  *box_w = 192;
+  *box_h = p.nsr_cap;
 }
 
 int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, size_t frame_stride, int batch,
@@ -343,10 +359,13 @@ int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, s
       const short2* ta = reinterpret_cast<const short2*>(ex->d_tab_a);
       if (p.smem > 48 * 1024)  // only reached with scale factors well above the reference's 1.2
         YD_CUDA(cudaFuncSetAttribute(k_pyr_resize<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+      PyrMap map;
+      map.m = ex->tmap_pyr[l];
+      const int frame0 = (int)((ex->d_pyr - ex->pyr_base) / g.pyr_bytes);
       if (p.ss == 192)
-        YD_CUDA(launch_chain(k_pyr_resize<192>, grid, dim3(256), p.smem, s, a, ex->d_tab_ofs, ta, ex->d_pyr));
+        YD_CUDA(launch_chain(k_pyr_resize<192>, grid, dim3(256), p.smem, s, map, frame0, a, ex->d_tab_ofs, ta, ex->d_pyr));
       else
-        YD_CUDA(launch_chain(k_pyr_resize<512>, grid, dim3(256), p.smem, s, a, ex->d_tab_ofs, ta, ex->d_pyr));
+        YD_CUDA(launch_chain(k_pyr_resize<512>, grid, dim3(256), p.smem, s, map, frame0, a, ex->d_tab_ofs, ta, ex->d_pyr));
     }
   }
   count_launches(g.n_levels);
