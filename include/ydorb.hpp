@@ -22,7 +22,13 @@
 
 #include "ydorb.h"
 
-namespace YDORBSLAM {
+// The classes below carry the reference's names in the reference's namespace.  A translation unit that still sees the
+// reference's own classes of the same names (tests, a staged migration) puts these elsewhere: -DYDORB_NAMESPACE=ydorb_abi
+#ifndef YDORB_NAMESPACE
+#define YDORB_NAMESPACE YDORBSLAM
+#endif
+
+namespace YDORB_NAMESPACE {
 
 typedef YdKeyPoint KeyPoint;  // layout of cv::KeyPoint: pt.x, pt.y, size, angle, response, octave, class_id
 
@@ -275,6 +281,22 @@ inline int OrbMatcher::searchWindows(FrameFeatures& _frame, const std::vector<Yd
   return n;
 }
 
+// EXTRA searchForInitialization: `north_star` names it, the reference has no such function (src/orbMatcher.hpp:24-66).
+// ORB-SLAM2's published algorithm on this reference's Frame hooks (ydorb_match_windowed_top2, no reference parity claim):
+// vbPrevMatched in/out as (x, y) pairs, vnMatches12[i1] = matched key point of _frame2 or -1; returns the match count.
+// areaMode 0 = the reference's getKeyPointsInArea predicate, 1 = ORB-SLAM2's own.
+inline int searchForInitialization(OrbMatcher& m, const std::vector<KeyPoint>& kps1, const std::vector<uint8_t>& desc1,
+                                   FrameFeatures& _frame2, std::vector<float>& vbPrevMatched, std::vector<int32_t>& vnMatches12,
+                                   int windowSize = 10, float nnRatio = 0.9f, bool checkOrientation = true, int areaMode = 0) {
+  vnMatches12.assign(kps1.size(), -1);
+  if (kps1.empty()) return 0;
+  vbPrevMatched.resize(2 * kps1.size());
+  int32_t n = 0;
+  check(ydorb_match_windowed_top2(_frame2.handle(), kps1.data(), desc1.data(), (int)kps1.size(), vbPrevMatched.data(), windowSize,
+                                  nnRatio, OrbMatcher::m_int_lowThd, checkOrientation ? 1 : 0, areaMode, vnMatches12.data(), &n));
+  return n;
+}
+
 // Frame::computeStereoMatches (src/frame.cpp:362-472) on the pyramids the two extractors hold from their last call.
 // referenceQuirks = true reproduces the reference (leftIdx lag etc.).
 inline void computeStereoMatches(OrbMatcher& m, const OrbExtractor& left, const OrbExtractor& right, const std::vector<KeyPoint>& kpsLeft,
@@ -354,5 +376,5 @@ class Vocabulary {
   YdVocabulary* m_h;
 };
 
-}  // namespace YDORBSLAM
+}  // namespace YDORB_NAMESPACE
 #endif  // YDORB_HPP
