@@ -218,6 +218,24 @@ class RefFrame:
                                            _p(out))
         return n, out[: self.n_left]
 
+    def search_last_current(self, last_kps, mp_pos, mp_desc, mp_obs_positive, outlier, last_t, cam, kp_occupied, thd, ratio,
+                            check_orientation=True):
+        """OrbMatcher(ratio, check).searchByProjectionInLastAndCurrentFrame(this frame [pose I], last frame, thd) of the
+        compiled reference (src/orbMatcher.cpp:65-155).  mp_pos [n_last][3] (NaN x: no map point), last_t: translation of
+        the last frame's pose, cam = (fx, fy, cx, cy, bf, baseline).  Returns (return value, match per current key point)."""
+        lk = np.ascontiguousarray(last_kps, dtype=KP_DTYPE)
+        pos = np.ascontiguousarray(mp_pos, dtype=np.float32)
+        mpd = np.ascontiguousarray(mp_desc, dtype=np.uint8)
+        obs = np.ascontiguousarray(mp_obs_positive, dtype=np.uint8)
+        out_ = np.ascontiguousarray(outlier, dtype=np.uint8)
+        lt = np.ascontiguousarray(last_t, dtype=np.float32)
+        cm = np.ascontiguousarray(cam, dtype=np.float32)
+        occ = None if kp_occupied is None else np.ascontiguousarray(kp_occupied, dtype=np.uint8)
+        match = np.full(max(self.n_left, 1), -1, np.int32)
+        n = lib().ref_search_last_current(self._h, _p(lk), len(lk), _p(pos), _p(mpd), _p(obs), _p(out_), _p(lt), _p(cm), _p(occ),
+                                          C.c_float(thd), C.c_float(ratio), int(bool(check_orientation)), _p(match))
+        return n, match[: self.n_left]
+
     def close(self):
         if self._h:
             lib().ref_frame_destroy(self._h)

@@ -143,6 +143,66 @@ int ref_search_by_projection(void* p, const RefMapPointProj* mps, const uint8_t*
   return ret;
 }
 
+/* M2  OrbMatcher::searchByProjectionInLastAndCurrentFrame (src/orbMatcher.cpp:65-155).  `p` is the CURRENT frame (made by
+ * ref_frame_from_keypoints + ref_frame_set_features), its pose is the identity.  The LAST frame is built here: key points
+ * last_kps, one MapPoint per key point at world position mp_pos[i] (built by the reference's own constructor; a NaN x
+ * means "no map point"), outlier flags, pose [I | last_t] (its z against the base line decides forward / backward,
+ * :79-80).  cam = {fx, fy, cx, cy, bf, baseline}.  match_out[i] = index in the last frame of the map point key point i
+ * of the current frame holds after the call, -1 = none.  Returns the function's return value. */
+int ref_search_last_current(void* p, const RefKeyPoint* last_kps, int n_last, const float* mp_pos, const uint8_t* mp_desc,
+                            const uint8_t* mp_obs_positive, const uint8_t* outlier, const float* last_t, const float* cam,
+                            const uint8_t* kp_occupied, float thd, float ratio, int check_orientation, int32_t* match_out) {
+  using namespace YDORBSLAM;
+  Frame* cur = static_cast<Frame*>(p);
+  const int n = (int)cur->m_v_keyPoints.size();
+  Frame::m_flt_fx = cam[0]; Frame::m_flt_fy = cam[1]; Frame::m_flt_cx = cam[2]; Frame::m_flt_cy = cam[3];
+  Frame::m_flt_baseLineTimesFx = cam[4];
+  Frame::m_flt_baseLine = cam[5];
+  cur->setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  Frame src;  // carries the map points' descriptors for the reference's MapPoint constructor
+  src.m_v_keyPoints.assign(n_last + 1, cv::KeyPoint());
+  src.m_v_scaleFactors = cur->m_v_scaleFactors;
+  src.m_cvMat_descriptors.create(n_last + 1, 32, CV_8UC1);
+  for (int i = 0; i < n_last; i++) memcpy(src.m_cvMat_descriptors.ptr(i), mp_desc + (size_t)32 * i, 32);
+  memset(src.m_cvMat_descriptors.ptr(n_last), 0, 32);
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  Frame last;
+  last.m_v_keyPoints.resize(n_last);
+  for (int i = 0; i < n_last; i++) {
+    cv::KeyPoint k;
+    k.pt.x = last_kps[i].x; k.pt.y = last_kps[i].y; k.size = last_kps[i].size; k.angle = last_kps[i].angle;
+    k.response = last_kps[i].response; k.octave = last_kps[i].octave; k.class_id = last_kps[i].class_id;
+    last.m_v_keyPoints[i] = k;
+  }
+  last.m_v_isOutliers.assign(n_last, false);
+  last.m_v_sptrMapPoints.assign(n_last, std::shared_ptr<MapPoint>());
+  std::map<const MapPoint*, int> index;
+  for (int i = 0; i < n_last; i++) {
+    last.m_v_isOutliers[i] = outlier && outlier[i];
+    if (mp_pos[3 * i] != mp_pos[3 * i]) continue;  // NaN: this key point has no map point
+    cv::Mat pos = (cv::Mat_<float>(3, 1) << mp_pos[3 * i], mp_pos[3 * i + 1], mp_pos[3 * i + 2]);
+    std::shared_ptr<ProbePoint> mp = std::make_shared<ProbePoint>(pos, src, i);
+    mp->observations(mp_obs_positive && mp_obs_positive[i] ? 1 : 0);
+    last.m_v_sptrMapPoints[i] = mp;
+    index[mp.get()] = i;
+  }
+  cv::Mat T = cv::Mat::eye(4, 4, CV_32F);
+  for (int k = 0; k < 3; k++) T.at<float>(k, 3) = last_t[k];
+  last.setCameraPoseByTransform_c2w(T);
+  cv::Mat pos0 = (cv::Mat_<float>(3, 1) << 0.f, 0.f, 1.f);
+  std::shared_ptr<ProbePoint> held = std::make_shared<ProbePoint>(pos0, src, n_last);
+  held->observations(1);
+  for (int i = 0; i < n; i++)
+    cur->m_v_sptrMapPoints[i] = (kp_occupied && kp_occupied[i]) ? std::static_pointer_cast<MapPoint>(held) : std::shared_ptr<MapPoint>();
+  OrbMatcher matcher(ratio, check_orientation != 0);
+  const int ret = matcher.searchByProjectionInLastAndCurrentFrame(*cur, last, thd);
+  for (int i = 0; i < n; i++) {
+    const MapPoint* q = cur->m_v_sptrMapPoints[i].get();
+    match_out[i] = (q && q != held.get()) ? index[q] : -1;
+  }
+  return ret;
+}
+
 /* M0 */
 int ref_descriptor_distance(const uint8_t* a, const uint8_t* b) {
   cv::Mat ma(1, 32, CV_8UC1, const_cast<uint8_t*>(a)), mb(1, 32, CV_8UC1, const_cast<uint8_t*>(b));

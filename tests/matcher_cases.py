@@ -163,3 +163,37 @@ def init_scene(n_clusters, n_noise, seed, area_mode, window=30, w=W, h=H):
     kps1, kps2 = pack(k1), pack(k2)
     perm = rng.permutation(len(kps2))  # frame 2 in arbitrary order
     return kps1, np.ascontiguousarray(np.array(d1, np.uint8)), kps2[perm], np.ascontiguousarray(np.array(d2, np.uint8)[perm])
+
+
+CAM = dict(fx=np.float32(718.856), fy=np.float32(718.856), cx=np.float32(320.0), cy=np.float32(240.0), bf=np.float32(386.1448),
+           baseline=np.float32(386.1448) / np.float32(718.856))
+
+
+def last_frame_scene(kps, desc, n_last, seed, thd):
+    """A 'last frame' for searchByProjectionInLastAndCurrentFrame against a current frame at the identity pose: world
+    positions whose projections (computed in float32 exactly as src/orbMatcher.cpp:86-91 does) land where window_scene
+    wants them, octaves / angles of the last frame's key points, outlier flags, missing map points (NaN)."""
+    mp = window_scene(kps, desc, n_last, seed, thd)
+    rng = np.random.RandomState(seed + 100)
+    z = rng.uniform(2.0, 20.0, n_last).astype(np.float32)
+    z[rng.rand(n_last) < 0.03] *= -1  # behind the camera: :92 drops them
+    X = ((mp["proj_x"].astype(np.float64) - float(CAM["cx"])) / float(CAM["fx"]) * z).astype(np.float32)
+    Y = ((mp["proj_y"].astype(np.float64) - float(CAM["cy"])) / float(CAM["fy"]) * z).astype(np.float32)
+    pos = np.stack([X, Y, z], 1).astype(np.float32)
+    has_mp = rng.rand(n_last) > 0.08
+    outlier = (rng.rand(n_last) < 0.05).astype(np.uint8)
+    # the reference's own arithmetic, one float32 rounding per operation
+    px = (CAM["fx"] * X / z + CAM["cx"]).astype(np.float32)
+    py = (CAM["fy"] * Y / z + CAM["cy"]).astype(np.float32)
+    prx = (px - CAM["bf"] / z).astype(np.float32)
+    in_image = (px >= 0) & (px < W) & (py >= 0) & (py < H)
+    active = has_mp & (outlier == 0) & (z >= 0) & in_image
+    last_kps = np.zeros(n_last, KP_DTYPE)
+    last_kps["octave"] = mp["level"]
+    last_kps["angle"] = mp["angle"]
+    last_kps["size"] = 31
+    last_kps["class_id"] = -1
+    pos_nan = pos.copy()
+    pos_nan[~has_mp, 0] = np.nan
+    return dict(last_kps=last_kps, pos=pos_nan, proj_x=px, proj_y=py, proj_right_x=prx, active=active, outlier=outlier,
+                obs_positive=mp["obs_positive"], desc=mp["desc"], right_x_kp=mp["right_x_kp"], occupied=mp["occupied"])

@@ -141,3 +141,29 @@ def test_cuda_search_by_projection_matches_compiled_reference(nkp, nmp, th, occu
     assert n == rn and np.array_equal(match, rmatch)
     assert n > 30
     fr.close(); m.close(); f.close()
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+@pytest.mark.parametrize("motion,tz", [("forward", 1.0), ("backward", -1.0), ("none", 0.0)])
+def test_cuda_last_and_current_frame_matches_compiled_reference(motion, tz):
+    """M2 + M7: CUDA window search == the reference's own searchByProjectionInLastAndCurrentFrame (src/orbMatcher.cpp:65-155
+    compiled unmodified: its cv::Mat projection, level window by motion, stereo gate, claims, rotation histogram)."""
+    from tests import matcher_cases as mc
+    from ydorbslam_b200 import OrbMatcher
+    from ydorbslam_b200 import queries as Q
+
+    kps, desc = mc.synth_keypoints(900, 21)
+    s = mc.last_frame_scene(kps, desc, 3000, 31, 7.0)
+    f = ref.RefFrame.from_keypoints(kps, (0, 0, mc.W, mc.H))
+    f.set_features(desc, s["right_x_kp"], mc.SF)
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    rn, rmatch = f.search_last_current(s["last_kps"], s["pos"], s["desc"], s["obs_positive"], s["outlier"], (0.0, 0.0, tz), cam,
+                                       s["occupied"], 7.0, 0.9, True)
+    q, prm = Q.last_and_current_frame(s["proj_x"], s["proj_y"], s["proj_right_x"], s["last_kps"]["octave"], s["last_kps"]["angle"],
+                                      s["active"], s["obs_positive"].astype(bool), mc.SF, 7.0, motion)
+    m = OrbMatcher(0.9)
+    fr = m.make_frame(kps, desc, s["right_x_kp"], bounds=(0, 0, mc.W, mc.H), scale_factors=mc.SF)
+    n, best, match = m.searchWindows(fr, q, s["desc"], prm, s["occupied"])
+    assert n == rn and np.array_equal(np.where(match < 0, -1, match), rmatch)
+    assert n > 40
+    fr.close(); m.close(); f.close()

@@ -102,3 +102,28 @@ def test_search_by_projection_reference_equals_oracle(nkp, nmp, th, occupied, se
     if nmp >= 3000:
         assert n > 30
     f.close()
+
+
+@pytest.mark.parametrize("motion,tz", [("forward", 1.0), ("backward", -1.0), ("none", 0.0)])
+@pytest.mark.parametrize("check_ori", [True, False])
+def test_search_last_and_current_frame_reference_equals_oracle(motion, tz, check_ori):
+    """M2 (+ M7): the reference's own searchByProjectionInLastAndCurrentFrame -- projection by its cv::Mat arithmetic,
+    level window by camera motion, stereo gate, greedy claims, rotation histogram + computeThreeMaxima -- == the
+    oracle's window search on queries projected with the same float32 operations."""
+    from ydorbslam_b200 import queries as Q
+
+    kps, desc = mc.synth_keypoints(900, 21)
+    s = mc.last_frame_scene(kps, desc, 3000, 31, 7.0)
+    f = ref.RefFrame.from_keypoints(kps, (0, 0, mc.W, mc.H))
+    f.set_features(desc, s["right_x_kp"], mc.SF)
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    n, match = f.search_last_current(s["last_kps"], s["pos"], s["desc"], s["obs_positive"], s["outlier"], (0.0, 0.0, tz), cam,
+                                     s["occupied"], 7.0, 0.9, check_ori)
+    q, prm = Q.last_and_current_frame(s["proj_x"], s["proj_y"], s["proj_right_x"], s["last_kps"]["octave"], s["last_kps"]["angle"],
+                                      s["active"], s["obs_positive"].astype(bool), mc.SF, 7.0, motion, check_orientation=check_ori)
+    g = orc.make_geom(orc.make_params(1000, 1.2, 8, 20), mc.W, mc.H)
+    on, obest, omatch = orc.search_windows(g, kps, desc, s["right_x_kp"], s["occupied"], q, s["desc"], prm)
+    assert n == on
+    assert np.array_equal(match, np.where(omatch < 0, -1, omatch))
+    assert n > 40
+    f.close()
