@@ -246,3 +246,18 @@ class RefFrame:
             self.close()
         except Exception:
             pass
+
+
+def search_by_bow_keyframe_frame(kps1, desc1, valid1, fv1, kps2, desc2, fv2, ratio, check_orientation=True):
+    """OrbMatcher::searchByBowInKeyFrameAndFrame (src/orbMatcher.cpp:303-379) of the compiled reference on a KeyFrame /
+    Frame pair built from the arrays; fv = (node_ids, node_start, items).  Returns (return value, match per side-2 key point)."""
+    k1, k2 = np.ascontiguousarray(kps1, dtype=KP_DTYPE), np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+    d1, d2 = np.ascontiguousarray(desc1, dtype=np.uint8), np.ascontiguousarray(desc2, dtype=np.uint8)
+    v1 = np.ascontiguousarray(valid1, dtype=np.uint8)
+    a = [np.ascontiguousarray(x, dtype=np.int32) for x in fv1]
+    b = [np.ascontiguousarray(x, dtype=np.int32) for x in fv2]
+    out = np.full(max(len(k2), 1), -1, np.int32)
+    n = lib().ref_search_by_bow_kf_frame(_p(k1), _p(d1), _p(v1), len(k1), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]), _p(k2), _p(d2),
+                                         len(k2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]), C.c_float(ratio), int(bool(check_orientation)),
+                                         _p(out))
+    return n, out[: len(k2)]

@@ -25,6 +25,7 @@
 #include <vector>
 
 #include "frame.hpp"
+#include "keyFrame.hpp"
 #include "mapPoint.hpp"
 #include "orbMatcher.hpp"
 
@@ -200,6 +201,53 @@ int ref_search_last_current(void* p, const RefKeyPoint* last_kps, int n_last, co
     const MapPoint* q = cur->m_v_sptrMapPoints[i].get();
     match_out[i] = (q && q != held.get()) ? index[q] : -1;
   }
+  return ret;
+}
+
+/* M5  OrbMatcher::searchByBowInKeyFrameAndFrame (src/orbMatcher.cpp:303-379) on a KeyFrame built by the reference's own
+ * constructor from side 1 (key points, descriptors, FeatureVector in CSR form, a MapPoint where valid1[i]) and a Frame
+ * from side 2.  match_out[i2] = key point of the key frame whose map point the call gave to key point i2, or -1. */
+int ref_search_by_bow_kf_frame(const RefKeyPoint* kps1, const uint8_t* desc1, const uint8_t* valid1, int n1,
+                               const int32_t* node_ids1, const int32_t* node_start1, const int32_t* items1, int n_nodes1,
+                               const RefKeyPoint* kps2, const uint8_t* desc2, int n2, const int32_t* node_ids2,
+                               const int32_t* node_start2, const int32_t* items2, int n_nodes2, float ratio,
+                               int check_orientation, int32_t* match_out) {
+  using namespace YDORBSLAM;
+  auto fill = [](Frame& f, const RefKeyPoint* kps, const uint8_t* desc, int n, const int32_t* ids, const int32_t* start,
+                 const int32_t* items, int nn) {
+    f.m_v_keyPoints.resize(n);
+    for (int i = 0; i < n; i++) {
+      cv::KeyPoint k;
+      k.pt.x = kps[i].x; k.pt.y = kps[i].y; k.size = kps[i].size; k.angle = kps[i].angle;
+      k.response = kps[i].response; k.octave = kps[i].octave; k.class_id = kps[i].class_id;
+      f.m_v_keyPoints[i] = k;
+    }
+    f.m_int_keyPointsNum = n;
+    f.m_cvMat_descriptors.create(std::max(n, 1), 32, CV_8UC1);
+    for (int i = 0; i < n; i++) memcpy(f.m_cvMat_descriptors.ptr(i), desc + (size_t)32 * i, 32);
+    for (int k = 0; k < nn; k++)
+      for (int t = start[k]; t < start[k + 1]; t++) f.m_bow_keyPointsVec.addFeature((DBoW3::NodeId)ids[k], (unsigned)items[t]);
+    f.m_v_sptrMapPoints.assign(n, std::shared_ptr<MapPoint>());
+  };
+  Frame side1, side2, src;
+  fill(side1, kps1, desc1, n1, node_ids1, node_start1, items1, n_nodes1);
+  fill(side2, kps2, desc2, n2, node_ids2, node_start2, items2, n_nodes2);
+  src.m_v_keyPoints.assign(std::max(n1, 1), cv::KeyPoint());
+  src.m_v_scaleFactors.assign(8, 1.0f);
+  src.m_cvMat_descriptors = side1.m_cvMat_descriptors.clone();
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  cv::Mat pos = (cv::Mat_<float>(3, 1) << 0.f, 0.f, 1.f);
+  std::map<const MapPoint*, int> index;
+  for (int i = 0; i < n1; i++)
+    if (valid1[i]) {
+      side1.m_v_sptrMapPoints[i] = std::make_shared<ProbePoint>(pos, src, i);
+      index[side1.m_v_sptrMapPoints[i].get()] = i;
+    }
+  std::shared_ptr<KeyFrame> kf = std::make_shared<KeyFrame>(side1, std::shared_ptr<Map>(), std::shared_ptr<KeyFrameDatabase>());
+  OrbMatcher matcher(ratio, check_orientation != 0);
+  std::vector<std::shared_ptr<MapPoint>> matched;
+  const int ret = matcher.searchByBowInKeyFrameAndFrame(kf, side2, matched);
+  for (int i = 0; i < n2; i++) match_out[i] = matched[i] ? index[matched[i].get()] : -1;
   return ret;
 }
 

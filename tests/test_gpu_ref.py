@@ -167,3 +167,19 @@ def test_cuda_last_and_current_frame_matches_compiled_reference(motion, tz):
     assert n == rn and np.array_equal(np.where(match < 0, -1, match), rmatch)
     assert n > 40
     fr.close(); m.close(); f.close()
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+@pytest.mark.parametrize("n1,n2,seed", [(800, 900, 3), (300, 1500, 5)])
+def test_cuda_search_by_bow_matches_compiled_reference(n1, n2, seed):
+    """M5: CUDA searchByBowInKeyFrameAndFrame == the reference's own (src/orbMatcher.cpp:303-379 compiled unmodified)."""
+    from tests import matcher_cases as mc
+    from ydorbslam_b200 import OrbMatcher
+
+    s = mc.bow_scene(n1, n2, seed)
+    rn, rmatch = ref.search_by_bow_keyframe_frame(s["k1"], s["d1"], s["v1"], s["fv1"], s["k2"], s["d2"], s["fv2"], 0.7, True)
+    m = OrbMatcher(0.7)
+    n, match = m.searchByBowInKeyFrameAndFrame(s["k1"], s["d1"], s["v1"], s["fv1"], s["k2"], s["d2"], s["fv2"])
+    assert n == rn and np.array_equal(match, rmatch)
+    assert n > 30
+    m.close()

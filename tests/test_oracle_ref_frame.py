@@ -127,3 +127,16 @@ def test_search_last_and_current_frame_reference_equals_oracle(motion, tz, check
     assert np.array_equal(match, np.where(omatch < 0, -1, omatch))
     assert n > 40
     f.close()
+
+
+@pytest.mark.parametrize("n1,n2,seed,check_ori", [(800, 900, 3, True), (800, 900, 4, False), (300, 1500, 5, True), (50, 40, 6, True)])
+def test_search_by_bow_reference_equals_oracle(n1, n2, seed, check_ori):
+    """M5: the reference's own searchByBowInKeyFrameAndFrame (on a KeyFrame built by its constructor, DBoW3 FeatureVector
+    std::maps filled through addFeature) == the oracle's CSR restatement."""
+    s = mc.bow_scene(n1, n2, seed)
+    n, match = ref.search_by_bow_keyframe_frame(s["k1"], s["d1"], s["v1"], s["fv1"], s["k2"], s["d2"], s["fv2"], 0.7, check_ori)
+    on, omatch = orc.search_by_bow(0, s["k1"], s["d1"], s["v1"], s["fv1"], s["k2"], s["d2"], None, s["fv2"], 0.7, check_ori)
+    assert n == on
+    assert np.array_equal(match, omatch)
+    if n1 >= 300:
+        assert n > 30
