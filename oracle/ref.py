@@ -236,6 +236,22 @@ class RefFrame:
                                           C.c_float(thd), C.c_float(ratio), int(bool(check_orientation)), _p(match))
         return n, match[: self.n_left]
 
+    def search_keyframe_current(self, kf_kps, mp_pos, mp_desc, min_dist, max_dist, is_bad, in_found, cam, kp_occupied, thd,
+                                orb_dist, ratio, check_orientation=True):
+        """OrbMatcher::searchByProjectionInKeyFrameAndCurrentFrame (src/orbMatcher.cpp:156-239) of the compiled reference,
+        this frame (pose I) as the current frame.  Returns (return value, match per current key point, dbg [n_kf][4] =
+        projX, projY, predicted level, gates passed -- evaluated by the reference's own methods)."""
+        kk = np.ascontiguousarray(kf_kps, dtype=KP_DTYPE)
+        arrs = [np.ascontiguousarray(a, dtype=t) for a, t in ((mp_pos, np.float32), (mp_desc, np.uint8), (min_dist, np.float32),
+                                                               (max_dist, np.float32), (is_bad, np.uint8), (in_found, np.uint8),
+                                                               (cam, np.float32))]
+        occ = None if kp_occupied is None else np.ascontiguousarray(kp_occupied, dtype=np.uint8)
+        match = np.full(max(self.n_left, 1), -1, np.int32)
+        dbg = np.zeros((max(len(kk), 1), 4), np.float32)
+        n = lib().ref_search_keyframe_current(self._h, _p(kk), len(kk), *[_p(a) for a in arrs], _p(occ), C.c_float(thd), int(orb_dist),
+                                              C.c_float(ratio), int(bool(check_orientation)), _p(match), _p(dbg))
+        return n, match[: self.n_left], dbg[: len(kk)]
+
     def close(self):
         if self._h:
             lib().ref_frame_destroy(self._h)

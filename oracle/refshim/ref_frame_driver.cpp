@@ -21,7 +21,9 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <map>
 #include <memory>
+#include <set>
 #include <vector>
 
 #include "frame.hpp"
@@ -72,6 +74,8 @@ struct GridFrame : YDORBSLAM::Frame {
 struct ProbePoint : YDORBSLAM::MapPoint {
   ProbePoint(const cv::Mat& pos, YDORBSLAM::Frame& f, int idx) : YDORBSLAM::MapPoint(pos, std::shared_ptr<YDORBSLAM::Map>(), f, idx) {}
   void observations(int n) { m_int_observationsNum = n; }
+  void distances(float mn, float mx) { m_flt_minDistance = mn; m_flt_maxDistance = mx; }
+  void bad(bool b) { m_b_bad = b; }
 };
 
 struct RefMapPointProj {  // = OrcMapPointProj = YdMapPointProj
@@ -88,6 +92,8 @@ void fill_features(YDORBSLAM::Frame* f, const uint8_t* desc, const float* right_
   if (right_x) f->m_v_rightXcords.assign(right_x, right_x + n);
   f->m_v_scaleFactors.assign(sf, sf + n_levels);
   f->m_int_scaleLevelsNum = n_levels;
+  f->m_flt_scaleFactor = n_levels > 1 ? sf[1] : 1.2f;
+  f->m_flt_logScaleFactor = log(f->m_flt_scaleFactor);  // as the Frame constructors do (src/frame.cpp:78)
   f->m_v_sptrMapPoints.assign(n, std::shared_ptr<YDORBSLAM::MapPoint>());
 }
 
@@ -248,6 +254,86 @@ int ref_search_by_bow_kf_frame(const RefKeyPoint* kps1, const uint8_t* desc1, co
   std::vector<std::shared_ptr<MapPoint>> matched;
   const int ret = matcher.searchByBowInKeyFrameAndFrame(kf, side2, matched);
   for (int i = 0; i < n2; i++) match_out[i] = matched[i] ? index[matched[i].get()] : -1;
+  return ret;
+}
+
+/* M3  OrbMatcher::searchByProjectionInKeyFrameAndCurrentFrame (src/orbMatcher.cpp:156-239).  `p` = current frame at the
+ * identity pose; the key frame holds n_kf key points (angles) with one MapPoint each at mp_pos[i] (NaN x: none), built by
+ * the reference's constructor, with the given invariance distances / bad flag / membership in _setFoundMapPoints.
+ * dbg (may be null) receives per map point {projX, projY, predicted level, passes the gates of :187-189} evaluated with
+ * the reference's own methods and the same float expressions as :171-183 -- the inputs a caller of the C ABI supplies. */
+int ref_search_keyframe_current(void* p, const RefKeyPoint* kf_kps, int n_kf, const float* mp_pos, const uint8_t* mp_desc,
+                                const float* min_dist, const float* max_dist, const uint8_t* is_bad, const uint8_t* in_found,
+                                const float* cam, const uint8_t* kp_occupied, float thd, int orb_dist, float ratio,
+                                int check_orientation, int32_t* match_out, float* dbg) {
+  using namespace YDORBSLAM;
+  Frame* cur = static_cast<Frame*>(p);
+  const int n = (int)cur->m_v_keyPoints.size();
+  Frame::m_flt_fx = cam[0]; Frame::m_flt_fy = cam[1]; Frame::m_flt_cx = cam[2]; Frame::m_flt_cy = cam[3];
+  Frame::m_flt_baseLineTimesFx = cam[4];
+  Frame::m_flt_baseLine = cam[5];
+  cur->setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  Frame src;
+  src.m_v_keyPoints.assign(n_kf + 1, cv::KeyPoint());
+  src.m_v_scaleFactors = cur->m_v_scaleFactors;
+  src.m_cvMat_descriptors.create(n_kf + 1, 32, CV_8UC1);
+  for (int i = 0; i < n_kf; i++) memcpy(src.m_cvMat_descriptors.ptr(i), mp_desc + (size_t)32 * i, 32);
+  memset(src.m_cvMat_descriptors.ptr(n_kf), 0, 32);
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  Frame kff;
+  kff.m_v_keyPoints.resize(n_kf);
+  for (int i = 0; i < n_kf; i++) {
+    cv::KeyPoint k;
+    k.pt.x = kf_kps[i].x; k.pt.y = kf_kps[i].y; k.size = kf_kps[i].size; k.angle = kf_kps[i].angle;
+    k.response = kf_kps[i].response; k.octave = kf_kps[i].octave; k.class_id = kf_kps[i].class_id;
+    kff.m_v_keyPoints[i] = k;
+  }
+  kff.m_int_keyPointsNum = n_kf;
+  kff.m_v_sptrMapPoints.assign(n_kf, std::shared_ptr<MapPoint>());
+  std::map<const MapPoint*, int> index;
+  std::set<std::shared_ptr<MapPoint>> found;
+  for (int i = 0; i < n_kf; i++) {
+    if (mp_pos[3 * i] != mp_pos[3 * i]) continue;
+    cv::Mat pos = (cv::Mat_<float>(3, 1) << mp_pos[3 * i], mp_pos[3 * i + 1], mp_pos[3 * i + 2]);
+    std::shared_ptr<ProbePoint> mp = std::make_shared<ProbePoint>(pos, src, i);
+    mp->distances(min_dist[i], max_dist[i]);
+    mp->bad(is_bad && is_bad[i]);
+    kff.m_v_sptrMapPoints[i] = mp;
+    index[mp.get()] = i;
+    if (in_found && in_found[i]) found.insert(mp);
+  }
+  std::shared_ptr<KeyFrame> kf = std::make_shared<KeyFrame>(kff, std::shared_ptr<Map>(), std::shared_ptr<KeyFrameDatabase>());
+  if (dbg) {
+    const cv::Mat R = cur->m_cvMat_T_c2w.rowRange(0, 3).colRange(0, 3), t = cur->m_cvMat_T_c2w.rowRange(0, 3).col(3);
+    const cv::Mat origin = -R * t;
+    for (int i = 0; i < n_kf; i++) {
+      float* d = dbg + 4 * i;
+      d[0] = d[1] = d[2] = d[3] = 0.f;
+      std::shared_ptr<MapPoint> mp = kff.m_v_sptrMapPoints[i];
+      if (!mp || mp->isBad() || found.count(mp)) continue;
+      cv::Mat pw = mp->getPosInWorld();
+      cv::Mat pc = R * pw + t;
+      const float x = pc.at<float>(0), y = pc.at<float>(1), z = pc.at<float>(2);
+      const float u = Frame::m_flt_fx * x / z + Frame::m_flt_cx;
+      const float v = Frame::m_flt_fy * y / z + Frame::m_flt_cy;
+      const float dist3D = cv::norm(pw - origin);
+      const float maxD = mp->getMaxDistanceInvariance(), minD = mp->getMinDistanceInvariance();
+      d[0] = u;
+      d[1] = v;
+      d[2] = (float)mp->predictScaleLevel(dist3D, *cur);
+      d[3] = (z >= 0.0 && cur->isInImage(u, v) && dist3D >= minD && dist3D <= maxD) ? 1.f : 0.f;
+    }
+  }
+  cv::Mat pos0 = (cv::Mat_<float>(3, 1) << 0.f, 0.f, 1.f);
+  std::shared_ptr<ProbePoint> held = std::make_shared<ProbePoint>(pos0, src, n_kf);
+  for (int i = 0; i < n; i++)
+    cur->m_v_sptrMapPoints[i] = (kp_occupied && kp_occupied[i]) ? std::static_pointer_cast<MapPoint>(held) : std::shared_ptr<MapPoint>();
+  OrbMatcher matcher(ratio, check_orientation != 0);
+  const int ret = matcher.searchByProjectionInKeyFrameAndCurrentFrame(*cur, kf, found, thd, orb_dist);
+  for (int i = 0; i < n; i++) {
+    const MapPoint* q = cur->m_v_sptrMapPoints[i].get();
+    match_out[i] = (q && q != held.get()) ? index[q] : -1;
+  }
   return ret;
 }
 

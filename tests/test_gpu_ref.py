@@ -183,3 +183,29 @@ def test_cuda_search_by_bow_matches_compiled_reference(n1, n2, seed):
     assert n == rn and np.array_equal(match, rmatch)
     assert n > 30
     m.close()
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+def test_cuda_keyframe_and_current_frame_matches_compiled_reference():
+    """M3: CUDA window search == the reference's own searchByProjectionInKeyFrameAndCurrentFrame (src/orbMatcher.cpp:156-239
+    compiled unmodified) on the queries the reference's own methods produce."""
+    from tests import matcher_cases as mc
+    from tests.test_oracle_ref_frame import _keyframe_scene
+    from ydorbslam_b200 import OrbMatcher
+    from ydorbslam_b200 import queries as Q
+
+    kps, desc = mc.synth_keypoints(900, 23)
+    s = _keyframe_scene(kps, desc, 3000, 33, 7.0)
+    f = ref.RefFrame.from_keypoints(kps, (0, 0, mc.W, mc.H))
+    f.set_features(desc, s["right_x_kp"], mc.SF)
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    rn, rmatch, dbg = f.search_keyframe_current(s["last_kps"], s["pos"], s["desc"], s["min_d"], s["max_d"], s["bad"], s["found"], cam,
+                                                s["occupied"], 7.0, 100, 0.9, True)
+    q, prm = Q.keyframe_and_current_frame(dbg[:, 0], dbg[:, 1], dbg[:, 2].astype(np.int32), s["last_kps"]["angle"], dbg[:, 3] > 0, mc.SF,
+                                          7.0, 100)
+    m = OrbMatcher(0.9)
+    fr = m.make_frame(kps, desc, s["right_x_kp"], bounds=(0, 0, mc.W, mc.H), scale_factors=mc.SF)
+    n, best, match = m.searchWindows(fr, q, s["desc"], prm, s["occupied"])
+    assert n == rn and np.array_equal(np.where(match < 0, -1, match), rmatch)
+    assert n > 40
+    fr.close(); m.close(); f.close()

@@ -140,3 +140,44 @@ def test_search_by_bow_reference_equals_oracle(n1, n2, seed, check_ori):
     assert np.array_equal(match, omatch)
     if n1 >= 300:
         assert n > 30
+
+
+def _keyframe_scene(kps, desc, n_kf, seed, thd):
+    """Map points of a key frame for M3: world positions projecting where window_scene wants them, invariance distances
+    around the actual distance (some out of range), bad / already-found flags."""
+    s = mc.last_frame_scene(kps, desc, n_kf, seed, thd)
+    rng = np.random.RandomState(seed + 7)
+    pos = np.where(np.isnan(s["pos"]), 0.0, s["pos"]).astype(np.float64)
+    dist = np.sqrt((pos ** 2).sum(1))
+    lvl = s["last_kps"]["octave"].astype(np.int64)
+    max_d = (dist * mc.SF[lvl] * rng.uniform(0.95, 1.05, n_kf)).astype(np.float32)
+    min_d = (max_d / mc.SF[-1]).astype(np.float32)
+    far = rng.rand(n_kf) < 0.05
+    max_d[far] *= np.float32(0.3)  # dist3D > 1.2 * maxDistance: dropped by :188
+    s.update(min_d=min_d, max_d=max_d, bad=(rng.rand(n_kf) < 0.04).astype(np.uint8), found=(rng.rand(n_kf) < 0.06).astype(np.uint8))
+    return s
+
+
+@pytest.mark.parametrize("check_ori,orb_dist", [(True, 100), (False, 64)])
+def test_search_keyframe_and_current_frame_reference_equals_oracle(check_ori, orb_dist):
+    """M3: the reference's own searchByProjectionInKeyFrameAndCurrentFrame == the oracle's window search on the queries
+    its own methods produce (projection, predictScaleLevel, invariance gate); also pins the +-1 level window, the
+    any-slot exclusion (:194) and the non-strict threshold (:202)."""
+    from ydorbslam_b200 import queries as Q
+
+    kps, desc = mc.synth_keypoints(900, 23)
+    s = _keyframe_scene(kps, desc, 3000, 33, 7.0)
+    f = ref.RefFrame.from_keypoints(kps, (0, 0, mc.W, mc.H))
+    f.set_features(desc, s["right_x_kp"], mc.SF)
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    n, match, dbg = f.search_keyframe_current(s["last_kps"], s["pos"], s["desc"], s["min_d"], s["max_d"], s["bad"], s["found"], cam,
+                                              s["occupied"], 7.0, orb_dist, 0.9, check_ori)
+    active = dbg[:, 3] > 0
+    q, prm = Q.keyframe_and_current_frame(dbg[:, 0], dbg[:, 1], dbg[:, 2].astype(np.int32), s["last_kps"]["angle"], active, mc.SF, 7.0,
+                                          orb_dist, check_orientation=check_ori)
+    g = orc.make_geom(orc.make_params(1000, 1.2, 8, 20), mc.W, mc.H)
+    on, obest, omatch = orc.search_windows(g, kps, desc, s["right_x_kp"], s["occupied"], q, s["desc"], prm)
+    assert n == on
+    assert np.array_equal(match, np.where(omatch < 0, -1, omatch))
+    assert n > 40 and active.sum() > 1000
+    f.close()
