@@ -147,6 +147,21 @@ __host__ __device__ inline int64_t level_origin(const LevelGeom& g) {
 
 }  // namespace ydorb
 
+// One captured extract pipeline (the kernels of a sub-batch): replayed with a single cudaGraphLaunch while the call's
+// arguments stay the same (extractor_api.cu: run_stages)
+struct YdGraphEntry {
+  int f0, n, stride, capacity, fast_choice;
+  size_t frame_stride;
+  const void* d_images;
+  const void* d_kps;
+  const void* d_desc;
+  const void* d_nout;
+  cudaGraphExec_t exec;
+  int launches;               // kernels in the graph (bookkeeping of ydorb_kernel_launches)
+  unsigned long long stamp;   // last use, for eviction
+};
+constexpr int kYdGraphSlots = 24;
+
 // The extractor handle (opaque to C callers).
 struct YdExtractor {
   YdExtractorParams params;
@@ -159,6 +174,9 @@ struct YdExtractor {
   cudaEvent_t ev_block;     // blocking-sync event of the batched host entry point
   cudaStream_t in_stream, out_stream;   // H2D and D2H copy streams of the chunked host entry point
   cudaEvent_t ev_in[16], ev_done[16];   // per chunk: input resident / results ready
+  YdGraphEntry graphs[kYdGraphSlots];  // captured pipelines of the current geometry
+  unsigned long long graph_clock;
+  int graphs_off;           // capture failed once (or YDORB_GRAPHS=0): launch kernel by kernel from now on
   int profiling;            // record per-stage events
   cudaEvent_t ev_ring[64][5];  // per call: pyramid | fast | quadtree | describe boundaries (ring of 64 calls)
   cudaEvent_t* ev;           // slot of the current call

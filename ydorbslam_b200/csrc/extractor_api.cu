@@ -16,7 +16,11 @@ namespace ydorb {
 static thread_local std::string g_last_error;
 static std::atomic<long long> g_launches{0};
 
-void count_launches(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+static thread_local long long t_launches = 0;  // this thread's share (graph capture counts the kernels of one capture)
+void count_launches(int n) {
+  g_launches.fetch_add(n, std::memory_order_relaxed);
+  t_launches += n;
+}
 
 bool pdl_enabled() {
   static const bool on = !(getenv("YDORB_PDL") && atoi(getenv("YDORB_PDL")) == 0);
@@ -167,6 +171,8 @@ static int build_geom(const YdExtractor* ex, int w, int h, HostGeom* out) {
   return YDORB_OK;
 }
 
+static void drop_graphs(YdExtractor* ex);
+
 static int set_size(YdExtractor* ex, int w, int h) {
   if (ex->cur_w == w && ex->cur_h == h) return YDORB_OK;
   HostGeom hg;
@@ -177,6 +183,7 @@ static int set_size(YdExtractor* ex, int w, int h) {
     set_error("image larger than the max_width/max_height the extractor was created with");
     return YDORB_E_CAPACITY;
   }
+  drop_graphs(ex);  // captured for the previous geometry
   ex->geom = hg.g;
   ex->max_cell_w = ex->max_cell_h = 8;
   for (const int4& c : hg.cells) {
@@ -267,9 +274,9 @@ static YdExtractor frame_view(const YdExtractor* ex, int f0, cudaStream_t s) {
   return v;
 }
 
-// stages of frames [f0, f0+n) on stream s, no profiling events (used by the chunked host entry point)
-static int run_stages(const YdExtractor* ex, int f0, int n, cudaStream_t s, const uint8_t* d_images, int stride,
-                      size_t frame_stride, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity, int32_t* d_nout) {
+// stages of frames [f0, f0+n) on stream s, kernel by kernel
+static int run_stages_direct(const YdExtractor* ex, int f0, int n, cudaStream_t s, const uint8_t* d_images, int stride,
+                             size_t frame_stride, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity, int32_t* d_nout) {
   const YdExtractor v = frame_view(ex, f0, s);
   int rc;
   if ((rc = launch_pyramid(&v, d_images, stride, frame_stride, n, s)) != YDORB_OK) return rc;
@@ -284,6 +291,72 @@ static int run_stages(const YdExtractor* ex, int f0, int n, cudaStream_t s, cons
   return launch_describe(&v, n, d_kps, d_desc, capacity, d_nout, s);
 }
 
+static void drop_graphs(YdExtractor* ex) {
+  for (YdGraphEntry& e : ex->graphs)
+    if (e.exec) {
+      cudaGraphExecDestroy(e.exec);
+      e.exec = nullptr;
+    }
+}
+
+// The ~20 launches of a sub-batch are captured into a CUDA graph the first time a (frames, buffers) combination is
+// seen and replayed with ONE cudaGraphLaunch afterwards: the kernels' arguments are all known on the host (no stage reads
+// anything back), the programmatic-dependent-launch edges are kept by the capture.  A caller that keeps handing in the
+// same buffers (a SLAM front-end does; so does the chunked host entry point, whose buffers belong to the handle) pays
+// the per-kernel launch cost once.  YDORB_GRAPHS=0 switches this off; a failed capture switches it off for the handle.
+static int run_stages(YdExtractor* ex, int f0, int n, cudaStream_t s, const uint8_t* d_images, int stride,
+                      size_t frame_stride, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity, int32_t* d_nout) {
+  static const bool env_off = getenv("YDORB_GRAPHS") && atoi(getenv("YDORB_GRAPHS")) == 0;
+  if (env_off || ex->graphs_off)
+    return run_stages_direct(ex, f0, n, s, d_images, stride, frame_stride, d_kps, d_desc, capacity, d_nout);
+  const char* fk = getenv("YDORB_FAST_KERNEL");  // read per call by launch_fast: part of the key
+  const int fast_choice = fk ? fk[0] : 0;
+  YdGraphEntry* hit = nullptr;
+  YdGraphEntry* victim = &ex->graphs[0];
+  for (YdGraphEntry& e : ex->graphs) {
+    if (e.exec && e.f0 == f0 && e.n == n && e.d_images == d_images && e.stride == stride && e.frame_stride == frame_stride &&
+        e.d_kps == d_kps && e.d_desc == d_desc && e.capacity == capacity && e.d_nout == d_nout && e.fast_choice == fast_choice) {
+      hit = &e;
+      break;
+    }
+    if (!e.exec || (victim->exec && e.stamp < victim->stamp)) victim = &e;
+  }
+  if (hit) {
+    hit->stamp = ++ex->graph_clock;
+    YD_CUDA(cudaGraphLaunch(hit->exec, s));
+    count_launches(hit->launches);
+    return YDORB_OK;
+  }
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(s, &st) != cudaSuccess || st != cudaStreamCaptureStatusNone)  // the caller captures already
+    return run_stages_direct(ex, f0, n, s, d_images, stride, frame_stride, d_kps, d_desc, capacity, d_nout);
+  const long long l0 = t_launches;
+  if (cudaStreamBeginCapture(s, cudaStreamCaptureModeRelaxed) != cudaSuccess) {
+    cudaGetLastError();
+    ex->graphs_off = 1;
+    return run_stages_direct(ex, f0, n, s, d_images, stride, frame_stride, d_kps, d_desc, capacity, d_nout);
+  }
+  const int rc = run_stages_direct(ex, f0, n, s, d_images, stride, frame_stride, d_kps, d_desc, capacity, d_nout);
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(s, &graph);
+  cudaGraphExec_t exec = nullptr;
+  if (rc == YDORB_OK && e == cudaSuccess && graph) e = cudaGraphInstantiate(&exec, graph, 0);
+  if (graph) cudaGraphDestroy(graph);
+  if (rc != YDORB_OK || e != cudaSuccess || !exec) {
+    cudaGetLastError();
+    g_launches.fetch_sub(t_launches - l0);
+    t_launches = l0;
+    if (rc != YDORB_OK) return rc;
+    ex->graphs_off = 1;  // this driver / stream cannot capture the chain: plain launches from now on
+    return run_stages_direct(ex, f0, n, s, d_images, stride, frame_stride, d_kps, d_desc, capacity, d_nout);
+  }
+  if (victim->exec) cudaGraphExecDestroy(victim->exec);
+  *victim = YdGraphEntry{f0, n, stride, capacity, fast_choice, frame_stride, d_images, d_kps, d_desc, d_nout, exec,
+                         (int)(t_launches - l0), ++ex->graph_clock};
+  YD_CUDA(cudaGraphLaunch(exec, s));  // (the capture counted the launches already)
+  return YDORB_OK;
+}
+
 static int run_pipeline(YdExtractor* ex, const uint8_t* d_images, int w, int h, int stride, size_t frame_stride,
                         int batch, YdKeyPoint* d_kps, uint8_t* d_desc, int capacity, int32_t* d_nout) {
   int rc = set_size(ex, w, h);
@@ -291,6 +364,7 @@ static int run_pipeline(YdExtractor* ex, const uint8_t* d_images, int w, int h, 
   ex->cur_batch = batch;
   cudaStream_t s = ex->stream;
   const bool prof = ex->profiling != 0;
+  if (!prof) return run_stages(ex, 0, batch, s, d_images, stride, frame_stride, d_kps, d_desc, capacity, d_nout);
   if (prof) ex->ev = ex->ev_ring[ex->prof_calls++ % 64];
   if (prof) YD_CUDA(cudaEventRecord(ex->ev[0], s));
   if ((rc = launch_pyramid(ex, d_images, stride, frame_stride, batch, s)) != YDORB_OK) return rc;
@@ -436,6 +510,7 @@ void ydorb_extractor_destroy(YdExtractor* ex) {
     if (p) cudaFree(p);
   for (int i = 0; i < 64 * 5; i++)
     if (ex->ev_ring[i / 5][i % 5]) cudaEventDestroy(ex->ev_ring[i / 5][i % 5]);
+  drop_graphs(ex);
   if (ex->ev_fork) cudaEventDestroy(ex->ev_fork);
   if (ex->ev_join) cudaEventDestroy(ex->ev_join);
   if (ex->ev_block) cudaEventDestroy(ex->ev_block);
