@@ -285,7 +285,7 @@ inline int OrbMatcher::searchWindows(FrameFeatures& _frame, const std::vector<Yd
 // ORB-SLAM2's published algorithm on this reference's Frame hooks (ydorb_match_windowed_top2, no reference parity claim):
 // vbPrevMatched in/out as (x, y) pairs, vnMatches12[i1] = matched key point of _frame2 or -1; returns the match count.
 // areaMode 0 = the reference's getKeyPointsInArea predicate, 1 = ORB-SLAM2's own.
-inline int searchForInitialization(OrbMatcher& m, const std::vector<KeyPoint>& kps1, const std::vector<uint8_t>& desc1,
+inline int searchForInitialization(OrbMatcher& /*matcher of _frame2*/, const std::vector<KeyPoint>& kps1, const std::vector<uint8_t>& desc1,
                                    FrameFeatures& _frame2, std::vector<float>& vbPrevMatched, std::vector<int32_t>& vnMatches12,
                                    int windowSize = 10, float nnRatio = 0.9f, bool checkOrientation = true, int areaMode = 0) {
   vnMatches12.assign(kps1.size(), -1);
