@@ -277,3 +277,27 @@ def search_by_bow_keyframe_frame(kps1, desc1, valid1, fv1, kps2, desc2, fv2, rat
                                          len(k2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]), C.c_float(ratio), int(bool(check_orientation)),
                                          _p(out))
     return n, out[: len(k2)]
+
+
+def search_for_triangulation(kps1, desc1, rx1, has_mp1, fv1, kps2, desc2, rx2, has_mp2, fv2, F, origin1, cam, sf, sf2, stereo_only,
+                             ratio=0.6, check_orientation=True):
+    """OrbMatcher::searchForTriangulation (src/orbMatcher.cpp:463-565) of the compiled reference on two KeyFrames built from
+    the arrays; origin1 = camera origin of key frame 1 in the frame of key frame 2 (identity pose).  Returns (return value,
+    pairs [n][2], epipole as the reference computed it)."""
+    k1, k2 = np.ascontiguousarray(kps1, dtype=KP_DTYPE), np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+    d1, d2 = np.ascontiguousarray(desc1, dtype=np.uint8), np.ascontiguousarray(desc2, dtype=np.uint8)
+    r1, r2 = np.ascontiguousarray(rx1, dtype=np.float32), np.ascontiguousarray(rx2, dtype=np.float32)
+    h1, h2 = np.ascontiguousarray(has_mp1, dtype=np.uint8), np.ascontiguousarray(has_mp2, dtype=np.uint8)
+    a = [np.ascontiguousarray(x, dtype=np.int32) for x in fv1]
+    b = [np.ascontiguousarray(x, dtype=np.int32) for x in fv2]
+    Fm = np.ascontiguousarray(F, dtype=np.float32).reshape(9)
+    o1 = np.ascontiguousarray(origin1, dtype=np.float32)
+    cm = np.ascontiguousarray(cam, dtype=np.float32)
+    sfa, sf2a = np.ascontiguousarray(sf, dtype=np.float32), np.ascontiguousarray(sf2, dtype=np.float32)
+    pairs = np.zeros((max(len(k1), 1), 2), np.int32)
+    ep = np.zeros(2, np.float32)
+    n = lib().ref_search_for_triangulation(_p(k1), _p(d1), _p(r1), _p(h1), len(k1), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]),
+                                           _p(k2), _p(d2), _p(r2), _p(h2), len(k2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]), _p(Fm),
+                                           _p(o1), _p(cm), _p(sfa), _p(sf2a), len(sfa), int(bool(stereo_only)), C.c_float(ratio),
+                                           int(bool(check_orientation)), _p(pairs), _p(ep))
+    return n, pairs[:n].copy(), (ep[0], ep[1])

@@ -337,6 +337,77 @@ int ref_search_keyframe_current(void* p, const RefKeyPoint* kf_kps, int n_kf, co
   return ret;
 }
 
+/* M6  OrbMatcher::searchForTriangulation (src/orbMatcher.cpp:463-565, epipolar gate :808-819) on two KeyFrames built by the
+ * reference's constructor: side i = key points, descriptors, rightX, FeatureVector (CSR), a MapPoint where has_mp[i].
+ * Key frame 2 sits at the identity pose, key frame 1 at [I | -origin1], so that the reference's own cv::Mat arithmetic
+ * (:465-470) puts the epipole where the caller wants it; epipole_out receives the value it computed.
+ * pairs_out: [2 * n] (first, second) indices; returns the function's return value. */
+int ref_search_for_triangulation(const RefKeyPoint* kps1, const uint8_t* desc1, const float* rx1, const uint8_t* has_mp1, int n1,
+                                 const int32_t* ids1, const int32_t* start1, const int32_t* items1, int nn1,
+                                 const RefKeyPoint* kps2, const uint8_t* desc2, const float* rx2, const uint8_t* has_mp2, int n2,
+                                 const int32_t* ids2, const int32_t* start2, const int32_t* items2, int nn2, const float* F,
+                                 const float* origin1, const float* cam, const float* sf, const float* sf2, int n_levels,
+                                 int stereo_only, float ratio, int check_orientation, int32_t* pairs_out, float* epipole_out) {
+  using namespace YDORBSLAM;
+  Frame::m_flt_fx = cam[0]; Frame::m_flt_fy = cam[1]; Frame::m_flt_cx = cam[2]; Frame::m_flt_cy = cam[3];
+  Frame::m_flt_baseLineTimesFx = cam[4];
+  Frame::m_flt_baseLine = cam[5];
+  Frame src;
+  src.m_v_keyPoints.assign(1, cv::KeyPoint());
+  src.m_v_scaleFactors.assign(sf, sf + n_levels);
+  src.m_cvMat_descriptors = cv::Mat::zeros(1, 32, CV_8UC1);
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  cv::Mat pos = (cv::Mat_<float>(3, 1) << 0.f, 0.f, 1.f);
+  std::shared_ptr<MapPoint> some = std::make_shared<ProbePoint>(pos, src, 0);
+  auto fill = [&](Frame& f, const RefKeyPoint* kps, const uint8_t* desc, const float* rx, const uint8_t* has, int n,
+                  const int32_t* ids, const int32_t* start, const int32_t* items, int nn) {
+    f.m_v_keyPoints.resize(n);
+    for (int i = 0; i < n; i++) {
+      cv::KeyPoint k;
+      k.pt.x = kps[i].x; k.pt.y = kps[i].y; k.size = kps[i].size; k.angle = kps[i].angle;
+      k.response = kps[i].response; k.octave = kps[i].octave; k.class_id = kps[i].class_id;
+      f.m_v_keyPoints[i] = k;
+    }
+    f.m_int_keyPointsNum = n;
+    f.m_cvMat_descriptors.create(std::max(n, 1), 32, CV_8UC1);
+    for (int i = 0; i < n; i++) memcpy(f.m_cvMat_descriptors.ptr(i), desc + (size_t)32 * i, 32);
+    f.m_v_rightXcords.assign(rx, rx + n);
+    f.m_v_scaleFactors.assign(sf, sf + n_levels);
+    f.m_v_scaleFactorSquares.assign(sf2, sf2 + n_levels);
+    f.m_int_scaleLevelsNum = n_levels;
+    for (int k = 0; k < nn; k++)
+      for (int t = start[k]; t < start[k + 1]; t++) f.m_bow_keyPointsVec.addFeature((DBoW3::NodeId)ids[k], (unsigned)items[t]);
+    f.m_v_sptrMapPoints.assign(n, std::shared_ptr<MapPoint>());
+    for (int i = 0; i < n; i++)
+      if (has[i]) f.m_v_sptrMapPoints[i] = some;
+  };
+  Frame a, b;
+  fill(a, kps1, desc1, rx1, has_mp1, n1, ids1, start1, items1, nn1);
+  fill(b, kps2, desc2, rx2, has_mp2, n2, ids2, start2, items2, nn2);
+  cv::Mat T1 = cv::Mat::eye(4, 4, CV_32F);
+  for (int k = 0; k < 3; k++) T1.at<float>(k, 3) = -origin1[k];
+  a.setCameraPoseByTransform_c2w(T1);
+  b.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  std::shared_ptr<KeyFrame> kf1 = std::make_shared<KeyFrame>(a, std::shared_ptr<Map>(), std::shared_ptr<KeyFrameDatabase>());
+  std::shared_ptr<KeyFrame> kf2 = std::make_shared<KeyFrame>(b, std::shared_ptr<Map>(), std::shared_ptr<KeyFrameDatabase>());
+  {
+    cv::Mat o1 = kf1->getCameraOriginInWorld(), R2 = kf2->getRotation_c2w(), t2 = kf2->getTranslation_c2w();
+    cv::Mat o = R2 * o1 + t2;
+    epipole_out[0] = Frame::m_flt_fx * o.at<float>(0) / o.at<float>(2) + Frame::m_flt_cx;
+    epipole_out[1] = Frame::m_flt_fy * o.at<float>(1) / o.at<float>(2) + Frame::m_flt_cy;
+  }
+  cv::Mat Fm(3, 3, CV_32F);
+  for (int i = 0; i < 9; i++) Fm.at<float>(i / 3, i % 3) = F[i];
+  OrbMatcher matcher(ratio, check_orientation != 0);
+  std::vector<std::pair<int, int>> pairs;
+  const int ret = matcher.searchForTriangulation(kf1, kf2, Fm, pairs, stereo_only != 0);
+  for (size_t i = 0; i < pairs.size(); i++) {
+    pairs_out[2 * i] = pairs[i].first;
+    pairs_out[2 * i + 1] = pairs[i].second;
+  }
+  return ret;
+}
+
 /* M0 */
 int ref_descriptor_distance(const uint8_t* a, const uint8_t* b) {
   cv::Mat ma(1, 32, CV_8UC1, const_cast<uint8_t*>(a)), mb(1, 32, CV_8UC1, const_cast<uint8_t*>(b));

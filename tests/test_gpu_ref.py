@@ -209,3 +209,25 @@ def test_cuda_keyframe_and_current_frame_matches_compiled_reference():
     assert n == rn and np.array_equal(np.where(match < 0, -1, match), rmatch)
     assert n > 40
     fr.close(); m.close(); f.close()
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+@pytest.mark.parametrize("stereo_only", [False, True])
+def test_cuda_search_for_triangulation_matches_compiled_reference(stereo_only):
+    """M6: CUDA searchForTriangulation == the reference's own (src/orbMatcher.cpp:463-565, :808-819 compiled unmodified)."""
+    from tests import matcher_cases as mc
+    from ydorbslam_b200 import OrbMatcher
+
+    s = mc.bow_scene(1000, 1100, 3)
+    F, ep = mc.fundamental(3)
+    has1, has2 = 1 - s["v1"], 1 - s["v2"]
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    origin1 = [(float(ep[0]) - float(mc.CAM["cx"])) / float(mc.CAM["fx"]), (float(ep[1]) - float(mc.CAM["cy"])) / float(mc.CAM["fy"]), 1.0]
+    rn, rpairs, rep = ref.search_for_triangulation(s["k1"], s["d1"], s["rx1"], has1, s["fv1"], s["k2"], s["d2"], s["rx2"], has2,
+                                                   s["fv2"], F, origin1, cam, mc.SF, mc.SF2, stereo_only, 0.6, True)
+    m = OrbMatcher(0.6, True)
+    n, pairs = m.searchForTriangulation(s["k1"], s["d1"], s["rx1"], has1, s["fv1"], s["k2"], s["d2"], s["rx2"], has2, s["fv2"],
+                                        F, rep, mc.SF, mc.SF2, stereo_only)
+    assert n == rn and np.array_equal(pairs, rpairs)
+    assert n > 15
+    m.close()

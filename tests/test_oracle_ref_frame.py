@@ -181,3 +181,23 @@ def test_search_keyframe_and_current_frame_reference_equals_oracle(check_ori, or
     assert np.array_equal(match, np.where(omatch < 0, -1, omatch))
     assert n > 40 and active.sum() > 1000
     f.close()
+
+
+@pytest.mark.parametrize("n1,n2,seed,stereo_only,check_ori", [(1000, 1100, 3, False, True), (1000, 1100, 4, True, True),
+                                                              (600, 400, 5, False, False)])
+def test_search_for_triangulation_reference_equals_oracle(n1, n2, seed, stereo_only, check_ori):
+    """M6: the reference's own searchForTriangulation (epipole from its cv::Mat arithmetic, epipole-distance gate,
+    isEpipolarLineDistCorrect, greedy exclusion, rotation histogram) == the oracle, on the epipole the reference computed."""
+    s = mc.bow_scene(n1, n2, seed)
+    F, ep = mc.fundamental(seed)
+    has1, has2 = 1 - s["v1"], 1 - s["v2"]
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    origin1 = [(float(ep[0]) - float(mc.CAM["cx"])) / float(mc.CAM["fx"]), (float(ep[1]) - float(mc.CAM["cy"])) / float(mc.CAM["fy"]), 1.0]
+    n, pairs, rep = ref.search_for_triangulation(s["k1"], s["d1"], s["rx1"], has1, s["fv1"], s["k2"], s["d2"], s["rx2"], has2, s["fv2"],
+                                                 F, origin1, cam, mc.SF, mc.SF2, stereo_only, 0.6, check_ori)
+    assert abs(rep[0] - ep[0]) < 1e-2 and abs(rep[1] - ep[1]) < 1e-2
+    on, opairs = orc.search_for_triangulation(s["k1"], s["d1"], s["rx1"], has1, s["fv1"], s["k2"], s["d2"], s["rx2"], has2, s["fv2"],
+                                              F, rep, mc.SF, mc.SF2, stereo_only, check_ori)
+    assert n == on and np.array_equal(pairs, opairs)
+    if n1 >= 1000:
+        assert n > 15
