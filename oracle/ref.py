@@ -301,3 +301,18 @@ def search_for_triangulation(kps1, desc1, rx1, has_mp1, fv1, kps2, desc2, rx2, h
                                            _p(o1), _p(cm), _p(sfa), _p(sf2a), len(sfa), int(bool(stereo_only)), C.c_float(ratio),
                                            int(bool(check_orientation)), _p(pairs), _p(ep))
     return n, pairs[:n].copy(), (ep[0], ep[1])
+
+
+def search_by_bow_two_keyframes(kps1, desc1, valid1, fv1, kps2, desc2, valid2, fv2, ratio, check_orientation=True):
+    """OrbMatcher::searchByBowInTwoKeyFrames (src/orbMatcher.cpp:380-462) of the compiled reference.  Returns (return
+    value, match per side-1 key point)."""
+    k1, k2 = np.ascontiguousarray(kps1, dtype=KP_DTYPE), np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+    d1, d2 = np.ascontiguousarray(desc1, dtype=np.uint8), np.ascontiguousarray(desc2, dtype=np.uint8)
+    v1, v2 = np.ascontiguousarray(valid1, dtype=np.uint8), np.ascontiguousarray(valid2, dtype=np.uint8)
+    a = [np.ascontiguousarray(x, dtype=np.int32) for x in fv1]
+    b = [np.ascontiguousarray(x, dtype=np.int32) for x in fv2]
+    out = np.full(max(len(k1), 1), -1, np.int32)
+    n = lib().ref_search_by_bow_two_keyframes(_p(k1), _p(d1), _p(v1), len(k1), _p(a[0]), _p(a[1]), _p(a[2]), len(a[0]), _p(k2), _p(d2),
+                                              _p(v2), len(k2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]), C.c_float(ratio),
+                                              int(bool(check_orientation)), _p(out))
+    return n, out[: len(k1)]

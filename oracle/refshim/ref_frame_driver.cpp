@@ -337,6 +337,54 @@ int ref_search_keyframe_current(void* p, const RefKeyPoint* kf_kps, int n_kf, co
   return ret;
 }
 
+/* M5b OrbMatcher::searchByBowInTwoKeyFrames (src/orbMatcher.cpp:380-462): both sides are KeyFrames with a MapPoint where
+ * valid[i].  match_out[i1] = key point of key frame 2 whose map point the call gave to key point i1, or -1. */
+int ref_search_by_bow_two_keyframes(const RefKeyPoint* kps1, const uint8_t* desc1, const uint8_t* valid1, int n1,
+                                    const int32_t* ids1, const int32_t* start1, const int32_t* items1, int nn1,
+                                    const RefKeyPoint* kps2, const uint8_t* desc2, const uint8_t* valid2, int n2,
+                                    const int32_t* ids2, const int32_t* start2, const int32_t* items2, int nn2, float ratio,
+                                    int check_orientation, int32_t* match_out) {
+  using namespace YDORBSLAM;
+  Frame src;
+  src.m_v_keyPoints.assign(std::max(n2, 1), cv::KeyPoint());
+  src.m_v_scaleFactors.assign(8, 1.0f);
+  src.m_cvMat_descriptors = cv::Mat::zeros(std::max(n2, 1), 32, CV_8UC1);
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  cv::Mat pos = (cv::Mat_<float>(3, 1) << 0.f, 0.f, 1.f);
+  std::map<const MapPoint*, int> index2;
+  auto fill = [&](Frame& f, const RefKeyPoint* kps, const uint8_t* desc, const uint8_t* valid, int n, const int32_t* ids,
+                  const int32_t* start, const int32_t* items, int nn, bool second) {
+    f.m_v_keyPoints.resize(n);
+    for (int i = 0; i < n; i++) {
+      cv::KeyPoint k;
+      k.pt.x = kps[i].x; k.pt.y = kps[i].y; k.size = kps[i].size; k.angle = kps[i].angle;
+      k.response = kps[i].response; k.octave = kps[i].octave; k.class_id = kps[i].class_id;
+      f.m_v_keyPoints[i] = k;
+    }
+    f.m_int_keyPointsNum = n;
+    f.m_cvMat_descriptors.create(std::max(n, 1), 32, CV_8UC1);
+    for (int i = 0; i < n; i++) memcpy(f.m_cvMat_descriptors.ptr(i), desc + (size_t)32 * i, 32);
+    for (int k = 0; k < nn; k++)
+      for (int t = start[k]; t < start[k + 1]; t++) f.m_bow_keyPointsVec.addFeature((DBoW3::NodeId)ids[k], (unsigned)items[t]);
+    f.m_v_sptrMapPoints.assign(n, std::shared_ptr<MapPoint>());
+    for (int i = 0; i < n; i++)
+      if (valid[i]) {
+        f.m_v_sptrMapPoints[i] = std::make_shared<ProbePoint>(pos, src, 0);
+        if (second) index2[f.m_v_sptrMapPoints[i].get()] = i;
+      }
+  };
+  Frame a, b;
+  fill(a, kps1, desc1, valid1, n1, ids1, start1, items1, nn1, false);
+  fill(b, kps2, desc2, valid2, n2, ids2, start2, items2, nn2, true);
+  std::shared_ptr<KeyFrame> kf1 = std::make_shared<KeyFrame>(a, std::shared_ptr<Map>(), std::shared_ptr<KeyFrameDatabase>());
+  std::shared_ptr<KeyFrame> kf2 = std::make_shared<KeyFrame>(b, std::shared_ptr<Map>(), std::shared_ptr<KeyFrameDatabase>());
+  OrbMatcher matcher(ratio, check_orientation != 0);
+  std::vector<std::shared_ptr<MapPoint>> matched;
+  const int ret = matcher.searchByBowInTwoKeyFrames(kf1, kf2, matched);
+  for (int i = 0; i < n1; i++) match_out[i] = matched[i] ? index2[matched[i].get()] : -1;
+  return ret;
+}
+
 /* M6  OrbMatcher::searchForTriangulation (src/orbMatcher.cpp:463-565, epipolar gate :808-819) on two KeyFrames built by the
  * reference's constructor: side i = key points, descriptors, rightX, FeatureVector (CSR), a MapPoint where has_mp[i].
  * Key frame 2 sits at the identity pose, key frame 1 at [I | -origin1], so that the reference's own cv::Mat arithmetic

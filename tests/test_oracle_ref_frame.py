@@ -201,3 +201,13 @@ def test_search_for_triangulation_reference_equals_oracle(n1, n2, seed, stereo_o
     assert n == on and np.array_equal(pairs, opairs)
     if n1 >= 1000:
         assert n > 15
+
+
+@pytest.mark.parametrize("n1,n2,seed,check_ori", [(800, 900, 3, True), (300, 1500, 5, False)])
+def test_search_by_bow_two_keyframes_reference_equals_oracle(n1, n2, seed, check_ori):
+    """M5 second mode: the reference's own searchByBowInTwoKeyFrames == the oracle (mode 1)."""
+    s = mc.bow_scene(n1, n2, seed)
+    n, match = ref.search_by_bow_two_keyframes(s["k1"], s["d1"], s["v1"], s["fv1"], s["k2"], s["d2"], s["v2"], s["fv2"], 0.7, check_ori)
+    on, omatch = orc.search_by_bow(1, s["k1"], s["d1"], s["v1"], s["fv1"], s["k2"], s["d2"], s["v2"], s["fv2"], 0.7, check_ori)
+    assert n == on and np.array_equal(match, omatch)
+    assert n > 30
