@@ -252,6 +252,18 @@ class RefFrame:
                                               C.c_float(ratio), int(bool(check_orientation)), _p(match), _p(dbg))
         return n, match[: self.n_left], dbg[: len(kk)]
 
+    def search_in_sim(self, mp_pos, mp_desc, min_dist, max_dist, is_bad, cam, kp_occupied, thd, ratio=0.6):
+        """OrbMatcher::searchByProjectionInSim (src/orbMatcher.cpp:240-302) of the compiled reference with the identity
+        similarity, this frame as the KeyFrame.  Returns (return value, match per key point, dbg [n_mp][4])."""
+        arrs = [np.ascontiguousarray(a, dtype=t) for a, t in ((mp_pos, np.float32), (mp_desc, np.uint8), (min_dist, np.float32),
+                                                               (max_dist, np.float32), (is_bad, np.uint8), (cam, np.float32))]
+        n_mp = len(arrs[0])
+        occ = None if kp_occupied is None else np.ascontiguousarray(kp_occupied, dtype=np.uint8)
+        match = np.full(max(self.n_left, 1), -1, np.int32)
+        dbg = np.zeros((max(n_mp, 1), 4), np.float32)
+        n = lib().ref_search_in_sim(self._h, n_mp, *[_p(a) for a in arrs], _p(occ), int(thd), C.c_float(ratio), _p(match), _p(dbg))
+        return n, match[: self.n_left], dbg[:n_mp]
+
     def close(self):
         if self._h:
             lib().ref_frame_destroy(self._h)

@@ -210,6 +210,80 @@ int ref_search_last_current(void* p, const RefKeyPoint* last_kps, int n_last, co
   return ret;
 }
 
+/* M4a OrbMatcher::searchByProjectionInSim (src/orbMatcher.cpp:240-302) with the identity similarity.  `p` (made by
+ * ref_frame_from_keypoints + ref_frame_set_features) becomes the KeyFrame through the reference's constructor; the map
+ * points are built like in M3.  kp_occupied[i]: _vSptrMatchedMapPoints[i] is non-null on entry.  match_out[i] = index of
+ * the map point the call put into slot i, -1 = none / was occupied.  dbg as in ref_search_keyframe_current. */
+int ref_search_in_sim(void* p, int n_mp, const float* mp_pos, const uint8_t* mp_desc, const float* min_dist, const float* max_dist,
+                      const uint8_t* is_bad, const float* cam, const uint8_t* kp_occupied, int thd, float ratio,
+                      int32_t* match_out, float* dbg) {
+  using namespace YDORBSLAM;
+  Frame* fr = static_cast<Frame*>(p);
+  const int n = (int)fr->m_v_keyPoints.size();
+  Frame::m_flt_fx = cam[0]; Frame::m_flt_fy = cam[1]; Frame::m_flt_cx = cam[2]; Frame::m_flt_cy = cam[3];
+  Frame::m_flt_baseLineTimesFx = cam[4];
+  Frame::m_flt_baseLine = cam[5];
+  fr->setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  fr->m_int_keyPointsNum = n;
+  std::shared_ptr<KeyFrame> kf = std::make_shared<KeyFrame>(*fr, std::shared_ptr<Map>(), std::shared_ptr<KeyFrameDatabase>());
+  Frame src;
+  src.m_v_keyPoints.assign(n_mp + 1, cv::KeyPoint());
+  src.m_v_scaleFactors = fr->m_v_scaleFactors;
+  src.m_cvMat_descriptors.create(n_mp + 1, 32, CV_8UC1);
+  for (int i = 0; i < n_mp; i++) memcpy(src.m_cvMat_descriptors.ptr(i), mp_desc + (size_t)32 * i, 32);
+  memset(src.m_cvMat_descriptors.ptr(n_mp), 0, 32);
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  std::vector<std::shared_ptr<MapPoint>> points(n_mp);
+  std::map<const MapPoint*, int> index;
+  for (int i = 0; i < n_mp; i++) {
+    if (mp_pos[3 * i] != mp_pos[3 * i]) continue;  // NaN: a null entry of _vSptrMapPoints
+    cv::Mat pos = (cv::Mat_<float>(3, 1) << mp_pos[3 * i], mp_pos[3 * i + 1], mp_pos[3 * i + 2]);
+    std::shared_ptr<ProbePoint> mp = std::make_shared<ProbePoint>(pos, src, i);
+    mp->distances(min_dist[i], max_dist[i]);
+    mp->bad(is_bad && is_bad[i]);
+    points[i] = mp;
+    index[mp.get()] = i;
+  }
+  cv::Mat pos0 = (cv::Mat_<float>(3, 1) << 0.f, 0.f, 1.f);
+  std::shared_ptr<MapPoint> held = std::make_shared<ProbePoint>(pos0, src, n_mp);
+  std::vector<std::shared_ptr<MapPoint>> matched(n);
+  for (int i = 0; i < n; i++)
+    if (kp_occupied && kp_occupied[i]) matched[i] = held;
+  cv::Mat sim = cv::Mat::eye(4, 4, CV_32F);
+  if (dbg) {  // the expressions of :242-268 on the same objects
+    cv::Mat sR = sim.rowRange(0, 3).colRange(0, 3);
+    const float scale = sqrt(sR.row(0).dot(sR.row(0)));
+    cv::Mat R = sR / scale;
+    cv::Mat t = sim.rowRange(0, 3).col(3);
+    cv::Mat origin = -R.t() * t;
+    for (int i = 0; i < n_mp; i++) {
+      float* d = dbg + 4 * i;
+      d[0] = d[1] = d[2] = d[3] = 0.f;
+      std::shared_ptr<MapPoint> mp = points[i];
+      if (!mp || mp->isBad()) continue;
+      cv::Mat pw = mp->getPosInWorld();
+      cv::Mat pc = R * pw + t;
+      const float x = pc.at<float>(0), y = pc.at<float>(1), z = pc.at<float>(2);
+      const float u = Frame::m_flt_fx * x / z + Frame::m_flt_cx;
+      const float v = Frame::m_flt_fy * y / z + Frame::m_flt_cy;
+      const float maxD = mp->getMaxDistanceInvariance(), minD = mp->getMinDistanceInvariance();
+      cv::Mat vec = pw - origin;
+      const float distance = cv::norm(vec);
+      d[0] = u;
+      d[1] = v;
+      d[2] = (float)mp->predictScaleLevel(distance, kf);
+      d[3] = (z >= 0.0 && kf->isInImage(u, v) && distance >= minD && distance <= maxD && vec.dot(mp->getNormal()) >= 0.5 * distance) ? 1.f : 0.f;
+    }
+  }
+  OrbMatcher matcher(ratio, true);
+  const int ret = matcher.searchByProjectionInSim(kf, sim, points, matched, thd);
+  for (int i = 0; i < n; i++) {
+    const MapPoint* q = matched[i].get();
+    match_out[i] = (q && q != held.get()) ? index[q] : -1;
+  }
+  return ret;
+}
+
 /* M5  OrbMatcher::searchByBowInKeyFrameAndFrame (src/orbMatcher.cpp:303-379) on a KeyFrame built by the reference's own
  * constructor from side 1 (key points, descriptors, FeatureVector in CSR form, a MapPoint where valid1[i]) and a Frame
  * from side 2.  match_out[i2] = key point of the key frame whose map point the call gave to key point i2, or -1. */

@@ -211,3 +211,23 @@ def test_search_by_bow_two_keyframes_reference_equals_oracle(n1, n2, seed, check
     on, omatch = orc.search_by_bow(1, s["k1"], s["d1"], s["v1"], s["fv1"], s["k2"], s["d2"], s["v2"], s["fv2"], 0.7, check_ori)
     assert n == on and np.array_equal(match, omatch)
     assert n > 30
+
+
+def test_search_by_projection_in_sim_reference_equals_oracle():
+    """M4 (first member): the reference's own searchByProjectionInSim (identity similarity) == the oracle's window search
+    with the octave gate [level-1, level] (:285-286), the matched-slot exclusion (:284) and the <= lowThd rule (:294)."""
+    from ydorbslam_b200 import queries as Q
+
+    kps, desc = mc.synth_keypoints(900, 25)
+    s = _keyframe_scene(kps, desc, 3000, 35, 7.0)
+    f = ref.RefFrame.from_keypoints(kps, (0, 0, mc.W, mc.H))
+    f.set_features(desc, s["right_x_kp"], mc.SF)
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    n, match, dbg = f.search_in_sim(s["pos"], s["desc"], s["min_d"], s["max_d"], s["bad"], cam, s["occupied"], 7, 0.6)
+    q, prm = Q.in_sim(dbg[:, 0], dbg[:, 1], dbg[:, 2].astype(np.int32), dbg[:, 3] > 0, mc.SF, 7)
+    g = orc.make_geom(orc.make_params(1000, 1.2, 8, 20), mc.W, mc.H)
+    on, obest, omatch = orc.search_windows(g, kps, desc, s["right_x_kp"], s["occupied"], q, s["desc"], prm)
+    assert n == on
+    assert np.array_equal(match, np.where(omatch < 0, -1, omatch))
+    assert n > 20 and (dbg[:, 3] > 0).sum() > 1000
+    f.close()
