@@ -121,7 +121,8 @@ constexpr int kCtrChanged = 4;
 
 __device__ __forceinline__ float search_radius(const SearchArgs& A, const YdMapPointProj& mp) {
   const float radius = __fmul_rn(A.th, ((double)mp.view_cos > 0.998) ? 2.5f : 4.0f);  // :30, :820-826
-  return __fmul_rn(radius, A.gp.sf[mp.level]);
+  // (the device entry point cannot validate levels that live in device memory: clamp the table index)
+  return __fmul_rn(radius, A.gp.sf[min(max(mp.level, 0), kMaxLevels - 1)]);
 }
 
 // the window walk of map point j (:31 getKeyPointsInArea order, then the gates of :41): f(idx, octave, dist)
