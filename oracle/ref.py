@@ -328,3 +328,24 @@ def search_by_bow_two_keyframes(kps1, desc1, valid1, fv1, kps2, desc2, valid2, f
                                               _p(v2), len(k2), _p(b[0]), _p(b[1]), _p(b[2]), len(b[0]), C.c_float(ratio),
                                               int(bool(check_orientation)), _p(out))
     return n, out[: len(k1)]
+
+
+def frustum(R, t, cam, bounds, scale_factor, n_levels, map_points, view_cos_limit=0.5):
+    """Frame::isInCameraFrustum + MapPoint::predictScaleLevel of the compiled reference (src/frame.cpp:295-326) for every map
+    point (orc.MAPPOINT3D_DTYPE).  Returns orc.MPPROJ_DTYPE records; fields other than `active` are what the reference
+    wrote into the MapPoint, i.e. meaningful where active."""
+    mp = np.ascontiguousarray(map_points, orc.MAPPOINT3D_DTYPE)
+    out = np.zeros(max(len(mp), 1), orc.MPPROJ_DTYPE)
+    a = [np.ascontiguousarray(x, dtype=np.float32) for x in (np.asarray(R).reshape(9), t, cam, bounds)]
+    lib().ref_frustum(*[_p(x) for x in a], C.c_float(scale_factor), int(n_levels), _p(mp), len(mp), C.c_float(view_cos_limit), _p(out))
+    return out[: len(mp)]
+
+
+def distinctive_descriptors(desc, start):
+    """MapPoint::computeDistinctiveDescriptors (src/mapPoint.cpp:169-218) of the compiled reference for CSR observation
+    sets; returns the [n_points][32] descriptors it left in the MapPoints (zeros where a point has no observation)."""
+    d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    s = np.ascontiguousarray(start, np.int32)
+    out = np.zeros((len(s) - 1, 32), np.uint8)
+    lib().ref_distinctive_descriptors(_p(d), _p(s), len(s) - 1, _p(out))
+    return out

@@ -19,6 +19,7 @@
  */
 #include <stdint.h>
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <map>
@@ -76,6 +77,11 @@ struct ProbePoint : YDORBSLAM::MapPoint {
   void observations(int n) { m_int_observationsNum = n; }
   void distances(float mn, float mx) { m_flt_minDistance = mn; m_flt_maxDistance = mx; }
   void bad(bool b) { m_b_bad = b; }
+  void normal(float x, float y, float z) { m_cvMat_normalVector = (cv::Mat_<float>(3, 1) << x, y, z); }
+};
+
+struct RefMapPoint3d {  // = OrcMapPoint3d = YdMapPoint3d
+  float pos[3], normal[3], max_distance, min_distance;
 };
 
 struct RefMapPointProj {  // = OrcMapPointProj = YdMapPointProj
@@ -528,6 +534,78 @@ int ref_search_for_triangulation(const RefKeyPoint* kps1, const uint8_t* desc1, 
     pairs_out[2 * i + 1] = pairs[i].second;
   }
   return ret;
+}
+
+/* N2  Frame::isInCameraFrustum + MapPoint::predictScaleLevel (src/frame.cpp:295-326, src/mapPoint.cpp:265-278) for n map
+ * points seen from a Frame with pose [R | t].  cam = {fx, fy, cx, cy, bf, baseline}, bounds = {minX, minY, maxX, maxY}.
+ * out[i] = the track fields the reference wrote into the MapPoint (active = its return value). */
+void ref_frustum(const float* R, const float* t, const float* cam, const float* bounds, float scale_factor, int n_levels,
+                 const RefMapPoint3d* mps, int n, float view_cos_limit, RefMapPointProj* out) {
+  using namespace YDORBSLAM;
+  Frame::m_flt_fx = cam[0]; Frame::m_flt_fy = cam[1]; Frame::m_flt_cx = cam[2]; Frame::m_flt_cy = cam[3];
+  Frame::m_flt_baseLineTimesFx = cam[4];
+  Frame::m_flt_baseLine = cam[5];
+  Frame::m_flt_minX = bounds[0]; Frame::m_flt_minY = bounds[1]; Frame::m_flt_maxX = bounds[2]; Frame::m_flt_maxY = bounds[3];
+  Frame f, src;
+  f.m_int_scaleLevelsNum = n_levels;
+  f.m_flt_scaleFactor = scale_factor;
+  f.m_flt_logScaleFactor = log(f.m_flt_scaleFactor);  // src/frame.cpp:78
+  cv::Mat T = cv::Mat::eye(4, 4, CV_32F);
+  for (int i = 0; i < 3; i++) {
+    for (int j = 0; j < 3; j++) T.at<float>(i, j) = R[3 * i + j];
+    T.at<float>(i, 3) = t[i];
+  }
+  f.setCameraPoseByTransform_c2w(T);
+  src.m_v_keyPoints.assign(1, cv::KeyPoint());
+  src.m_v_scaleFactors.assign(n_levels, 1.0f);
+  src.m_cvMat_descriptors = cv::Mat::zeros(1, 32, CV_8UC1);
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  for (int i = 0; i < n; i++) {
+    cv::Mat pos = (cv::Mat_<float>(3, 1) << mps[i].pos[0], mps[i].pos[1], mps[i].pos[2]);
+    std::shared_ptr<ProbePoint> mp = std::make_shared<ProbePoint>(pos, src, 0);
+    mp->distances(mps[i].min_distance, mps[i].max_distance);
+    mp->normal(mps[i].normal[0], mps[i].normal[1], mps[i].normal[2]);
+    const bool in = f.isInCameraFrustum(mp, view_cos_limit);
+    out[i].proj_x = mp->m_flt_trackProjX;
+    out[i].proj_y = mp->m_flt_trackProjY;
+    out[i].proj_right_x = mp->m_flt_trackProjRightX;
+    out[i].view_cos = mp->m_flt_trackViewCos;
+    out[i].level = mp->m_int_trackScaleLevel;
+    out[i].active = (in && mp->m_b_isTrackInView) ? 1 : 0;
+  }
+}
+
+/* N3  MapPoint::computeDistinctiveDescriptors (src/mapPoint.cpp:169-218).  Point p has the observations
+ * desc[start[p] .. start[p+1]); observation k of every point lives in key frame k of a pool whose members are ordered by
+ * address, so that the std::map<shared_ptr<KeyFrame>, int> the reference iterates (:181) visits them in the given
+ * order.  out receives the 32 bytes the reference left in the MapPoint (unchanged = all zero when it has no observations). */
+void ref_distinctive_descriptors(const uint8_t* desc, const int32_t* start, int n_points, uint8_t* out) {
+  using namespace YDORBSLAM;
+  int kmax = 0;
+  for (int p = 0; p < n_points; p++) kmax = std::max(kmax, start[p + 1] - start[p]);
+  Frame src;
+  src.m_v_keyPoints.assign(1, cv::KeyPoint());
+  src.m_v_scaleFactors.assign(8, 1.0f);
+  src.m_cvMat_descriptors = cv::Mat::zeros(1, 32, CV_8UC1);
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  std::vector<std::shared_ptr<KeyFrame>> pool(kmax);
+  {
+    Frame proto;
+    proto.m_v_rightXcords.assign(std::max(n_points, 1), -1.0f);
+    proto.m_cvMat_descriptors = cv::Mat::zeros(std::max(n_points, 1), 32, CV_8UC1);
+    for (int k = 0; k < kmax; k++) pool[k] = std::make_shared<KeyFrame>(proto, std::shared_ptr<Map>(), std::shared_ptr<KeyFrameDatabase>());
+  }
+  std::sort(pool.begin(), pool.end(), [](const std::shared_ptr<KeyFrame>& a, const std::shared_ptr<KeyFrame>& b) { return a.get() < b.get(); });
+  for (int p = 0; p < n_points; p++)
+    for (int k = 0; k < start[p + 1] - start[p]; k++) memcpy(pool[k]->m_cvMat_descriptors.ptr(p), desc + (size_t)32 * (start[p] + k), 32);
+  cv::Mat pos = (cv::Mat_<float>(3, 1) << 0.f, 0.f, 1.f);
+  for (int p = 0; p < n_points; p++) {
+    std::shared_ptr<ProbePoint> mp = std::make_shared<ProbePoint>(pos, src, 0);
+    for (int k = 0; k < start[p + 1] - start[p]; k++) mp->addObservation(pool[k], p);
+    mp->computeDistinctiveDescriptors();
+    const cv::Mat d = mp->getDescriptor();
+    memcpy(out + (size_t)32 * p, d.ptr(0), 32);
+  }
 }
 
 /* M0 */

@@ -231,3 +231,38 @@ def test_search_by_projection_in_sim_reference_equals_oracle():
     assert np.array_equal(match, np.where(omatch < 0, -1, omatch))
     assert n > 20 and (dbg[:, 3] > 0).sum() > 1000
     f.close()
+
+
+def test_frustum_reference_equals_oracle():
+    """N2: the reference's own Frame::isInCameraFrustum + MapPoint::predictScaleLevel == the oracle, every gate exercised on
+    both sides (behind the camera, outside the image, out of the invariance range, oblique normal)."""
+    from tests import map_cases
+
+    cam, mp = map_cases.camera_and_points(4000, 5)
+    R, t = np.array(cam.R[:], np.float32), np.array(cam.t[:], np.float32)
+    base = np.float32(cam.bf) / np.float32(cam.fx)
+    got = ref.frustum(R, t, (cam.fx, cam.fy, cam.cx, cam.cy, cam.bf, base), (cam.min_x, cam.min_y, cam.max_x, cam.max_y), 1.2,
+                      cam.n_levels, mp, 0.5)
+    want = orc.frustum(cam, mp, 0.5)
+    assert np.array_equal(got["active"], want["active"])
+    a = want["active"] != 0
+    assert 200 < a.sum() < len(mp) - 200
+    for f in ("proj_x", "proj_y", "proj_right_x", "view_cos"):
+        assert np.array_equal(got[f][a].view(np.uint32), want[f][a].view(np.uint32)), f
+    assert np.array_equal(got["level"][a], want["level"][a])
+
+
+def test_distinctive_descriptors_reference_equals_oracle():
+    """N3: the reference's own MapPoint::computeDistinctiveDescriptors (observations through addObservation on KeyFrames,
+    the float distance matrix, std::sort median at index 0.5 * n) picks the descriptor the oracle picks."""
+    from tests import map_cases
+
+    desc, start = map_cases.observation_sets(400, 11)
+    got = ref.distinctive_descriptors(desc, start)
+    best = orc.distinctive_descriptors(desc, start)
+    for p in range(len(best)):
+        if best[p] < 0:
+            assert not got[p].any(), p  # no observation: the MapPoint keeps what it had
+        else:
+            assert np.array_equal(got[p], desc[start[p] + best[p]]), p
+    assert (best >= 0).sum() > 300
