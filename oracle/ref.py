@@ -349,3 +349,54 @@ def distinctive_descriptors(desc, start):
     out = np.zeros((len(s) - 1, 32), np.uint8)
     lib().ref_distinctive_descriptors(_p(d), _p(s), len(s) - 1, _p(out))
     return out
+
+
+def search_by_sim3(side1, side2, cam, bounds, sf, thd, pre1=None):
+    """OrbMatcher::searchBySim3 (src/orbMatcher.cpp:566-681) of the compiled reference between two KeyFrames at the identity
+    pose.  side = dict(kps, desc, pos [n][3] (NaN x: no map point), mp_desc, min_d, max_d, bad).  pre1[i] >= 0: slot i is
+    matched on entry to a map point key frame 2 observes at key point pre1[i].  Returns (return value, match per side-1 key
+    point (-2 = pre-matched), dbg1, dbg2)."""
+    def arrs(sd):
+        return (np.ascontiguousarray(sd["kps"], dtype=KP_DTYPE), np.ascontiguousarray(sd["desc"], dtype=np.uint8),
+                np.ascontiguousarray(sd["pos"], dtype=np.float32), np.ascontiguousarray(sd["mp_desc"], dtype=np.uint8),
+                np.ascontiguousarray(sd["min_d"], dtype=np.float32), np.ascontiguousarray(sd["max_d"], dtype=np.float32),
+                np.ascontiguousarray(sd["bad"], dtype=np.uint8))
+    a, b = arrs(side1), arrs(side2)
+    n1, n2 = len(a[0]), len(b[0])
+    pre = np.full(max(n1, 1), -1, np.int32) if pre1 is None else np.ascontiguousarray(pre1, dtype=np.int32)
+    cm, bd, sfa = (np.ascontiguousarray(x, dtype=np.float32) for x in (cam, bounds, sf))
+    match = np.full(max(n1, 1), -1, np.int32)
+    dbg1, dbg2 = np.zeros((max(n1, 1), 4), np.float32), np.zeros((max(n2, 1), 4), np.float32)
+    n = lib().ref_search_by_sim3(_p(a[0]), _p(a[1]), n1, _p(a[2]), _p(a[3]), _p(a[4]), _p(a[5]), _p(a[6]), _p(pre),
+                                 _p(b[0]), _p(b[1]), n2, _p(b[2]), _p(b[3]), _p(b[4]), _p(b[5]), _p(b[6]), _p(cm), _p(bd), _p(sfa),
+                                 len(sfa), C.c_float(thd), _p(match), _p(dbg1), _p(dbg2))
+    return n, match[:n1], dbg1[:n1], dbg2[:n2]
+
+
+def fuse(mode, kps, desc, right_x, slot_kind, slot_obs, points, cam, bounds, sf, thd, sim_scale=1.0, sim_t=(0.0, 0.0, 0.0)):
+    """OrbMatcher::fuseByProjection (mode 0, src/orbMatcher.cpp:682-745) / fuseBySim3 (mode 1, :746-807) of the compiled
+    reference on a KeyFrame at the identity pose.  points = dict(pos [m][3] (NaN x: null entry), desc, min_d, max_d,
+    normal [m][3], bad, obs).  Entities are named slot point i -> i, candidate j -> n + j, none -> -1.  Returns a dict:
+    fused (return value), slot (occupant per key point), slot_repl, slot_obs, mp_repl, mp_obs, mp_bad, dbg [m][5]."""
+    k = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+    n, m = len(k), len(points["pos"])
+    d = np.ascontiguousarray(desc, dtype=np.uint8)
+    rx = np.ascontiguousarray(right_x, dtype=np.float32)
+    sk, so = np.ascontiguousarray(slot_kind, dtype=np.uint8), np.ascontiguousarray(slot_obs, dtype=np.int32)
+    pos, mpd = np.ascontiguousarray(points["pos"], dtype=np.float32), np.ascontiguousarray(points["desc"], dtype=np.uint8)
+    mind, maxd = np.ascontiguousarray(points["min_d"], dtype=np.float32), np.ascontiguousarray(points["max_d"], dtype=np.float32)
+    nrm, bad = np.ascontiguousarray(points["normal"], dtype=np.float32), np.ascontiguousarray(points["bad"], dtype=np.uint8)
+    obs = np.ascontiguousarray(points["obs"], dtype=np.int32)
+    cm, bd, sfa, st = (np.ascontiguousarray(x, dtype=np.float32) for x in (cam, bounds, sf, sim_t))
+    out = dict(slot=np.zeros(max(n, 1), np.int32), slot_repl=np.zeros(max(n, 1), np.int32), slot_obs=np.zeros(max(n, 1), np.int32),
+               mp_repl=np.zeros(max(m, 1), np.int32), mp_obs=np.zeros(max(m, 1), np.int32), mp_bad=np.zeros(max(m, 1), np.uint8),
+               dbg=np.zeros((max(m, 1), 5), np.float32))
+    out["fused"] = lib().ref_fuse(mode, _p(k), _p(d), _p(rx), n, _p(sk), _p(so), _p(pos), _p(mpd), _p(mind), _p(maxd), _p(nrm), _p(bad),
+                                  _p(obs), m, _p(cm), _p(bd), _p(sfa), len(sfa), C.c_float(thd), C.c_float(sim_scale), _p(st),
+                                  _p(out["slot"]), _p(out["slot_repl"]), _p(out["slot_obs"]), _p(out["mp_repl"]), _p(out["mp_obs"]),
+                                  _p(out["mp_bad"]), _p(out["dbg"]))
+    for key in ("slot", "slot_repl", "slot_obs"):
+        out[key] = out[key][:n]
+    for key in ("mp_repl", "mp_obs", "mp_bad", "dbg"):
+        out[key] = out[key][:m]
+    return out

@@ -74,6 +74,8 @@ struct GridFrame : YDORBSLAM::Frame {
 /* protected state of a MapPoint is reachable from a derived class; nothing is overridden */
 struct ProbePoint : YDORBSLAM::MapPoint {
   ProbePoint(const cv::Mat& pos, YDORBSLAM::Frame& f, int idx) : YDORBSLAM::MapPoint(pos, std::shared_ptr<YDORBSLAM::Map>(), f, idx) {}
+  ProbePoint(const cv::Mat& pos, std::shared_ptr<YDORBSLAM::Map> map, YDORBSLAM::Frame& f, int idx)
+      : YDORBSLAM::MapPoint(pos, map, f, idx) {}
   void observations(int n) { m_int_observationsNum = n; }
   void distances(float mn, float mx) { m_flt_minDistance = mn; m_flt_maxDistance = mx; }
   void bad(bool b) { m_b_bad = b; }
@@ -286,6 +288,242 @@ int ref_search_in_sim(void* p, int n_mp, const float* mp_pos, const uint8_t* mp_
   for (int i = 0; i < n; i++) {
     const MapPoint* q = matched[i].get();
     match_out[i] = (q && q != held.get()) ? index[q] : -1;
+  }
+  return ret;
+}
+
+/* M4b OrbMatcher::searchBySim3 (src/orbMatcher.cpp:566-681).  Two KeyFrames at the identity pose built by the reference's
+ * constructor from (key points, descriptors, one MapPoint per key point at mp_pos (NaN x: none) with its own descriptor,
+ * invariance distances, bad flag); the grids by its assignKeyPointsToGrid.  pre1[i] >= 0: _vSptrMatchedMapPoints[i] is
+ * non-null on entry and that map point is observed by key frame 2 at key point pre1[i] (:580-588).
+ * match_out[i] = key point of key frame 2 whose map point the call put into slot i, -1 = none, -2 = pre-matched.
+ * dbg1 / dbg2: per map point of side 1 / 2 {projX, projY, predicted level, gates passed} in the OTHER key frame. */
+int ref_search_by_sim3(const RefKeyPoint* kps1, const uint8_t* desc1, int n1, const float* pos1, const uint8_t* mpd1,
+                       const float* mind1, const float* maxd1, const uint8_t* bad1, const int32_t* pre1, const RefKeyPoint* kps2,
+                       const uint8_t* desc2, int n2, const float* pos2, const uint8_t* mpd2, const float* mind2,
+                       const float* maxd2, const uint8_t* bad2, const float* cam, const float* bounds, const float* sf,
+                       int n_levels, float thd, int32_t* match_out, float* dbg1, float* dbg2) {
+  using namespace YDORBSLAM;
+  Frame::m_flt_fx = cam[0]; Frame::m_flt_fy = cam[1]; Frame::m_flt_cx = cam[2]; Frame::m_flt_cy = cam[3];
+  Frame::m_flt_baseLineTimesFx = cam[4];
+  Frame::m_flt_baseLine = cam[5];
+  Frame::m_flt_minX = bounds[0]; Frame::m_flt_minY = bounds[1]; Frame::m_flt_maxX = bounds[2]; Frame::m_flt_maxY = bounds[3];
+  Frame::m_flt_gridCellWidthInv = static_cast<float>(Frame::m_int_gridColsNum) / (bounds[2] - bounds[0]);
+  Frame::m_flt_gridCellHeightInv = static_cast<float>(Frame::m_int_gridRowsNum) / (bounds[3] - bounds[1]);
+  const int nmax = std::max(n1, n2);
+  Frame src;
+  src.m_v_keyPoints.assign(nmax + 1, cv::KeyPoint());
+  src.m_v_scaleFactors.assign(sf, sf + n_levels);
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  auto make = [&](const RefKeyPoint* kps, const uint8_t* desc, int n, const float* pos, const uint8_t* mpd, const float* mind,
+                  const float* maxd, const uint8_t* bad, std::map<const MapPoint*, int>& index) {
+    GridFrame f;
+    f.m_v_keyPoints.resize(n);
+    for (int i = 0; i < n; i++) {
+      cv::KeyPoint k;
+      k.pt.x = kps[i].x; k.pt.y = kps[i].y; k.size = kps[i].size; k.angle = kps[i].angle;
+      k.response = kps[i].response; k.octave = kps[i].octave; k.class_id = kps[i].class_id;
+      f.m_v_keyPoints[i] = k;
+    }
+    f.m_int_keyPointsNum = n;
+    f.m_cvMat_descriptors.create(std::max(n, 1), 32, CV_8UC1);
+    for (int i = 0; i < n; i++) memcpy(f.m_cvMat_descriptors.ptr(i), desc + (size_t)32 * i, 32);
+    f.m_v_rightXcords.assign(n, -1.0f);
+    f.m_v_scaleFactors.assign(sf, sf + n_levels);
+    f.m_int_scaleLevelsNum = n_levels;
+    f.m_flt_scaleFactor = n_levels > 1 ? sf[1] : 1.2f;
+    f.m_flt_logScaleFactor = log(f.m_flt_scaleFactor);
+    f.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+    f.assign();
+    src.m_cvMat_descriptors.create(nmax + 1, 32, CV_8UC1);
+    for (int i = 0; i < n; i++) memcpy(src.m_cvMat_descriptors.ptr(i), mpd + (size_t)32 * i, 32);
+    f.m_v_sptrMapPoints.assign(n, std::shared_ptr<MapPoint>());
+    for (int i = 0; i < n; i++) {
+      if (pos[3 * i] != pos[3 * i]) continue;
+      cv::Mat p3 = (cv::Mat_<float>(3, 1) << pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]);
+      std::shared_ptr<ProbePoint> mp = std::make_shared<ProbePoint>(p3, src, i);
+      mp->distances(mind[i], maxd[i]);
+      mp->bad(bad && bad[i]);
+      f.m_v_sptrMapPoints[i] = mp;
+      index[mp.get()] = i;
+    }
+    return std::make_shared<KeyFrame>(f, std::shared_ptr<Map>(), std::shared_ptr<KeyFrameDatabase>());
+  };
+  std::map<const MapPoint*, int> index1, index2;
+  std::shared_ptr<KeyFrame> kf1 = make(kps1, desc1, n1, pos1, mpd1, mind1, maxd1, bad1, index1);
+  std::shared_ptr<KeyFrame> kf2 = make(kps2, desc2, n2, pos2, mpd2, mind2, maxd2, bad2, index2);
+  // pre-matched slots: a map point observed by key frame 2 at pre1[i]
+  std::vector<std::shared_ptr<MapPoint>> matched(n1);
+  std::vector<std::shared_ptr<MapPoint>> held;
+  cv::Mat pos0 = (cv::Mat_<float>(3, 1) << 0.f, 0.f, 1.f);
+  src.m_cvMat_descriptors.create(nmax + 1, 32, CV_8UC1);
+  for (int i = 0; i < n1; i++)
+    if (pre1 && pre1[i] >= 0) {
+      std::shared_ptr<ProbePoint> h = std::make_shared<ProbePoint>(pos0, src, nmax);
+      h->addObservation(kf2, pre1[i]);
+      matched[i] = h;
+      held.push_back(h);
+    }
+  auto debug = [&](const std::shared_ptr<KeyFrame>& from, const std::shared_ptr<KeyFrame>& into, int n, float* dbg) {
+    if (!dbg) return;
+    cv::Mat R = into->getRotation_c2w(), t = into->getTranslation_c2w();
+    const std::vector<std::shared_ptr<MapPoint>> pts = from->getMatchedMapPointsVec();
+    for (int i = 0; i < n; i++) {
+      float* d = dbg + 4 * i;
+      d[0] = d[1] = d[2] = d[3] = 0.f;
+      std::shared_ptr<MapPoint> mp = pts[i];
+      if (!mp || mp->isBad()) continue;
+      cv::Mat pw = mp->getPosInWorld();
+      cv::Mat pc = R * pw + t;
+      const float x = pc.at<float>(0), y = pc.at<float>(1), z = pc.at<float>(2);
+      const float u = Frame::m_flt_fx * x / z + Frame::m_flt_cx;
+      const float v = Frame::m_flt_fy * y / z + Frame::m_flt_cy;
+      const float dist3D = cv::norm(pc);
+      const float maxD = mp->getMaxDistanceInvariance(), minD = mp->getMinDistanceInvariance();
+      d[0] = u;
+      d[1] = v;
+      d[2] = (float)mp->predictScaleLevel(dist3D, into);
+      d[3] = (z >= 0.0 && into->isInImage(u, v) && dist3D >= minD && dist3D <= maxD) ? 1.f : 0.f;
+    }
+  };
+  debug(kf1, kf2, n1, dbg1);
+  debug(kf2, kf1, n2, dbg2);
+  OrbMatcher matcher(0.6f, true);
+  cv::Mat R12 = cv::Mat::eye(3, 3, CV_32F), t12 = cv::Mat::zeros(3, 1, CV_32F);
+  const int ret = matcher.searchBySim3(kf1, kf2, matched, 1.0f, R12, t12, thd);
+  for (int i = 0; i < n1; i++) {
+    const MapPoint* q = matched[i].get();
+    if (!q) match_out[i] = -1;
+    else if (index2.count(q)) match_out[i] = index2[q];
+    else match_out[i] = -2;
+  }
+  return ret;
+}
+
+/* M4  OrbMatcher::fuseByProjection (src/orbMatcher.cpp:682-745; mode 0) and OrbMatcher::fuseBySim3 (:746-807; mode 1,
+ * similarity = scale * I | sim_t) on a KeyFrame at the identity pose built by the reference's constructor.
+ * Key point i holds: nothing (slot_kind 0), a good map point (1) or a bad one (2), observing the key frame, with
+ * slot_obs[i] observations counted before that one.  The nmp candidate map points carry mp_obs[j] observations.
+ * After the call, entities are named by id: slot point i -> i, candidate j -> n + j, nothing -> -1.
+ *   slot_out[i]   occupant of key point i           slot_repl[i] / mp_repl[j]   replacement of that entity
+ *   slot_obs_out / mp_obs_out   observation counts  mp_bad_out[j]               isBad() of candidate j
+ *   dbg[j] = {projX, projY, projRightX, predicted level, gates (:703-707 / :771-775 without the empty-window test)}  */
+int ref_fuse(int mode, const RefKeyPoint* kps, const uint8_t* desc, const float* right_x, int n, const uint8_t* slot_kind,
+             const int32_t* slot_obs, const float* pos, const uint8_t* mpd, const float* mind, const float* maxd,
+             const float* normal, const uint8_t* bad, const int32_t* mp_obs, int nmp, const float* cam, const float* bounds,
+             const float* sf, int n_levels, float thd, float sim_scale, const float* sim_t, int32_t* slot_out,
+             int32_t* slot_repl, int32_t* slot_obs_out, int32_t* mp_repl, int32_t* mp_obs_out, uint8_t* mp_bad_out, float* dbg) {
+  using namespace YDORBSLAM;
+  Frame::m_flt_fx = cam[0]; Frame::m_flt_fy = cam[1]; Frame::m_flt_cx = cam[2]; Frame::m_flt_cy = cam[3];
+  Frame::m_flt_baseLineTimesFx = cam[4];
+  Frame::m_flt_baseLine = cam[5];
+  Frame::m_flt_minX = bounds[0]; Frame::m_flt_minY = bounds[1]; Frame::m_flt_maxX = bounds[2]; Frame::m_flt_maxY = bounds[3];
+  Frame::m_flt_gridCellWidthInv = static_cast<float>(Frame::m_int_gridColsNum) / (bounds[2] - bounds[0]);
+  Frame::m_flt_gridCellHeightInv = static_cast<float>(Frame::m_int_gridRowsNum) / (bounds[3] - bounds[1]);
+  std::shared_ptr<Map> map = std::make_shared<Map>();
+  const int nmax = std::max(n, nmp);
+  Frame src;
+  src.m_v_keyPoints.assign(nmax + 1, cv::KeyPoint());
+  src.m_v_scaleFactors.assign(sf, sf + n_levels);
+  src.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  src.m_cvMat_descriptors.create(nmax + 1, 32, CV_8UC1);
+  GridFrame f;
+  f.m_v_keyPoints.resize(n);
+  for (int i = 0; i < n; i++) {
+    cv::KeyPoint k;
+    k.pt.x = kps[i].x; k.pt.y = kps[i].y; k.size = kps[i].size; k.angle = kps[i].angle;
+    k.response = kps[i].response; k.octave = kps[i].octave; k.class_id = kps[i].class_id;
+    f.m_v_keyPoints[i] = k;
+  }
+  f.m_int_keyPointsNum = n;
+  fill_features(&f, desc, right_x, sf, n_levels);
+  f.m_v_invScaleFactorSquares.resize(n_levels);
+  for (int l = 0; l < n_levels; l++) f.m_v_invScaleFactorSquares[l] = 1.0f / (sf[l] * sf[l]);
+  f.setCameraPoseByTransform_c2w(cv::Mat::eye(4, 4, CV_32F));
+  f.assign();
+  std::map<const MapPoint*, int> id;
+  std::vector<std::shared_ptr<ProbePoint>> slot(n), cand(nmp);
+  cv::Mat pos0 = (cv::Mat_<float>(3, 1) << 0.f, 0.f, 1.f);
+  for (int i = 0; i < n; i++) memcpy(src.m_cvMat_descriptors.ptr(i), desc + (size_t)32 * i, 32);
+  for (int i = 0; i < n; i++)
+    if (slot_kind[i]) {
+      slot[i] = std::make_shared<ProbePoint>(pos0, map, src, i);
+      slot[i]->observations(slot_obs[i]);
+      f.m_v_sptrMapPoints[i] = slot[i];
+      id[slot[i].get()] = i;
+    }
+  std::shared_ptr<KeyFrame> kf = std::make_shared<KeyFrame>(f, map, std::shared_ptr<KeyFrameDatabase>());
+  for (int i = 0; i < n; i++)
+    if (slot[i]) {
+      slot[i]->addObservation(kf, i);
+      slot[i]->bad(slot_kind[i] == 2);
+    }
+  for (int j = 0; j < nmp; j++) memcpy(src.m_cvMat_descriptors.ptr(j), mpd + (size_t)32 * j, 32);
+  std::vector<std::shared_ptr<MapPoint>> points(nmp);
+  for (int j = 0; j < nmp; j++) {
+    if (pos[3 * j] != pos[3 * j]) continue;  // null entry of the list
+    cv::Mat p3 = (cv::Mat_<float>(3, 1) << pos[3 * j], pos[3 * j + 1], pos[3 * j + 2]);
+    cand[j] = std::make_shared<ProbePoint>(p3, map, src, j);
+    cand[j]->distances(mind[j], maxd[j]);
+    cand[j]->normal(normal[3 * j], normal[3 * j + 1], normal[3 * j + 2]);
+    cand[j]->observations(mp_obs[j]);
+    cand[j]->bad(bad[j]);
+    points[j] = cand[j];
+    id[cand[j].get()] = n + j;
+  }
+  cv::Mat sim = cv::Mat::eye(4, 4, CV_32F);
+  for (int r = 0; r < 3; r++) {
+    sim.at<float>(r, r) = sim_scale;
+    sim.at<float>(r, 3) = sim_t[r];
+  }
+  // the projections the calls are about to make, by the same cv::Mat operations
+  cv::Mat R, t, origin;
+  if (mode == 0) {
+    R = kf->getRotation_c2w(); t = kf->getTranslation_c2w(); origin = kf->getCameraOriginInWorld();
+  } else {
+    cv::Mat sR = sim.rowRange(0, 3).colRange(0, 3);
+    const float sc = sqrt(sR.row(0).dot(sR.row(0)));
+    R = sR / sc;
+    t = sim.rowRange(0, 3).col(3);
+    origin = -R.t() * t;
+  }
+  for (int j = 0; j < nmp; j++) {
+    float* d = dbg + 5 * j;
+    d[0] = d[1] = d[2] = d[3] = d[4] = 0.f;
+    if (!cand[j] || cand[j]->isBad()) continue;
+    cv::Mat pw = cand[j]->getPosInWorld();
+    cv::Mat pc = R * pw + t;
+    const float x = pc.at<float>(0), y = pc.at<float>(1), z = pc.at<float>(2);
+    const float u = Frame::m_flt_fx * x / z + Frame::m_flt_cx;
+    const float v = Frame::m_flt_fy * y / z + Frame::m_flt_cy;
+    cv::Mat ray = pw - origin;
+    const float dist3D = cv::norm(ray);
+    d[0] = u;
+    d[1] = v;
+    d[2] = u - Frame::m_flt_baseLineTimesFx / z;
+    d[3] = (float)cand[j]->predictScaleLevel(dist3D, kf);
+    d[4] = (z >= 0.0 && kf->isInImage(u, v) && dist3D >= cand[j]->getMinDistanceInvariance() &&
+            dist3D <= cand[j]->getMaxDistanceInvariance() && ray.dot(cand[j]->getNormal()) >= 0.5 * dist3D)
+               ? 1.f : 0.f;
+  }
+  OrbMatcher matcher(0.6f, true);
+  int ret;
+  if (mode == 0) {
+    ret = matcher.fuseByProjection(kf, points, thd);
+  } else {
+    std::vector<std::shared_ptr<MapPoint>> replacement(nmp);
+    ret = matcher.fuseBySim3(kf, sim, points, thd, replacement);
+  }
+  auto name = [&](const std::shared_ptr<MapPoint>& q) { return q ? id[q.get()] : -1; };
+  for (int i = 0; i < n; i++) {
+    slot_out[i] = name(kf->getMapPoint(i));
+    slot_repl[i] = slot[i] ? name(slot[i]->getReplacement()) : -1;
+    slot_obs_out[i] = slot[i] ? slot[i]->getObservationsNum() : 0;
+  }
+  for (int j = 0; j < nmp; j++) {
+    mp_repl[j] = cand[j] ? name(cand[j]->getReplacement()) : -1;
+    mp_obs_out[j] = cand[j] ? cand[j]->getObservationsNum() : 0;
+    mp_bad_out[j] = cand[j] ? (cand[j]->isBad() ? 1 : 0) : 0;
   }
   return ret;
 }

@@ -212,6 +212,59 @@ def test_cuda_keyframe_and_current_frame_matches_compiled_reference():
 
 
 @pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+def test_cuda_search_by_sim3_matches_compiled_reference():
+    """M4: CUDA searchBySim3 (two window searches + agreement) == the reference's own (src/orbMatcher.cpp:566-681 compiled
+    unmodified), pre-matched slots included."""
+    from tests import matcher_cases as mc
+    from tests.test_oracle_ref_frame import _sim3_sides
+    from ydorbslam_b200 import OrbMatcher
+
+    side1, side2 = _sim3_sides(41)
+    n1, n2 = len(side1["kps"]), len(side2["kps"])
+    rng = np.random.RandomState(3)
+    pre = np.where(rng.rand(n1) < 0.05, rng.randint(0, n2, n1), -1).astype(np.int32)
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    rn, rmatch, dbg1, dbg2 = ref.search_by_sim3(side1, side2, cam, (0, 0, mc.W, mc.H), mc.SF, 7.5, pre)
+    blocked2 = np.zeros(n2, bool)
+    blocked2[pre[pre >= 0]] = True
+    m = OrbMatcher(0.9)
+    none1, none2 = np.full(n1, -1, np.float32), np.full(n2, -1, np.float32)
+    f1 = m.make_frame(side1["kps"], side1["desc"], none1, bounds=(0, 0, mc.W, mc.H), scale_factors=mc.SF)
+    f2 = m.make_frame(side2["kps"], side2["desc"], none2, bounds=(0, 0, mc.W, mc.H), scale_factors=mc.SF)
+    n, out = m.searchBySim3(f1, f2, (dbg1[:, 0], dbg1[:, 1], dbg1[:, 2].astype(np.int32), (dbg1[:, 3] > 0) & (pre < 0), side1["mp_desc"]),
+                            (dbg2[:, 0], dbg2[:, 1], dbg2[:, 2].astype(np.int32), (dbg2[:, 3] > 0) & ~blocked2, side2["mp_desc"]), mc.SF, 7.5)
+    assert n == rn and np.array_equal(out, np.where(rmatch == -2, -1, rmatch))
+    assert n > 20
+    f1.close(); f2.close(); m.close()
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
+@pytest.mark.parametrize("mode,thd,sim_t", [(0, 1.2, (0, 0, 0)), (1, 4.0, (0.3, -0.2, 0.5))])
+def test_cuda_fuse_matches_compiled_reference(mode, thd, sim_t):
+    """M4: CUDA candidate search of fuseByProjection / fuseBySim3 + the caller-side replay == every observable of the
+    reference's own call (src/orbMatcher.cpp:682-807 compiled unmodified)."""
+    from tests import matcher_cases as mc
+    from tests.test_oracle_ref_frame import check_fuse, fuse_scene, replay_fuse
+    from ydorbslam_b200 import OrbMatcher
+
+    s = fuse_scene(mode, 61 + mode, thd, sim_t)
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    r = ref.fuse(mode, s["kps"], s["desc"], s["right_x"], s["slot_kind"], s["slot_obs"], s["points"], cam, (0, 0, mc.W, mc.H), mc.SF, thd,
+                 2.0 if mode else 1.0, sim_t)
+    dbg = r["dbg"]
+    active, level = dbg[:, 4] > 0, dbg[:, 3].astype(np.int32)
+    m = OrbMatcher(0.6)
+    fr = m.make_frame(s["kps"], s["desc"], s["right_x"], bounds=(0, 0, mc.W, mc.H), scale_factors=mc.SF)
+    if mode == 0:
+        _, best = m.fuseByProjectionCandidates(fr, dbg[:, 0], dbg[:, 1], dbg[:, 2], level, active, s["points"]["desc"], mc.SF, mc.INV_SF2, thd)
+    else:
+        _, best = m.fuseBySim3Candidates(fr, dbg[:, 0], dbg[:, 1], level, active, s["points"]["desc"], mc.SF, thd)
+    check_fuse(r, replay_fuse(mode, best, s), s)
+    assert r["fused"] > 30
+    fr.close(); m.close()
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref not shipped")
 @pytest.mark.parametrize("stereo_only", [False, True])
 def test_cuda_search_for_triangulation_matches_compiled_reference(stereo_only):
     """M6: CUDA searchForTriangulation == the reference's own (src/orbMatcher.cpp:463-565, :808-819 compiled unmodified)."""

@@ -266,3 +266,172 @@ def test_distinctive_descriptors_reference_equals_oracle():
         else:
             assert np.array_equal(got[p], desc[start[p] + best[p]]), p
     assert (best >= 0).sum() > 300
+
+
+def _sim3_sides(seed):
+    """Two key frames at the identity pose seeing the same scene: about 60% of frame 2's key points are frame 1's moved
+    to just outside the window radius with a few descriptor bits flipped, the rest are unrelated.  Every key point owns a map point on its
+    own viewing ray, so both directions find candidates and most related pairs agree (:669-679); some do not (heavy
+    descriptor noise, bad points, invariance distance out of range, crowded windows)."""
+    rng = np.random.RandomState(seed)
+    k1, d1 = mc.synth_keypoints(700, seed)
+    ke, de = mc.synth_keypoints(800, seed + 1)
+    k2, d2 = ke.copy(), de.copy()
+    twin = rng.permutation(800)[:420]  # frame-2 slots that copy a frame-1 key point
+    src = rng.permutation(700)[:420]
+    k2[twin] = k1[src]
+    rad = 7.5 * mc.SF[k1["octave"][src].astype(np.int64)]  # SURVEY F9: a candidate lies OUTSIDE the radius in x, inside in y
+    k2["x"][twin] += (np.where(rng.rand(420) < 0.5, 1.0, -1.0) * (rad + 0.05 + rng.uniform(0, 6, 420))).astype(np.float32)
+    k2["y"][twin] += (rng.uniform(-0.9, 0.9, 420) * rad).astype(np.float32)
+    k2["x"][twin] = np.clip(k2["x"][twin], 1, mc.W - 2)
+    k2["y"][twin] = np.clip(k2["y"][twin], 1, mc.H - 2)
+    d2[twin] = d1[src]
+    flips = rng.randint(0, 256, (420, 40))
+    nflip = np.where(rng.rand(420) < 0.15, 40, rng.randint(0, 14, 420))
+    for r in range(420):
+        for b in flips[r, : nflip[r]]:
+            d2[twin[r], b >> 3] ^= np.uint8(1 << (b & 7))
+
+    def side(k, d, sd):
+        r = np.random.RandomState(sd)
+        n = len(k)
+        z = r.uniform(2.0, 9.0, n)
+        pos = np.stack([(k["x"] - mc.CAM["cx"]) / mc.CAM["fx"] * z, (k["y"] - mc.CAM["cy"]) / mc.CAM["fy"] * z, z], 1).astype(np.float32)
+        dist = np.sqrt((pos.astype(np.float64) ** 2).sum(1))
+        max_d = (dist * mc.SF[k["octave"].astype(np.int64)] * r.uniform(0.93, 1.0, n)).astype(np.float32)  # predicted level == octave, mostly
+        min_d = (max_d / mc.SF[-1]).astype(np.float32)
+        max_d[r.rand(n) < 0.04] *= np.float32(0.3)
+        pos[r.rand(n) < 0.05, 0] = np.nan  # no map point in this slot
+        return dict(kps=k, desc=d, pos=pos, mp_desc=d.copy(), min_d=min_d, max_d=max_d, bad=(r.rand(n) < 0.04).astype(np.uint8))
+
+    return side(k1, d1, seed + 2), side(k2, d2, seed + 3)
+
+
+def test_search_by_sim3_reference_equals_oracle():
+    """M4 (second member): the reference's own searchBySim3 -- both directions, the pre-matched exclusions (:580-588) and
+    the agreement check (:669-679) -- == two oracle window searches + sim3_agreement."""
+    from ydorbslam_b200 import queries as Q
+
+    side1, side2 = _sim3_sides(41)
+    n1, n2 = len(side1["kps"]), len(side2["kps"])
+    rng = np.random.RandomState(3)
+    pre = np.where(rng.rand(n1) < 0.05, rng.randint(0, n2, n1), -1).astype(np.int32)
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    n, match, dbg1, dbg2 = ref.search_by_sim3(side1, side2, cam, (0, 0, mc.W, mc.H), mc.SF, 7.5, pre)
+    g = orc.make_geom(orc.make_params(1000, 1.2, 8, 20), mc.W, mc.H)
+    act1 = (dbg1[:, 3] > 0) & (pre < 0)
+    blocked2 = np.zeros(n2, bool)
+    blocked2[pre[pre >= 0]] = True
+    act2 = (dbg2[:, 3] > 0) & ~blocked2
+    q1, p1 = Q.sim3_direction(dbg1[:, 0], dbg1[:, 1], dbg1[:, 2].astype(np.int32), act1, mc.SF, 7.5)
+    q2, p2 = Q.sim3_direction(dbg2[:, 0], dbg2[:, 1], dbg2[:, 2].astype(np.int32), act2, mc.SF, 7.5)
+    none1, none2 = np.full(n1, -1, np.float32), np.full(n2, -1, np.float32)
+    _, best12, _ = orc.search_windows(g, side2["kps"], side2["desc"], none2, None, q1, side1["mp_desc"], p1)
+    _, best21, _ = orc.search_windows(g, side1["kps"], side1["desc"], none1, None, q2, side2["mp_desc"], p2)
+    found, out = Q.sim3_agreement(best12, best21)
+    assert n == found
+    assert np.array_equal(np.where(match == -2, -1, match), out)
+    assert (match == -2).sum() == (pre >= 0).sum()
+    assert found > 150 and (best12 >= 0).sum() > found + 20
+
+
+def fuse_scene(mode, seed, thd, sim_t=(0.0, 0.0, 0.0)):
+    """A key frame (some key points already holding good or bad map points) and candidate map points whose projections
+    land where window_scene wants them; about three candidates per key point, so replace chains occur (:728-735)."""
+    kps, desc = mc.synth_keypoints(900, seed)
+    nmp = 3000
+    ws = mc.window_scene(kps, desc, nmp, seed + 1, thd, dx_extra=1.0 if mode == 0 else 8.0)
+    rng = np.random.RandomState(seed + 2)
+    z = (float(mc.CAM["bf"]) / 10.0 * rng.uniform(0.98, 1.02, nmp)).astype(np.float32)  # projRightX ~ projX - 10, as the scene's rightX
+    z[rng.rand(nmp) < 0.03] *= -1
+    pc = np.stack([(ws["proj_x"].astype(np.float64) - float(mc.CAM["cx"])) / float(mc.CAM["fx"]) * z,
+                   (ws["proj_y"].astype(np.float64) - float(mc.CAM["cy"])) / float(mc.CAM["fy"]) * z, z], 1)
+    pos = (pc - np.asarray(sim_t, np.float64)).astype(np.float32)  # camera = world + t
+    dist = np.sqrt((pc ** 2).sum(1))
+    max_d = (dist * mc.SF[ws["level"]] * rng.uniform(0.93, 1.0, nmp)).astype(np.float32)
+    min_d = (max_d / mc.SF[-1]).astype(np.float32)
+    max_d[rng.rand(nmp) < 0.04] *= np.float32(0.3)
+    normal = (pc / dist[:, None]).astype(np.float32)
+    normal[rng.rand(nmp) < 0.05] *= -1  # seen from behind: :706 / :774 drop it
+    pos[rng.rand(nmp) < 0.03, 0] = np.nan
+    points = dict(pos=pos, desc=ws["desc"], min_d=min_d, max_d=max_d, normal=normal, bad=(rng.rand(nmp) < 0.04).astype(np.uint8),
+                  obs=rng.randint(0, 6, nmp).astype(np.int32))
+    u = rng.rand(900)
+    slot_kind = np.where(u < 0.4, 0, np.where(u < 0.92, 1, 2)).astype(np.uint8)
+    return dict(kps=kps, desc=desc, right_x=ws["right_x_kp"], slot_kind=slot_kind, slot_obs=rng.randint(0, 6, 900).astype(np.int32),
+                points=points)
+
+
+def replay_fuse(mode, best, s):
+    """What the caller of the candidate search does with best[j] (src/orbMatcher.cpp:728-739 / :791-800 and
+    MapPoint::beReplacedBy, src/mapPoint.cpp:128-156): entity ids as ref.fuse names them."""
+    n, m = len(s["kps"]), len(best)
+    step = np.where(s["right_x"] >= 0, 2, 1)  # MapPoint::addObservation, src/mapPoint.cpp:96-100
+    occupant = np.where(s["slot_kind"] > 0, np.arange(n), -1)
+    obs = np.concatenate([s["slot_obs"] + np.where(s["slot_kind"] > 0, step, 0), s["points"]["obs"]]).astype(np.int64)
+    bad = np.concatenate([s["slot_kind"] == 2, s["points"]["bad"] > 0])
+    where = np.concatenate([np.where(s["slot_kind"] > 0, np.arange(n), -1), np.full(m, -1)])  # key point the entity is observed at
+    repl = np.full(n + m, -1)
+    fused = 0
+    for j in range(m):
+        idx, me = int(best[j]), n + j
+        if idx < 0:
+            continue
+        fused += 1
+        o = int(occupant[idx])
+        if o < 0:
+            where[me], occupant[idx] = idx, me
+            obs[me] += step[idx]
+            continue
+        if bad[o]:
+            continue
+        loser, winner = (me, o) if (mode == 1 or obs[o] > obs[me]) else (o, me)
+        bad[loser], repl[loser] = True, winner
+        if where[loser] >= 0:
+            at = int(where[loser])
+            if where[winner] < 0:
+                occupant[at], where[winner] = winner, at
+                obs[winner] += step[at]
+            else:
+                occupant[at] = -1
+            where[loser] = -1
+    return dict(fused=fused, slot=occupant, slot_repl=repl[:n], mp_repl=repl[n:], slot_obs=np.where(s["slot_kind"] > 0, obs[:n], 0),
+                mp_obs=obs[n:], mp_bad=bad[n:])
+
+
+def fuse_queries(mode, r, s, thd):
+    from ydorbslam_b200 import queries as Q
+
+    dbg = r["dbg"]
+    active, level = dbg[:, 4] > 0, dbg[:, 3].astype(np.int32)
+    if mode == 0:
+        return Q.fuse_by_projection(dbg[:, 0], dbg[:, 1], dbg[:, 2], level, active, mc.SF, mc.INV_SF2, thd)
+    return Q.fuse_by_sim3(dbg[:, 0], dbg[:, 1], level, active, mc.SF, thd)
+
+
+def check_fuse(r, mine, s):
+    assert r["fused"] == mine["fused"]
+    for key in ("slot", "slot_repl", "mp_repl", "slot_obs"):
+        assert np.array_equal(r[key], mine[key]), key
+    live = ~np.isnan(s["points"]["pos"][:, 0])  # null entries of the list have no state
+    assert np.array_equal(r["mp_obs"][live], mine["mp_obs"][live])
+    assert np.array_equal(r["mp_bad"][live] > 0, mine["mp_bad"][live])
+
+
+@pytest.mark.parametrize("mode,thd,sim_t", [(0, 1.2, (0, 0, 0)), (1, 4.0, (0, 0, 0)), (1, 4.0, (0.3, -0.2, 0.5))])
+def test_fuse_reference_equals_oracle(mode, thd, sim_t):
+    """M4 (third and fourth members): the reference's own fuseByProjection / fuseBySim3 -- projection, gates, window,
+    chi-square test, best candidate, and the map mutation that follows -- == the oracle's candidate search + the
+    caller-side replay, on every observable: occupant per key point, replacements, observation counts, bad flags."""
+    s = fuse_scene(mode, 61 + mode, thd, sim_t)
+    cam = [mc.CAM[k] for k in ("fx", "fy", "cx", "cy", "bf", "baseline")]
+    r = ref.fuse(mode, s["kps"], s["desc"], s["right_x"], s["slot_kind"], s["slot_obs"], s["points"], cam, (0, 0, mc.W, mc.H), mc.SF, thd,
+                 2.0 if mode else 1.0, sim_t)
+    q, prm = fuse_queries(mode, r, s, thd)
+    g = orc.make_geom(orc.make_params(1000, 1.2, 8, 20), mc.W, mc.H)
+    _, best, _ = orc.search_windows(g, s["kps"], s["desc"], s["right_x"], None, q, s["points"]["desc"], prm)
+    mine = replay_fuse(mode, best, s)
+    check_fuse(r, mine, s)
+    assert r["fused"] > (100 if mode else 30)
+    assert (r["mp_repl"] >= 0).sum() > 10
+    assert ((r["slot_repl"] >= 0).sum() > 5) == (mode == 0)  # only fuseByProjection ever replaces the key frame's own point
