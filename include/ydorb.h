@@ -402,9 +402,15 @@ typedef struct {
 #define YDORB_VOC_MAX_FEATURES 16384 /* descriptors per frame one transform accepts */
 
 int ydorb_vocabulary_create(YdMatcher* m, const YdVocabularyDesc* desc, YdVocabulary** out);
-/* Reads the uncompressed binary stream Vocabulary::toStream writes (Vocabulary.cpp:1180-1226; parsed as
- * Vocabulary::fromStream does, :1335-1409).  QuickLZ-compressed files are refused with YDORB_E_INVALID. */
+/* Reads the binary stream Vocabulary::toStream writes (Vocabulary.cpp:1180-1256; parsed as Vocabulary::fromStream
+ * does, :1335-1409) -- what Vocabulary::load(filename) tries first (:1080-1108) and what the reference's orbvoc.dbow3
+ * is.  Both forms: plain, and the default one cut into QuickLZ (level 1) chunks.  The .yml / .txt forms are refused
+ * with YDORB_E_INVALID. */
 int ydorb_vocabulary_load(YdMatcher* m, const char* path, YdVocabulary** out);
+/* Host only (no device needed): the plain form of a binary vocabulary stream given as a file image -- a compressed
+ * stream comes back inflated (header flag cleared, chunk framing removed), a plain one unchanged.  *out_len receives
+ * the size; with out == NULL nothing is copied (size query), else capacity must hold it. */
+int ydorb_vocabulary_stream_inflate(const uint8_t* stream, size_t n, uint8_t* out, size_t capacity, size_t* out_len);
 void ydorb_vocabulary_destroy(YdVocabulary* v);
 /* n_nodes, k, L, weighting, scoring, number of words (leaves) */
 int ydorb_vocabulary_info(const YdVocabulary* v, int32_t* info6);

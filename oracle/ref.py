@@ -400,3 +400,50 @@ def fuse(mode, kps, desc, right_x, slot_kind, slot_obs, points, cam, bounds, sf,
     for key in ("mp_repl", "mp_obs", "mp_bad", "dbg"):
         out[key] = out[key][:m]
     return out
+
+
+class RefVocabulary:
+    """The reference's own DBoW3::Vocabulary (thirdParty/DBow3/src/Vocabulary.cpp compiled unmodified)."""
+
+    def __init__(self, handle):
+        assert handle, "the reference could not build / load the vocabulary"
+        self._h = C.c_void_p(handle)
+
+    @classmethod
+    def create(cls, k, L, weighting, scoring, desc, image_start, seed=1):
+        """Vocabulary(k, L, weighting, scoring).create(training features): the reference's own k-means++ / k-medians."""
+        lib().ref_voc_create.restype = C.c_void_p
+        d = np.ascontiguousarray(desc, dtype=np.uint8)
+        st = np.ascontiguousarray(image_start, dtype=np.int32)
+        return cls(lib().ref_voc_create(k, L, weighting, scoring, _p(d), _p(st), len(st) - 1, C.c_uint(seed)))
+
+    @classmethod
+    def load(cls, path):
+        lib().ref_voc_load.restype = C.c_void_p
+        return cls(lib().ref_voc_load(str(path).encode()))
+
+    def save(self, path, compressed):
+        assert lib().ref_voc_save(self._h, str(path).encode(), int(compressed)) == 0
+
+    def info(self):
+        out = np.zeros(5, np.int32)
+        lib().ref_voc_info(self._h, _p(out))
+        return dict(k=int(out[0]), L=int(out[1]), weighting=int(out[2]), scoring=int(out[3]), n_words=int(out[4]))
+
+    def transform(self, desc, levels_up=4):
+        d = np.ascontiguousarray(desc, dtype=np.uint8).reshape(-1, 32)
+        n = len(d)
+        m = max(n, 1)
+        word, node, wgt = np.zeros(m, np.int32), np.zeros(m, np.int32), np.zeros(m, np.float64)
+        bi, bv = np.zeros(m, np.int32), np.zeros(m, np.float64)
+        fi, fs, ft = np.zeros(m, np.int32), np.zeros(m + 1, np.int32), np.zeros(m, np.int32)
+        nb, nf = C.c_int32(0), C.c_int32(0)
+        lib().ref_voc_transform(self._h, _p(d), n, levels_up, _p(word), _p(node), _p(wgt), _p(bi), _p(bv), C.byref(nb), _p(fi), _p(fs),
+                                _p(ft), C.byref(nf))
+        return dict(word_id=word[:n], node_id=node[:n], weight=wgt[:n], bow_ids=bi[: nb.value], bow_values=bv[: nb.value],
+                    fv_node_ids=fi[: nf.value], fv_node_start=fs[: nf.value + 1], fv_items=ft[: int(fs[nf.value])])
+
+    def close(self):
+        if self._h:
+            lib().ref_voc_destroy(self._h)
+            self._h = None

@@ -194,6 +194,11 @@ struct Scalar {
     val[1] = val[2] = val[3] = 0;
   }
   double operator[](int i) const { return val[i]; }
+  static Scalar all(double v) {
+    Scalar s;
+    s.val[0] = s.val[1] = s.val[2] = s.val[3] = v;
+    return s;
+  }
 };
 
 /* core/types.hpp KeyPoint: 28 bytes, same field order */
@@ -215,8 +220,38 @@ class KeyPoint {
 /* ---- Mat ---------------------------------------------------------------------------------------------------- */
 class Mat;
 class MatExpr;
-class FileStorage;  /* persistence is never used on the hot path: declaration only */
-class FileNode;
+/* core/persistence.hpp: the YAML / XML store.  The interface is here so that translation units naming it compile;
+ * the stand-in holds no parser -- opening a store reports "not opened", touching one throws.  DBoW3's binary vocabulary
+ * format (Vocabulary::toStream / fromStream) does not go through it. */
+class FileNode {
+ public:
+  FileNode() {}
+  FileNode operator[](const std::string&) const { return fail(); }
+  FileNode operator[](const char*) const { return fail(); }
+  FileNode operator[](int) const { return fail(); }
+  size_t size() const { return 0; }
+  operator int() const { return fail(), 0; }
+  operator float() const { return fail(), 0.f; }
+  operator double() const { return fail(), 0.0; }
+  operator std::string() const { return fail(), std::string(); }
+
+ private:
+  static FileNode fail() { throw std::runtime_error("cv::FileNode: YAML persistence is not part of the OpenCV stand-in"); }
+};
+class FileStorage {
+ public:
+  enum Mode { READ = 0, WRITE = 1, APPEND = 2, MEMORY = 4 };
+  FileStorage() {}
+  FileStorage(const std::string&, int) {}
+  bool isOpened() const { return false; }
+  void release() {}
+  FileNode operator[](const std::string&) const { return FileNode()[0]; }
+  FileNode operator[](const char*) const { return FileNode()[0]; }
+  template <class T>
+  FileStorage& operator<<(const T&) {
+    throw std::runtime_error("cv::FileStorage: YAML persistence is not part of the OpenCV stand-in");
+  }
+};
 
 static inline size_t cvshim_elem_size1(int depth) {
   static const size_t tab[8] = {1, 1, 2, 2, 4, 4, 8, 2};

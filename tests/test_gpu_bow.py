@@ -74,9 +74,9 @@ def test_load_binary_stream(tmp_path):
     q = synth.synth_vocabulary_queries(v, 777, seed=8)
     bow_cases.same(voc.transform(q, 2), orc.voc_transform(_orc_voc(v, 1, 1), q, 2))
     raw = bytearray(p.read_bytes())
-    raw[8] = 1  # compressed flag
+    raw[8] = 1  # claims to be compressed, is not
     (tmp_path / "c.dbow3").write_bytes(bytes(raw))
-    with pytest.raises(Exception, match="QuickLZ"):
+    with pytest.raises(Exception, match="compressed vocabulary stream"):
         Vocabulary.load(m, tmp_path / "c.dbow3")
     (tmp_path / "t.dbow3").write_bytes(bytes(raw[: len(raw) // 2]))
     with pytest.raises(Exception):
@@ -141,3 +141,25 @@ def test_feature_vector_feeds_search_by_bow():
     n_ref, ref = orc.search_by_bow(1, kps1, d1, valid, fv(o1), kps2, d2, valid, fv(o2), 0.75, 1)
     assert n_got == n_ref and np.array_equal(got, ref)
     assert (got >= 0).sum() > 100
+
+
+
+def test_load_what_the_reference_saves(tmp_path):
+    """Vocabulary::save of the compiled reference (oracle/_ref), in its default QuickLZ-compressed form and plain, of a
+    vocabulary its own k-means trained -> ydorb_vocabulary_load -> transform == the reference's own transform."""
+    from oracle import ref
+    from tests.test_oracle_ref_vocabulary import same_where_defined, trained
+    from ydorbslam_b200.vocabulary import read_dbow3_binary
+
+    if not ref.available():
+        pytest.skip("oracle/_ref not shipped")
+    rv, desc, v = trained(10, 4, 0, 0, 17, tmp_path)
+    m = OrbMatcher()
+    undefined = 0
+    for name in ("packed.dbow3", "plain.dbow3"):
+        voc = Vocabulary.load(m, tmp_path / name)
+        assert voc.info()["n_words"] == rv.info()["n_words"]
+        for n, levels_up in [(2000, 2), (1, 4), (3000, 0), (777, 3)]:
+            q = synth.flip_bits(desc[:n], 0.1, n)
+            undefined += same_where_defined(rv.transform(q, levels_up), voc.transform(q, levels_up), v, levels_up)
+    rv.close()

@@ -7,6 +7,7 @@
 // (node ids ascending, features in push_back order = ascending feature index), the form ydorb_search_by_bow consumes.
 // Word values are doubles accumulated in exactly the reference's order (feature order inside a word, ascending word
 // order for the norm), so they are bit-identical, not merely close.
+#include "vocabulary_stream.h"
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
@@ -335,6 +336,31 @@ int ydorb_vocabulary_info(const YdVocabulary* v, int32_t* info6) {
   return YDORB_OK;
 }
 
+int ydorb_vocabulary_stream_inflate(const uint8_t* stream, size_t n, uint8_t* out, size_t capacity, size_t* out_len) {
+  YD_REQUIRE(stream && out_len, "null argument");
+  *out_len = 0;
+  uint64_t sig = 0;
+  YD_REQUIRE(n >= 13, "truncated vocabulary header");
+  std::memcpy(&sig, stream, 8);
+  YD_REQUIRE(sig == 88877711233ull, "not a DBoW3 binary vocabulary (bad signature)");
+  std::vector<uint8_t> payload;
+  const uint8_t* body = stream + 13;
+  size_t body_len = n - 13;
+  if (stream[8]) {
+    std::string why;
+    YD_REQUIRE(dbow3_inflate_chunks(body, body_len, payload, &why), "compressed vocabulary stream: " + why);
+    body = payload.data();
+    body_len = payload.size();
+  }
+  *out_len = 13 + body_len;
+  if (!out) return YDORB_OK;
+  YD_REQUIRE(capacity >= *out_len, "output buffer too small");
+  std::memcpy(out, stream, 13);
+  out[8] = 0;
+  if (body_len) std::memcpy(out + 13, body, body_len);
+  return YDORB_OK;
+}
+
 int ydorb_vocabulary_load(YdMatcher* m, const char* path, YdVocabulary** out) {
   YD_REQUIRE(m && path && out, "null argument");
   *out = nullptr;
@@ -350,15 +376,16 @@ int ydorb_vocabulary_load(YdMatcher* m, const char* path, YdVocabulary** out) {
     std::fclose(f);
     YD_REQUIRE(got == buf.size(), "short read of the vocabulary file");
   }
+  const std::vector<uint8_t>* src = &buf;
   size_t pos = 0;
   bool ok = true;
   auto rd = [&](void* dst, size_t n) {
-    if (!ok || pos + n > buf.size()) {
+    if (!ok || pos + n > src->size()) {
       ok = false;
       std::memset(dst, 0, n);
       return;
     }
-    std::memcpy(dst, buf.data() + pos, n);
+    std::memcpy(dst, src->data() + pos, n);
     pos += n;
   };
   uint64_t sig = 0;
@@ -369,8 +396,14 @@ int ydorb_vocabulary_load(YdMatcher* m, const char* path, YdVocabulary** out) {
   rd(&compressed, 1);                                                                   // :1343-1344 (sizeof(bool) = 1)
   rd(&nnodes, 4);                                                                       // :1345-1346
   YD_REQUIRE(ok, "truncated vocabulary header");
-  YD_REQUIRE(!compressed, "QuickLZ-compressed vocabulary streams are not supported: re-save with binary_compressed = false");
   YD_REQUIRE(nnodes >= 2 && nnodes < (1u << 30), "vocabulary has no words");
+  std::vector<uint8_t> payload;
+  if (compressed) {  // :1350-1367: 10 000-byte chunks through QuickLZ (level 1) -- what save() writes by default
+    std::string why;
+    YD_REQUIRE(dbow3_inflate_chunks(buf.data() + pos, buf.size() - pos, payload, &why), "compressed vocabulary stream: " + why);
+    src = &payload;
+    pos = 0;
+  }
   int32_t k = 0, L = 0, scoring = 0, weighting = 0;
   rd(&k, 4); rd(&L, 4); rd(&scoring, 4); rd(&weighting, 4);                             // :1371-1374
   std::vector<int32_t> parent(nnodes, -1), word(nnodes, 0), order;                      // Node(): word_id(0)

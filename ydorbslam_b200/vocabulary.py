@@ -115,3 +115,45 @@ def write_dbow3_binary(path, voc, weighting=TF_IDF, scoring=L1_NORM):
         out.append(struct.pack("<II", int(voc["word_ids"][nid]), nid))
     with open(path, "wb") as f:
         f.write(b"".join(out))
+
+
+def inflate_stream(data):
+    """ydorb_vocabulary_stream_inflate: the plain form of a binary vocabulary stream (bytes in, bytes out).  Host only."""
+    src = np.frombuffer(bytes(data), np.uint8)
+    n = C.c_size_t(0)
+    check(lib().ydorb_vocabulary_stream_inflate(ptr(src), C.c_size_t(len(src)), None, C.c_size_t(0), C.byref(n)))
+    out = np.zeros(n.value, np.uint8)
+    check(lib().ydorb_vocabulary_stream_inflate(ptr(src), C.c_size_t(len(src)), ptr(out), C.c_size_t(len(out)), C.byref(n)))
+    return out[: n.value].tobytes()
+
+
+def read_dbow3_binary(data):
+    """Parses a PLAIN binary vocabulary stream (bytes) into the dict form synth.synth_vocabulary uses, the way
+    Vocabulary::fromStream does (Vocabulary.cpp:1371-1405): a test/tool helper, the product loader is ydorb_vocabulary_load."""
+    import struct
+
+    sig, comp, n = struct.unpack_from("<QBI", data, 0)
+    assert sig == 88877711233 and comp == 0
+    k, L, scoring, weighting = struct.unpack_from("<iiii", data, 13)
+    at = 29
+    parent, weights, desc = np.full(n, -1, np.int64), np.zeros(n, np.float64), np.zeros((n, 32), np.uint8)
+    order = []
+    for _ in range(n - 1):
+        nid, pid, w, cols, rows, typ = struct.unpack_from("<IIdiii", data, at)
+        assert (cols, rows, typ) == (32, 1, 0)
+        desc[nid] = np.frombuffer(data, np.uint8, 32, at + 28)
+        parent[nid], weights[nid] = pid, w
+        order.append(nid)
+        at += 60
+    (nw,) = struct.unpack_from("<I", data, at)
+    words = np.frombuffer(data, np.uint32, 2 * nw, at + 4).reshape(nw, 2)
+    word_ids = np.zeros(n, np.int32)
+    word_ids[words[:, 1]] = words[:, 0]
+    kids = [[] for _ in range(n)]
+    for c in order:
+        kids[parent[c]].append(c)
+    child_start = np.zeros(n + 1, np.int32)
+    child_start[1:] = np.cumsum([len(x) for x in kids])
+    children = np.asarray([c for x in kids for c in x], np.int32)
+    return dict(k=k, L=L, scoring=scoring, weighting=weighting, child_start=child_start, children=children, descriptors=desc,
+                weights=weights, word_ids=word_ids)
