@@ -27,6 +27,7 @@ W, H, NFEAT = 640, 480, 1000
 EXTRACTOR_ARGS = (NFEAT, 1.2, 8, 20, 7)
 RATIO, TH_LOW = 0.6, 50
 HAMMING_NQ, HAMMING_NDB = 2000, 1_000_000
+E2E_CALL_FRAMES = int(os.environ.get("YDORB_E2E_CALL_FRAMES", "128"))  # frames per host call of the threaded e2e leg
 E2E_THREADS = int(os.environ.get("YDORB_E2E_THREADS", "4"))  # host threads (one extractor + matcher handle each) of the e2e leg
 
 
@@ -361,17 +362,19 @@ def run_gpu(args):
     h_top2 = torch.zeros(B, cap, 4, dtype=torch.int32).pin_memory()
     h_acc = torch.zeros(B, cap, dtype=torch.uint8).pin_memory()
 
-    def make_worker(exh, mh, f0, n):
+    def make_worker(exh, mh, f0, n, outs, stride=1, first=0):
+        """Frames [f0, f0 + n) of steps first, first + stride, ... through the two synchronous host calls."""
         qf = np.arange(n, dtype=np.int32)
         df = ((np.arange(n) - 1) % n).astype(np.int32)
+        o_kps, o_desc, o_n, o_top2, o_acc = outs
 
         def run(steps):
-            for _ in range(steps):
+            for _ in range(first, steps, stride):
                 check(lib().ydorb_extract_batch(exh._h, C.c_void_p(h_img[f0:].data_ptr()), W, H, W, C.c_size_t(W * H), n,
-                                                C.c_void_p(h_kps[f0:].data_ptr()), C.c_void_p(h_desc[f0:].data_ptr()), cap,
-                                                C.c_void_p(h_n[f0:].data_ptr())))
+                                                C.c_void_p(o_kps[f0:].data_ptr()), C.c_void_p(o_desc[f0:].data_ptr()), cap,
+                                                C.c_void_p(o_n[f0:].data_ptr())))
                 check(lib().ydorb_match_frames(mh._h, exh._h, ptr(qf), ptr(df), n, C.c_float(RATIO), TH_LOW,
-                                               C.c_void_p(h_top2[f0:].data_ptr()), C.c_void_p(h_acc[f0:].data_ptr())))
+                                               C.c_void_p(o_top2[f0:].data_ptr()), C.c_void_p(o_acc[f0:].data_ptr())))
 
         return run
 
@@ -398,25 +401,39 @@ def run_gpu(args):
 
     ke = max(min(K, 10), 1)
 
-    def e2e_measure(workers):
-        timed(workers, max(Wm, 1))
+    def e2e_measure(workers, warm):
+        timed(workers, warm)
         barrier()
         t = torch.tensor([timed(workers, ke)], dtype=torch.float64, device=dev)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return world * B * ke / float(t.item())
 
-    e2e_single = e2e_measure([make_worker(ex, m, 0, B)])
+    outs0 = (h_kps, h_desc, h_n, h_top2, h_acc)
+    e2e_single = e2e_measure([make_worker(ex, m, 0, B, outs0)], max(Wm, 1))
     assert np.array_equal(h_n.numpy(), n_kp), "host-API and device-API keypoint counts differ"
-    # the synchronous entry points spin while they wait: keep the ranks' threads within the host's cores
+    # Threaded: every host call carries E2E_CALL_FRAMES frames (128: below that the kernels of a call are too small to
+    # fill the GPU -- tools/e2e_batch_probe.py: 4 threads x 64 frames 110.8 k frames/s, 4 x 128 127.3 k), so a step is
+    # B / 128 calls, each on its own thread and handle, and T / (B / 128) steps are in flight at a time, each with its
+    # own pinned result buffers.  The synchronous entry points poll while they wait: keep the ranks' threads within
+    # the host's cores.
     T = max(1, min(E2E_THREADS, B // 8, max(1, (os.cpu_count() or 4) // world)))
-    bounds = [B * t // T for t in range(T + 1)]
-    handles = [(OrbExtractor(*EXTRACTOR_ARGS, max_width=W, max_height=H, max_batch=bounds[t + 1] - bounds[t], device=local),
-                OrbMatcher(RATIO, device=local)) for t in range(T)]
-    h_n.zero_()
-    e2e_value = e2e_measure([make_worker(handles[t][0], handles[t][1], bounds[t], bounds[t + 1] - bounds[t]) for t in range(T)])
-    assert np.array_equal(h_n.numpy(), n_kp), "threaded host-API and device-API keypoint counts differ"
-    del handles
+    call = min(B, max(8, E2E_CALL_FRAMES))
+    slots = max(1, min(T, B // call))          # calls (threads) per step
+    pipes = max(1, T // slots)                 # steps in flight
+    T = slots * pipes
+    bounds = [B * t // slots for t in range(slots + 1)]
+    outs = [outs0] + [tuple(torch.zeros_like(x).pin_memory() for x in outs0) for _ in range(pipes - 1)]
+    handles = [(OrbExtractor(*EXTRACTOR_ARGS, max_width=W, max_height=H, max_batch=bounds[t % slots + 1] - bounds[t % slots],
+                             device=local), OrbMatcher(RATIO, device=local)) for t in range(T)]
+    for o in outs:
+        o[2].zero_()
+    workers = [make_worker(handles[t][0], handles[t][1], bounds[t % slots], bounds[t % slots + 1] - bounds[t % slots],
+                           outs[t // slots], pipes, t // slots) for t in range(T)]
+    e2e_value = e2e_measure(workers, max(Wm, pipes))
+    for o in outs[: min(pipes, ke)]:
+        assert np.array_equal(o[2].numpy(), n_kp), "threaded host-API and device-API keypoint counts differ"
+    del handles, workers, outs
     h2d = B * W * H + 2 * 4 * B
     d2h = B * cap * (28 + 32) + 4 * B + B * cap * (16 + 1)
 
@@ -550,8 +567,10 @@ def run_gpu(args):
             "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "timing": f"host wall clock around the synchronous host-pointer C-ABI calls (ydorb_extract_batch + "
                               f"ydorb_match_frames), pinned buffers; {T} host threads, each with its own extractor + matcher "
-                              "handle and 1/T of every step's frames, steps back to back per thread",
-                    "host_threads": T, "single_thread_value": e2e_single},
+                              f"handle: a step is {slots} call(s) of {B // slots} frames on {slots} thread(s), {pipes} step(s) in "
+                              "flight, each thread's calls back to back",
+                    "host_threads": T, "frames_per_call": B // slots, "steps_in_flight": pipes,
+                    "single_thread_value": e2e_single},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": names[dom], "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,

@@ -163,6 +163,17 @@ struct YdGraphEntry {
 constexpr int kYdGraphSlots = 24;
 
 // The extractor handle (opaque to C callers).
+namespace ydorb {
+// first staged source column / row of every tile column / row of a resize launch, as launch parameters (constant
+// bank): the thread that issues the TMA box load does not have to wait for a global-memory table read first
+constexpr int kPyStartX = 40, kPyStartY = 120;
+struct PyrStart {
+  short sxa[kPyStartX];
+  short sy_lo[kPyStartY];
+  int in_params;  // 0: the grid is larger than the arrays, the kernel reads the tables
+};
+}  // namespace ydorb
+
 struct YdExtractor {
   YdExtractorParams params;
   int device;
@@ -195,6 +206,7 @@ struct YdExtractor {
   // device buffers
   uint8_t* d_pyr;        // [max_batch][cap_pyr_bytes]
   int* d_tab_ofs;        // resize source offsets
+  ydorb::PyrStart pyr_start[ydorb::kMaxLevels];  // per destination level: tile start coordinates, passed as launch parameters
   short* d_tab_a;        // resize weights (a0,a1 interleaved)
   ydorb::FastBlock* d_fast_blocks;  // [cap_cells] cell blocks of the current geometry (fast2.cu)
   uint32_t* d_fast_seams;           // [kMaxLevels][276] per-level cell-seam masks of the NMS (fast2.cu)

@@ -191,6 +191,7 @@ static int set_size(YdExtractor* ex, int w, int h) {
     ex->max_cell_h = std::max(ex->max_cell_h, c.w - c.y);
   }
   YD_CUDA(cudaMemcpyAsync(ex->d_geom, &ex->geom, sizeof(FrameGeomDev), cudaMemcpyHostToDevice, ex->stream));
+  pyramid_tile_starts(ex->geom, hg.tab_ofs, ex->pyr_start);
   if (!hg.tab_ofs.empty()) {
     YD_CUDA(cudaMemcpyAsync(ex->d_tab_ofs, hg.tab_ofs.data(), hg.tab_ofs.size() * sizeof(int), cudaMemcpyHostToDevice, ex->stream));
     YD_CUDA(cudaMemcpyAsync(ex->d_tab_a, hg.tab_a.data(), hg.tab_a.size() * sizeof(short), cudaMemcpyHostToDevice, ex->stream));

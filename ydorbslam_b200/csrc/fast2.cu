@@ -142,7 +142,8 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
               const FastBlock* __restrict__ blocks, const uint32_t* __restrict__ seams, int frame0, int ini_th, int min_th, uint32_t* __restrict__ raw,
               int* __restrict__ raw_counter, int* __restrict__ cell_count, int* __restrict__ cell_start,
               int* __restrict__ status) {
-  pdl_wait();
+  // Up to pdl_wait() only launch parameters and geometry tables are read (never the pyramid the predecessor wrote):
+  // that part overlaps the predecessor's tail, and thread 0 issues the box load the moment the pyramid is complete.
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
   int* s_qn = reinterpret_cast<int*>(smem + 8);
@@ -170,9 +171,7 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
     if (tid == 0) {
       mbar_init(bar, 1);
       *s_qn = 0;
-    }
-    __syncthreads();
-    if (tid == 0) {
+      pdl_wait();
       mbar_expect_tx(bar, (uint32_t)(kF2BoxW * kF2BoxH));
       tma_load_3d(smem + kF2OffScore, &maps.lv[b.level], bar, box_x, kPad + b.y0, frame0 + frame);
     }
@@ -182,6 +181,8 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
       const uint32_t* src = seams + b.level * kF2SeamWords;
       for (int i = tid; i < kF2SeamWords; i += kF2Threads) cmL[i] = src[i];
     }
+    if (tid != 0) pdl_wait();
+    __syncthreads();  // thread 0's barrier init and *s_qn are visible
     mbar_wait(bar, 0);
     // ---- bytes -> pixel pairs: tile bytes a + 4w .. a + 4w + 3 of row r = columns 4w - 1 .. 4w + 2 -> words 2w, 2w + 1
     // words needed: 0 .. j1 + 2 (the reject / score of the last tested pair reads two words to its right)
@@ -270,6 +271,8 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
       }
     }
     __syncthreads();
+  } else {
+    pdl_wait();  // nothing to test in this block: its cells still report zero candidates below
   }
 
   // ---- cells: warp per cell, lane per row

@@ -10,6 +10,7 @@ int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, s
 // appends the resize tile descriptors to the int table array (host side of the geometry set-up)
 int pyramid_tile_tables(FrameGeomDev* g, std::vector<int>* tab);
 void pyramid_box(const FrameGeomDev& g, int l, int* box_w, int* box_h);
+void pyramid_tile_starts(const FrameGeomDev& g, const std::vector<int>& tab, PyrStart* out);
 // E3 per-cell FAST with threshold fallback (src/orbExtractor.cpp:562-593)
 int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s);
 // CTA-per-cell-block form (fast2.cu) and its host-side set-up

@@ -135,12 +135,10 @@ struct PyrArgs {
 struct PyrMap {
   CUtensorMap m;  // source level as u8 [frame][row][byte], box = 192 bytes x nsr_cap rows
 };
-
 template <int SS>  // SS: row stride (bytes) of the staged source copies; 192 (the reference's scale factors): staged by TMA
-__global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrMap map, int frame0, const PyrArgs a,
-                                                    const int* __restrict__ tab_ofs, const short2* __restrict__ tab_a,
+__global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrMap map, const __grid_constant__ PyrStart st,
+                                                    int frame0, const PyrArgs a, const int* __restrict__ tab_ofs, const short2* __restrict__ tab_a,
                                                     uint8_t* __restrict__ pyr) {
-  pdl_wait();
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* s_a = smem;                                                       // [nsr_cap][SS]  (TMA destination)
   uint8_t* s_b = s_a + a.nsr_cap * SS;                                       // [nsr_cap][SS], s_b[j] = s_a[j+1]
@@ -155,6 +153,24 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrM
 
   // tile geometry precomputed on the host (pyramid_tile_tables): nothing below depends on the thread
   const int4* td = reinterpret_cast<const int4*>(tab_ofs + a.tile_base);
+  // Everything up to pdl_wait() reads launch parameters and tables written when the geometry was set, never the
+  // predecessor's output: it overlaps the tail of the previous level's launch.
+  if (SS == 192 && tid == 0) {
+    // one TMA box load of the source rows (192 bytes x nsr_cap rows from the 16-byte aligned column the host chose),
+    // issued before anything else; copy B, shifted by one byte, is derived from shared memory once it has landed
+    int bx_src, by_src;
+    if (st.in_params) {
+      bx_src = st.sxa[blockIdx.x];
+      by_src = st.sy_lo[blockIdx.y];
+    } else {
+      bx_src = __ldg(td + 2 * blockIdx.x).w;
+      by_src = __ldg(td + 2 * gridDim.x + blockIdx.y).x;
+    }
+    mbar_init(bar, 1);
+    pdl_wait();
+    mbar_expect_tx(bar, (uint32_t)(SS * a.nsr_cap));
+    tma_load_3d(s_a, &map.m, bar, kPad + bx_src, kPad + by_src, frame0 + (int)blockIdx.z);
+  }
   const int4 X0 = __ldg(td + 2 * blockIdx.x), X1 = __ldg(td + 2 * blockIdx.x + 1), Y = __ldg(td + 2 * gridDim.x + blockIdx.y);
   const int sxa = X0.w, nchunk = X1.x;
   const int sy_lo = Y.x, nsr = Y.y;
@@ -170,16 +186,10 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrM
     }
     s_row[tid] = r;
   }
+  if (SS != 192 || tid != 0) pdl_wait();
   // ---- stage
   if (SS == 192) {
-    // one TMA box load of the source rows (192 bytes x nsr_cap rows from the 16-byte aligned column the host chose);
-    // copy B, shifted by one byte, is then derived from shared memory
-    if (tid == 0) mbar_init(bar, 1);
-    __syncthreads();
-    if (tid == 0) {
-      mbar_expect_tx(bar, (uint32_t)(SS * a.nsr_cap));
-      tma_load_3d(s_a, &map.m, bar, kPad + sxa, kPad + sy_lo, frame0 + (int)blockIdx.z);
-    }
+    __syncthreads();  // the barrier thread 0 initialised is visible
     mbar_wait(bar, 0);
     for (int c = tid & 15; c < nchunk; c += 16)
       for (int r = tid >> 4; r < nsr; r += 16) {
@@ -323,6 +333,23 @@ int pyramid_tile_tables(FrameGeomDev* g, std::vector<int>* tab) {
   return YDORB_OK;
 }
 
+// per destination level: the tile start coordinates of pyramid_tile_tables, in the form the kernel takes as a parameter
+void pyramid_tile_starts(const FrameGeomDev& g, const std::vector<int>& tab, PyrStart* out) {
+  for (int l = 1; l < g.n_levels; l++) {
+    const LevelGeom& lv = g.lv[l];
+    ResizePlan p;
+    PyrStart& st = out[l];
+    st.in_params = 0;
+    if (!plan_resize(g.lv[l - 1], lv, &p)) continue;
+    const int nbx = (lv.stride + kPyTW - 1) / kPyTW, nby = (lv.h + 2 * kPad + p.th - 1) / p.th;
+    if (nbx > kPyStartX || nby > kPyStartY) continue;
+    const int* td = tab.data() + lv.tile_base;
+    for (int bx = 0; bx < nbx; bx++) st.sxa[bx] = (short)td[8 * bx + 3];
+    for (int by = 0; by < nby; by++) st.sy_lo[by] = (short)td[8 * nbx + 4 * by];
+    st.in_params = 1;
+  }
+}
+
 // box of the TMA map that stages the SOURCE level of destination level l (0 x 0: that launch does not use TMA)
 void pyramid_box(const FrameGeomDev& g, int l, int* box_w, int* box_h) {
   ResizePlan p;
@@ -361,11 +388,12 @@ int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, s
         YD_CUDA(cudaFuncSetAttribute(k_pyr_resize<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
       PyrMap map;
       map.m = ex->tmap_pyr[l];
+      const PyrStart& st = ex->pyr_start[l];
       const int frame0 = (int)((ex->d_pyr - ex->pyr_base) / g.pyr_bytes);
       if (p.ss == 192)
-        YD_CUDA(launch_chain(k_pyr_resize<192>, grid, dim3(256), p.smem, s, map, frame0, a, ex->d_tab_ofs, ta, ex->d_pyr));
+        YD_CUDA(launch_chain(k_pyr_resize<192>, grid, dim3(256), p.smem, s, map, st, frame0, a, ex->d_tab_ofs, ta, ex->d_pyr));
       else
-        YD_CUDA(launch_chain(k_pyr_resize<512>, grid, dim3(256), p.smem, s, map, frame0, a, ex->d_tab_ofs, ta, ex->d_pyr));
+        YD_CUDA(launch_chain(k_pyr_resize<512>, grid, dim3(256), p.smem, s, map, st, frame0, a, ex->d_tab_ofs, ta, ex->d_pyr));
     }
   }
   count_launches(g.n_levels);
