@@ -71,21 +71,21 @@ struct DescKp {
   int bx, by;           // TMA box origin in the padded level (byte column on a 16-byte boundary, row)
 };
 
-__device__ __forceinline__ DescKp desc_setup(const DescLevel* __restrict__ lvl, int n_levels, int n_quota, int slot,
-                                             const int4* __restrict__ sel_frame, int capacity) {
+// qb: lane l holds level l's first slot (INT_MAX for l = 0 and l >= n_levels); kp: the slot's quadtree record, loaded by
+// the caller for all of the warp's slots at once.  Everything here is uniform over the warp.
+__device__ __forceinline__ DescKp desc_setup(const DescLevel* __restrict__ lvl, int qb, int n_quota, int slot, int4 kp,
+                                             int capacity) {
   DescKp d;
   d.valid = 0;
   if (slot >= n_quota) return d;
-  int level = 0;
-  for (int l = 1; l < n_levels; l++)
-    if (slot >= lvl[l].quota_base) level = l;
+  const int level = __popc(__ballot_sync(0xffffffffu, slot >= qb));  // quota bases ascend
   const DescLevel L = lvl[level];
   const int j = slot - L.quota_base;
   if (j >= L.cnt) return d;
   d.oi = L.out_base + j;
   if (d.oi >= capacity) return d;
   d.level = level;
-  d.kp = sel_frame[slot];
+  d.kp = kp;
   // the 19 px reflect-101 pad makes every byte the kernel reads a pixel of the level: keypoints are >= 16 px from the
   // edge; the box may reach past the row / buffer end, TMA zero-fills there and nothing reads it
   const int px = kPad + d.kp.x - 26;  // >= 9
@@ -115,7 +115,6 @@ __global__ void __launch_bounds__(kDescWarps * 32, 5)
 k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict__ g, int frame0,
            const int4* __restrict__ sel, const int* __restrict__ sel_n, YdKeyPoint* __restrict__ kps,
            uint8_t* __restrict__ desc, int capacity, int32_t* __restrict__ n_out, int* __restrict__ status) {
-  pdl_wait();
   __shared__ __align__(128) uint8_t s_patch[kDescWarps][2][kPatchBytes];  // double buffered TMA destinations
   __shared__ __align__(8) uint64_t s_bar[kDescWarps][2];
   __shared__ __align__(16) uint16_t s_hb[kDescWarps][kHbCols * kHbColStride];
@@ -131,6 +130,7 @@ k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict
     mbar_init(&s_bar[threadIdx.x >> 5][0], 1);
     mbar_init(&s_bar[threadIdx.x >> 5][1], 1);
   }
+  pdl_wait();  // above: constants and geometry only; below: what the quadtree wrote
   if (threadIdx.x < n_levels) {
     const int l = threadIdx.x;
     const int* cnt = sel_n + (size_t)frame * kMaxLevels;
@@ -157,13 +157,20 @@ k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict
   uint16_t* hb = s_hb[warp];
   // software pipeline over the warp's keypoints: the next neighbourhood's box is in flight (TMA into the other patch
   // buffer) while this one computes; buffer b is used by keypoints b, b + 2, ...: its mbarrier phase is (k >> 1) & 1
-  DescKp cur = desc_setup(s_lvl, n_levels, n_quota, slot0, sel_frame, capacity);
+  const int qb = (lane >= 1 && lane < n_levels) ? s_lvl[lane].quota_base : 0x7FFFFFFF;
+  int4 mine = make_int4(0, 0, 0, 0);  // lane i: the record of slot0 + i (slots past a level's count hold stale records, unused)
+  if (lane < KPW && slot0 + lane < n_quota) mine = sel_frame[slot0 + lane];
+  auto record = [&](int k) {
+    return make_int4(__shfl_sync(0xffffffffu, mine.x, k), __shfl_sync(0xffffffffu, mine.y, k), __shfl_sync(0xffffffffu, mine.z, k),
+                     __shfl_sync(0xffffffffu, mine.w, k));
+  };
+  DescKp cur = desc_setup(s_lvl, qb, n_quota, slot0, record(0), capacity);
   if (cur.valid) desc_prefetch(cur, lane, s_patch[warp][0], &s_bar[warp][0], &maps.lv[cur.level], frame0 + frame);
   for (int k = 0; k < KPW; k++) {
     DescKp nxt;
     nxt.valid = 0;
     if (k + 1 < KPW) {
-      nxt = desc_setup(s_lvl, n_levels, n_quota, slot0 + k + 1, sel_frame, capacity);
+      nxt = desc_setup(s_lvl, qb, n_quota, slot0 + k + 1, record(k + 1), capacity);
       // the other buffer was last read by keypoint k - 1, whose compute ended with a __syncwarp
       if (nxt.valid) desc_prefetch(nxt, lane, s_patch[warp][(k + 1) & 1], &s_bar[warp][(k + 1) & 1], &maps.lv[nxt.level], frame0 + frame);
     }
