@@ -5,7 +5,7 @@
 // (cell j tests [iniX_j + 3, iniX_j + wCell + 3)).  The FAST score of a pixel does not depend on the cell it is tested
 // in -- only non-max suppression (a cv::Mat ROI is a standalone image: neighbours outside the cell count as 0), the
 // empty-cell threshold fallback and the order of the candidate list are per cell.  So a CTA owns a block of up to
-// 4 x 2 cells and works in dense phases over the whole block:
+// 4 x 1 cells (YD_F2_CELL_COLS x YD_F2_CELL_ROWS) and works in dense phases over the whole block:
 //   stage    one TMA box load (cp.async.bulk.tensor.3d) of the block's ROI (the box starts on a 16-byte boundary left
 //            of the ROI: TMA needs that); bytes -> s16x2 pixel-pair plane, shifted so that word j of a row holds ROI
 //            columns (2j - 1, 2j): the first tested column (3) is then the low half of word 2 and a row of up to
@@ -19,7 +19,7 @@
 //            an empty cell re-runs NMS at minThFAST (:582-585); the cell reserves a slice of the frame's candidate
 //            buffer and every lane walks its row's bits, which is the reference's row-major order.
 // Results are bit-identical to fast.cu's warp-per-cell kernel (tests run both); that kernel remains the choice for
-// launches too small to fill the GPU with 8-warp CTAs (single frames).
+// launches too small to fill the GPU with these CTAs (single frames).
 #include <algorithm>
 #include <cstdlib>
 
@@ -28,26 +28,45 @@
 
 namespace ydorb {
 
-constexpr int kF2Threads = 256;
+// Block shape (compile-time, -DYD_F2_*): threads per CTA, rows of cells per block, resident CTAs per SM the register
+// budget is set for.  One row of cells and 4 warps: the phases of a CTA are separated by barriers, so many small CTAs
+// per SM interleave better than few large ones (measured per 256 frames: 8 warps x 4 x 2 cells 0.614 ms, 4 warps x 4 x 1
+// cells 0.584 ms, 4 warps x 2 x 1 cells 0.635 ms -- the 6 px halo of every block is scored twice).
+#ifndef YD_F2_THREADS
+#define YD_F2_THREADS 128
+#endif
+#ifndef YD_F2_CELL_ROWS
+#define YD_F2_CELL_ROWS 1
+#endif
+#ifndef YD_F2_CELL_COLS
+#define YD_F2_CELL_COLS 4
+#endif
+#ifndef YD_F2_CTAS
+#define YD_F2_CTAS 8
+#endif
+constexpr int kF2Threads = YD_F2_THREADS;
 constexpr int kF2Warps = kF2Threads / 32;
-constexpr int kF2MaxW = 134, kF2MaxH = 70;  // largest block ROI: 4 cells of 32 + 6, 2 cells of 32 + 6
-constexpr int kF2BoxW = 160, kF2BoxH = 70;  // TMA box: up to 15 + 1 bytes left of the ROI, one word of look-ahead
-constexpr int kF2Wpr = 68;                  // pair words per plane row: word j = ROI columns (2j - 1, 2j), j <= 67
-constexpr int kF2KeepWords = 5;             // keep bitmap words per row (tile columns 0..159)
-constexpr int kF2QueueCap = 64 * 64;        // tested pairs of the largest block
+constexpr int kF2CellRows = YD_F2_CELL_ROWS;
+constexpr int kF2CellCols = YD_F2_CELL_COLS;
+constexpr int kF2MaxW = 32 * kF2CellCols + 6, kF2MaxH = 70;  // largest block ROI: 4 (2) cells of 32 + 6 wide, 2 cells of 32 + 6 (1 of 64 + 6) high
+constexpr int kF2BoxW = (15 + kF2MaxW + 4 + 15) & ~15;  // TMA box: up to 15 + 1 bytes left of the ROI, one word of look-ahead (160 / 96)
+constexpr int kF2Wpr = kF2MaxW / 2 + 1;     // pair words per plane row: word j = ROI columns (2j - 1, 2j), j <= 67 (35)
+constexpr int kF2KeepWords = (kF2BoxW + 31) / 32;  // keep bitmap words per row (tile columns 0..159)
 constexpr int kF2MaxCells = 8;
 constexpr int kF2SeamWords = 2 * kF2Wpr + 2 * kF2MaxH;  // cmL[68] cmR[68] rmU[70] rmD[70] of one level
 
-// shared memory map (bytes)
+// shared memory map (bytes).  The small tables have room for kF2MaxH rows; the queue and the two planes are sized for
+// the tallest block ROI of the CURRENT geometry (`rows`, a launch parameter; also the height of the TMA box): with one
+// row of cells per block that is 36-46 rows for the usual image sizes, ~30 KB per CTA.
 constexpr int kF2OffTab = 128;                                         // cmL[68] cmR[68] rmU[70] rmD[70]
 constexpr int kF2OffKeep = kF2OffTab + 4 * (2 * kF2Wpr + 2 * kF2MaxH); // keep bitmap [70][5]
 constexpr int kF2OffRowBase = (kF2OffKeep + 4 * kF2MaxH * kF2KeepWords + 15) & ~15;  // u16 [8][64]
-constexpr int kF2OffQueue = kF2OffRowBase + 2 * kF2MaxCells * 64;      // u16 [4096]
-constexpr int kF2OffPair = (kF2OffQueue + 2 * kF2QueueCap + 127) & ~127;
-constexpr int kF2PlaneBytes = 4 * kF2Wpr * kF2MaxH;
-constexpr int kF2OffScore = (kF2OffPair + kF2PlaneBytes + 127) & ~127;  // the TMA byte tile lands here first
-constexpr int kF2SmemBytes = kF2OffScore + kF2PlaneBytes;
-static_assert(kF2BoxW * kF2BoxH <= kF2PlaneBytes, "the byte tile aliases the score plane");
+constexpr int kF2OffQueue = kF2OffRowBase + 2 * kF2MaxCells * 64;      // u16 [(kF2Wpr - 4) * (rows - 6)] tested pairs of a block
+__host__ __device__ constexpr int f2_plane_bytes(int rows) { return 4 * kF2Wpr * rows; }
+__host__ __device__ constexpr int f2_off_pair(int rows) { return (kF2OffQueue + 2 * (kF2Wpr - 4) * (rows - 6) + 127) & ~127; }
+__host__ __device__ constexpr int f2_off_score(int rows) { return (f2_off_pair(rows) + f2_plane_bytes(rows) + 127) & ~127; }
+__host__ __device__ constexpr int f2_smem_bytes(int rows) { return f2_off_score(rows) + f2_plane_bytes(rows); }
+static_assert(kF2BoxW <= 4 * kF2Wpr, "the byte tile aliases the score plane");
 
 struct Fast2Maps {
   CUtensorMap lv[kMaxLevels];
@@ -137,9 +156,9 @@ __device__ __forceinline__ int fast2_row_count(const uint32_t* __restrict__ krow
 }
 
 template <int REJECT>  // 4: four antipodal pairs in the reject, 2: vertical + horizontal only
-__global__ void __launch_bounds__(kF2Threads, 4)
+__global__ void __launch_bounds__(kF2Threads, YD_F2_CTAS)
 k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
-              const FastBlock* __restrict__ blocks, const uint32_t* __restrict__ seams, int frame0, int ini_th, int min_th, uint32_t* __restrict__ raw,
+              const FastBlock* __restrict__ blocks, const uint32_t* __restrict__ seams, int rows_cap, int frame0, int ini_th, int min_th, uint32_t* __restrict__ raw,
               int* __restrict__ raw_counter, int* __restrict__ cell_count, int* __restrict__ cell_start,
               int* __restrict__ status) {
   // Up to pdl_wait() only launch parameters and geometry tables are read (never the pyramid the predecessor wrote):
@@ -154,9 +173,9 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
   uint32_t* keep = reinterpret_cast<uint32_t*>(smem + kF2OffKeep);       // [70][5] bit x of row r: pixel survives NMS
   uint16_t* rowbase = reinterpret_cast<uint16_t*>(smem + kF2OffRowBase);  // [8][64] survivors of the cell above row
   uint16_t* queue = reinterpret_cast<uint16_t*>(smem + kF2OffQueue);
-  uint32_t* pair = reinterpret_cast<uint32_t*>(smem + kF2OffPair);        // [70][68]
-  uint32_t* score = reinterpret_cast<uint32_t*>(smem + kF2OffScore);      // [70][68]
-  const uint32_t* tile8 = reinterpret_cast<const uint32_t*>(smem + kF2OffScore);
+  uint32_t* pair = reinterpret_cast<uint32_t*>(smem + f2_off_pair(rows_cap));        // [rows_cap][68]
+  uint32_t* score = reinterpret_cast<uint32_t*>(smem + f2_off_score(rows_cap));      // [rows_cap][68]
+  const uint32_t* tile8 = score;  // the TMA byte tile lands in the score plane first
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const int frame = blockIdx.y;
@@ -172,8 +191,8 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
       mbar_init(bar, 1);
       *s_qn = 0;
       pdl_wait();
-      mbar_expect_tx(bar, (uint32_t)(kF2BoxW * kF2BoxH));
-      tma_load_3d(smem + kF2OffScore, &maps.lv[b.level], bar, box_x, kPad + b.y0, frame0 + frame);
+      mbar_expect_tx(bar, (uint32_t)(kF2BoxW * rows_cap));
+      tma_load_3d(score, &maps.lv[b.level], bar, box_x, kPad + b.y0, frame0 + frame);
     }
     // ---- while the box is in flight: keep bitmap := 0, this level's seam masks (host-built, fast2_build_blocks)
     {
@@ -208,7 +227,7 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
     __syncthreads();  // pair plane complete; the byte tile is dead, its memory becomes the score plane
     {
       uint4* z = reinterpret_cast<uint4*>(score);
-      for (int i = tid; i < kF2PlaneBytes / 16; i += kF2Threads) z[i] = make_uint4(0u, 0u, 0u, 0u);
+      for (int i = tid; i < f2_plane_bytes(rows_cap) / 16; i += kF2Threads) z[i] = make_uint4(0u, 0u, 0u, 0u);
     }
     // tested pixels: columns [3, W - 4] = words [2, j1], rows [3, H - 4]
     const int ipw = j1 - 1, ih = H - 6;
@@ -393,7 +412,7 @@ int fast2_build_blocks(const FrameGeomDev& g, const std::vector<int4>& cells, st
         t[2 * kF2Wpr + kF2MaxH + r] = first(r + 1, lv.cell_h) ? 0u : 0xFFFFFFFFu;
       }
     }
-    const int bx = std::max(1, std::min(4, (kMaxW - 6) / lv.cell_w)), by = std::max(1, std::min(2, (kMaxH - 6) / lv.cell_h));
+    const int bx = std::max(1, std::min(kF2CellCols, (kMaxW - 6) / lv.cell_w)), by = std::max(1, std::min(kF2CellRows, (kMaxH - 6) / lv.cell_h));
     for (int cy = 0; cy < lv.cell_rows; cy += by)
       for (int cx = 0; cx < lv.cell_cols; cx += bx) {
         FastBlock b = {};
@@ -442,11 +461,11 @@ int fast2_build_blocks(const FrameGeomDev& g, const std::vector<int4>& cells, st
   return YDORB_OK;
 }
 
-size_t fast2_smem_bytes(int, int) { return (size_t)kF2SmemBytes; }
+size_t fast2_smem_bytes(int, int max_h) { return (size_t)f2_smem_bytes(std::max(max_h, 8)); }
 
-void fast2_box(int, int, int* box_w, int* box_h) {
+void fast2_box(int, int max_h, int* box_w, int* box_h) {
   *box_w = kF2BoxW;
-  *box_h = kF2BoxH;
+  *box_h = std::max(max_h, 8);
 }
 
 int launch_fast_blocks(const YdExtractor* ex, int batch, cudaStream_t s) {
@@ -460,7 +479,7 @@ int launch_fast_blocks(const YdExtractor* ex, int batch, cudaStream_t s) {
   for (int l = 0; l < kMaxLevels; l++) maps.lv[l] = ex->tmap_level[l];
   const int frame0 = (int)((ex->d_pyr - ex->pyr_base) / ex->geom.pyr_bytes);
   dim3 grid(ex->n_fast_blocks, batch);
-  YD_CUDA(launch_chain(kernel, grid, dim3(kF2Threads), smem, s, maps, ex->d_geom, ex->d_cells, ex->d_fast_blocks, ex->d_fast_seams, frame0,
+  YD_CUDA(launch_chain(kernel, grid, dim3(kF2Threads), smem, s, maps, ex->d_geom, ex->d_cells, ex->d_fast_blocks, ex->d_fast_seams, std::max(ex->fb_max_h, 8), frame0,
                        ini, mn, ex->d_raw, ex->d_raw_counter, ex->d_cell_count, ex->d_cell_start,
                        ex->d_status));
   count_launches(1);
