@@ -115,7 +115,19 @@ __global__ void __launch_bounds__(256) k_pyr_level0(const uint8_t* __restrict__ 
 // kPyHS-1 is kept zero and stands in for the stride padding beyond the padded width.
 constexpr int kPyTW = 128;             // padded destination columns per CTA
 constexpr int kPyHS = kPyTW + 4;       // row stride of H (ints)
-constexpr int kPyMaxTH = 32;           // destination rows per CTA (the host shrinks it for large scale factors)
+// CTA shape (measured per 256 frames of 640x480, all 7 resize launches + level 0): 256 threads x 32 rows 0.324 ms,
+// 128 x 24 0.330, 128 x 16 0.316, 128 x 12 0.319, 256 x 16 0.371.  A version that walked several tiles per CTA with the
+// next tile's TMA box in flight (double-buffered staging, 4 CTAs/SM instead of 5) was slower: 0.345 ms -- the hardware's
+// interleaving of many small CTAs hides the box latency better than a software pipeline inside fewer, larger ones.
+#ifndef YD_PYR_THREADS
+#define YD_PYR_THREADS 128
+#endif
+#ifndef YD_PYR_TH
+#define YD_PYR_TH 16
+#endif
+constexpr int kPyThreads = YD_PYR_THREADS;  // 128 or 256
+constexpr int kPyStreams = kPyThreads / kPyTW;  // source rows a phase-A pass covers
+constexpr int kPyMaxTH = YD_PYR_TH;    // destination rows per CTA (the host shrinks it for large scale factors)
 
 struct PyrArgs {
   int dw, dh, dstride;   // destination level
@@ -136,7 +148,7 @@ struct PyrMap {
   CUtensorMap m;  // source level as u8 [frame][row][byte], box = 192 bytes x nsr_cap rows
 };
 template <int SS>  // SS: row stride (bytes) of the staged source copies; 192 (the reference's scale factors): staged by TMA
-__global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrMap map, const __grid_constant__ PyrStart st,
+__global__ void __launch_bounds__(kPyThreads) k_pyr_resize(const __grid_constant__ PyrMap map, const __grid_constant__ PyrStart st,
                                                     int frame0, const PyrArgs a, const int* __restrict__ tab_ofs, const short2* __restrict__ tab_a,
                                                     uint8_t* __restrict__ pyr) {
   extern __shared__ __align__(128) uint8_t smem[];
@@ -192,7 +204,7 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrM
     __syncthreads();  // the barrier thread 0 initialised is visible
     mbar_wait(bar, 0);
     for (int c = tid & 15; c < nchunk; c += 16)
-      for (int r = tid >> 4; r < nsr; r += 16) {
+      for (int r = tid >> 4; r < nsr; r += kPyThreads / 16) {
         const uint4 v = *reinterpret_cast<const uint4*>(s_a + r * SS + 16 * c);
         const uint32_t nx = (c + 1 < nchunk) ? *reinterpret_cast<const uint32_t*>(s_a + r * SS + 16 * c + 16) : 0u;
         *reinterpret_cast<uint4*>(s_b + r * SS + 16 * c) =
@@ -202,12 +214,12 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrM
   } else {
     constexpr int kStageIlp = YD_PYR_STAGE_ILP;  // rows whose loads are in flight together per thread
     for (int c = tid & 15; c < nchunk; c += 16) {
-      for (int r0 = tid >> 4; r0 < nsr; r0 += 16 * kStageIlp) {
+      for (int r0 = tid >> 4; r0 < nsr; r0 += (kPyThreads / 16) * kStageIlp) {
         uint4 v[kStageIlp];
         uint32_t nx[kStageIlp];
 #pragma unroll
         for (int k = 0; k < kStageIlp; k++) {
-          const int r = r0 + 16 * k;
+          const int r = r0 + (kPyThreads / 16) * k;
           if (r < nsr) {
             const uint8_t* gp = src0 + (long long)(sy_lo + r) * a.sstride + sxa + 16 * c;
             v[k] = *reinterpret_cast<const uint4*>(gp);
@@ -216,7 +228,7 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrM
         }
 #pragma unroll
         for (int k = 0; k < kStageIlp; k++) {
-          const int r = r0 + 16 * k;
+          const int r = r0 + (kPyThreads / 16) * k;
           if (r < nsr) {
             *reinterpret_cast<uint4*>(s_a + r * SS + 16 * c) = v[k];
             *reinterpret_cast<uint4*>(s_b + r * SS + 16 * c) =
@@ -234,7 +246,7 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrM
     const int c = tid & (kPyTW - 1);
     const int px = px0 + c;
     int* hp = s_h + (tid >> 7) * kPyHS + c;
-    const int n = (nsr - (tid >> 7) + 1) >> 1;  // rows tid>>7, +2, +4, ...
+    const int n = (nsr - (tid >> 7) + kPyStreams - 1) / kPyStreams;  // rows tid>>7, +kPyStreams, ...
     if (px < pw) {
       const int dx = reflect101(px - kPad, a.dw);
       const int o0 = tab_ofs[a.xb + dx] - sxa;
@@ -243,9 +255,9 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrM
       const uint8_t* sp = ((o0 & 1) ? s_b : s_a) + (o0 & ~1) + (tid >> 7) * SS;
 #pragma unroll 4
       for (int i = 0; i < n; i++)
-        hp[i * 2 * kPyHS] = (int)(__dp2a_lo(wpk, (uint32_t) * reinterpret_cast<const uint16_t*>(sp + i * 2 * SS), 0u) >> 4);
+        hp[i * kPyStreams * kPyHS] = (int)(__dp2a_lo(wpk, (uint32_t) * reinterpret_cast<const uint16_t*>(sp + i * kPyStreams * SS), 0u) >> 4);
     } else {
-      for (int i = 0; i < n; i++) hp[i * 2 * kPyHS] = 0;
+      for (int i = 0; i < n; i++) hp[i * kPyStreams * kPyHS] = 0;
     }
   }
   __syncthreads();
@@ -254,7 +266,7 @@ __global__ void __launch_bounds__(256) k_pyr_resize(const __grid_constant__ PyrM
   const int px4 = px0 + c0;
   if (px4 >= a.dstride) return;
   uint8_t* dcol = fbase + a.doff + px4;
-  for (int i = tid >> 5; i < a.th; i += 8) {
+  for (int i = tid >> 5; i < a.th; i += kPyThreads / 32) {
     const int py = py0 + i;
     if (py >= ph) break;
     const int4 r = s_row[i];
@@ -391,9 +403,9 @@ int launch_pyramid(const YdExtractor* ex, const uint8_t* d_images, int stride, s
       const PyrStart& st = ex->pyr_start[l];
       const int frame0 = (int)((ex->d_pyr - ex->pyr_base) / g.pyr_bytes);
       if (p.ss == 192)
-        YD_CUDA(launch_chain(k_pyr_resize<192>, grid, dim3(256), p.smem, s, map, st, frame0, a, ex->d_tab_ofs, ta, ex->d_pyr));
+        YD_CUDA(launch_chain(k_pyr_resize<192>, grid, dim3(kPyThreads), p.smem, s, map, st, frame0, a, ex->d_tab_ofs, ta, ex->d_pyr));
       else
-        YD_CUDA(launch_chain(k_pyr_resize<512>, grid, dim3(256), p.smem, s, map, st, frame0, a, ex->d_tab_ofs, ta, ex->d_pyr));
+        YD_CUDA(launch_chain(k_pyr_resize<512>, grid, dim3(kPyThreads), p.smem, s, map, st, frame0, a, ex->d_tab_ofs, ta, ex->d_pyr));
     }
   }
   count_launches(g.n_levels);
