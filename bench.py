@@ -274,10 +274,38 @@ def run_gpu(args):
     d_acc = torch.zeros(B, cap, dtype=torch.uint8, device=dev)
     torch.cuda.synchronize()
 
+    # Steps are issued back to back.  The matcher has its own stream and the step's results alternate between two
+    # buffer sets, so the Hamming match of step i (ALU-bound) runs beside the extraction of step i + 1 (latency-bound):
+    # extraction i waits for match i - 2 (same buffers), match i for extraction i.  YDORB_BENCH_PIPE=0: one stream.
+    pipe = os.environ.get("YDORB_BENCH_PIPE", "1") != "0"
+    mstream = torch.cuda.Stream(device=dev)
+    sets = [(d_kps, d_desc, d_n, d_top2, d_acc)]
+    if pipe:
+        sets.append(tuple(torch.zeros_like(x) for x in sets[0]))
+        m.set_stream(mstream.cuda_stream)
+    ev_ext = [torch.cuda.Event() for _ in sets]
+    ev_match = [torch.cuda.Event() for _ in sets]
+    counter = [0]
+
     def step():
-        ex.extract_batch_device(d_img.data_ptr(), W, H, B, d_kps.data_ptr(), d_desc.data_ptr(), cap, d_n.data_ptr())
-        m.top2_frames_device(d_desc.data_ptr(), d_n.data_ptr(), cap, d_qf.data_ptr(), d_df.data_ptr(), B, d_top2.data_ptr(),
-                             d_acc.data_ptr(), RATIO, TH_LOW)
+        i = counter[0] % len(sets)
+        counter[0] += 1
+        kps_, desc_, n_, top2_, acc_ = sets[i]
+        if pipe:
+            stream.wait_event(ev_match[i])
+        ex.extract_batch_device(d_img.data_ptr(), W, H, B, kps_.data_ptr(), desc_.data_ptr(), cap, n_.data_ptr())
+        if pipe:
+            ev_ext[i].record(stream)
+            mstream.wait_event(ev_ext[i])
+        m.top2_frames_device(desc_.data_ptr(), n_.data_ptr(), cap, d_qf.data_ptr(), d_df.data_ptr(), B, top2_.data_ptr(),
+                             acc_.data_ptr(), RATIO, TH_LOW)
+        if pipe:
+            ev_match[i].record(mstream)
+
+    def join():  # the timed stream waits for the matches still in flight
+        if pipe:
+            for e in ev_match:
+                stream.wait_event(e)
 
     def barrier():
         torch.cuda.synchronize()
@@ -299,6 +327,7 @@ def run_gpu(args):
         e0.record(stream)
         for _ in range(K):
             step()
+        join()
         e1.record(stream)
     barrier()
     ms_total = e0.elapsed_time(e1)
@@ -316,6 +345,7 @@ def run_gpu(args):
             s0.record(stream)
             for _ in range(ks):
                 step()
+            join()
             s1.record(stream)
         barrier()
         ts_ms = torch.tensor([s0.elapsed_time(s1)], dtype=torch.float64, device=dev)
@@ -326,6 +356,10 @@ def run_gpu(args):
     # per-stage times: the same K steps again with the handle's stage events on (serial stages, one stream); the timed
     # region above runs the production path, which overlaps two sub-batches on two streams
     ex.set_profiling(True)
+    barrier()
+    pipe = False  # the serial pass: matcher back on the extractor's stream, one buffer set
+    m.set_stream(stream.cuda_stream)
+    sets = sets[:1]
     p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with torch.cuda.stream(stream):
         p0.record(stream)
