@@ -143,6 +143,16 @@ int ydorb_hamming_top2(YdMatcher* m, const uint8_t* queries, int nq, const uint8
                        YdTop2* out);
 int ydorb_hamming_top2_device(YdMatcher* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, int ndb, int idx_base,
                               YdTop2* d_out);
+/* The same scan as ydorb_hamming_top2_device for callers that may not allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * The per-query fold state lives in a file-scope device array of the library (~256 KB, held by
+ * every GPU that loads the library until exit) instead of the handle's grow-only cudaMalloc'ed buffer: the call
+ * reaches no cudaMalloc / cudaFree.  nq > YDORB_NOALLOC_MAX_QUERIES fails with YDORB_E_CAPACITY (split the queries;
+ * ndb is not limited by it).  Same results as ydorb_hamming_top2_device, asynchronous on the matcher's stream.  All
+ * calls and handles on a device share the array: calls that overlap on the GPU race -- keep them on one stream. */
+#define YDORB_NOALLOC_MAX_QUERIES 16384
+int ydorb_hamming_top2_device_noalloc(YdMatcher* m, const uint8_t* d_queries, int nq, const uint8_t* d_db, int ndb,
+                                      int idx_base, YdTop2* d_out);
 /* batched dense top-2 between frames of one descriptor block d_desc[frame][capacity][32] with per-frame counts
  * d_n[frame]: pair p matches the descriptors of frame d_q_frame[p] against those of frame d_db_frame[p] (e.g. frame
  * t against frame t-1).  d_out[p*capacity + i]; d_accept (may be NULL) gets the ratio test of src/orbMatcher.cpp:336. */
