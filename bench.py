@@ -672,6 +672,19 @@ def run_gpu(args):
                                    "every pair; exact score 106 (two 9-arc trees 2 x 32, two 16-way reductions 2 x 8, 10 shifts, "
                                    "16 compare / select) on the pairs that pass (DESIGN.md 4)",
                 "source": tr.get("source")}
+        # The whole step against the same ceiling: warp instructions of all five stages (same capture) per step / the
+        # timed step, over the issue rate of the GPU.  This, not HBM, is the roofline the path as built sits under.
+        wis = tr.get("warp_inst_per_frame", {})
+        if all(k in wis for k in names + ["match"]) and clocks and clocks.get("sm_mhz"):
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            peak_issue = sms * 4 * clocks["sm_mhz"] * 1e6
+            total = sum(wis[k] for k in names + ["match"])
+            line["issue_roofline_step"] = {
+                "bound": "instruction issue (4 warp-instructions per clock per SM)", "warp_inst_per_frame": total,
+                "by_stage": {k: wis[k] for k in names + ["match"]},
+                "achieved_gwarp_inst_s": total * B / (ms_total / K * 1e-3) / 1e9, "peak_gwarp_inst_s": peak_issue / 1e9,
+                "frac": total * B / (ms_total / K * 1e-3) / peak_issue,
+                "ms_per_step_at_full_issue": total * B / peak_issue * 1e3, "source": tr.get("source")}
         if os.path.exists(traffic_path):
             # dram__bytes_read.sum + dram__bytes_write.sum per frame of each stage kernel, from the committed
             # `ncu --set full` capture (profiles/): scaled to this launch's batch

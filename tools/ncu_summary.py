@@ -10,6 +10,10 @@ import sys
 
 raw, tag, fpl = sys.argv[1], sys.argv[2], int(sys.argv[3])
 note = sys.argv[4] if len(sys.argv) > 4 else ""
+# frames one launch of each stage covers: the extractor's kernels run per sub-batch (fpl frames), the frame-pair match once
+# per step over both sub-batches
+match_fpl = int(sys.argv[5]) if len(sys.argv) > 5 else 2 * fpl
+frames_of = lambda stage: match_fpl if stage == "match" else fpl  # noqa: E731
 rows = list(csv.reader(open(raw)))
 hdr, units = rows[0], rows[1]
 keys = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
@@ -62,9 +66,9 @@ for k, v in agg.items():
 stages = ("pyramid", "fast", "quadtree", "describe", "match")
 d = {"source": f"profiles/{tag}_ncu_full_summary.txt (ncu --set full, {fpl}-frame launches as in the timed bench; "
                "dram__bytes_read.sum + dram__bytes_write.sum, smsp__inst_executed.sum; pipe / issue percentages are time-weighted over the stage's kernels)",
-     "frames_per_launch": fpl,
-     "bytes_per_frame": {k: agg[k]["bytes"] / fpl for k in stages if k in agg},
-     "warp_inst_per_frame": {k: agg[k]["inst"] / fpl for k in stages if k in agg},
+     "frames_per_launch": fpl, "match_frames_per_launch": match_fpl,
+     "bytes_per_frame": {k: agg[k]["bytes"] / frames_of(k) for k in stages if k in agg},
+     "warp_inst_per_frame": {k: agg[k]["inst"] / frames_of(k) for k in stages if k in agg},
      "alu_pipe_pct_ncu": {k: agg[k]["alu"] / agg[k]["w"] for k in stages if k in agg},
      "issue_active_pct_ncu": {k: agg[k]["issue"] / agg[k]["w"] for k in stages if k in agg},
      "ncu_us_per_launch": {k: agg[k]["us"] for k in stages if k in agg}}
