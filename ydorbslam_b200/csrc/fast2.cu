@@ -11,7 +11,7 @@
 //            columns (2j - 1, 2j): the first tested column (3) is then the low half of word 2 and a row of up to
 //            128 tested pixels is exactly 64 fully tested pairs;
 //   reject   a warp per row, a thread per two adjacent pairs (one LDS.64 feeds both): antipodal necessary condition
-//            (fast_common.cuh); survivors go to one CTA-wide queue with a warp-aggregated shared-memory atomic;
+//            (fast_common.cuh); survivors go to the warp's own queue (running count in a register, no atomics);
 //   score    exact branch-free score of the queued pairs on full warps -> score plane, max(m - low_th, 0) per half;
 //   nms      queued pairs with a non-zero score: 8-neighbour maximum with the neighbours across a cell seam masked
 //            to 0 (per-column / per-row seam masks); survivors set their bit in a per-row keep bitmap;
@@ -62,8 +62,10 @@ constexpr int kF2OffTab = 128;                                         // cmL[68
 constexpr int kF2OffKeep = kF2OffTab + 4 * (2 * kF2Wpr + 2 * kF2MaxH); // keep bitmap [70][5]
 constexpr int kF2OffRowBase = (kF2OffKeep + 4 * kF2MaxH * kF2KeepWords + 15) & ~15;  // u16 [8][64]
 constexpr int kF2OffQueue = kF2OffRowBase + 2 * kF2MaxCells * 64;      // u16 [(kF2Wpr - 4) * (rows - 6)] tested pairs of a block
+// entries of one warp's survivor queue: a warp does at most ceil(tested rows / warps) reject steps of <= 64 pairs each
+__host__ __device__ constexpr int f2_queue_cap(int rows) { return 64 * ((rows - 6 + kF2Warps - 1) / kF2Warps); }
 __host__ __device__ constexpr int f2_plane_bytes(int rows) { return 4 * kF2Wpr * rows; }
-__host__ __device__ constexpr int f2_off_pair(int rows) { return (kF2OffQueue + 2 * (kF2Wpr - 4) * (rows - 6) + 127) & ~127; }
+__host__ __device__ constexpr int f2_off_pair(int rows) { return (kF2OffQueue + 2 * f2_queue_cap(rows) * kF2Warps + 127) & ~127; }
 __host__ __device__ constexpr int f2_off_score(int rows) { return (f2_off_pair(rows) + f2_plane_bytes(rows) + 127) & ~127; }
 __host__ __device__ constexpr int f2_smem_bytes(int rows) { return f2_off_score(rows) + f2_plane_bytes(rows); }
 static_assert(kF2BoxW <= 4 * kF2Wpr, "the byte tile aliases the score plane");
@@ -165,18 +167,18 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
   // that part overlaps the predecessor's tail, and thread 0 issues the box load the moment the pyramid is complete.
   extern __shared__ __align__(128) uint8_t smem[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem);
-  int* s_qn = reinterpret_cast<int*>(smem + 8);
+  int* s_qn = reinterpret_cast<int*>(smem + 8);  // [kF2Warps] entries of the warps' survivor queues
   uint32_t* cmL = reinterpret_cast<uint32_t*>(smem + kF2OffTab);  // [68] seam masks of the left / right neighbours
   uint32_t* cmR = cmL + kF2Wpr;
   uint32_t* rmU = cmR + kF2Wpr;                                   // [70] row above / below in the same cell
   uint32_t* rmD = rmU + kF2MaxH;
   uint32_t* keep = reinterpret_cast<uint32_t*>(smem + kF2OffKeep);       // [70][5] bit x of row r: pixel survives NMS
   uint16_t* rowbase = reinterpret_cast<uint16_t*>(smem + kF2OffRowBase);  // [8][64] survivors of the cell above row
-  uint16_t* queue = reinterpret_cast<uint16_t*>(smem + kF2OffQueue);
   uint32_t* pair = reinterpret_cast<uint32_t*>(smem + f2_off_pair(rows_cap));        // [rows_cap][68]
   uint32_t* score = reinterpret_cast<uint32_t*>(smem + f2_off_score(rows_cap));      // [rows_cap][68]
   const uint32_t* tile8 = score;  // the TMA byte tile lands in the score plane first
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  uint16_t* queue = reinterpret_cast<uint16_t*>(smem + kF2OffQueue) + warp * f2_queue_cap(rows_cap);  // this warp's survivors
   const uint32_t lt_mask = (1u << lane) - 1u;
   const int frame = blockIdx.y;
   const FastBlock b = blocks[blockIdx.x];
@@ -189,7 +191,6 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
     const int bx = kPad + b.x0 - 1, box_x = bx & ~15, a = bx & 15;
     if (tid == 0) {
       mbar_init(bar, 1);
-      *s_qn = 0;
       pdl_wait();
       mbar_expect_tx(bar, (uint32_t)(kF2BoxW * rows_cap));
       tma_load_3d(score, &maps.lv[b.level], bar, box_x, kPad + b.y0, frame0 + frame);
@@ -201,7 +202,7 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
       for (int i = tid; i < kF2SeamWords; i += kF2Threads) cmL[i] = src[i];
     }
     if (tid != 0) pdl_wait();
-    __syncthreads();  // thread 0's barrier init and *s_qn are visible
+    __syncthreads();  // thread 0's barrier init is visible
     mbar_wait(bar, 0);
     // ---- bytes -> pixel pairs: tile bytes a + 4w .. a + 4w + 3 of row r = columns 4w - 1 .. 4w + 2 -> words 2w, 2w + 1
     // words needed: 0 .. j1 + 2 (the reject / score of the last tested pair reads two words to its right)
@@ -231,7 +232,8 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
     }
     // tested pixels: columns [3, W - 4] = words [2, j1], rows [3, H - 4]
     const int ipw = j1 - 1, ih = H - 6;
-    // ---- reject: a thread per two adjacent pairs, tpr threads per row
+    // ---- reject: a thread per two adjacent pairs, tpr threads per row; survivors into the warp's own queue
+    int qn = 0;  // entries of this warp's queue (warp-uniform)
     {
       const uint32_t k1 = (uint32_t)(0x7FFF - (low_th + 256)) * 0x10001u;
       const int ipw2 = (ipw + 1) >> 1;
@@ -248,24 +250,37 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
           pb = pb && colB;
         }
         const uint32_t ba = __ballot_sync(0xffffffffu, pa), bb = __ballot_sync(0xffffffffu, pb);
-        if ((ba | bb) != 0u) {
-          int at = 0;
-          const int na = __popc(ba);
-          if (lane == 0) at = atomicAdd(s_qn, na + __popc(bb));
-          at = __shfl_sync(0xffffffffu, at, 0);
-          const uint32_t e = (uint32_t)((r << 7) | j);
-          if (pa) queue[at + __popc(ba & lt_mask)] = (uint16_t)e;
-          if (pb) queue[at + na + __popc(bb & lt_mask)] = (uint16_t)(e + 1u);
-        }
+        const int na = __popc(ba);
+        const uint32_t e = (uint32_t)((r << 7) | j);
+        if (pa) queue[qn + __popc(ba & lt_mask)] = (uint16_t)e;
+        if (pb) queue[qn + na + __popc(bb & lt_mask)] = (uint16_t)(e + 1u);
+        qn += na + __popc(bb);
       }
+      if (lane == 0) s_qn[warp] = qn;
     }
-    __syncthreads();
-    const int qn = *s_qn;
+    __syncthreads();  // the score plane is zero everywhere (all warps cleared their share) before any score lands in it
+    // the warps' queues as one list (balanced over the CTA): entry i lives in queue w at i - first[w]
+    int first[kF2Warps + 1];
+    first[0] = 0;
+#pragma unroll
+    for (int w = 0; w < kF2Warps; w++) first[w + 1] = first[w] + s_qn[w];
+    const int total = first[kF2Warps];
+    const uint16_t* qbase = reinterpret_cast<const uint16_t*>(smem + kF2OffQueue);
+    const int qcap = f2_queue_cap(rows_cap);
+    auto entry = [&](int i) -> uint32_t {
+      int w = 0;
+#pragma unroll
+      for (int k = 1; k < kF2Warps; k++) w += (i >= first[k]) ? 1 : 0;
+      int f = first[0];
+#pragma unroll
+      for (int k = 1; k < kF2Warps; k++) f = (i >= first[k]) ? first[k] : f;
+      return qbase[w * qcap + i - f];
+    };
     // ---- exact score of the survivors
     {
       const uint32_t kc = (uint32_t)(256 + low_th) * 0x10001u;
-      for (int i = tid; i < qn; i += kF2Threads) {
-        const uint32_t e = queue[i];
+      for (int i = tid; i < total; i += kF2Threads) {
+        const uint32_t e = entry(i);
         const int r = (int)(e >> 7), j = (int)(e & 127u);
         const uint32_t mm = fast_score_pair(pair + r * S + j, S);  // m + 256
         uint32_t s = __vmaxs2(mm, kc) - kc;                        // max(m - low_th, 0), no borrow
@@ -277,8 +292,8 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
     // ---- non-max suppression at iniThFAST over the survivors -> keep bitmap
     {
       const uint32_t kd = (uint32_t)(min(max(ini_th, 0), 255) - low_th) * 0x10001u;
-      for (int i = tid; i < qn; i += kF2Threads) {
-        const uint32_t e = queue[i];
+      for (int i = tid; i < total; i += kF2Threads) {
+        const uint32_t e = entry(i);
         const int r = (int)(e >> 7), j = (int)(e & 127u);
         const uint32_t* p = score + r * S + j;
         const uint32_t c = __vmaxs2(p[0], kd) - kd;
