@@ -52,7 +52,6 @@ constexpr int kF2MaxW = 32 * kF2CellCols + 6, kF2MaxH = 70;  // largest block RO
 constexpr int kF2BoxW = (15 + kF2MaxW + 4 + 15) & ~15;  // TMA box: up to 15 + 1 bytes left of the ROI, one word of look-ahead (160 / 96)
 constexpr int kF2Wpr = kF2MaxW / 2 + 1;     // pair words per plane row: word j = ROI columns (2j - 1, 2j), j <= 67 (35)
 constexpr int kF2KeepWords = (kF2BoxW + 31) / 32;  // keep bitmap words per row (tile columns 0..159)
-constexpr int kF2MaxCells = 8;
 constexpr int kF2SeamWords = 2 * kF2Wpr + 2 * kF2MaxH;  // cmL[68] cmR[68] rmU[70] rmD[70] of one level
 
 // shared memory map (bytes).  The small tables have room for kF2MaxH rows; the queue and the two planes are sized for
@@ -60,8 +59,7 @@ constexpr int kF2SeamWords = 2 * kF2Wpr + 2 * kF2MaxH;  // cmL[68] cmR[68] rmU[7
 // row of cells per block that is 36-46 rows for the usual image sizes, ~30 KB per CTA.
 constexpr int kF2OffTab = 128;                                         // cmL[68] cmR[68] rmU[70] rmD[70]
 constexpr int kF2OffKeep = kF2OffTab + 4 * (2 * kF2Wpr + 2 * kF2MaxH); // keep bitmap [70][5]
-constexpr int kF2OffRowBase = (kF2OffKeep + 4 * kF2MaxH * kF2KeepWords + 15) & ~15;  // u16 [8][64]
-constexpr int kF2OffQueue = kF2OffRowBase + 2 * kF2MaxCells * 64;      // u16 [(kF2Wpr - 4) * (rows - 6)] tested pairs of a block
+constexpr int kF2OffQueue = (kF2OffKeep + 4 * kF2MaxH * kF2KeepWords + 15) & ~15;  // u16 [warps][f2_queue_cap(rows)] survivors of the reject
 // entries of one warp's survivor queue: a warp does at most ceil(tested rows / warps) reject steps of <= 64 pairs each
 __host__ __device__ constexpr int f2_queue_cap(int rows) { return 64 * ((rows - 6 + kF2Warps - 1) / kF2Warps); }
 __host__ __device__ constexpr int f2_plane_bytes(int rows) { return 4 * kF2Wpr * rows; }
@@ -173,7 +171,6 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
   uint32_t* rmU = cmR + kF2Wpr;                                   // [70] row above / below in the same cell
   uint32_t* rmD = rmU + kF2MaxH;
   uint32_t* keep = reinterpret_cast<uint32_t*>(smem + kF2OffKeep);       // [70][5] bit x of row r: pixel survives NMS
-  uint16_t* rowbase = reinterpret_cast<uint16_t*>(smem + kF2OffRowBase);  // [8][64] survivors of the cell above row
   uint32_t* pair = reinterpret_cast<uint32_t*>(smem + f2_off_pair(rows_cap));        // [rows_cap][68]
   uint32_t* score = reinterpret_cast<uint32_t*>(smem + f2_off_score(rows_cap));      // [rows_cap][68]
   const uint32_t* tile8 = score;  // the TMA byte tile lands in the score plane first
@@ -309,7 +306,8 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
     pdl_wait();  // nothing to test in this block: its cells still report zero candidates below
   }
 
-  // ---- cells: warp per cell, lane per row
+  // ---- cells: warp per cell; lane = rpl consecutive rows (rpl = 1 up to 32 tested rows, 2 up to 64), so that one warp
+  // scan gives every lane the offset of its first row and the lane that counted a row is the one that emits it
   const int n_cells = g->n_cells;
   for (int ci = warp; ci < b.ncx * b.ncy; ci += kF2Warps) {
     const int cyi = ci >= b.ncx ? 1 : 0, cxi = ci - cyi * b.ncx;  // at most two rows of cells
@@ -324,22 +322,19 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
     // tested columns [xa, xb), rows [ya, yb) in tile coordinates
     const int xa = roi.x - b.x0 + 3, xb = roi.z - b.x0 - 3, ya = roi.y - b.y0 + 3, yb = roi.w - b.y0 - 3;
     const int nrows = yb - ya;
-    uint16_t* rbase = rowbase + ci * 64;
+    const int rpl = (nrows + 31) >> 5, row_lo = min(lane * rpl, nrows), row_hi = min(row_lo + rpl, nrows);
+    int lane_first = 0;  // survivors of the cell in the rows above this lane's
     auto count_rows = [&]() -> int {
-      int total = 0;
-      for (int r0 = 0; r0 < nrows; r0 += 32) {
-        const int rr = r0 + lane;
-        const int n = rr < nrows ? fast2_row_count(keep + (ya + rr) * kF2KeepWords, xa, xb) : 0;
-        int inc = n;
+      int n = 0;
+      for (int rr = row_lo; rr < row_hi; rr++) n += fast2_row_count(keep + (ya + rr) * kF2KeepWords, xa, xb);
+      int inc = n;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-          const int t = __shfl_up_sync(0xffffffffu, inc, d);
-          if (lane >= d) inc += t;
-        }
-        if (rr < nrows) rbase[rr] = (uint16_t)(total + inc - n);
-        total += __shfl_sync(0xffffffffu, inc, 31);
+      for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
       }
-      return total;
+      lane_first = inc - n;
+      return __shfl_sync(0xffffffffu, inc, 31);
     };
     int count = count_rows();
     if (count == 0 && min_th != ini_th) {
@@ -380,9 +375,9 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
     {
       const uint32_t pos_base = ((uint32_t)(b.y0 - kBorder) << 20) + ((uint32_t)(b.x0 - kBorder) << 8) + (uint32_t)(low_th - 1);
       uint32_t* dst = raw + (size_t)frame * g->raw_cap + start;
-      for (int rr = lane; rr < nrows; rr += 32) {
+      uint32_t* o = dst + lane_first;
+      for (int rr = row_lo; rr < row_hi; rr++) {
         const int r = ya + rr;
-        uint32_t* o = dst + rbase[rr];
         const uint32_t* krow = keep + r * kF2KeepWords;
         for (int k = xa >> 5; k <= (xb - 1) >> 5; k++) {
           uint32_t m = krow[k];
