@@ -203,10 +203,14 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
     for (int k = 0; k < 5; k++) {
       const int v = 11 + k, d = hw[k];
       int vs = 0;
-      for (int u = -d + lane; u <= d; u += 32) {
-        const int pos = ctr[v * kPatchStride + u], neg = ctr[-v * kPatchStride + u];
-        vs += pos - neg;
-        m10 += u * (pos + neg);
+#pragma unroll
+      for (int step = 0; step < 2; step++) {  // 2d + 1 <= 53 columns: two predicated steps, no loop control
+        const int u = lane - d + 32 * step;
+        if (u <= d) {
+          const int pos = ctr[v * kPatchStride + u], neg = ctr[-v * kPatchStride + u];
+          vs += pos - neg;
+          m10 += u * (pos + neg);
+        }
       }
       m01 += v * vs;
     }
@@ -226,10 +230,10 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
   {
     const uint32_t* pbase = reinterpret_cast<const uint32_t*>(patch) + 1 + (a >> 2);
     const int r8 = lane & 7, g4 = lane >> 3;
-#pragma unroll 1
-    for (int gb = 0; gb < kHbGroups; gb += 4) {
+#pragma unroll
+    for (int gb = 0; gb < kHbGroups; gb += 4) {  // fully unrolled: every load / store offset is an immediate
       const int grp = gb + g4;
-#pragma unroll 2
+#pragma unroll
       for (int rb = 0; rb < kPatchRows; rb += 8) {
         const int r = rb + r8;
         if (grp < kHbGroups && r < kPatchRows) {
