@@ -71,7 +71,7 @@ k_top2_sharded(const uint4* __restrict__ q, const uint4* __restrict__ db, int nd
       for (int i = tid; i < 2 * rows; i += kTopThreads) s_db[i] = db[2 * (size_t)t0 + i];
       __syncthreads();
       const uint32_t local0 = (uint32_t)(t0 - row_begin);
-#pragma unroll 2
+#pragma unroll 4
       for (int r = 0; r < rows; r++) {
         const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1];
 #pragma unroll
@@ -240,7 +240,7 @@ k_top2_frames(const uint4* __restrict__ desc, const int32_t* __restrict__ n_of, 
     __syncthreads();
     for (int i = tid; i < 2 * rows; i += THR) s_db[i] = db[2 * (size_t)t0 + i];
     __syncthreads();
-#pragma unroll 2
+#pragma unroll 4
     for (int r = 0; r < rows; r++) {
       const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1];
 #pragma unroll
