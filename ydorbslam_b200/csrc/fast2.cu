@@ -482,7 +482,9 @@ int launch_fast_blocks(const YdExtractor* ex, int batch, cudaStream_t s) {
   const int ini = ex->params.ini_th_fast;
   const int mn = ex->params.reference_min_th_quirk ? ini : ex->params.min_th_fast;
   const size_t smem = fast2_smem_bytes(ex->fb_max_w, ex->fb_max_h);
-  static const int reject = getenv("YDORB_FAST_REJECT") ? atoi(getenv("YDORB_FAST_REJECT")) : 4;  // tuning knob
+  // reject test: 2 = vertical + horizontal antipodal pairs only (weaker, so more pairs reach the exact score, but half
+  // the arithmetic on every pair: 0.569 -> 0.556 ms per 256 frames), 4 = all four pairs.  Same results either way.
+  static const int reject = getenv("YDORB_FAST_REJECT") ? atoi(getenv("YDORB_FAST_REJECT")) : 2;
   auto kernel = reject == 2 ? k_fast_blocks<2> : k_fast_blocks<4>;
   if (smem > 48 * 1024) YD_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   Fast2Maps maps;
