@@ -927,7 +927,7 @@ __global__ void __launch_bounds__(kTieWarps * 32) k_qt_ties(QtArgs A) {
 }
 
 // list order, then the first min(M, want) winners (:541-543), coordinates back in level space (:597-598)
-__global__ void __launch_bounds__(kQtThreads) k_qt_emit(QtArgs A) {
+__global__ void __launch_bounds__(kQtThreads, 3) k_qt_emit(QtArgs A) {
   pdl_wait();
   __shared__ QtSmem sm;
   const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
