@@ -668,8 +668,8 @@ def run_gpu(args):
                 "thread_inst_per_level_pixel": wi * 32 / px, "issue_rate_gwarp_inst_s": rate / 1e9,
                 "issue_peak_gwarp_inst_s": sms * 4 * f_hz / 1e9, "frac_issue": rate / (sms * 4 * f_hz),
                 "frac_alu_pipe_ncu": None if not alu else alu / 100.0,
-                "algorithmic_ops": "per tested pixel pair: reject 21 packed ALU ops (8 min/max antipodal, 4 combine, 9 compare) on "
-                                   "every pair; exact score 106 (two 9-arc trees 2 x 32, two 16-way reductions 2 x 8, 10 shifts, "
+                "algorithmic_ops": "per tested pixel pair: reject about 15 packed ALU ops (vertical + horizontal antipodal pairs: 2 shifts, "
+                                   "6 min/max, 7 add / compare) on every pair; exact score 106 (two 9-arc trees 2 x 32, two 16-way reductions 2 x 8, 10 shifts, "
                                    "16 compare / select) on the pairs that pass (DESIGN.md 4)",
                 "source": tr.get("source")}
         # The whole step against the same ceiling: warp instructions of all five stages (same capture) per step / the
