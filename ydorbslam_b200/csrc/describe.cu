@@ -239,12 +239,13 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
         if (grp < kHbGroups && r < kPatchRows) {
           const uint32_t* pw = pbase + r * (kPatchStride / 4) + grp;
           const uint32_t A = pw[0], B = pw[1], C = pw[2];
-          const uint32_t k_lo = 0x38302212u, k_hi = 0x00122230u;  // (18,34,48,56), (48,34,18,0) little endian
+          // the window of output k starts k bytes into (A, B, C): the TAPS are shifted, not the pixels -- 10 DP4A and no
+          // funnel shifts (taps 18 34 48 56 48 34 18, little endian)
           uint16_t* o = hb + (4 * grp) * kHbColStride + r;
-          o[0] = (uint16_t)__dp4a(A, k_lo, __dp4a(B, k_hi, 0u));
-          o[kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 8), k_lo, __dp4a(__funnelshift_r(B, C, 8), k_hi, 0u));
-          o[2 * kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 16), k_lo, __dp4a(__funnelshift_r(B, C, 16), k_hi, 0u));
-          o[3 * kHbColStride] = (uint16_t)__dp4a(__funnelshift_r(A, B, 24), k_lo, __dp4a(__funnelshift_r(B, C, 24), k_hi, 0u));
+          o[0] = (uint16_t)__dp4a(A, 0x38302212u, __dp4a(B, 0x00122230u, 0u));
+          o[kHbColStride] = (uint16_t)__dp4a(A, 0x30221200u, __dp4a(B, 0x12223038u, 0u));
+          o[2 * kHbColStride] = (uint16_t)__dp4a(A, 0x22120000u, __dp4a(B, 0x22303830u, __dp4a(C, 0x00000012u, 0u)));
+          o[3 * kHbColStride] = (uint16_t)__dp4a(A, 0x12000000u, __dp4a(B, 0x30383022u, __dp4a(C, 0x00001222u, 0u)));
         }
       }
     }
