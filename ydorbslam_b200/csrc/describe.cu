@@ -256,7 +256,7 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
   float cosA, sinB;
   glibc_sincosf(a_rad, sinB, cosA);                                                  // :426 (float overloads: sincosf)
   // 32-bit view of hb; a sample at (rr, cc) reads rows 18+rr .. 24+rr of column 19+a+cc: four consecutive words,
-  // realigned by a funnel shift when the first row is odd, then 4 x DP2A with the tap pairs (18,34)(48,56)(48,34)(18,0)
+  // 4 x DP2A with the tap pairs (18,34)(48,56)(48,34)(18,0), moved by one slot when the first row is odd
   const uint32_t* hw32 = reinterpret_cast<const uint32_t*>(hb) + (26 + (a & 3) - kHbCol0) * (kHbColStride / 2);
   uint32_t byte = 0;
 #pragma unroll
@@ -270,12 +270,14 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
       const int cc = __float2int_rn(__fsub_rn(__fmul_rn(px, cosA), __fmul_rn(py, sinB)));  // :429
       const int row0 = rr + 18;
       const uint32_t* h = hw32 + cc * (kHbColStride / 2) + (row0 >> 1);
-      const int sh = (row0 & 1) * 16;
+      // an odd first row starts in the high half of w0: the TAPS move by one slot, not the data (18 34 48 56 48 34 18)
+      const bool odd = (row0 & 1) != 0;
+      const uint32_t t01 = odd ? 0x30221200u : 0x38302212u, t23 = odd ? 0x12223038u : 0x00122230u;
       const uint32_t w0 = h[0], w1 = h[1], w2 = h[2], w3 = h[3];
-      uint32_t acc = __dp2a_lo(__funnelshift_r(w0, w1, sh), 0x2212u, 0u);
-      acc = __dp2a_lo(__funnelshift_r(w1, w2, sh), 0x3830u, acc);
-      acc = __dp2a_lo(__funnelshift_r(w2, w3, sh), 0x2230u, acc);
-      acc = __dp2a_lo(w3 >> sh, 0x0012u, acc);
+      uint32_t acc = __dp2a_lo(w0, t01, 0u);
+      acc = __dp2a_hi(w1, t01, acc);
+      acc = __dp2a_lo(w2, t23, acc);
+      acc = __dp2a_hi(w3, t23, acc);
       val[e] = (int)((acc + 32768u) >> 16);
     }
     byte |= (uint32_t)(val[0] < val[1]) << b;
