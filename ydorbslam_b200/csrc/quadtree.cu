@@ -491,6 +491,11 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
   __shared__ int s_misc[4];
   const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const FrameGeomDev* g = A.g;
+  // the segment's occupancy bitmap: one 16-byte load per thread, requested first -- its address depends on nothing, while
+  // the candidate count below sits behind two dependent loads (geometry, then the cell ranks)
+  static_assert(kQtMapWords == 4 * kQtThreads, "one uint4 per thread");
+  uint4* gm4 = reinterpret_cast<uint4*>(A.bitmap + ((size_t)frame * kMaxLevels + level) * kQtMapWords);
+  const uint4 map_v = gm4[tid];
   const LevelGeom lv = g->lv[level];
   const int* rank = A.cell_rank + (size_t)frame * (g->n_cells + 1);
   const int level_base = rank[lv.cell_base];
@@ -513,12 +518,9 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
     return;
   }
   {
-    // one 16-byte load per thread (the whole bitmap in a single round trip), then zero it for the next call
-    static_assert(kQtMapWords == 4 * kQtThreads, "one uint4 per thread");
-    uint4* gm4 = reinterpret_cast<uint4*>(gmap);
-    const uint4 v = gm4[tid];
+    // the whole bitmap arrived in a single round trip; zero it for the next call
     gm4[tid] = make_uint4(0u, 0u, 0u, 0u);
-    reinterpret_cast<uint4*>(s_map)[tid] = v;
+    reinterpret_cast<uint4*>(s_map)[tid] = map_v;
     reinterpret_cast<uint4*>(s_fold)[tid] = make_uint4(0u, 0u, 0u, 0u);
   }
   if (tid <= kQtMapDig) s_cnt[tid] = 0;
