@@ -403,6 +403,8 @@ struct QtArgs {
   int* sel_n;
   int* level_ncand;
   int* status;
+  int n_cells, raw_cap, n_levels;  // of the current geometry: launch parameters, so that no kernel starts with a
+                                   // global load that everything else depends on
 };
 
 // writes (key, packed candidate) of every candidate of the level at its candidate-order position
@@ -410,9 +412,9 @@ __device__ void qt_fill(const QtArgs& A, const LevelGeom& lv, int frame, int lev
                         uint32_t* bitmap) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int ncell = lv.cell_cols * lv.cell_rows;
-  const size_t cbase = (size_t)frame * A.g->n_cells + lv.cell_base;
-  const int* rank = A.cell_rank + (size_t)frame * (A.g->n_cells + 1) + lv.cell_base;
-  const uint32_t* raw = A.raw + (size_t)frame * A.g->raw_cap;
+  const size_t cbase = (size_t)frame * A.n_cells + lv.cell_base;
+  const int* rank = A.cell_rank + (size_t)frame * (A.n_cells + 1) + lv.cell_base;
+  const uint32_t* raw = A.raw + (size_t)frame * A.raw_cap;
   for (int c = warp; c < ncell; c += kQtWarps) {
     const int cnt = A.cell_count[cbase + c];
     if (cnt == 0) continue;
@@ -445,15 +447,15 @@ __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
   // (no warp-level collectives below, the groups of a warp simply diverge)
   const int frame = blockIdx.y, lane = threadIdx.x & (kCodeLanes - 1);
   const int c = blockIdx.x * kCodeCells + threadIdx.x / kCodeLanes;  // cell index within the frame
-  if (c >= g->n_cells) return;
-  const int cnt = A.cell_count[(size_t)frame * g->n_cells + c];
+  if (c >= A.n_cells) return;
+  const int cnt = A.cell_count[(size_t)frame * A.n_cells + c];
   if (cnt == 0) return;
   int level = 0;
-  for (int l = 1; l < g->n_levels && c >= g->lv[l].cell_base; l++) level = l;  // cell bases ascend with the level
+  for (int l = 1; l < A.n_levels && c >= g->lv[l].cell_base; l++) level = l;  // cell bases ascend with the level
   const int root_w = g->lv[level].root_w, root_h = g->lv[level].root_h;
-  const int start = A.cell_start[(size_t)frame * g->n_cells + c];
-  const size_t pos0 = (size_t)frame * g->raw_cap + A.cell_rank[(size_t)frame * (g->n_cells + 1) + c];
-  const uint32_t* raw = A.raw + (size_t)frame * g->raw_cap;
+  const int start = A.cell_start[(size_t)frame * A.n_cells + c];
+  const size_t pos0 = (size_t)frame * A.raw_cap + A.cell_rank[(size_t)frame * (A.n_cells + 1) + c];
+  const uint32_t* raw = A.raw + (size_t)frame * A.raw_cap;
   uint32_t* bitmap = A.bitmap + ((size_t)frame * kMaxLevels + level) * kQtMapWords;
   for (int e = lane; e < cnt; e += kCodeLanes) {
     const uint32_t r = raw[start + e];  // y:12 | x:12 | response:8, border-relative coordinates
@@ -497,7 +499,7 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
   uint4* gm4 = reinterpret_cast<uint4*>(A.bitmap + ((size_t)frame * kMaxLevels + level) * kQtMapWords);
   const uint4 map_v = gm4[tid];
   const LevelGeom lv = g->lv[level];
-  const int* rank = A.cell_rank + (size_t)frame * (g->n_cells + 1);
+  const int* rank = A.cell_rank + (size_t)frame * (A.n_cells + 1);
   const int level_base = rank[lv.cell_base];
   const int n = rank[lv.cell_base + lv.cell_cols * lv.cell_rows] - level_base;
   const int want = lv.quota;
@@ -625,7 +627,7 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
   __syncthreads();
   const int M = s_misc[2];
   // node tables of the segment: best key, member count, tie count
-  const size_t seg = (size_t)frame * g->raw_cap + level_base;
+  const size_t seg = (size_t)frame * A.raw_cap + level_base;
   uint32_t *best = A.keys[1] + seg, *cnt = A.vals[1] + seg, *ties = A.keys[2] + seg;
   for (int m = tid; m < M; m += kQtThreads) { best[m] = 0; cnt[m] = 0; ties[m] = 0; }
   if (tid == 0) { meta[kMetaN] = n; meta[kMetaD] = D; meta[kMetaM] = M; meta[kMetaDeep] = 0; }
@@ -634,23 +636,21 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
 // segment of a candidate position and its node index; returns false for positions past the frame's candidates or in
 // segments the node-table path does not handle
 struct QtWhere { int level, i, D; size_t seg; uint32_t m; };
-__device__ __forceinline__ bool qt_locate(const QtArgs& A, int frame, int pos, QtWhere* w) {
-  const FrameGeomDev* g = A.g;
-  if (pos >= A.cell_rank[(size_t)frame * (g->n_cells + 1) + g->n_cells]) return false;
+__device__ __forceinline__ bool qt_locate(const QtArgs& A, int frame, int pos, int total, uint32_t code, QtWhere* w) {
+  if (pos >= total) return false;
   const int* meta = A.meta + (size_t)frame * kMaxLevels * 8;
   int level = 0;
-  for (int l = 1; l < g->n_levels; l++)
+  for (int l = 1; l < A.n_levels; l++)
     if (pos >= meta[l * 8 + kMetaBase]) level = l;
   meta += level * 8;
   if (meta[kMetaDeep] || meta[kMetaN] == 0) return false;
   const int base = meta[kMetaBase], D = meta[kMetaD];
-  const uint32_t code = A.keys[0][(size_t)frame * g->raw_cap + pos];
   const uint32_t p = D == 0 ? 0u : code >> (kQtBits - 2 * D);
   const uint32_t* fold = A.fold + ((size_t)frame * kMaxLevels + level) * 2 * kQtMapWords;
   w->level = level;
   w->i = pos - base;
   w->D = D;
-  w->seg = (size_t)frame * g->raw_cap + base;
+  w->seg = (size_t)frame * A.raw_cap + base;
   w->m = fold[kQtMapWords + (p >> 5)] + __popc(fold[p >> 5] & ((1u << (p & 31u)) - 1u));
   return true;
 }
@@ -661,15 +661,20 @@ __device__ __forceinline__ bool qt_locate(const QtArgs& A, int frame, int pos, Q
 __global__ void __launch_bounds__(256) k_qt_pass1(QtArgs A) {
   pdl_wait();
   const int frame = blockIdx.y, lane = threadIdx.x & 31;
-  const int total = A.cell_rank[(size_t)frame * (A.g->n_cells + 1) + A.g->n_cells];
+  const int total = A.cell_rank[(size_t)frame * (A.n_cells + 1) + A.n_cells];
   for (int base = blockIdx.x * 256 + (threadIdx.x & ~31); base < total; base += gridDim.x * 256) {  // warp-uniform
     const int pos = base + lane;
+    // the candidate's own words first: their addresses depend on nothing but pos, the segment lookup is a chain of loads
+    uint32_t code = 0, r = 0;
+    if (pos < total) {
+      code = A.keys[0][(size_t)frame * A.raw_cap + pos];
+      r = A.vals[0][(size_t)frame * A.raw_cap + pos];
+    }
     QtWhere w;
-    const bool ok = qt_locate(A, frame, pos, &w);
+    const bool ok = qt_locate(A, frame, pos, total, code, &w);
     uint32_t key = 0;
     if (ok) {
-      const uint32_t r = A.vals[0][(size_t)frame * A.g->raw_cap + pos];
-      A.vals[2][(size_t)frame * A.g->raw_cap + pos] = w.m;  // node index, reused by pass 2
+      A.vals[2][(size_t)frame * A.raw_cap + pos] = w.m;  // node index, reused by pass 2
       key = ((r & 255u) << 24) | (0xFFFFFFu - (uint32_t)w.i);  // max response, then first position
     }
     const uint32_t group = ok ? ((uint32_t)w.level << 16) | w.m : 0x80000000u | (uint32_t)lane;
@@ -685,8 +690,7 @@ __global__ void __launch_bounds__(256) k_qt_pass1(QtArgs A) {
 __global__ void __launch_bounds__(256) k_qt_pass2(QtArgs A) {
   pdl_wait();
   const int frame = blockIdx.y, lane = threadIdx.x & 31;
-  const FrameGeomDev* g = A.g;
-  const int total = A.cell_rank[(size_t)frame * (g->n_cells + 1) + g->n_cells];
+  const int total = A.cell_rank[(size_t)frame * (A.n_cells + 1) + A.n_cells];
   const int* fmeta = A.meta + (size_t)frame * kMaxLevels * 8;
   for (int base = blockIdx.x * 256 + (threadIdx.x & ~31); base < total; base += gridDim.x * 256) {  // warp-uniform
     const int pos = base + lane;
@@ -694,14 +698,14 @@ __global__ void __launch_bounds__(256) k_qt_pass2(QtArgs A) {
     uint32_t group = 0x80000000u | (uint32_t)lane;
     size_t slot = 0;
     if (pos < total) {
+      const uint32_t r = A.vals[0][(size_t)frame * A.raw_cap + pos];  // requested before the segment lookup
+      const uint32_t m = A.vals[2][(size_t)frame * A.raw_cap + pos];
       int level = 0;
-      for (int l = 1; l < g->n_levels; l++)
+      for (int l = 1; l < A.n_levels; l++)
         if (pos >= fmeta[l * 8 + kMetaBase]) level = l;
       const int* meta = fmeta + level * 8;
       if (!meta[kMetaDeep] && meta[kMetaN] != 0) {
-        const uint32_t r = A.vals[0][(size_t)frame * g->raw_cap + pos];
-        const uint32_t m = A.vals[2][(size_t)frame * g->raw_cap + pos];
-        slot = (size_t)frame * g->raw_cap + meta[kMetaBase] + m;
+        slot = (size_t)frame * A.raw_cap + meta[kMetaBase] + m;
         tie = (r & 255u) == (A.keys[1][slot] >> 24);
         group = ((uint32_t)level << 16) | m;
       }
@@ -740,12 +744,16 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_records(QtArgs A) {
   __shared__ QtFinSmem fs;
   QtSmem& sm = fs.q;
   const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
-  const FrameGeomDev* g = A.g;
   int* meta = A.meta + ((size_t)frame * kMaxLevels + level) * 8;
+  // both tables of the segment are full kQtMapWords arrays: one 16-byte load each per thread, requested before the
+  // segment's meta data is known (their addresses depend on nothing; an empty segment just drops them)
+  static_assert(kQtMapWords == 4 * kQtThreads, "one uint4 per thread and table");
+  const uint4* gf4 = reinterpret_cast<const uint4*>(A.fold + ((size_t)frame * kMaxLevels + level) * 2 * kQtMapWords);
+  const uint4 tab_bm = gf4[tid], tab_pf = gf4[kQtMapWords / 4 + tid];
   const int n = meta[kMetaN];
   if (n == 0 || meta[kMetaDeep]) return;
   const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase];
-  const size_t seg = (size_t)frame * g->raw_cap + level_base;
+  const size_t seg = (size_t)frame * A.raw_cap + level_base;
   const uint32_t* CV = A.vals[0] + seg;   // packed candidates, candidate order
   uint32_t* best = A.keys[1] + seg;       // node winners (NV) once the records are written
   uint32_t* cnt = A.vals[1] + seg;
@@ -753,13 +761,10 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_records(QtArgs A) {
   uint32_t* NK = A.vals[2] + seg;         // order keys [0, M), then the flagged list (3 words per entry)
   uint32_t* NV = best;
   uint32_t* flagged = NK + M;             // M + 3 * #(nodes with > 16 members) <= n
-  const uint32_t* gfold = A.fold + ((size_t)frame * kMaxLevels + level) * 2 * kQtMapWords;
   const int nbits = 1 << (2 * D), nwords = (nbits + 31) >> 5;
-  if (4 * tid < nwords) {  // both tables are full kQtMapWords arrays: one 16-byte load each per thread, one round trip
-    const uint4* gf4 = reinterpret_cast<const uint4*>(gfold);
-    const uint4 bm = gf4[tid], pf = gf4[kQtMapWords / 4 + tid];
-    reinterpret_cast<uint4*>(sm.bitmap)[tid] = bm;
-    reinterpret_cast<uint4*>(fs.prefix)[tid] = pf;
+  if (4 * tid < nwords) {
+    reinterpret_cast<uint4*>(sm.bitmap)[tid] = tab_bm;
+    reinterpret_cast<uint4*>(fs.prefix)[tid] = tab_pf;
   }
   if (tid == 0) sm.misc[4] = 0;
   __syncthreads();
@@ -810,7 +815,7 @@ __global__ void __launch_bounds__(kTieWarps * 32) k_qt_ties(QtArgs A) {
   const int frame = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const FrameGeomDev* g = A.g;
   int* fmeta = A.meta + (size_t)frame * kMaxLevels * 8;
-  const int n_levels = g->n_levels;
+  const int n_levels = A.n_levels;
   // lane l holds level l's flagged count and the inclusive prefix over the levels (most warps find nothing to do:
   // keep that path to one round trip)
   static_assert(kMaxLevels <= 32, "one lane per level");
@@ -834,15 +839,15 @@ __global__ void __launch_bounds__(kTieWarps * 32) k_qt_ties(QtArgs A) {
     const LevelGeom lv = g->lv[level];
     const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase];
     const int sh = kQtBits - 2 * D;
-    const size_t seg = (size_t)frame * g->raw_cap + level_base;
+    const size_t seg = (size_t)frame * A.raw_cap + level_base;
     const uint32_t* CK = A.keys[0] + seg;
     const uint32_t* CV = A.vals[0] + seg;
     uint32_t* NV = A.keys[1] + seg;
     const uint32_t* flagged = A.vals[2] + seg + M;
     uint32_t* big_buf = A.keys[2] + seg;  // node tables are dead by now: scratch for nodes with more than 128 members
     uint32_t* big_pos = A.vals[1] + seg;
-    const size_t cbase = (size_t)frame * g->n_cells + lv.cell_base;
-    const int* rank = A.cell_rank + (size_t)frame * (g->n_cells + 1) + lv.cell_base;
+    const size_t cbase = (size_t)frame * A.n_cells + lv.cell_base;
+    const int* rank = A.cell_rank + (size_t)frame * (A.n_cells + 1) + lv.cell_base;
       const int m = (int)flagged[3 * f], len = (int)flagged[3 * f + 2];
       const uint32_t pre = flagged[3 * f + 1];
       // rectangle of the node: replay divideNode on the prefix digits, tracking the true bounds of the members
@@ -939,7 +944,7 @@ __global__ void __launch_bounds__(kQtThreads, 3) k_qt_emit(QtArgs A) {
   if (n == 0 || meta[kMetaDeep]) return;
   const LevelGeom lv = g->lv[level];
   const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase], want = lv.quota;
-  const size_t seg = (size_t)frame * g->raw_cap + level_base;
+  const size_t seg = (size_t)frame * A.raw_cap + level_base;
   uint32_t* NV = A.keys[1] + seg;
   uint32_t* cnt = A.vals[1] + seg;
   uint32_t* ties = A.keys[2] + seg;
@@ -1001,7 +1006,7 @@ __global__ void __launch_bounds__(kQtThreads, 3) k_quadtree(QtArgs A) {
   const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
   const FrameGeomDev* g = A.g;
   const LevelGeom lv = g->lv[level];
-  const int* rank = A.cell_rank + (size_t)frame * (g->n_cells + 1);
+  const int* rank = A.cell_rank + (size_t)frame * (A.n_cells + 1);
   const int level_base = rank[lv.cell_base];
   const int level_end = rank[lv.cell_base + lv.cell_cols * lv.cell_rows];
   const int n = level_end - level_base;
@@ -1012,7 +1017,7 @@ __global__ void __launch_bounds__(kQtThreads, 3) k_quadtree(QtArgs A) {
     if (tid == 0) *sel_n = 0;
     return;
   }
-  const size_t seg = (size_t)frame * g->raw_cap + level_base;
+  const size_t seg = (size_t)frame * A.raw_cap + level_base;
   uint32_t* K[3] = {A.keys[0] + seg, A.keys[1] + seg, A.keys[2] + seg};
   uint32_t* V[3] = {A.vals[0] + seg, A.vals[1] + seg, A.vals[2] + seg};
 
@@ -1250,6 +1255,9 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
   A.sel_n = ex->d_sel_n;
   A.level_ncand = ex->d_level_ncand;
   A.status = ex->d_status;
+  A.n_cells = ex->geom.n_cells;
+  A.raw_cap = ex->geom.raw_cap;
+  A.n_levels = ex->geom.n_levels;
   if (ex->geom.n_cells > 0)
   {
     if ((long long)ex->geom.n_cells * batch >= 148 * 8 * 32) {  // measured: 0.276 -> 0.266 ms per 256 frames; a single frame prefers 32
