@@ -157,7 +157,7 @@ __device__ __forceinline__ int fast2_row_count(const uint32_t* __restrict__ krow
 
 template <int REJECT>  // 4: four antipodal pairs in the reject, 2: vertical + horizontal only
 __global__ void __launch_bounds__(kF2Threads, YD_F2_CTAS)
-k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
+k_fast_blocks(const __grid_constant__ Fast2Maps maps, int n_cells, int raw_cap, const int4* __restrict__ cells,
               const FastBlock* __restrict__ blocks, const uint32_t* __restrict__ seams, int rows_cap, int frame0, int ini_th, int min_th, uint32_t* __restrict__ raw,
               int* __restrict__ raw_counter, int* __restrict__ cell_count, int* __restrict__ cell_start,
               int* __restrict__ status) {
@@ -308,7 +308,6 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
 
   // ---- cells: warp per cell; lane = rpl consecutive rows (rpl = 1 up to 32 tested rows, 2 up to 64), so that one warp
   // scan gives every lane the offset of its first row and the lane that counted a row is the one that emits it
-  const int n_cells = g->n_cells;
   for (int ci = warp; ci < b.ncx * b.ncy; ci += kF2Warps) {
     const int cyi = ci >= b.ncx ? 1 : 0, cxi = ci - cyi * b.ncx;  // at most two rows of cells
     const int cell = b.cell0 + cyi * b.cols + cxi;
@@ -365,7 +364,7 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
     int start = 0;
     if (lane == 0) start = atomicAdd(raw_counter + frame, count);
     start = __shfl_sync(0xffffffffu, start, 0);
-    if (start + count > g->raw_cap) {  // candidate buffer exhausted: report, drop the cell
+    if (start + count > raw_cap) {  // candidate buffer exhausted: report, drop the cell
       if (lane == 0) { atomicOr(status, kStatusRawOverflow); *out_count = 0; *out_start = 0; }
       continue;
     }
@@ -374,7 +373,7 @@ k_fast_blocks(const __grid_constant__ Fast2Maps maps, const FrameGeomDev* __rest
     // response = m - 1 = stored + low_th - 1
     {
       const uint32_t pos_base = ((uint32_t)(b.y0 - kBorder) << 20) + ((uint32_t)(b.x0 - kBorder) << 8) + (uint32_t)(low_th - 1);
-      uint32_t* dst = raw + (size_t)frame * g->raw_cap + start;
+      uint32_t* dst = raw + (size_t)frame * raw_cap + start;
       uint32_t* o = dst + lane_first;
       for (int rr = row_lo; rr < row_hi; rr++) {
         const int r = ya + rr;
@@ -491,7 +490,7 @@ int launch_fast_blocks(const YdExtractor* ex, int batch, cudaStream_t s) {
   for (int l = 0; l < kMaxLevels; l++) maps.lv[l] = ex->tmap_level[l];
   const int frame0 = (int)((ex->d_pyr - ex->pyr_base) / ex->geom.pyr_bytes);
   dim3 grid(ex->n_fast_blocks, batch);
-  YD_CUDA(launch_chain(kernel, grid, dim3(kF2Threads), smem, s, maps, ex->d_geom, ex->d_cells, ex->d_fast_blocks, ex->d_fast_seams, std::max(ex->fb_max_h, 8), frame0,
+  YD_CUDA(launch_chain(kernel, grid, dim3(kF2Threads), smem, s, maps, ex->geom.n_cells, ex->geom.raw_cap, ex->d_cells, ex->d_fast_blocks, ex->d_fast_seams, std::max(ex->fb_max_h, 8), frame0,
                        ini, mn, ex->d_raw, ex->d_raw_counter, ex->d_cell_count, ex->d_cell_start,
                        ex->d_status));
   count_launches(1);

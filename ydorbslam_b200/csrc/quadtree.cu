@@ -403,7 +403,9 @@ struct QtArgs {
   int* sel_n;
   int* level_ncand;
   int* status;
-  int n_cells, raw_cap, n_levels;  // of the current geometry: launch parameters, so that no kernel starts with a
+  int cell_base[kMaxLevels], cell_end[kMaxLevels], quota[kMaxLevels];  // per level: first cell, one past its last, keypoints wanted
+  int quota_base[kMaxLevels];  // first output slot of the level in a frame's selection
+  int n_cells, raw_cap, n_levels, n_quota;  // of the current geometry: launch parameters, so that no kernel starts with a
                                    // global load that everything else depends on
 };
 
@@ -442,7 +444,6 @@ template <int kCodeLanes>
 __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
   constexpr int kCodeCells = kCodeWarps * 32 / kCodeLanes;  // cells per CTA
   pdl_wait();
-  const FrameGeomDev* g = A.g;
   // a cell holds a handful of candidates (~6 on a 640x480 frame): kCodeLanes lanes per cell, several cells per warp
   // (no warp-level collectives below, the groups of a warp simply diverge)
   const int frame = blockIdx.y, lane = threadIdx.x & (kCodeLanes - 1);
@@ -450,6 +451,7 @@ __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
   if (c >= A.n_cells) return;
   const int cnt = A.cell_count[(size_t)frame * A.n_cells + c];
   if (cnt == 0) return;
+  const FrameGeomDev* g = A.g;
   int level = 0;
   for (int l = 1; l < A.n_levels && c >= g->lv[l].cell_base; l++) level = l;  // cell bases ascend with the level
   const int root_w = g->lv[level].root_w, root_h = g->lv[level].root_h;
@@ -492,17 +494,15 @@ __global__ void __launch_bounds__(kQtThreads) k_qt_depth(QtArgs A) {
   __shared__ int s_scan[kQtWarps];
   __shared__ int s_misc[4];
   const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const FrameGeomDev* g = A.g;
   // the segment's occupancy bitmap: one 16-byte load per thread, requested first -- its address depends on nothing, while
   // the candidate count below sits behind two dependent loads (geometry, then the cell ranks)
   static_assert(kQtMapWords == 4 * kQtThreads, "one uint4 per thread");
   uint4* gm4 = reinterpret_cast<uint4*>(A.bitmap + ((size_t)frame * kMaxLevels + level) * kQtMapWords);
   const uint4 map_v = gm4[tid];
-  const LevelGeom lv = g->lv[level];
   const int* rank = A.cell_rank + (size_t)frame * (A.n_cells + 1);
-  const int level_base = rank[lv.cell_base];
-  const int n = rank[lv.cell_base + lv.cell_cols * lv.cell_rows] - level_base;
-  const int want = lv.quota;
+  const int level_base = rank[A.cell_base[level]];
+  const int n = rank[A.cell_end[level]] - level_base;
+  const int want = A.quota[level];
   int* meta = A.meta + ((size_t)frame * kMaxLevels + level) * 8;
   uint32_t* gmap = A.bitmap + ((size_t)frame * kMaxLevels + level) * kQtMapWords;
   if (tid == 0) {
@@ -938,19 +938,17 @@ __global__ void __launch_bounds__(kQtThreads, 3) k_qt_emit(QtArgs A) {
   pdl_wait();
   __shared__ QtSmem sm;
   const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
-  const FrameGeomDev* g = A.g;
   const int* meta = A.meta + ((size_t)frame * kMaxLevels + level) * 8;
   const int n = meta[kMetaN];
   if (n == 0 || meta[kMetaDeep]) return;
-  const LevelGeom lv = g->lv[level];
-  const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase], want = lv.quota;
+  const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase], want = A.quota[level];
   const size_t seg = (size_t)frame * A.raw_cap + level_base;
   uint32_t* NV = A.keys[1] + seg;
   uint32_t* cnt = A.vals[1] + seg;
   uint32_t* ties = A.keys[2] + seg;
   uint32_t* NK = A.vals[2] + seg;
   const int m_out = min(M, want);
-  int4* sel = A.sel + (size_t)frame * g->n_quota + lv.quota_base;
+  int4* sel = A.sel + (size_t)frame * A.n_quota + A.quota_base[level];
   constexpr int kSmemSort = kQtWarps * 256 / 2;  // 64-bit (order key, winner) pairs that fit the radix counters' space
   if (M <= kSmemSort) {
     // few nodes: bitonic sort of the pairs in shared memory (order keys are unique)
@@ -1258,6 +1256,13 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
   A.n_cells = ex->geom.n_cells;
   A.raw_cap = ex->geom.raw_cap;
   A.n_levels = ex->geom.n_levels;
+  A.n_quota = ex->geom.n_quota;
+  for (int l = 0; l < kMaxLevels; l++) {
+    A.cell_base[l] = ex->geom.lv[l].cell_base;
+    A.cell_end[l] = ex->geom.lv[l].cell_base + ex->geom.lv[l].cell_cols * ex->geom.lv[l].cell_rows;
+    A.quota[l] = ex->geom.lv[l].quota;
+    A.quota_base[l] = ex->geom.lv[l].quota_base;
+  }
   if (ex->geom.n_cells > 0)
   {
     if ((long long)ex->geom.n_cells * batch >= 148 * 8 * 32) {  // measured: 0.276 -> 0.266 ms per 256 frames; a single frame prefers 32
