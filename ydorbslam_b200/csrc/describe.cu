@@ -131,6 +131,12 @@ k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict
     mbar_init(&s_bar[threadIdx.x >> 5][1], 1);
   }
   pdl_wait();  // above: constants and geometry only; below: what the quadtree wrote
+  // the warp's quadtree records first: their address depends on nothing that is loaded below
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slot0 = (blockIdx.x * kDescWarps + warp) * KPW;
+  const int4* sel_frame = sel + (size_t)frame * n_quota;
+  int4 mine = make_int4(0, 0, 0, 0);  // lane i: the record of slot0 + i (slots past a level's count hold stale records, unused)
+  if (lane < KPW && slot0 + lane < n_quota) mine = sel_frame[slot0 + lane];
   if (threadIdx.x < n_levels) {
     const int l = threadIdx.x;
     const int* cnt = sel_n + (size_t)frame * kMaxLevels;
@@ -151,15 +157,10 @@ k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict
     }
   }
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int slot0 = (blockIdx.x * kDescWarps + warp) * KPW;
-  const int4* sel_frame = sel + (size_t)frame * n_quota;
   uint16_t* hb = s_hb[warp];
   // software pipeline over the warp's keypoints: the next neighbourhood's box is in flight (TMA into the other patch
   // buffer) while this one computes; buffer b is used by keypoints b, b + 2, ...: its mbarrier phase is (k >> 1) & 1
   const int qb = (lane >= 1 && lane < n_levels) ? s_lvl[lane].quota_base : 0x7FFFFFFF;
-  int4 mine = make_int4(0, 0, 0, 0);  // lane i: the record of slot0 + i (slots past a level's count hold stale records, unused)
-  if (lane < KPW && slot0 + lane < n_quota) mine = sel_frame[slot0 + lane];
   auto record = [&](int k) {
     return make_int4(__shfl_sync(0xffffffffu, mine.x, k), __shfl_sync(0xffffffffu, mine.y, k), __shfl_sync(0xffffffffu, mine.z, k),
                      __shfl_sync(0xffffffffu, mine.w, k));
