@@ -343,13 +343,12 @@ struct StdSortEmu {
 };
 
 // ---- per-frame exclusive scan of the per-cell candidate counts (candidate order = cell-major)
-__global__ void __launch_bounds__(256) k_cell_scan(const FrameGeomDev* __restrict__ g, const int* __restrict__ cell_count,
+__global__ void __launch_bounds__(256) k_cell_scan(int nc, const int* __restrict__ cell_count,
                                                    int* __restrict__ cell_rank) {
   pdl_wait();
   __shared__ int s_warp[8];
   __shared__ int s_carry;
   const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int nc = g->n_cells;
   const int* cnt = cell_count + (size_t)frame * nc;
   int* rank = cell_rank + (size_t)frame * (nc + 1);
   if (tid == 0) s_carry = 0;
@@ -1237,7 +1236,7 @@ __global__ void __launch_bounds__(kQtThreads, 3) k_quadtree(QtArgs A) {
 }
 
 int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
-  YD_CUDA(launch_chain(k_cell_scan, dim3(batch), dim3(256), 0, s, ex->d_geom, ex->d_cell_count, ex->d_cell_rank));
+  YD_CUDA(launch_chain(k_cell_scan, dim3(batch), dim3(256), 0, s, ex->geom.n_cells, ex->d_cell_count, ex->d_cell_rank));
   QtArgs A;
   A.g = ex->d_geom;
   A.cells = ex->d_cells;
