@@ -386,6 +386,8 @@ __global__ void __launch_bounds__(256) k_cell_scan(int nc, const int* __restrict
   if (tid == 0) rank[nc] = s_carry;
 }
 
+// what the per-node walk needs of a level's geometry
+struct QtLevel { int cell_base, cell_cols, cell_rows, cell_w, cell_h, root_w, root_h; };
 struct QtArgs {
   const FrameGeomDev* g;
   const int4* cells;
@@ -403,6 +405,7 @@ struct QtArgs {
   int* level_ncand;
   int* status;
   int cell_base[kMaxLevels], cell_end[kMaxLevels], quota[kMaxLevels];  // per level: first cell, one past its last, keypoints wanted
+  QtLevel lv[kMaxLevels];
   int quota_base[kMaxLevels];  // first output slot of the level in a frame's selection
   int n_cells, raw_cap, n_levels, n_quota;  // of the current geometry: launch parameters, so that no kernel starts with a
                                    // global load that everything else depends on
@@ -812,7 +815,6 @@ __global__ void __launch_bounds__(kTieWarps * 32) k_qt_ties(QtArgs A) {
   pdl_wait();
   __shared__ alignas(8) uint32_t s_buf[kTieWarps][256];
   const int frame = blockIdx.y, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const FrameGeomDev* g = A.g;
   int* fmeta = A.meta + (size_t)frame * kMaxLevels * 8;
   const int n_levels = A.n_levels;
   // lane l holds level l's flagged count and the inclusive prefix over the levels (most warps find nothing to do:
@@ -835,7 +837,7 @@ __global__ void __launch_bounds__(kTieWarps * 32) k_qt_ties(QtArgs A) {
     const int level = __popc(__ballot_sync(0xffffffffu, lincl <= item));  // lanes past n_levels hold `total` > item
     const int f = item - (__shfl_sync(0xffffffffu, lincl, level) - __shfl_sync(0xffffffffu, lc, level));
     int* meta = fmeta + level * 8;
-    const LevelGeom lv = g->lv[level];
+    const QtLevel lv = A.lv[level];  // launch parameters: no load between the meta data and the node's record
     const int D = meta[kMetaD], M = meta[kMetaM], level_base = meta[kMetaBase];
     const int sh = kQtBits - 2 * D;
     const size_t seg = (size_t)frame * A.raw_cap + level_base;
@@ -1260,6 +1262,8 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
     A.cell_base[l] = ex->geom.lv[l].cell_base;
     A.cell_end[l] = ex->geom.lv[l].cell_base + ex->geom.lv[l].cell_cols * ex->geom.lv[l].cell_rows;
     A.quota[l] = ex->geom.lv[l].quota;
+    const LevelGeom& hl = ex->geom.lv[l];
+    A.lv[l] = QtLevel{hl.cell_base, hl.cell_cols, hl.cell_rows, hl.cell_w, hl.cell_h, hl.root_w, hl.root_h};
     A.quota_base[l] = ex->geom.lv[l].quota_base;
   }
   if (ex->geom.n_cells > 0)
