@@ -71,8 +71,16 @@ k_top2_sharded(const uint4* __restrict__ q, const uint4* __restrict__ db, int nd
       for (int i = tid; i < 2 * rows; i += kTopThreads) s_db[i] = db[2 * (size_t)t0 + i];
       __syncthreads();
       const uint32_t local0 = (uint32_t)(t0 - row_begin);
-#pragma unroll 4
-      for (int r = 0; r < rows; r++) {
+      int r = 0;
+#pragma unroll 2
+      for (; r + 1 < rows; r += 2) {  // rows in pairs: 5 min/max per two keys (top2_push2)
+        const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1], lo2 = s_db[2 * r + 2], hi2 = s_db[2 * r + 3];
+#pragma unroll
+        for (int k = 0; k < kTopQpt; k++)
+          top2_push2(ham256_key(qa[k], lo, hi, local0 + (uint32_t)r), ham256_key(qa[k], lo2, hi2, local0 + (uint32_t)r + 1u),
+                     best[k], second[k]);
+      }
+      if (r < rows) {
         const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1];
 #pragma unroll
         for (int k = 0; k < kTopQpt; k++) {
@@ -240,8 +248,16 @@ k_top2_frames(const uint4* __restrict__ desc, const int32_t* __restrict__ n_of, 
     __syncthreads();
     for (int i = tid; i < 2 * rows; i += THR) s_db[i] = db[2 * (size_t)t0 + i];
     __syncthreads();
-#pragma unroll 4
-    for (int r = 0; r < rows; r++) {
+    int r = 0;
+#pragma unroll 2
+    for (; r + 1 < rows; r += 2) {  // rows in pairs: 5 min/max per two keys (top2_push2)
+      const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1], lo2 = s_db[2 * r + 2], hi2 = s_db[2 * r + 3];
+#pragma unroll
+      for (int k = 0; k < QPT; k++)
+        top2_push2(ham256_key(qa[k], lo, hi, (uint32_t)(t0 + r)), ham256_key(qa[k], lo2, hi2, (uint32_t)(t0 + r + 1)), best[k],
+                   second[k]);
+    }
+    if (r < rows) {
       const uint4 lo = s_db[2 * r], hi = s_db[2 * r + 1];
 #pragma unroll
       for (int k = 0; k < QPT; k++) {

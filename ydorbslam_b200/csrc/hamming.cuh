@@ -53,6 +53,14 @@ __device__ __forceinline__ void top2_push(unsigned long long key, unsigned long 
   s = min(s, max(b, key));
   b = min(b, key);
 }
+// two new keys into a running (best, second) pair of 32-bit keys (all keys distinct: the row index is in the low bits):
+// 5 min/max instead of 2 x 3.  best' = min(best, m); second' = second smallest of {best, second, m, M} with m <= M,
+// best <= second, which is min(second, max(best, m), M).
+__device__ __forceinline__ void top2_push2(uint32_t ka, uint32_t kb, uint32_t& best, uint32_t& second) {
+  const uint32_t m = min(ka, kb), M = max(ka, kb);
+  second = __vimin3_u32(second, max(best, m), M);
+  best = min(best, m);
+}
 __device__ __forceinline__ YdTop2 top2_unpack(unsigned long long b, unsigned long long s) {
   YdTop2 o;
   o.best_idx = (b == ~0ull) ? -1 : (int)(uint32_t)b;
