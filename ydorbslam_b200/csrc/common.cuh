@@ -223,6 +223,8 @@ struct YdExtractor {
   int* d_raw_counter;    // [max_batch]
   uint32_t* d_qt_keys[3];  // [max_batch][cap_raw] quadtree sort scratch
   uint32_t* d_qt_vals[3];
+  uint8_t* d_qt_xpath;   // per level and border-relative column: the 8 leading x-decisions of divideNode (quadtree.cu)
+  int qt_xoff[ydorb::kMaxLevels], qt_xlen[ydorb::kMaxLevels], cap_xpath;
   uint32_t* d_qt_bitmap; // [max_batch][kMaxLevels][kQtMapWords] occupancy of 8-digit path prefixes (zero between calls)
   uint32_t* d_qt_fold;   // [max_batch][kMaxLevels][2][kQtMapWords] D-digit occupancy + exclusive popcount prefix per word
   int* d_qt_meta;        // [max_batch][kMaxLevels][8] per segment: n, D, M, deep, level_base

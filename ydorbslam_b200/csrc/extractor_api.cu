@@ -196,6 +196,34 @@ static int set_size(YdExtractor* ex, int w, int h) {
     YD_CUDA(cudaMemcpyAsync(ex->d_tab_ofs, hg.tab_ofs.data(), hg.tab_ofs.size() * sizeof(int), cudaMemcpyHostToDevice, ex->stream));
     YD_CUDA(cudaMemcpyAsync(ex->d_tab_a, hg.tab_a.data(), hg.tab_a.size() * sizeof(short), cudaMemcpyHostToDevice, ex->stream));
   }
+  {
+    // x-decisions of divideNode per column (src/orbExtractor.cpp:7-33: which half a point falls into horizontally depends
+    // on its x alone): bit 7 - d of entry x = "right" at split d, d = 0..7
+    std::vector<uint8_t> xp;
+    for (int l = 0; l < kMaxLevels; l++) {
+      ex->qt_xoff[l] = (int)xp.size();
+      ex->qt_xlen[l] = 0;
+      if (l >= hg.g.n_levels) continue;
+      const int rw = hg.g.lv[l].root_w, len = std::max(rw, 0) + 64;
+      ex->qt_xlen[l] = len;
+      for (int x = 0; x < len; x++) {
+        int tlx = 0, trx = rw;
+        uint32_t bits = 0;
+        for (int d = 0; d < 8; d++) {
+          const int cx = (trx + tlx + 1) >> 1;
+          const bool right = x >= cx;
+          if (right) tlx = cx; else trx = cx;
+          bits = (bits << 1) | (right ? 1u : 0u);
+        }
+        xp.push_back((uint8_t)bits);
+      }
+    }
+    if ((int)xp.size() > ex->cap_xpath) {
+      set_error("image larger than the max_width the extractor was created with");
+      return YDORB_E_CAPACITY;
+    }
+    YD_CUDA(cudaMemcpyAsync(ex->d_qt_xpath, xp.data(), xp.size(), cudaMemcpyHostToDevice, ex->stream));
+  }
   if (!hg.cells.empty())
     YD_CUDA(cudaMemcpyAsync(ex->d_cells, hg.cells.data(), hg.cells.size() * sizeof(int4), cudaMemcpyHostToDevice, ex->stream));
   // fast2.cu: cell blocks and one tensor map per level whose box is the largest block's tile
@@ -474,6 +502,8 @@ int ydorb_extractor_create(const YdExtractorParams* params, int max_width, int m
     alloc((void**)&ex->d_qt_keys[i], sizeof(uint32_t) * B * ex->cap_raw);
     alloc((void**)&ex->d_qt_vals[i], sizeof(uint32_t) * B * ex->cap_raw);
   }
+  ex->cap_xpath = (ex->max_w + 64) * kMaxLevels;
+  alloc((void**)&ex->d_qt_xpath, (size_t)ex->cap_xpath);
   alloc((void**)&ex->d_qt_bitmap, sizeof(uint32_t) * B * kMaxLevels * kQtMapWords);
   alloc((void**)&ex->d_qt_fold, sizeof(uint32_t) * B * kMaxLevels * 2 * kQtMapWords);
   alloc((void**)&ex->d_qt_meta, sizeof(int) * B * kMaxLevels * 8);
@@ -505,7 +535,7 @@ void ydorb_extractor_destroy(YdExtractor* ex) {
   cudaSetDevice(ex->device);
   void* ptrs[] = {ex->d_geom, ex->d_pyr, ex->d_tab_ofs, ex->d_tab_a, ex->d_cells, ex->d_fast_blocks, ex->d_fast_seams, ex->d_cell_count, ex->d_cell_start,
                   ex->d_cell_rank, ex->d_raw, ex->d_raw_counter, ex->d_qt_keys[0], ex->d_qt_keys[1], ex->d_qt_keys[2],
-                  ex->d_qt_vals[0], ex->d_qt_vals[1], ex->d_qt_vals[2], ex->d_qt_bitmap, ex->d_qt_fold, ex->d_qt_meta, ex->d_level_ncand, ex->d_sel, ex->d_sel_n,
+                  ex->d_qt_vals[0], ex->d_qt_vals[1], ex->d_qt_vals[2], ex->d_qt_xpath, ex->d_qt_bitmap, ex->d_qt_fold, ex->d_qt_meta, ex->d_level_ncand, ex->d_sel, ex->d_sel_n,
                   ex->d_status, ex->d_images, ex->d_kps, ex->d_desc, ex->d_nout};
   for (void* p : ptrs)
     if (p) cudaFree(p);

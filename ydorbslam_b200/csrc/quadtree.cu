@@ -406,6 +406,8 @@ struct QtArgs {
   int* status;
   int cell_base[kMaxLevels], cell_end[kMaxLevels], quota[kMaxLevels];  // per level: first cell, one past its last, keypoints wanted
   QtLevel lv[kMaxLevels];
+  const uint8_t* xpath;  // x-decisions of the 8 leading splits per level and column (set_size)
+  int xoff[kMaxLevels], xlen[kMaxLevels];
   int quota_base[kMaxLevels];  // first output slot of the level in a frame's selection
   int n_cells, raw_cap, n_levels, n_quota;  // of the current geometry: launch parameters, so that no kernel starts with a
                                    // global load that everything else depends on
@@ -456,14 +458,31 @@ __global__ void __launch_bounds__(kCodeWarps * 32) k_qt_codes(QtArgs A) {
   const FrameGeomDev* g = A.g;
   int level = 0;
   for (int l = 1; l < A.n_levels && c >= g->lv[l].cell_base; l++) level = l;  // cell bases ascend with the level
-  const int root_w = g->lv[level].root_w, root_h = g->lv[level].root_h;
+  const int root_h = g->lv[level].root_h;
   const int start = A.cell_start[(size_t)frame * A.n_cells + c];
   const size_t pos0 = (size_t)frame * A.raw_cap + A.cell_rank[(size_t)frame * (A.n_cells + 1) + c];
   const uint32_t* raw = A.raw + (size_t)frame * A.raw_cap;
+  const uint8_t* xp = A.xpath + A.xoff[level];
+  const int xmax = A.xlen[level] - 1;
   uint32_t* bitmap = A.bitmap + ((size_t)frame * kMaxLevels + level) * kQtMapWords;
   for (int e = lane; e < cnt; e += kCodeLanes) {
     const uint32_t r = raw[start + e];  // y:12 | x:12 | response:8, border-relative coordinates
-    const uint32_t code = qt_code<kQtMapDig>((int)((r >> 8) & 4095u), (int)(r >> 20), root_w, root_h);
+    // divideNode splits x by x alone, so the 8 x-decisions come from a per-column table; only the y side (which the
+    // child-4 quirk F6 couples to the x-decisions) is replayed here.  Same codes as qt_code<kQtMapDig>.
+    const uint32_t xb = xp[min((int)((r >> 8) & 4095u), xmax)];
+    const int y = (int)(r >> 20);
+    int tly = 0, bly = root_h;
+    uint32_t code = 0;
+#pragma unroll
+    for (int d = 0; d < kQtMapDig; d++) {
+      const int cy = (bly + tly + 1) >> 1;
+      const bool low = y >= cy, right = ((xb >> (kQtMapDig - 1 - d)) & 1u) != 0u;
+      const int t = tly;
+      tly = low ? cy : tly;
+      bly = low ? (right ? t : bly) : cy;  // child 4: bl.y := parent tl.y (F6)
+      code = (code << 2) | (low ? 2u : 0u) | (right ? 1u : 0u);
+    }
+    code <<= 2 * (kQtDig - kQtMapDig);
     A.keys[0][pos0 + e] = code;
     A.vals[0][pos0 + e] = r;
     const uint32_t p8 = code >> (kQtBits - 2 * kQtMapDig);
@@ -1258,6 +1277,7 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
   A.raw_cap = ex->geom.raw_cap;
   A.n_levels = ex->geom.n_levels;
   A.n_quota = ex->geom.n_quota;
+  A.xpath = ex->d_qt_xpath;
   for (int l = 0; l < kMaxLevels; l++) {
     A.cell_base[l] = ex->geom.lv[l].cell_base;
     A.cell_end[l] = ex->geom.lv[l].cell_base + ex->geom.lv[l].cell_cols * ex->geom.lv[l].cell_rows;
@@ -1265,6 +1285,8 @@ int launch_quadtree(const YdExtractor* ex, int batch, cudaStream_t s) {
     const LevelGeom& hl = ex->geom.lv[l];
     A.lv[l] = QtLevel{hl.cell_base, hl.cell_cols, hl.cell_rows, hl.cell_w, hl.cell_h, hl.root_w, hl.root_h};
     A.quota_base[l] = ex->geom.lv[l].quota_base;
+    A.xoff[l] = ex->qt_xoff[l];
+    A.xlen[l] = ex->qt_xlen[l];
   }
   if (ex->geom.n_cells > 0)
   {
