@@ -324,8 +324,9 @@ k_fast_cells(const FrameGeomDev* __restrict__ g, const int4* __restrict__ cells,
 
 int launch_fast(const YdExtractor* ex, int batch, cudaStream_t s) {
   YD_CUDA(cudaMemsetAsync(ex->d_raw_counter, 0, sizeof(int) * batch, s));
-  // launches that fill the GPU with 8-warp CTAs take the CTA-per-cell-block kernel (fast2.cu); a single frame's ~100
-  // blocks would leave SMs idle, the warp-per-cell kernel below spreads its ~800 cells over all of them.
+  // launches of a few frames or more take the CTA-per-cell-block kernel (fast2.cu); a single frame's ~230 4-warp blocks
+  // leave SMs idle, the warp-per-cell kernel below spreads its ~800 cells over all of them (640x480, measured: 1 frame
+  // 29 us against 45 us, 2-4 frames equal, 16 frames 76 us against 68 us).
   // YDORB_FAST_KERNEL=cells|blocks forces one of them (tests run both and compare).
   {
     const char* force = getenv("YDORB_FAST_KERNEL");  // read per call: tests flip it in-process
