@@ -105,18 +105,21 @@ __device__ __forceinline__ void desc_prefetch(const DescKp& d, int lane, uint8_t
   }
 }
 
+// nxt / bar / nxt_map / tma_frame: the next key point of the warp, whose box is requested into the SAME patch buffer as
+// soon as this key point's last read of it (the horizontal blur) is over
 __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, int lane, uint8_t* __restrict__ patch,
                              uint16_t* __restrict__ hb, const uint32_t* __restrict__ s_pat, YdKeyPoint* __restrict__ kps,
-                             uint8_t* __restrict__ desc, int capacity);
+                             uint8_t* __restrict__ desc, int capacity, const DescKp& nxt, uint64_t* bar,
+                             const CUtensorMap* nxt_map, int tma_frame);
 
 // KPW = consecutive keypoint slots a warp works through (8 for batches that fill the GPU; fewer spreads a small batch)
 template <int KPW>
-__global__ void __launch_bounds__(kDescWarps * 32, 5)
+__global__ void __launch_bounds__(kDescWarps * 32, 6)
 k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict__ g, int frame0,
            const int4* __restrict__ sel, const int* __restrict__ sel_n, YdKeyPoint* __restrict__ kps,
            uint8_t* __restrict__ desc, int capacity, int32_t* __restrict__ n_out, int* __restrict__ status) {
-  __shared__ __align__(128) uint8_t s_patch[kDescWarps][2][kPatchBytes];  // double buffered TMA destinations
-  __shared__ __align__(8) uint64_t s_bar[kDescWarps][2];
+  __shared__ __align__(128) uint8_t s_patch[kDescWarps][kPatchBytes];  // TMA destination, one per warp
+  __shared__ __align__(8) uint64_t s_bar[kDescWarps];
   __shared__ __align__(16) uint16_t s_hb[kDescWarps][kHbCols * kHbColStride];
   __shared__ uint32_t s_pat[256];  // [bit b][lane]: the two pattern points (x0,y0,x1,y1 as s8) of bit b of byte `lane`
   __shared__ DescLevel s_lvl[kMaxLevels];
@@ -127,8 +130,7 @@ k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict
     s_pat[i] = reinterpret_cast<const uint32_t*>(c_pattern)[l * 8 + b];
   }
   if ((threadIdx.x & 31) == 0) {
-    mbar_init(&s_bar[threadIdx.x >> 5][0], 1);
-    mbar_init(&s_bar[threadIdx.x >> 5][1], 1);
+    mbar_init(&s_bar[threadIdx.x >> 5], 1);
   }
   pdl_wait();  // above: constants and geometry only; below: what the quadtree wrote
   // the warp's quadtree records first: their address depends on nothing that is loaded below
@@ -158,26 +160,31 @@ k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict
   }
   __syncthreads();
   uint16_t* hb = s_hb[warp];
-  // software pipeline over the warp's keypoints: the next neighbourhood's box is in flight (TMA into the other patch
-  // buffer) while this one computes; buffer b is used by keypoints b, b + 2, ...: its mbarrier phase is (k >> 1) & 1
+  // pipeline over the warp's key points with ONE patch buffer per warp (7.3 KB of shared memory per warp instead of 10.8:
+  // more resident warps): a key point reads the patch for its angle and horizontal blur only, so the next one's box is
+  // requested right after the blur and lands while the descriptor bits are sampled from the blurred buffer.  Every
+  // request completes one phase of the warp's mbarrier; `phase` counts them (key points without work request nothing).
   const int qb = (lane >= 1 && lane < n_levels) ? s_lvl[lane].quota_base : 0x7FFFFFFF;
   auto record = [&](int k) {
     return make_int4(__shfl_sync(0xffffffffu, mine.x, k), __shfl_sync(0xffffffffu, mine.y, k), __shfl_sync(0xffffffffu, mine.z, k),
                      __shfl_sync(0xffffffffu, mine.w, k));
   };
+  uint32_t phase = 0;
   DescKp cur = desc_setup(s_lvl, qb, n_quota, slot0, record(0), capacity);
-  if (cur.valid) desc_prefetch(cur, lane, s_patch[warp][0], &s_bar[warp][0], &maps.lv[cur.level], frame0 + frame);
+  if (cur.valid) desc_prefetch(cur, lane, s_patch[warp], &s_bar[warp], &maps.lv[cur.level], frame0 + frame);
   for (int k = 0; k < KPW; k++) {
     DescKp nxt;
     nxt.valid = 0;
-    if (k + 1 < KPW) {
-      nxt = desc_setup(s_lvl, qb, n_quota, slot0 + k + 1, record(k + 1), capacity);
-      // the other buffer was last read by keypoint k - 1, whose compute ended with a __syncwarp
-      if (nxt.valid) desc_prefetch(nxt, lane, s_patch[warp][(k + 1) & 1], &s_bar[warp][(k + 1) & 1], &maps.lv[nxt.level], frame0 + frame);
-    }
+    nxt.level = 0;
+    if (k + 1 < KPW) nxt = desc_setup(s_lvl, qb, n_quota, slot0 + k + 1, record(k + 1), capacity);
+    const CUtensorMap* nxt_map = &maps.lv[nxt.valid ? nxt.level : 0];
     if (cur.valid) {
-      mbar_wait(&s_bar[warp][k & 1], (uint32_t)((k >> 1) & 1));
-      desc_compute(cur, s_lvl[cur.level], frame, lane, s_patch[warp][k & 1], hb, s_pat, kps, desc, capacity);
+      mbar_wait(&s_bar[warp], phase);
+      phase ^= 1u;
+      desc_compute(cur, s_lvl[cur.level], frame, lane, s_patch[warp], hb, s_pat, kps, desc, capacity, nxt, &s_bar[warp], nxt_map,
+                   frame0 + frame);
+    } else if (nxt.valid) {  // nothing in flight, nobody reads the buffer
+      desc_prefetch(nxt, lane, s_patch[warp], &s_bar[warp], nxt_map, frame0 + frame);
     }
     __syncwarp();
     cur = nxt;
@@ -187,7 +194,8 @@ k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict
 // pixel (dx, dy) of the keypoint's neighbourhood sits at patch[(dy+21)*kPatchStride + dx+26+a], a = 0..15
 __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, int lane, uint8_t* __restrict__ patch,
                              uint16_t* __restrict__ hb, const uint32_t* __restrict__ s_pat, YdKeyPoint* __restrict__ kps,
-                             uint8_t* __restrict__ desc, int capacity) {
+                             uint8_t* __restrict__ desc, int capacity, const DescKp& nxt, uint64_t* bar,
+                             const CUtensorMap* nxt_map, int tma_frame) {
   const int a = d.a, oi = d.oi, level = d.level;
   const int4 kp = d.kp;
   // ---- E5 IC angle
@@ -252,6 +260,8 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
     }
   }
   __syncwarp();
+  // the patch is dead from here (rBRIEF samples the blurred buffer): the next key point's box lands under the sampling
+  if (nxt.valid) desc_prefetch(nxt, lane, patch, bar, nxt_map, tma_frame);
   // ---- E7 rBRIEF
   const float a_rad = __fmul_rn(angle, (float)(3.14159265358979323846 / 180.0));  // :425
   float cosA, sinB;
