@@ -114,7 +114,7 @@ __device__ void desc_compute(const DescKp& d, const DescLevel& lv, int frame, in
 
 // KPW = consecutive keypoint slots a warp works through (8 for batches that fill the GPU; fewer spreads a small batch)
 template <int KPW>
-__global__ void __launch_bounds__(kDescWarps * 32, 6)
+__global__ void __launch_bounds__(kDescWarps * 32, 7)
 k_describe(const __grid_constant__ DescMaps maps, const FrameGeomDev* __restrict__ g, int frame0,
            const int4* __restrict__ sel, const int* __restrict__ sel_n, YdKeyPoint* __restrict__ kps,
            uint8_t* __restrict__ desc, int capacity, int32_t* __restrict__ n_out, int* __restrict__ status) {
